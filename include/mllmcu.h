@@ -1,0 +1,135 @@
+/*
+ * mllmcu.h -- the thin C ABI under mllm's CUDA backend (libmllmcu.so).
+ *
+ * This is the drop-in boundary for the quantized-inference hot path: the
+ * entry points below are exactly what `mllm/backends/cuda/CUDA*.cpp` op classes
+ * call from their Op::execute() (and what the tests bind with ctypes).  Each
+ * one names the reference CPU function it replaces (paths relative to
+ * /root/reference/mllm).  Conventions:
+ *   - every pointer is a DEVICE pointer owned by the caller unless it says host;
+ *   - no hidden allocation, no global state: scratch memory is passed in
+ *     explicitly (`ws`, sized by the matching *_workspace_bytes());
+ *   - `stream` is a cudaStream_t passed as void*; all work is asynchronous on it;
+ *   - return value: 0 = ok, otherwise a cudaError_t value (>0) or a negative
+ *     MLLMCU_E* argument error.  Nothing falls back to the CPU.
+ * Activations are fp32 in mllm's BSHD layout (Types.hpp:99-112); weights are
+ * the `.mllm` file's native blocks, uploaded byte-for-byte (DataType.hpp:75-163).
+ */
+#ifndef MLLMCU_H
+#define MLLMCU_H
+#include <stddef.h>
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MLLMCU_EINVAL (-1)   /* bad shape / alignment */
+#define MLLMCU_ENOSUP (-2)   /* dtype or size not supported by this build */
+#define MLLMCU_EWS (-3)      /* workspace too small */
+
+/* DataType values, identical to mllm/Types.hpp:64-74 */
+#define MLLMCU_TYPE_F32 0
+#define MLLMCU_TYPE_F16 1
+#define MLLMCU_TYPE_Q4_0 2
+#define MLLMCU_TYPE_Q8_0 8
+/* RoPEType values, identical to mllm/Types.hpp RoPEType */
+#define MLLMCU_ROPE_LLAMA 2
+#define MLLMCU_ROPE_HF 4
+
+int mllmcu_version(void);
+int mllmcu_device_count(void);
+int mllmcu_set_device(int dev);
+/* name: >=256 bytes host buffer; sm_count/mem_bytes host out-params */
+int mllmcu_device_info(int dev, char *name, int *sm_major, int *sm_minor, int *sm_count, size_t *mem_bytes);
+
+/* ---- memory: what Backend::alloc_device / free_device / copy_from_host /
+ * copy_to_host (Backend.hpp:60-71) and load_from_file (:118) reduce to. */
+int mllmcu_malloc(void **dptr, size_t bytes);
+int mllmcu_free(void *dptr);
+int mllmcu_memset(void *dptr, int value, size_t bytes, void *stream);
+int mllmcu_memcpy_h2d(void *dst, const void *host_src, size_t bytes, void *stream);
+int mllmcu_memcpy_d2h(void *host_dst, const void *src, size_t bytes, void *stream);
+int mllmcu_memcpy_d2d(void *dst, const void *src, size_t bytes, void *stream);
+int mllmcu_host_alloc(void **hptr, size_t bytes); /* pinned host memory */
+int mllmcu_host_free(void *hptr);
+int mllmcu_stream_create(void **stream);
+int mllmcu_stream_destroy(void *stream);
+int mllmcu_stream_sync(void *stream);
+
+/* ---- quantize_row_q8_0 (ggml/QuantizeQ8.cpp:57-189, AVX2 body) for `rows`
+ * fp32 rows of length k (row stride ldx floats) -> rows x k/32 native
+ * block_q8_0 (34 B each).  Bytes are identical to the reference's. */
+int mllmcu_quantize_q8_0(const float *x, void *y_blocks, int rows, int k, int ldx, void *stream);
+
+/* ---- the integer part of vec_dot_q4_0_q8_0 (ggml/VecDotQ4.cpp:523-543):
+ * out[n][m][kb] = sum_{e<32} (w[n][kb].q[e]-8) * x[m][kb].q[e]  (int32, exact).
+ * W: N rows of K/32 block_q4_0; xq: M rows of K/32 block_q8_0.  Test/diagnostic
+ * entry point proving the block dot products are bit-exact. */
+int mllmcu_block_isums_q4_0_q8_0(const void *W, const void *xq_blocks, int32_t *out, int M, int N, int K, void *stream);
+
+/* ---- Linear: CPULinear::execute -> mat_mul (op/CPULinear.cpp:97-233,
+ * compute/Matmul.cpp:19-279).  y[m][n] = sum_k x[m][k] * W[n][k] + bias[n],
+ * computed as the reference does: x rows quantised to Q8_0 (bit-identical),
+ * integer block dots, fp32 scale-accumulate; bias added in fp32; result stored
+ * fp32 or (out_f16) fp16 RNE -- the latter is how v_proj writes into the KV
+ * cache slice (Matmul.cpp:262-268).
+ *   wtype: MLLMCU_TYPE_Q4_0 | MLLMCU_TYPE_Q8_0;  W: [N][K/32] native blocks,
+ *   x: [M][K] fp32 row stride ldx;  y: [M][N] row stride ldy (elements).
+ * ws: scratch of at least mllmcu_linear_workspace_bytes(M,K). */
+size_t mllmcu_linear_workspace_bytes(int M, int K);
+int mllmcu_linear(int wtype, const void *W, const float *x, const float *bias, void *y, int M, int N, int K, int ldx,
+                  int ldy, int out_f16, void *ws, size_t ws_bytes, void *stream);
+
+/* ---- RMSNorm: CPURMSNorm::execute (op/CPURMSNorm.cpp:31-95): double sum of
+ * squares, y = (x * rsqrt) * w  (or * (1+w) when add_unit_offset). */
+int mllmcu_rmsnorm(const float *x, const float *w, float *y, int rows, int dim, float eps, int add_unit_offset, void *stream);
+/* ---- LayerNorm: CPULayerNorm::execute (op/CPULayerNorm.cpp:49-89); w/b may be NULL */
+int mllmcu_layernorm(const float *x, const float *w, const float *b, float *y, int rows, int dim, float eps, void *stream);
+
+/* ---- RoPE: CPURoPE::rope_llama / rope_hf (op/CPURoPE.cpp:200-372) with the
+ * host-built sin/cos tables ([pos_max][tdim], built as :75-128 does).  x is
+ * [B][S][H][D] fp32; output element (b,s,h,d) goes to
+ *   out + b*out_bstride + s*out_sstride + h*D + d   (element units)
+ * as fp32 or fp16 (RNE) -- so k_rope can write straight into the cache slice
+ * exactly as the reference's child-tensor aliasing does (Tensor.cpp:225-275).
+ * Row s uses table row pos0 + s (h_cnt_, CPURoPE.cpp:449-515). */
+int mllmcu_rope(int rope_type, const float *x, void *out, int B, int S, int H, int D, int rot_dim, int pos0,
+                const float *sin_t, const float *cos_t, int tdim, int out_f16, long long out_bstride,
+                long long out_sstride, void *stream);
+
+/* ---- SiLU: mllm_vec_silu_f32 (compute/ActivationFunction.cpp:5-27, polynomial
+ * exp of ActivationFunction.hpp:96-141 restated lane-exactly); and the fused
+ * SiLU(gate)*up of LLaMAMLP (models/llama/modeling_llama.hpp:29-36). */
+int mllmcu_silu(const float *x, float *y, size_t n, void *stream);
+int mllmcu_silu_mul(const float *gate, const float *up, float *y, size_t n, void *stream);
+/* ---- element-wise tensor-tensor ops: CPUaddTwoFunction / CPUmulTwoFunction (op/CPUBinaryFunc.hpp) */
+int mllmcu_add(const float *a, const float *b, float *y, size_t n, void *stream);
+int mllmcu_mul(const float *a, const float *b, float *y, size_t n, void *stream);
+
+/* ---- Embedding: CPUEmbedding::execute, Q4_0 table (op/CPUEmbedding.cpp:66-81):
+ * ids are fp32 (device); negative id leaves the row untouched. */
+int mllmcu_embedding_q4_0(const void *table, const float *ids, float *out, int n_ids, int hidden, void *stream);
+
+/* ---- Flash attention 2 with fp32 Q and fp16 K/V cache:
+ * CPUFlashAttention2Func::execute -> flash_attention_2_forward
+ * (op/CPUFlashAttention2Func.hpp:49-125, compute/FlashAttention2.hpp:1212-2284).
+ * q,o: [B][Sq][Hq][D] fp32; k,v: fp16, element (b,s,h,d) at
+ * b*kv_bstride + s*Hkv*D + h*D + d (the cache's BSHD layout, op/CPUKVCache.cpp:10-66).
+ * causal: key c visible to query r iff c <= r + (Sk - Sq).
+ * ws: scratch of at least mllmcu_flash_attn_workspace_bytes(B,Sq,Hq,D). */
+size_t mllmcu_flash_attn_workspace_bytes(int B, int Sq, int Hq, int D);
+int mllmcu_flash_attn_f16kv(const float *q, const void *k, const void *v, float *o, int B, int Sq, int Sk, int Hq,
+                            int Hkv, int D, int causal, long long kv_bstride, void *ws, size_t ws_bytes, void *stream);
+
+/* ---- fp32 -> fp16 RNE rows (KV-cache append of a tensor that is not produced
+ * by a Linear/RoPE writing in place). dst row stride ld_dst, src row stride ld_src (elements) */
+int mllmcu_f32_to_f16_rows(const float *src, void *dst, int rows, int cols, long long ld_src, long long ld_dst, void *stream);
+
+/* ---- greedy sampling: LlmTextGenerator argmax (Generate.cpp:46-53) on device;
+ * first maximum wins, as std::max_element does. out: int32 per row. */
+int mllmcu_argmax(const float *logits, int rows, int n, int *out, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

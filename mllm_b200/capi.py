@@ -1,0 +1,217 @@
+"""ctypes binding of the C ABI in include/mllmcu.h (libmllmcu.so).
+
+This module is plumbing for tests and bench.py: it passes raw device pointers
+(from torch tensors) and the current CUDA stream to the C entry points.  There
+is no CPU fallback: a missing library raises, a non-zero return code raises.
+"""
+import ctypes as C
+import os
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "lib", "libmllmcu.so")
+
+TYPE_F32, TYPE_F16, TYPE_Q4_0, TYPE_Q8_0 = 0, 1, 2, 8
+ROPE_LLAMA, ROPE_HF = 2, 4
+Q4_0_BYTES, Q8_0_BYTES = 18, 34
+
+# every symbol include/mllmcu.h declares: (restype, argtypes)
+_vp, _i, _sz, _ll, _f = C.c_void_p, C.c_int, C.c_size_t, C.c_longlong, C.c_float
+SYMBOLS = {
+    "mllmcu_version": (_i, []),
+    "mllmcu_device_count": (_i, []),
+    "mllmcu_set_device": (_i, [_i]),
+    "mllmcu_device_info": (_i, [_i, C.c_char_p, C.POINTER(_i), C.POINTER(_i), C.POINTER(_i), C.POINTER(_sz)]),
+    "mllmcu_malloc": (_i, [C.POINTER(_vp), _sz]),
+    "mllmcu_free": (_i, [_vp]),
+    "mllmcu_memset": (_i, [_vp, _i, _sz, _vp]),
+    "mllmcu_memcpy_h2d": (_i, [_vp, _vp, _sz, _vp]),
+    "mllmcu_memcpy_d2h": (_i, [_vp, _vp, _sz, _vp]),
+    "mllmcu_memcpy_d2d": (_i, [_vp, _vp, _sz, _vp]),
+    "mllmcu_host_alloc": (_i, [C.POINTER(_vp), _sz]),
+    "mllmcu_host_free": (_i, [_vp]),
+    "mllmcu_stream_create": (_i, [C.POINTER(_vp)]),
+    "mllmcu_stream_destroy": (_i, [_vp]),
+    "mllmcu_stream_sync": (_i, [_vp]),
+    "mllmcu_quantize_q8_0": (_i, [_vp, _vp, _i, _i, _i, _vp]),
+    "mllmcu_block_isums_q4_0_q8_0": (_i, [_vp, _vp, _vp, _i, _i, _i, _vp]),
+    "mllmcu_linear_workspace_bytes": (_sz, [_i, _i]),
+    "mllmcu_linear": (_i, [_i, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _vp, _sz, _vp]),
+    "mllmcu_rmsnorm": (_i, [_vp, _vp, _vp, _i, _i, _f, _i, _vp]),
+    "mllmcu_layernorm": (_i, [_vp, _vp, _vp, _vp, _i, _i, _f, _vp]),
+    "mllmcu_rope": (_i, [_i, _vp, _vp, _i, _i, _i, _i, _i, _i, _vp, _vp, _i, _i, _ll, _ll, _vp]),
+    "mllmcu_silu": (_i, [_vp, _vp, _sz, _vp]),
+    "mllmcu_silu_mul": (_i, [_vp, _vp, _vp, _sz, _vp]),
+    "mllmcu_add": (_i, [_vp, _vp, _vp, _sz, _vp]),
+    "mllmcu_mul": (_i, [_vp, _vp, _vp, _sz, _vp]),
+    "mllmcu_embedding_q4_0": (_i, [_vp, _vp, _vp, _i, _i, _vp]),
+    "mllmcu_flash_attn_workspace_bytes": (_sz, [_i, _i, _i, _i]),
+    "mllmcu_flash_attn_f16kv": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _ll, _vp, _sz, _vp]),
+    "mllmcu_f32_to_f16_rows": (_i, [_vp, _vp, _i, _i, _ll, _ll, _vp]),
+    "mllmcu_argmax": (_i, [_vp, _i, _i, _vp, _vp]),
+}
+
+_lib = None
+
+
+class MllmcuError(RuntimeError):
+    pass
+
+
+def lib():
+    """Load libmllmcu.so (raises if it has not been built -- there is no fallback)."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise MllmcuError(f"{LIB_PATH} missing: run `python -m mllm_b200.build` (no CPU fallback exists)")
+        L = C.CDLL(LIB_PATH)
+        for name, (res, args) in SYMBOLS.items():
+            fn = getattr(L, name)  # AttributeError if the library does not export a declared symbol
+            fn.restype = res
+            fn.argtypes = args
+        _lib = L
+    return _lib
+
+
+def check(rc, what=""):
+    if rc != 0:
+        raise MllmcuError(f"{what} failed with code {rc}")
+
+
+def _stream():
+    import torch
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _ptr(t):
+    return None if t is None else t.data_ptr()
+
+
+# ---------------------------------------------------------------- torch-facing helpers
+def quantize_q8_0(x):
+    """x: cuda fp32 [rows,k] contiguous -> cuda uint8 [rows, k/32*34] native block_q8_0."""
+    import torch
+    rows, k = x.shape
+    y = torch.empty((rows, k // 32 * Q8_0_BYTES), dtype=torch.uint8, device=x.device)
+    check(lib().mllmcu_quantize_q8_0(_ptr(x), _ptr(y), rows, k, x.stride(0), _stream()), "quantize_q8_0")
+    return y
+
+
+def block_isums_q4_0_q8_0(W, xq, K):
+    import torch
+    N, M = W.shape[0], xq.shape[0]
+    out = torch.empty((N, M, K // 32), dtype=torch.int32, device=W.device)
+    check(lib().mllmcu_block_isums_q4_0_q8_0(_ptr(W), _ptr(xq), _ptr(out), M, N, K, _stream()), "block_isums")
+    return out
+
+
+_ws_cache = {}
+
+
+def _workspace(nbytes, device):
+    import torch
+    key = (device.index, "ws")
+    t = _ws_cache.get(key)
+    if t is None or t.numel() < nbytes:
+        t = torch.empty(max(nbytes, 1 << 20), dtype=torch.uint8, device=device)
+        _ws_cache[key] = t
+    return t
+
+
+def linear(W, x, bias=None, wtype=TYPE_Q4_0, out_f16=False, out=None, ldy=None):
+    """x cuda fp32 [M,K]; W cuda uint8 [N, K/32*blk]; returns y [M,N] fp32 (or fp16)."""
+    import torch
+    M, K = x.shape
+    N = W.shape[0]
+    if out is None:
+        out = torch.empty((M, N), dtype=torch.float16 if out_f16 else torch.float32, device=x.device)
+        ldy = N
+    need = lib().mllmcu_linear_workspace_bytes(M, K)
+    ws = _workspace(need, x.device)
+    check(lib().mllmcu_linear(wtype, _ptr(W), _ptr(x), _ptr(bias), _ptr(out), M, N, K, x.stride(0), ldy, int(out_f16),
+                              _ptr(ws), ws.numel(), _stream()), "linear")
+    return out
+
+
+def rmsnorm(x, w, eps, add_unit_offset=False):
+    import torch
+    y = torch.empty_like(x)
+    rows = x.numel() // x.shape[-1]
+    check(lib().mllmcu_rmsnorm(_ptr(x), _ptr(w), _ptr(y), rows, x.shape[-1], eps, int(add_unit_offset), _stream()), "rmsnorm")
+    return y
+
+
+def layernorm(x, w, b, eps):
+    import torch
+    y = torch.empty_like(x)
+    rows = x.numel() // x.shape[-1]
+    check(lib().mllmcu_layernorm(_ptr(x), _ptr(w), _ptr(b), _ptr(y), rows, x.shape[-1], eps, _stream()), "layernorm")
+    return y
+
+
+def rope(rope_type, x, pos0, sin_t, cos_t, rot=None, out_f16=False, out=None, out_bstride=None, out_sstride=None):
+    """x cuda fp32 [B,S,H,D]."""
+    import torch
+    B, S, H, D = x.shape
+    rot = D if rot is None else rot
+    if out is None:
+        out = torch.empty((B, S, H, D), dtype=torch.float16 if out_f16 else torch.float32, device=x.device)
+        out_bstride, out_sstride = S * H * D, H * D
+    check(lib().mllmcu_rope(rope_type, _ptr(x), _ptr(out), B, S, H, D, rot, pos0, _ptr(sin_t), _ptr(cos_t), sin_t.shape[1],
+                            int(out_f16), out_bstride, out_sstride, _stream()), "rope")
+    return out
+
+
+def _ew(fn, a, b=None):
+    import torch
+    y = torch.empty_like(a)
+    if b is None:
+        check(fn(_ptr(a), _ptr(y), a.numel(), _stream()))
+    else:
+        check(fn(_ptr(a), _ptr(b), _ptr(y), a.numel(), _stream()))
+    return y
+
+
+def silu(x):
+    return _ew(lib().mllmcu_silu, x)
+
+
+def silu_mul(g, u):
+    return _ew(lib().mllmcu_silu_mul, g, u)
+
+
+def add(a, b):
+    return _ew(lib().mllmcu_add, a, b)
+
+
+def mul(a, b):
+    return _ew(lib().mllmcu_mul, a, b)
+
+
+def embedding_q4_0(table, ids, hidden):
+    import torch
+    n = ids.numel()
+    out = torch.zeros((n, hidden), dtype=torch.float32, device=table.device)
+    check(lib().mllmcu_embedding_q4_0(_ptr(table), _ptr(ids), _ptr(out), n, hidden, _stream()), "embedding")
+    return out
+
+
+def flash_attn_f16kv(q, k, v, causal=True, kv_bstride=None):
+    """q cuda fp32 [B,Sq,Hq,D]; k,v cuda fp16 [B,Sk,Hkv,D] (or a cache with batch stride kv_bstride)."""
+    import torch
+    B, Sq, Hq, D = q.shape
+    Sk, Hkv = k.shape[1], k.shape[2]
+    kv_bstride = k.stride(0) if kv_bstride is None else kv_bstride
+    o = torch.empty_like(q)
+    need = lib().mllmcu_flash_attn_workspace_bytes(B, Sq, Hq, D)
+    ws = _workspace(need, q.device)
+    check(lib().mllmcu_flash_attn_f16kv(_ptr(q), _ptr(k), _ptr(v), _ptr(o), B, Sq, Sk, Hq, Hkv, D, int(causal), kv_bstride,
+                                        _ptr(ws), ws.numel(), _stream()), "flash_attn")
+    return o
+
+
+def argmax(logits):
+    import torch
+    rows, n = logits.shape
+    out = torch.empty((rows,), dtype=torch.int32, device=logits.device)
+    check(lib().mllmcu_argmax(_ptr(logits), rows, n, _ptr(out), _stream()), "argmax")
+    return out

@@ -1,0 +1,60 @@
+// common.cuh -- shared device helpers for the mllm CUDA backend kernels (sm_100a).
+#pragma once
+#include <cuda_runtime.h>
+#include <cuda_fp16.h>
+#include <stdint.h>
+
+#define MLLMCU_API extern "C" __attribute__((visibility("default")))
+
+#define QK 32
+// Native block layouts, byte-identical to mllm/DataType.hpp:75-78 (block_q4_0)
+// and :137-140 (block_q8_0).  Kept packed: rows of these are uploaded as-is.
+struct __align__(2) block_q4_0 { __half d; uint8_t qs[16]; };
+struct __align__(2) block_q8_0 { __half d; int8_t qs[32]; };
+static_assert(sizeof(block_q4_0) == 18, "q4_0 block");
+static_assert(sizeof(block_q8_0) == 34, "q8_0 block");
+
+#define CU_TRY(x)                                   \
+    do {                                            \
+        cudaError_t e__ = (x);                      \
+        if (e__ != cudaSuccess) return (int)e__;    \
+    } while (0)
+#define CU_LAUNCH_CHECK() CU_TRY(cudaGetLastError())
+
+static __device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+static __device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+static __device__ __forceinline__ double warp_sum_d(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+static __device__ __forceinline__ int warp_sum_i(int v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+// Q8_0 quantisation of one value given the block's amax; bit-identical to the
+// AVX2 body of quantize_row_q8_0 (ggml/QuantizeQ8.cpp:128-150): id = 127/amax
+// is its own IEEE division, the product is rounded once (no FMA contraction)
+// and converted with round-half-even.
+static __device__ __forceinline__ int q8_0_quant(float x, float amax) {
+    const float id = (amax != 0.0f) ? __fdiv_rn(127.f, amax) : 0.0f;
+    return __float2int_rn(__fmul_rn(x, id));
+}
+static __device__ __forceinline__ __half q8_0_scale(float amax) { return __float2half_rn(__fdiv_rn(amax, 127.f)); }
+
+// 128-bit streaming load that does not allocate in L1 (weights are read once).
+static __device__ __forceinline__ uint4 ld_stream_u4(const void *p) {
+    uint4 r;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+    return r;
+}

@@ -1,0 +1,47 @@
+// runtime.cu -- device/memory/stream entry points of the C ABI (include/mllmcu.h).
+// These are what CUDABackend::alloc_device / free_device / copy_from_host /
+// copy_to_host / load_from_file reduce to (reference interface: mllm/Backend.hpp:60-71,118).
+#include "common.cuh"
+#include <string.h>
+
+MLLMCU_API int mllmcu_version(void) { return 100; }
+MLLMCU_API int mllmcu_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) return 0;
+    return n;
+}
+MLLMCU_API int mllmcu_set_device(int dev) { CU_TRY(cudaSetDevice(dev)); return 0; }
+MLLMCU_API int mllmcu_device_info(int dev, char *name, int *sm_major, int *sm_minor, int *sm_count, size_t *mem_bytes) {
+    cudaDeviceProp p;
+    CU_TRY(cudaGetDeviceProperties(&p, dev));
+    if (name) { strncpy(name, p.name, 255); name[255] = 0; }
+    if (sm_major) *sm_major = p.major;
+    if (sm_minor) *sm_minor = p.minor;
+    if (sm_count) *sm_count = p.multiProcessorCount;
+    if (mem_bytes) *mem_bytes = p.totalGlobalMem;
+    return 0;
+}
+MLLMCU_API int mllmcu_malloc(void **dptr, size_t bytes) { CU_TRY(cudaMalloc(dptr, bytes)); return 0; }
+MLLMCU_API int mllmcu_free(void *dptr) { CU_TRY(cudaFree(dptr)); return 0; }
+MLLMCU_API int mllmcu_memset(void *dptr, int value, size_t bytes, void *stream) {
+    CU_TRY(cudaMemsetAsync(dptr, value, bytes, (cudaStream_t)stream)); return 0;
+}
+MLLMCU_API int mllmcu_memcpy_h2d(void *dst, const void *src, size_t bytes, void *stream) {
+    CU_TRY(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, (cudaStream_t)stream)); return 0;
+}
+MLLMCU_API int mllmcu_memcpy_d2h(void *dst, const void *src, size_t bytes, void *stream) {
+    CU_TRY(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, (cudaStream_t)stream)); return 0;
+}
+MLLMCU_API int mllmcu_memcpy_d2d(void *dst, const void *src, size_t bytes, void *stream) {
+    CU_TRY(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToDevice, (cudaStream_t)stream)); return 0;
+}
+MLLMCU_API int mllmcu_host_alloc(void **hptr, size_t bytes) { CU_TRY(cudaHostAlloc(hptr, bytes, cudaHostAllocDefault)); return 0; }
+MLLMCU_API int mllmcu_host_free(void *hptr) { CU_TRY(cudaFreeHost(hptr)); return 0; }
+MLLMCU_API int mllmcu_stream_create(void **stream) {
+    cudaStream_t s;
+    CU_TRY(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking));
+    *stream = (void *)s;
+    return 0;
+}
+MLLMCU_API int mllmcu_stream_destroy(void *stream) { CU_TRY(cudaStreamDestroy((cudaStream_t)stream)); return 0; }
+MLLMCU_API int mllmcu_stream_sync(void *stream) { CU_TRY(cudaStreamSynchronize((cudaStream_t)stream)); return 0; }

@@ -1,0 +1,121 @@
+/* model_runner.c -- see model_runner.h.  TEST INFRASTRUCTURE ONLY. */
+#include "model_runner.h"
+#include <math.h>
+#include <stdlib.h>
+#include <string.h>
+#include <omp.h>
+
+/* oracle.c restatements (used by both builds for norm / rope / embedding) */
+void orc_rmsnorm(const float *x, const float *w, float *y, int rows, int dim, float eps, int add_unit_offset);
+void orc_rope_tables(int type, int pos_max, int dim, float base, float *sin_t, float *cos_t);
+void orc_rope_apply(int type, const float *x, void *out, int S, int H, int D, int rot, int pos0, const float *sin_t,
+                    const float *cos_t, int tdim, int out_fp16, size_t out_ld);
+void orc_embedding_q4_0(const void *table, const float *ids, float *out, int n_ids, int hidden);
+
+#if defined(RUNNER_REF)
+int ref_linear(int wtype, const void *W, const float *x, const float *bias, void *y, int M, int N, int K, int ldx, int ldy, int out_fp16);
+void ref_silu(const float *x, float *y, size_t n);
+void ref_flash_attn_f16kv(const float *Q, const uint16_t *K, const uint16_t *V, float *O, int Sq, int Sk, int Hq, int Hkv, int D, int causal, int threads);
+#define K_LINEAR ref_linear
+static void k_silu(const float *x, float *y, size_t n) { ref_silu(x, y, n); }
+static void k_attn(const float *Q, const uint16_t *K, const uint16_t *V, float *O, int Sq, int Sk, int Hq, int Hkv, int D) {
+    ref_flash_attn_f16kv(Q, K, V, O, Sq, Sk, Hq, Hkv, D, 1, omp_get_max_threads());
+}
+#else
+int orc_linear(int wtype, const void *W, const float *x, const float *bias, void *y, int M, int N, int K, int ldx, int ldy, int out_fp16);
+void orc_silu(const float *x, float *y, size_t n, int vec_width);
+void orc_flash_attn_f16kv(const float *Q, const uint16_t *K, const uint16_t *V, float *O, int Sq, int Sk, int Hq, int Hkv, int D, int causal, size_t kv_ld);
+#define K_LINEAR orc_linear
+static void k_silu(const float *x, float *y, size_t n) { orc_silu(x, y, n, 8); }
+static void k_attn(const float *Q, const uint16_t *K, const uint16_t *V, float *O, int Sq, int Sk, int Hq, int Hkv, int D) {
+    orc_flash_attn_f16kv(Q, K, V, O, Sq, Sk, Hq, Hkv, D, 1, (size_t)Hkv * D);
+}
+#endif
+
+typedef struct {
+    int vocab, hidden, layers, heads, kv_heads, head_dim, ffn, rope_type, cache_limit, max_batch, wtype, pos_max;
+    float rope_theta, rms_eps;
+    const void **lt; /* [layers][MR_N_ROLES] */
+    const void *g[MR_N_GLOBAL];
+    uint16_t *kc, *vc; /* [layers][max_batch][cache_limit][kv_heads][head_dim] */
+    float *sin_t, *cos_t;
+    int cache_len;
+} mr_t;
+
+void *mr_create(const int *ci, const float *cf) {
+    mr_t *m = (mr_t *)calloc(1, sizeof(mr_t));
+    m->vocab = ci[0]; m->hidden = ci[1]; m->layers = ci[2]; m->heads = ci[3]; m->kv_heads = ci[4];
+    m->head_dim = ci[5]; m->ffn = ci[6]; m->rope_type = ci[7]; m->cache_limit = ci[8]; m->max_batch = ci[9];
+    m->wtype = ci[10]; m->pos_max = ci[11];
+    m->rope_theta = cf[0]; m->rms_eps = cf[1];
+    m->lt = (const void **)calloc((size_t)m->layers * MR_N_ROLES, sizeof(void *));
+    size_t csz = (size_t)m->layers * m->max_batch * m->cache_limit * m->kv_heads * m->head_dim;
+    /* CPUKVCache zero-fills the cache at construction: op/CPUKVCache.cpp:53-66 */
+    m->kc = (uint16_t *)calloc(csz, 2);
+    m->vc = (uint16_t *)calloc(csz, 2);
+    m->sin_t = (float *)malloc(sizeof(float) * (size_t)m->pos_max * m->head_dim);
+    m->cos_t = (float *)malloc(sizeof(float) * (size_t)m->pos_max * m->head_dim);
+    orc_rope_tables(m->rope_type, m->pos_max, m->head_dim, m->rope_theta, m->sin_t, m->cos_t);
+    return m;
+}
+void mr_destroy(void *h) {
+    mr_t *m = (mr_t *)h;
+    free(m->lt); free(m->kc); free(m->vc); free(m->sin_t); free(m->cos_t); free(m);
+}
+void mr_set_layer(void *h, int layer, int role, const void *p) { ((mr_t *)h)->lt[(size_t)layer * MR_N_ROLES + role] = p; }
+void mr_set_global(void *h, int role, const void *p) { ((mr_t *)h)->g[role] = p; }
+void mr_reset(void *h) { ((mr_t *)h)->cache_len = 0; } /* KVCache::clearCache + RoPE::clearCache */
+int mr_cache_len(void *h) { return ((mr_t *)h)->cache_len; }
+
+int mr_forward(void *h, const float *ids, int B, int S, float *logits, float *dump) {
+    mr_t *m = (mr_t *)h;
+    const int H = m->hidden, Hq = m->heads, Hkv = m->kv_heads, D = m->head_dim, F = m->ffn;
+    const int T = B * S, pos0 = m->cache_len, Sk = pos0 + S;
+    if (B > m->max_batch || Sk > m->cache_limit) return -1; /* CPUKVCache exits here: op/CPUKVCache.cpp:121-126 */
+    float *x = (float *)malloc(sizeof(float) * (size_t)T * H);
+    float *xn = (float *)malloc(sizeof(float) * (size_t)T * H);
+    float *q = (float *)malloc(sizeof(float) * (size_t)T * Hq * D);
+    float *qr = (float *)malloc(sizeof(float) * (size_t)T * Hq * D);
+    float *k = (float *)malloc(sizeof(float) * (size_t)T * Hkv * D);
+    float *ao = (float *)malloc(sizeof(float) * (size_t)T * Hq * D);
+    float *t1 = (float *)malloc(sizeof(float) * (size_t)T * H);
+    float *gt = (float *)malloc(sizeof(float) * (size_t)T * F);
+    float *up = (float *)malloc(sizeof(float) * (size_t)T * F);
+    const size_t kvrow = (size_t)Hkv * D;
+    orc_embedding_q4_0(m->g[MR_G_EMBED], ids, x, T, H);
+    if (dump) memcpy(dump, x, sizeof(float) * (size_t)T * H);
+    for (int L = 0; L < m->layers; L++) {
+        const void **lt = m->lt + (size_t)L * MR_N_ROLES;
+        uint16_t *kc = m->kc + (size_t)L * m->max_batch * m->cache_limit * kvrow;
+        uint16_t *vc = m->vc + (size_t)L * m->max_batch * m->cache_limit * kvrow;
+        orc_rmsnorm(x, (const float *)lt[MR_ATTN_NORM], xn, T, H, m->rms_eps, 0);
+        K_LINEAR(m->wtype, lt[MR_WQ], xn, (const float *)lt[MR_BQ], q, T, Hq * D, H, H, Hq * D, 0);
+        K_LINEAR(m->wtype, lt[MR_WK], xn, (const float *)lt[MR_BK], k, T, Hkv * D, H, H, Hkv * D, 0);
+        for (int b = 0; b < B; b++) {
+            uint16_t *kcb = kc + ((size_t)b * m->cache_limit + pos0) * kvrow;
+            uint16_t *vcb = vc + ((size_t)b * m->cache_limit + pos0) * kvrow;
+            /* v_proj writes fp16 straight into the cache slice (Matmul.cpp:262-268) */
+            K_LINEAR(m->wtype, lt[MR_WV], xn + (size_t)b * S * H, (const float *)lt[MR_BV], vcb, S, Hkv * D, H, H, Hkv * D, 1);
+            orc_rope_apply(m->rope_type, q + (size_t)b * S * Hq * D, qr + (size_t)b * S * Hq * D, S, Hq, D, D, pos0, m->sin_t, m->cos_t, D, 0, (size_t)Hq * D);
+            orc_rope_apply(m->rope_type, k + (size_t)b * S * Hkv * D, kcb, S, Hkv, D, D, pos0, m->sin_t, m->cos_t, D, 1, kvrow);
+            k_attn(qr + (size_t)b * S * Hq * D, kc + (size_t)b * m->cache_limit * kvrow, vc + (size_t)b * m->cache_limit * kvrow,
+                   ao + (size_t)b * S * Hq * D, S, Sk, Hq, Hkv, D);
+        }
+        K_LINEAR(m->wtype, lt[MR_WO], ao, NULL, t1, T, H, Hq * D, Hq * D, H, 0);
+        for (size_t i = 0; i < (size_t)T * H; i++) t1[i] = t1[i] + x[i]; /* tmp = x + inputs[0] */
+        orc_rmsnorm(t1, (const float *)lt[MR_FFN_NORM], xn, T, H, m->rms_eps, 0);
+        K_LINEAR(m->wtype, lt[MR_W_GATE], xn, NULL, gt, T, F, H, H, F, 0);
+        k_silu(gt, gt, (size_t)T * F);
+        K_LINEAR(m->wtype, lt[MR_W_UP], xn, NULL, up, T, F, H, H, F, 0);
+        for (size_t i = 0; i < (size_t)T * F; i++) gt[i] = gt[i] * up[i];
+        K_LINEAR(m->wtype, lt[MR_W_DOWN], gt, NULL, x, T, H, F, F, H, 0);
+        for (size_t i = 0; i < (size_t)T * H; i++) x[i] = x[i] + t1[i];
+        if (dump) memcpy(dump + (size_t)(L + 1) * T * H, x, sizeof(float) * (size_t)T * H);
+    }
+    orc_rmsnorm(x, (const float *)m->g[MR_G_NORM], xn, T, H, m->rms_eps, 0);
+    for (int b = 0; b < B; b++) /* clip to the last token when S>1: modeling_llama.hpp:109-112 */
+        K_LINEAR(m->wtype, m->g[MR_G_LM_HEAD], xn + ((size_t)b * S + S - 1) * H, NULL, logits + (size_t)b * m->vocab, 1, m->vocab, H, H, m->vocab, 0);
+    m->cache_len = Sk;
+    free(x); free(xn); free(q); free(qr); free(k); free(ao); free(t1); free(gt); free(up);
+    return 0;
+}

@@ -1,0 +1,246 @@
+"""ctypes access to the CPU checkers.  TEST INFRASTRUCTURE ONLY.
+
+`port()` -> oracle/liboracle.so (plain-C restatement, oracle.c)
+`ref()`  -> oracle/_ref/libmllm_ref.so (the reference's own sources, compiled by
+            oracle/Makefile) or None when it has not been built.
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl
+reference legs may import this module; mllm_b200/ never does.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+_port = None
+_ref = None
+
+Q4_0, Q8_0 = 2, 8  # mllm/Types.hpp:64-68 DataType values
+Q4_0_BYTES, Q8_0_BYTES = 18, 34
+
+
+def build():
+    """(Re)build liboracle.so and, where /root/reference exists, _ref/libmllm_ref.so."""
+    subprocess.run(["make", "-s", "-C", HERE], check=True)
+
+
+def _p(a):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+class Lib:
+    """Uniform numpy front-end over either library (prefix 'orc_' or 'ref_')."""
+
+    def __init__(self, path, prefix):
+        self.lib = C.CDLL(path)
+        self.prefix = prefix
+        self.path = path
+        L = self.lib
+        for name in ("fp32_to_fp16",):
+            f = getattr(L, prefix + name)
+            f.restype = C.c_uint16
+            f.argtypes = [C.c_float]
+        f = getattr(L, prefix + "fp16_to_fp32")
+        f.restype = C.c_float
+        f.argtypes = [C.c_uint16]
+        L.mr_create.restype = C.c_void_p
+        L.mr_create.argtypes = [C.c_void_p, C.c_void_p]
+        L.mr_destroy.argtypes = [C.c_void_p]
+        L.mr_set_layer.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p]
+        L.mr_set_global.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
+        L.mr_reset.argtypes = [C.c_void_p]
+        L.mr_cache_len.argtypes = [C.c_void_p]
+        L.mr_forward.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
+        L.mr_forward.restype = C.c_int
+
+    def fn(self, name):
+        return getattr(self.lib, self.prefix + name)
+
+    # ---- rows
+    def quantize_q8_0(self, x):
+        x = np.ascontiguousarray(x, dtype=np.float32)
+        rows, k = x.reshape(-1, x.shape[-1]).shape
+        out = np.empty((rows, k // 32 * Q8_0_BYTES), dtype=np.uint8)
+        f = self.fn("quantize_row_q8_0")
+        xr = x.reshape(rows, k)
+        for r in range(rows):
+            f(_p(xr[r]), _p(out[r]), C.c_int(k))
+        return out
+
+    def quantize_q4_0(self, x):
+        x = np.ascontiguousarray(x, dtype=np.float32)
+        rows, k = x.reshape(-1, x.shape[-1]).shape
+        out = np.empty((rows, k // 32 * Q4_0_BYTES), dtype=np.uint8)
+        f = self.fn("quantize_row_q4_0")
+        xr = x.reshape(rows, k)
+        for r in range(rows):
+            f(_p(xr[r]), _p(out[r]), C.c_int(k))
+        return out
+
+    def dequantize_q4_0(self, w, k):
+        w = np.ascontiguousarray(w, dtype=np.uint8).reshape(-1, k // 32 * Q4_0_BYTES)
+        out = np.empty((w.shape[0], k), dtype=np.float32)
+        f = self.fn("dequantize_row_q4_0")
+        for r in range(w.shape[0]):
+            f(_p(w[r]), _p(out[r]), C.c_int(k))
+        return out
+
+    def vec_dot_q4_0_q8_0(self, wrow, xrow, k):
+        s = C.c_float(0)
+        self.fn("vec_dot_q4_0_q8_0")(C.c_int(k), C.byref(s), _p(wrow), _p(xrow))
+        return np.float32(s.value)
+
+    def linear(self, W, x, bias=None, wtype=Q4_0, out_fp16=False):
+        """x [M,K] fp32, W [N, K/32*blk] uint8 -> y [M,N] fp32 (or uint16 holding fp16)."""
+        x = np.ascontiguousarray(x, dtype=np.float32)
+        M, K = x.shape
+        N = W.shape[0]
+        y = np.empty((M, N), dtype=np.uint16 if out_fp16 else np.float32)
+        b = _p(np.ascontiguousarray(bias, dtype=np.float32)) if bias is not None else None
+        rc = self.fn("linear")(C.c_int(wtype), _p(W), _p(x), b, _p(y), M, N, K, K, N, int(out_fp16))
+        assert rc == 0
+        return y
+
+    def silu(self, x):
+        x = np.ascontiguousarray(x, dtype=np.float32)
+        y = np.empty_like(x)
+        if self.prefix == "orc_":
+            self.fn("silu")(_p(x), _p(y), C.c_size_t(x.size), 8)
+        else:
+            self.fn("silu")(_p(x), _p(y), C.c_size_t(x.size))
+        return y
+
+    def flash_attn_f16kv(self, q, k, v, causal=True, threads=1):
+        """q [Sq,Hq,D] fp32; k,v [Sk,Hkv,D] uint16 (fp16 bits) contiguous -> o [Sq,Hq,D]."""
+        q = np.ascontiguousarray(q, dtype=np.float32)
+        k = np.ascontiguousarray(k, dtype=np.uint16)
+        v = np.ascontiguousarray(v, dtype=np.uint16)
+        Sq, Hq, D = q.shape
+        Sk, Hkv, _ = k.shape
+        o = np.empty_like(q)
+        if self.prefix == "orc_":
+            self.fn("flash_attn_f16kv")(_p(q), _p(k), _p(v), _p(o), Sq, Sk, Hq, Hkv, D, int(causal), C.c_size_t(Hkv * D))
+        else:
+            self.fn("flash_attn_f16kv")(_p(q), _p(k), _p(v), _p(o), Sq, Sk, Hq, Hkv, D, int(causal), threads)
+        return o
+
+
+class PortOnly:
+    """Functions that exist only in the restatement (no compilable reference twin)."""
+
+    def __init__(self, lib):
+        self.L = lib.lib
+
+    def rmsnorm(self, x, w, eps, add_unit_offset=False):
+        x = np.ascontiguousarray(x, dtype=np.float32)
+        rows, dim = x.reshape(-1, x.shape[-1]).shape
+        y = np.empty_like(x)
+        w = np.ascontiguousarray(w, dtype=np.float32)
+        self.L.orc_rmsnorm(_p(x), _p(w), _p(y), rows, dim, C.c_float(eps), int(add_unit_offset))
+        return y
+
+    def layernorm(self, x, w, b, eps):
+        x = np.ascontiguousarray(x, dtype=np.float32)
+        rows, dim = x.reshape(-1, x.shape[-1]).shape
+        y = np.empty_like(x)
+        self.L.orc_layernorm(_p(x), _p(w) if w is not None else None, _p(b) if b is not None else None, _p(y), rows, dim, C.c_float(eps))
+        return y
+
+    def rope_tables(self, rtype, pos_max, dim, base):
+        s = np.empty((pos_max, dim), dtype=np.float32)
+        c = np.empty((pos_max, dim), dtype=np.float32)
+        self.L.orc_rope_tables(rtype, pos_max, dim, C.c_float(base), _p(s), _p(c))
+        return s, c
+
+    def rope_apply(self, rtype, x, pos0, sin_t, cos_t, rot=None, out_fp16=False):
+        x = np.ascontiguousarray(x, dtype=np.float32)
+        S, H, D = x.shape
+        rot = D if rot is None else rot
+        out = np.empty((S, H, D), dtype=np.uint16 if out_fp16 else np.float32)
+        self.L.orc_rope_apply(rtype, _p(x), _p(out), S, H, D, rot, pos0, _p(sin_t), _p(cos_t), sin_t.shape[1], int(out_fp16), C.c_size_t(H * D))
+        return out
+
+    def embedding_q4_0(self, table, ids, hidden):
+        ids = np.ascontiguousarray(ids, dtype=np.float32).reshape(-1)
+        out = np.zeros((ids.size, hidden), dtype=np.float32)
+        self.L.orc_embedding_q4_0(_p(table), _p(ids), _p(out), ids.size, hidden)
+        return out
+
+    def block_isums_q4_0_q8_0(self, wrow, xrow, k):
+        out = np.empty(k // 32, dtype=np.int32)
+        self.L.orc_block_isums_q4_0_q8_0(k, _p(wrow), _p(xrow), _p(out))
+        return out
+
+    def fp32_to_fp16_bits(self, x):
+        x = np.ascontiguousarray(x, dtype=np.float32)
+        f = self.L.orc_fp32_to_fp16
+        f.restype = C.c_uint16
+        f.argtypes = [C.c_float]
+        return np.array([f(float(v)) for v in x.reshape(-1)], dtype=np.uint16).reshape(x.shape)
+
+
+def port():
+    global _port
+    if _port is None:
+        so = os.path.join(HERE, "liboracle.so")
+        if not os.path.exists(so):
+            build()
+        _port = Lib(so, "orc_")
+        _port.only = PortOnly(_port)
+    return _port
+
+
+def ref():
+    """The compiled reference, or None if oracle/_ref has not been built."""
+    global _ref
+    if _ref is None:
+        so = os.path.join(HERE, "_ref", "libmllm_ref.so")
+        if not os.path.exists(so):
+            return None
+        _ref = Lib(so, "ref_")
+    return _ref
+
+
+class ModelRunner:
+    """CPU forward of a LLaMA-family model held in a dict name -> numpy array (see mllm_b200.mllm_file)."""
+
+    ROLES = dict(attn_norm=0, wq=1, wk=2, wv=3, wo=4, bq=5, bk=6, bv=7, ffn_norm=8, w_gate=9, w_up=10, w_down=11)
+
+    def __init__(self, lib, cfg, tensors, names, max_batch=1, cache_limit=None):
+        self.lib = lib.lib
+        self.cfg = cfg
+        self.keep = tensors
+        cache_limit = cache_limit or cfg["cache_limit"]
+        ci = np.array([cfg["vocab"], cfg["hidden"], cfg["layers"], cfg["heads"], cfg["kv_heads"], cfg["head_dim"],
+                       cfg["ffn"], cfg["rope_type"], cache_limit, max_batch, Q4_0, cfg.get("pos_max", cache_limit)], dtype=np.int32)
+        cf = np.array([cfg["rope_theta"], cfg["rms_eps"]], dtype=np.float32)
+        self.h = C.c_void_p(self.lib.mr_create(_p(ci), _p(cf)))
+        for L in range(cfg["layers"]):
+            for role, idx in self.ROLES.items():
+                nm = names.layer(L, role)
+                if nm in tensors:
+                    self.lib.mr_set_layer(self.h, L, idx, _p(tensors[nm]))
+        self.lib.mr_set_global(self.h, 0, _p(tensors[names.embed]))
+        self.lib.mr_set_global(self.h, 1, _p(tensors[names.norm]))
+        self.lib.mr_set_global(self.h, 2, _p(tensors[names.lm_head]))
+
+    def reset(self):
+        self.lib.mr_reset(self.h)
+
+    def forward(self, ids, dump=False):
+        ids = np.ascontiguousarray(ids, dtype=np.float32)
+        B, S = ids.shape
+        logits = np.empty((B, self.cfg["vocab"]), dtype=np.float32)
+        d = np.empty((self.cfg["layers"] + 1, B * S, self.cfg["hidden"]), dtype=np.float32) if dump else None
+        rc = self.lib.mr_forward(self.h, _p(ids), B, S, _p(logits), _p(d) if dump else None)
+        if rc != 0:
+            raise RuntimeError("KV cache limit exceeded")
+        return (logits, d) if dump else logits
+
+    def __del__(self):
+        try:
+            self.lib.mr_destroy(self.h)
+        except Exception:
+            pass
