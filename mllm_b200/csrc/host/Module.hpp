@@ -1,0 +1,97 @@
+// Module.hpp -- the thin slice of mllm's eager front-end the hot path is entered through
+// (mllm/Layer.hpp:116-222 Layer::run / initOp, mllm/Module.hpp:193-261 load / operator()),
+// and the LLaMA-family graph exactly as the reference's model headers compose it
+// (models/llama/modeling_llama.hpp:29-115, models/transformer/modeling_transformer.hpp:132-212).
+// Inside the mllm tree none of this is needed: the unchanged model headers drive the
+// CUDABackend through Backend::runOp.  Here it lets the same op sequence run standalone.
+#pragma once
+#include "mllm_cuda.hpp"
+
+namespace mllm {
+
+struct ModuleState { // Module::doLoad / doTrace / loader (mllm/Module.hpp)
+    CUDABackend *backend = nullptr;
+    ParamLoader *loader = nullptr;
+    bool doLoad = false;
+};
+
+class Layer { // mllm/Layer.hpp:30-222
+public:
+    Layer() = default;
+    Layer(ModuleState *st, OpType type, const string &name, OpParam p = {}) : st_(st), name_(name), param_(std::move(p)) { param_["type"] = (float)type; }
+    bool ready() const { return st_ != nullptr; }
+    Tensor operator()(Tensor x) { return run({x})[0]; }
+    vector<Tensor> run(vector<Tensor> inputs) {
+        if (!op_) op_.reset(st_->backend->opCreate(param_, name_)); // part 2: initOp
+        if (st_->doLoad && !loaded_) {                                // part 3: load params
+            op_->load(*st_->loader);
+            loaded_ = true;
+        }
+        return st_->backend->runOp(op_.get(), inputs, {"out-" + name_}, false); // part 4
+    }
+    Op *op() { return op_.get(); }
+
+private:
+    ModuleState *st_ = nullptr;
+    string name_;
+    OpParam param_;
+    std::unique_ptr<Op> op_;
+    bool loaded_ = false;
+};
+
+// Tensor::runFunc-style functional ops (mllm/Tensor.cpp:361-422): ops created per call site, cached by name.
+class FuncCache {
+public:
+    explicit FuncCache(ModuleState *st) : st_(st) {}
+    Tensor run(OpType t, const string &out_name, OpParam p, vector<Tensor> in) {
+        auto it = ops_.find(out_name);
+        if (it == ops_.end()) {
+            p["type"] = (float)t;
+            it = ops_.emplace(out_name, std::unique_ptr<Op>(st_->backend->opCreate(p, out_name))).first;
+        }
+        return st_->backend->runOp(it->second.get(), in, {out_name}, false)[0];
+    }
+
+private:
+    ModuleState *st_;
+    map<string, std::unique_ptr<Op>> ops_;
+};
+
+struct LlamaNames { // LLaMANameConfig::init (models/llama/configuration_llama.hpp:20-60)
+    string blk, attn, ffn, q, k, v, o, gate, up, down, attn_norm, ffn_norm, embd, post_norm, lm_head;
+    static LlamaNames make(int rope_type);
+};
+
+struct LlamaConfig {
+    int vocab = 32000, hidden = 4096, heads = 32, kv_heads = 32, ffn = 11008, layers = 32;
+    int rope_type = LLAMAROPE, cache_limit = 1024, max_pos = 16384;
+    float rope_theta = 10000.f, rms_eps = 1e-6f;
+    bool qkv_bias = false;
+    int head_dim() const { return hidden / heads; }
+};
+
+class LlamaModel {
+public:
+    LlamaModel(CUDABackend *bn, const LlamaConfig &cfg);
+    void load(const string &path); // Module::load: trace pass with doLoad, then ready
+    // ids: device fp32 [B,1,S,1]; returns logits [B,1,1,vocab] (device).  dump (optional, device
+    // fp32 [(layers+1)*B*S*hidden]) receives the hidden state after the embedding and each block.
+    Tensor forward(Tensor ids, float *dump = nullptr);
+    void clear_kvcache();
+    const LlamaConfig &config() const { return cfg_; }
+    CUDABackend *backend() { return st_.backend; }
+
+private:
+    struct Block {
+        Layer norm1, norm2, q, k, v, o, q_rope, k_rope, k_cache, v_cache, gate, up, down, silu;
+    };
+    Tensor block_forward(Block &b, int idx, Tensor x);
+    LlamaConfig cfg_;
+    ModuleState st_;
+    FuncCache fn_;
+    Layer embedding_, norm_, lm_head_;
+    vector<Block> blocks_;
+    std::unique_ptr<ParamLoader> loader_;
+};
+
+} // namespace mllm

@@ -1,0 +1,151 @@
+// capi_host.cpp -- C entry points over the host-side backend, so tests and bench.py can
+// drive CUDABackend / ops / LlamaModel through ctypes with HOST buffers, the way an mllm
+// demo drives a Module (examples/demo_llama.cpp, examples/mllm_benchmark.cpp:53-78,
+// Module::generate mllm/Module.cpp:63-205).  Errors: C++ exceptions are caught, the message
+// is kept for mllm_cuda_last_error(), and a negative code is returned.
+#include "Module.hpp"
+
+#include <chrono>
+#include <cstring>
+
+using namespace mllm;
+
+#define HAPI extern "C" __attribute__((visibility("default")))
+
+static thread_local std::string g_err;
+#define GUARD(...)                           \
+    try {                                    \
+        __VA_ARGS__;                         \
+        return 0;                            \
+    } catch (const std::exception &e) {      \
+        g_err = e.what();                    \
+        return -1;                           \
+    }
+
+struct HostModel {
+    std::unique_ptr<LlamaModel> model;
+    double last_ms = 0;
+};
+
+HAPI const char *mllm_cuda_last_error() { return g_err.c_str(); }
+
+// Backend::global_backends[MLLM_CUDA] = make_unique<CUDABackend>() -- the `case MLLM_CUDA:` of
+// Module::initBackend (mllm/Module.hpp:151-190)
+HAPI int mllm_cuda_init_backend(int device) {
+    GUARD({
+        if (!Backend::global_backends.count(MLLM_CUDA)) Backend::global_backends[MLLM_CUDA] = std::make_unique<CUDABackend>(device);
+    })
+}
+static CUDABackend *backend() {
+    auto it = Backend::global_backends.find(MLLM_CUDA);
+    if (it == Backend::global_backends.end()) throw std::runtime_error("[mllm-cuda] backend not initialised (mllm_cuda_init_backend)");
+    return static_cast<CUDABackend *>(it->second.get());
+}
+HAPI int mllm_cuda_shutdown() { GUARD({ Backend::global_backends.erase(MLLM_CUDA); }) }
+
+// cfg_i: vocab, hidden, layers, heads, kv_heads, ffn, rope_type, cache_limit, max_pos, qkv_bias ; cfg_f: rope_theta, rms_eps
+HAPI int mllm_cuda_llama_create(const int *ci, const float *cf, void **out) {
+    GUARD({
+        LlamaConfig c;
+        c.vocab = ci[0]; c.hidden = ci[1]; c.layers = ci[2]; c.heads = ci[3]; c.kv_heads = ci[4]; c.ffn = ci[5];
+        c.rope_type = ci[6]; c.cache_limit = ci[7]; c.max_pos = ci[8]; c.qkv_bias = ci[9] != 0;
+        c.rope_theta = cf[0]; c.rms_eps = cf[1];
+        auto *h = new HostModel();
+        h->model = std::make_unique<LlamaModel>(backend(), c);
+        *out = h;
+    })
+}
+HAPI int mllm_cuda_llama_destroy(void *h) { GUARD({ delete (HostModel *)h; }) }
+HAPI int mllm_cuda_llama_load(void *h, const char *path) { GUARD({ ((HostModel *)h)->model->load(path); }) }
+HAPI int mllm_cuda_llama_clear_kvcache(void *h) { GUARD({ ((HostModel *)h)->model->clear_kvcache(); }) }
+
+// model({input_ids}) with host buffers: ids_host [B,S] fp32 token ids -> logits_host [B,vocab].
+// dump_host (optional) [(layers+1), B*S, hidden].  Wall time of H2D + forward + D2H is recorded.
+HAPI int mllm_cuda_llama_forward(void *hv, const float *ids_host, int B, int S, float *logits_host, float *dump_host) {
+    GUARD({
+        auto *h = (HostModel *)hv;
+        CUDABackend *bn = h->model->backend();
+        const auto t0 = std::chrono::steady_clock::now();
+        Tensor ids(B, 1, S, 1, bn);
+        ids.setName("input_ids");
+        ids.copyFromHost(ids_host);
+        Tensor dump;
+        const LlamaConfig &c = h->model->config();
+        if (dump_host) dump = Tensor(1, 1, (c.layers + 1) * B * S, c.hidden, bn);
+        Tensor logits = h->model->forward(ids, dump_host ? dump.devPtr<float>() : nullptr);
+        logits.copyToHost(logits_host);
+        if (dump_host) dump.copyToHost(dump_host);
+        h->last_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    })
+}
+
+// Greedy generation, the loop of Module::generate (mllm/Module.cpp:63-100,146-205): forward,
+// D2H logits, host argmax (LlmTextGenerator greedy, Generate.cpp:46-53), feed the token back.
+// ids_host [B,S]; out_tokens [B,max_new] int32.
+HAPI int mllm_cuda_llama_generate(void *hv, const float *ids_host, int B, int S, int max_new, int *out_tokens) {
+    GUARD({
+        auto *h = (HostModel *)hv;
+        CUDABackend *bn = h->model->backend();
+        const int V = h->model->config().vocab;
+        std::vector<float> logits((size_t)B * V), next((size_t)B);
+        std::vector<float> cur(ids_host, ids_host + (size_t)B * S);
+        int s = S;
+        for (int step = 0; step < max_new; step++) {
+            Tensor ids(B, 1, s, 1, bn);
+            ids.setName("input_ids");
+            ids.copyFromHost(cur.data());
+            Tensor lg = h->model->forward(ids);
+            lg.copyToHost(logits.data());
+            for (int b = 0; b < B; b++) {
+                const float *row = logits.data() + (size_t)b * V;
+                int best = 0;
+                for (int i = 1; i < V; i++) if (row[i] > row[best]) best = i;
+                out_tokens[(size_t)b * max_new + step] = best;
+                next[b] = (float)best;
+            }
+            cur.assign(next.begin(), next.end());
+            s = 1;
+        }
+    })
+}
+
+HAPI double mllm_cuda_llama_last_forward_ms(void *h) { return ((HostModel *)h)->last_ms; }
+HAPI long long mllm_cuda_kernel_launches() {
+    try { return backend()->kernel_launches; } catch (...) { return -1; }
+}
+HAPI int mllm_cuda_pool_stats(size_t *bytes, size_t *hits, size_t *misses) {
+    GUARD({
+        CUDABackend *b = backend();
+        *bytes = b->bytes_allocated; *hits = b->pool_hits; *misses = b->pool_misses;
+    })
+}
+HAPI int mllm_cuda_sync() { GUARD({ backend()->sync(); }) }
+
+// ---- per-op access for the per-op parity tests (test/cpu/CPUTest.hpp pattern: construct an Op
+// from the backend, reshape -> setUp -> load -> execute, compare tensors).
+// Runs ONE op given OpParam as parallel key/value arrays; inputs are host fp32 buffers with
+// shapes [n_in][4] (b,h,s,d); weights come from the .mllm at `path` (may be empty).
+HAPI int mllm_cuda_run_op(const char **keys, const float *vals, int n_params, const char *name, const char *path,
+                          const float **inputs, const int *in_shapes, int n_in, float *out_host, int *out_shape) {
+    GUARD({
+        CUDABackend *bn = backend();
+        OpParam p;
+        for (int i = 0; i < n_params; i++) p[keys[i]] = vals[i];
+        std::unique_ptr<Op> op(bn->opCreate(p, name));
+        ParamLoader loader(path ? path : "");
+        op->load(loader);
+        vector<Tensor> in;
+        for (int i = 0; i < n_in; i++) {
+            const int *s = in_shapes + 4 * i;
+            Tensor t(s[0], s[1], s[2], s[3], bn);
+            t.setName(string("in") + std::to_string(i));
+            t.copyFromHost(inputs[i]);
+            in.push_back(t);
+        }
+        vector<Tensor> out = bn->runOp(op.get(), in, {string("out-") + name}, false);
+        Tensor &o = out[0];
+        out_shape[0] = o.batch(); out_shape[1] = o.head(); out_shape[2] = o.sequence(); out_shape[3] = o.dimension();
+        if (o.dtype() != MLLM_TYPE_F32 || !o.contiguous()) throw std::runtime_error("run_op: output must be dense fp32");
+        o.copyToHost(out_host);
+    })
+}
