@@ -1,0 +1,331 @@
+#!/usr/bin/env python
+"""bench.py -- LLaMA-2-7B Q4_0, prefill 512 + decode 256 (BASELINE.json configs[1]) on the CUDA backend.
+
+A step = one request: clear the KV cache, prefill 512 synthetic tokens, then 256 greedy decode steps.
+  value : tokens/s of the whole request with inputs resident in HBM (device-timed, CUDA events).
+  e2e   : the same request through the host-buffer API (Module::generate-style loop: ids H2D every
+          forward, logits D2H every step, host argmax), wall clock around synchronous calls.
+  roofline : the decode GEMV (k_gemv*, the dominant kernel) -- algorithmic weight bytes / launch time,
+          measured live with CUDA events on the backend stream over all Linear shapes of a decode step.
+  cpu_baseline : the reference's CPU kernels (oracle/_ref) or the port, on a bounded sample.
+`--impl reference` times only the CPU arm.  N>1: one replica per GPU, no collective ("weak").
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+from mllm_b200 import mllm_file as mf  # noqa: E402
+
+PREFILL, DECODE, LIMIT = 512, 256, 1024
+MODEL = "llama2-7b"
+METRIC = "llama2_7b_q4_0_prefill512_decode256_tok_s"
+
+
+def log(*a):
+    print(*a, file=sys.stderr, flush=True)
+
+
+# ----------------------------------------------------------------------------- model file
+def make_model_file(cfg, path, device="cuda", seed=1234):
+    """Random-init .mllm (W ~ N(0,0.02^2) -> Q4_0 with the reference quantiser's arithmetic, norms 1+N(0,0.02^2)).
+    Generated on the GPU with torch (plumbing only), written in the reference's container format."""
+    import torch
+    want = 12 + sum(4 + len(n.encode()) + 20 for n, *_ in mf.tensor_list(cfg)) + mf.model_bytes(cfg)
+    if os.path.exists(path) and os.path.getsize(path) == want:
+        return path
+    g = torch.Generator(device=device).manual_seed(seed)
+
+    def q4_0(rows, cols):
+        out = np.empty((rows, cols // 32 * 18), dtype=np.uint8)
+        step = max(1, (1 << 26) // cols)
+        for r0 in range(0, rows, step):
+            r = min(step, rows - r0)
+            w = torch.randn((r, cols // 32, 32), generator=g, device=device) * 0.02
+            idx = w.abs().argmax(dim=2, keepdim=True)
+            mx = torch.gather(w, 2, idx)
+            d = mx / -8.0
+            idv = torch.where(d != 0, 1.0 / d, torch.zeros_like(d))
+            q = torch.clamp(((w * idv) + 8.5).to(torch.int8), max=15).to(torch.uint8)
+            blk = torch.empty((r, cols // 32, 18), dtype=torch.uint8, device=device)
+            blk[..., 0:2] = d.to(torch.float16).view(torch.uint8).reshape(r, cols // 32, 2)
+            blk[..., 2:] = q[..., :16] | (q[..., 16:] << 4)
+            out[r0:r0 + r] = blk.reshape(r, -1).cpu().numpy()
+        return out
+
+    tensors, dts = {}, {}
+    for name, rows, cols, dt in mf.tensor_list(cfg):
+        dts[name] = dt
+        if dt == mf.F32:
+            base = 1.0 if "norm" in name else 0.0
+            tensors[name] = (base + 0.02 * torch.randn(cols, generator=g, device=device)).cpu().numpy().astype(np.float32)
+        else:
+            tensors[name] = q4_0(rows, cols)
+    tmp = path + ".tmp"
+    mf.write_mllm(tmp, tensors, dts)
+    os.replace(tmp, path)
+    return path
+
+
+# ----------------------------------------------------------------------------- clocks
+class ClockSampler:
+    Q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index):
+        self.index, self.rows, self.p = index, [], None
+
+    def start(self):
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "200"],
+                                      stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.p = None
+
+    def _read(self):
+        for line in self.p.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.p is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.p.terminate()
+        try:
+            self.p.wait(timeout=3)
+        except Exception:
+            self.p.kill()
+        sm, mx, reasons = [], None, set()
+        for r in self.rows:
+            try:
+                sm.append(float(r[0]))
+                mx = float(r[1])
+                for name, v in zip(["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"], r[3:7]):
+                    if v.lower().startswith("active"):
+                        reasons.add(name)
+            except Exception:
+                pass
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ----------------------------------------------------------------------------- CPU arm
+def cpu_arm(cfg, path, prefill, decode, reps=1):
+    """Reference CPU kernels (oracle/_ref: the reference's ggml + FlashAttention2 sources) or the C port, all host threads."""
+    from oracle import pyoracle as po
+    po.build()
+    L = po.ref()
+    kind = "reference"
+    if L is None:
+        L, kind = po.port(), "port"
+    tensors, _ = mf.read_mllm(path)
+    runner = po.ModelRunner(L, cfg, tensors, mf.Names(cfg["rope_type"]), cache_limit=prefill + decode + 8)
+    rng = np.random.default_rng(7)
+    ids = rng.integers(0, cfg["vocab"], (1, prefill)).astype(np.float32)
+    times = []
+    for _ in range(reps):
+        runner.reset()
+        t0 = time.perf_counter()
+        lg = runner.forward(ids)
+        t1 = time.perf_counter()
+        for _ in range(decode):
+            lg = runner.forward(np.array([[lg.argmax()]], dtype=np.float32))
+        t2 = time.perf_counter()
+        times.append((t1 - t0, t2 - t1))
+    tp = float(np.mean([t[0] for t in times]))
+    td = float(np.mean([t[1] for t in times]))
+    cores = int(os.environ.get("OMP_NUM_THREADS", os.cpu_count() or 1))
+    return {"value": (prefill + decode) / (tp + td), "unit": "tok/s", "cores": cores, "kind": kind,
+            "sample": f"full {cfg['name']} Q4_0 graph, prefill {prefill} + decode {decode} tokens (bounded sample of the 512+256 request)",
+            "prefill_tok_s": prefill / tp, "decode_tok_s": decode / td if decode else None, "seconds": tp + td}
+
+
+# ----------------------------------------------------------------------------- GPU arm
+def gemv_roofline(cfg, peaks):
+    """Time the decode Linear (activation quantise + GEMV kernels) for every Linear shape of one decode step, live,
+    with CUDA events on the launching stream; weights rotate over buffers larger than L2 (cold HBM reads)."""
+    import torch
+    from mllm_b200 import capi
+    H, F, V, D = cfg["hidden"], cfg["ffn"], cfg["vocab"], cfg["head_dim"]
+    shapes = [("qkvo", H, H, 2 * cfg["layers"] + 2 * cfg["layers"] * cfg["kv_heads"] // cfg["heads"]),
+              ("gate_up", F, H, 2 * cfg["layers"]), ("down", H, F, cfg["layers"]), ("lm_head", V, H, 1)]
+    x_cache, total_t, total_b, per = {}, 0.0, 0.0, {}
+    for tag, N, K, count in shapes:
+        wbytes = N * (K // 32) * 18
+        nbuf = max(2, int(160e6 // wbytes) + 1)
+        bufs = [torch.randint(0, 255, (N, K // 32 * 18), dtype=torch.uint8, device="cuda") for _ in range(nbuf)]
+        x = x_cache.setdefault(K, torch.randn((1, K), device="cuda"))
+        for b in bufs[:2]:
+            capi.linear(b, x)
+        reps = max(3 * nbuf, 24)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize()
+        e0.record()
+        for i in range(reps):
+            capi.linear(bufs[i % nbuf], x)
+        e1.record()
+        torch.cuda.synchronize()
+        t = e0.elapsed_time(e1) / reps * 1e-3
+        per[tag] = {"N": N, "K": K, "us": round(t * 1e6, 2), "GBs": round(wbytes / t / 1e9, 1), "launches_per_step": count}
+        total_t += t * count
+        total_b += wbytes * count
+        del bufs
+    achieved = total_b / total_t / 1e9
+    peak = peaks.get("hbm_gbs", 6650.0)
+    return {"bound": "hbm", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s", "frac": round(achieved / peak, 4),
+            "traffic": None, "kernel": "k_gemv (decode Linear: Q8_0 activation quantise + Q4_0 GEMV), launch-weighted over one decode step",
+            "peak_source": "measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in peaks else "fallback 6650",
+            "per_shape": per}
+
+
+def gpu_arm(args, rank, world, local_rank):
+    import torch
+    torch.cuda.set_device(local_rank)
+    from mllm_b200 import backend, build
+    build.build_all()
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    cfg = mf.config(MODEL, cache_limit=LIMIT)
+    path = os.environ.get("MLLM_BENCH_MODEL", f"/tmp/mllm_bench_{MODEL}_q4_0.mllm")
+    t0 = time.time()
+    if rank == 0:
+        make_model_file(cfg, path, device=f"cuda:{local_rank}")
+    if world > 1:
+        import torch.distributed as dist
+        dist.barrier()
+    log(f"[rank {rank}] model file ready in {time.time() - t0:.1f}s")
+    t0 = time.time()
+    model = backend.LlamaModel(cfg, device=local_rank).load(path)
+    log(f"[rank {rank}] loaded {mf.model_bytes(cfg) / 1e9:.2f} GB through ParamLoader in {time.time() - t0:.1f}s")
+    rng = np.random.default_rng(1234 + rank)
+    ids = rng.integers(0, cfg["vocab"], (1, PREFILL)).astype(np.float32)
+
+    def request():
+        model.clear_kvcache()
+        return model.request_device(ids, DECODE)
+
+    for _ in range(args.warmup):
+        request()
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    if world > 1:
+        import torch.distributed as dist
+        dist.barrier()
+    torch.cuda.synchronize()
+    l0 = backend.kernel_launches()
+    tp, td = [], []
+    for _ in range(args.steps):
+        a, b, _ = request()
+        tp.append(a)
+        td.append(b)
+    torch.cuda.synchronize()
+    launches = backend.kernel_launches() - l0
+    total_ms = float(np.sum(tp) + np.sum(td))
+    # e2e: host-buffer API (H2D ids every forward, D2H logits every step, host argmax), wall clock
+    e2e_ms = []
+    for _ in range(max(1, min(args.steps, 2))):
+        model.clear_kvcache()
+        w0 = time.perf_counter()
+        model.generate(ids, DECODE)
+        e2e_ms.append((time.perf_counter() - w0) * 1e3)
+    clocks = sampler.stop()
+    if world > 1:
+        import torch.distributed as dist
+        t = torch.tensor([total_ms, float(np.mean(e2e_ms))], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        total_ms, e2e_mean = t[0].item(), t[1].item()
+    else:
+        e2e_mean = float(np.mean(e2e_ms))
+    if rank != 0:
+        return
+    ms_per_step = total_ms / args.steps
+    toks = (PREFILL + DECODE) * world
+    roof = gemv_roofline(cfg, peaks)
+    wbytes = mf.decode_weight_bytes(cfg)
+    kv_bytes = 2 * cfg["layers"] * (PREFILL + DECODE / 2) * cfg["kv_heads"] * cfg["head_dim"] * 2
+    dec_ms = float(np.mean(td)) / DECODE
+    out = {
+        "metric": METRIC, "value": round(toks / ms_per_step * 1e3, 2), "unit": "tok/s", "n_gpus": world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": round(ms_per_step, 3), "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "int8 block dot (Q4_0 x Q8_0) + fp32 accumulate, fp16 KV", "data": "synthetic",
+        "config": {"workload": "LLaMA-2-7B Q4_0 (BASELINE configs[1]): prefill 512 + greedy decode 256, batch 1, cache limit 1024, "
+                               "random-init .mllm loaded through ParamLoader; one replica per GPU",
+                   "l2": "weights 3.7 GB per step >> 126 MB L2 (inputs larger than L2)", "parallelism": f"dp{world} replicas, no collective"},
+        "prefill_tok_s": round(PREFILL / (float(np.mean(tp)) * 1e-3), 1), "decode_tok_s": round(1e3 / dec_ms, 1),
+        "decode_step": {"ms": round(dec_ms, 4), "algorithmic_GB": round((wbytes + kv_bytes) / 1e9, 4),
+                        "GBs": round((wbytes + kv_bytes) / (dec_ms * 1e-3) / 1e9, 1),
+                        "frac_of_hbm_peak": round((wbytes + kv_bytes) / (dec_ms * 1e-3) / 1e9 / peaks.get("hbm_gbs", 6650.0), 4)},
+        "prefill": {"ms": round(float(np.mean(tp)), 3), "int8_TOPs": round(2 * (wbytes / 0.5625) * PREFILL / (float(np.mean(tp)) * 1e-3) / 1e12, 1)},
+        "e2e": {"value": round(toks / e2e_mean * 1e3, 2), "unit": "tok/s", "h2d_bytes_per_step": (PREFILL + DECODE - 1) * 4,
+                "d2h_bytes_per_step": DECODE * cfg["vocab"] * 4, "ms_per_step": round(e2e_mean, 2)},
+        "gpu_launches": int(launches), "clocks": clocks, "roofline": roof,
+    }
+    if not args.no_cpu:
+        try:
+            out["cpu_baseline"] = cpu_arm(cfg, path, args.cpu_prefill, args.cpu_decode)
+        except Exception as e:  # the CPU arm is a reported baseline; never let it take the GPU line down
+            out["cpu_baseline"] = {"error": str(e)}
+    print(json.dumps(out), flush=True)
+
+
+def reference_arm(args, rank, world):
+    if rank != 0:
+        return
+    cfg = mf.config(MODEL, cache_limit=LIMIT)
+    path = os.environ.get("MLLM_BENCH_MODEL", f"/tmp/mllm_bench_{MODEL}_q4_0.mllm")
+    if not os.path.exists(path):
+        import torch
+        make_model_file(cfg, path, device="cuda" if torch.cuda.is_available() else "cpu")
+    for _ in range(min(args.warmup, 1)):
+        cpu_arm(cfg, path, 4, 1)
+    r = cpu_arm(cfg, path, args.cpu_prefill, args.cpu_decode, reps=args.steps)
+    ms = r["seconds"] * 1e3
+    out = {"impl": "reference", "metric": METRIC, "value": round(r["value"], 3), "unit": "tok/s", "n_gpus": world, "steps": args.steps,
+           "warmup": args.warmup, "ms_per_step": round(ms, 1), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+           "dtype": "int8 block dot (Q4_0 x Q8_0) + fp32 accumulate, fp16 KV", "data": "synthetic",
+           "config": {"workload": "LLaMA-2-7B Q4_0 (BASELINE configs[1]) on the host CPU: " + r["sample"]},
+           "cpu_baseline": {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")},
+           "prefill_tok_s": round(r["prefill_tok_s"], 3), "decode_tok_s": round(r["decode_tok_s"], 3) if r["decode_tok_s"] else None,
+           "e2e": {"value": round(r["value"], 3), "unit": "tok/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(out), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--cpu-prefill", type=int, default=32)
+    ap.add_argument("--cpu-decode", type=int, default=8)
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", 0))
+    world = int(os.environ.get("WORLD_SIZE", 1))
+    local_rank = int(os.environ.get("LOCAL_RANK", 0))
+    if args.impl == "reference":
+        return reference_arm(args, rank, world)
+    if world > 1:
+        import torch
+        import torch.distributed as dist
+        torch.cuda.set_device(local_rank)
+        dist.init_process_group("nccl")
+    gpu_arm(args, rank, world, local_rank)
+    if world > 1:
+        import torch.distributed as dist
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

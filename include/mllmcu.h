@@ -55,6 +55,13 @@ int mllmcu_host_free(void *hptr);
 int mllmcu_stream_create(void **stream);
 int mllmcu_stream_destroy(void *stream);
 int mllmcu_stream_sync(void *stream);
+/* CUDA events recorded on the caller's stream: device-side timing (what Module::profiling's wall
+ * clock, mllm/Module.cpp:25-61, becomes on an asynchronous backend) */
+int mllmcu_event_create(void **ev);
+int mllmcu_event_destroy(void *ev);
+int mllmcu_event_record(void *ev, void *stream);
+int mllmcu_event_sync(void *ev);
+int mllmcu_event_elapsed_ms(void *start, void *stop, float *ms);
 
 /* ---- quantize_row_q8_0 (ggml/QuantizeQ8.cpp:57-189, AVX2 body) for `rows`
  * fp32 rows of length k (row stride ldx floats) -> rows x k/32 native
@@ -128,6 +135,9 @@ int mllmcu_f32_to_f16_rows(const float *src, void *dst, int rows, int cols, long
 /* ---- greedy sampling: LlmTextGenerator argmax (Generate.cpp:46-53) on device;
  * first maximum wins, as std::max_element does. out: int32 per row. */
 int mllmcu_argmax(const float *logits, int rows, int n, int *out, void *stream);
+/* same, writing the winning index as an fp32 token id (mllm feeds token ids as fp32,
+ * tokenizers/Tokenizer.hpp:78-101) so the next step's input never leaves the device */
+int mllmcu_argmax_ids(const float *logits, int rows, int n, float *ids_out, void *stream);
 
 #ifdef __cplusplus
 }

@@ -32,6 +32,9 @@ def lib():
         L.mllm_cuda_llama_clear_kvcache.argtypes = [C.c_void_p]
         L.mllm_cuda_llama_forward.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
         L.mllm_cuda_llama_generate.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p]
+        L.mllm_cuda_stream.restype = C.c_void_p
+        L.mllm_cuda_llama_request_device.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_float),
+                                                     C.POINTER(C.c_float), C.c_void_p]
         L.mllm_cuda_run_op.argtypes = [C.POINTER(C.c_char_p), C.c_void_p, C.c_int, C.c_char_p, C.c_char_p, C.POINTER(C.c_void_p),
                                        C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
         _lib = L
@@ -91,6 +94,16 @@ class LlamaModel:
         out = np.empty((B, max_new), dtype=np.int32)
         _check(lib().mllm_cuda_llama_generate(self.h, _p(ids), B, S, max_new, _p(out)))
         return out
+
+    def request_device(self, ids, n_decode):
+        """Prefill + n_decode greedy steps with inputs resident in HBM; returns (ms_prefill, ms_decode, tokens[B,n_decode])
+        timed with CUDA events on the backend stream."""
+        ids = np.ascontiguousarray(ids, dtype=np.float32)
+        B, S = ids.shape
+        toks = np.zeros((B, max(n_decode, 1)), dtype=np.int32)
+        a, b = C.c_float(0), C.c_float(0)
+        _check(lib().mllm_cuda_llama_request_device(self.h, _p(ids), B, S, n_decode, C.byref(a), C.byref(b), _p(toks)))
+        return a.value, b.value, toks[:, :n_decode]
 
     def last_forward_ms(self):
         return float(lib().mllm_cuda_llama_last_forward_ms(self.h))

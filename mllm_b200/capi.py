@@ -32,6 +32,11 @@ SYMBOLS = {
     "mllmcu_stream_create": (_i, [C.POINTER(_vp)]),
     "mllmcu_stream_destroy": (_i, [_vp]),
     "mllmcu_stream_sync": (_i, [_vp]),
+    "mllmcu_event_create": (_i, [C.POINTER(_vp)]),
+    "mllmcu_event_destroy": (_i, [_vp]),
+    "mllmcu_event_record": (_i, [_vp, _vp]),
+    "mllmcu_event_sync": (_i, [_vp]),
+    "mllmcu_event_elapsed_ms": (_i, [_vp, _vp, C.POINTER(_f)]),
     "mllmcu_quantize_q8_0": (_i, [_vp, _vp, _i, _i, _i, _vp]),
     "mllmcu_block_isums_q4_0_q8_0": (_i, [_vp, _vp, _vp, _i, _i, _i, _vp]),
     "mllmcu_linear_workspace_bytes": (_sz, [_i, _i]),
@@ -48,6 +53,7 @@ SYMBOLS = {
     "mllmcu_flash_attn_f16kv": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _ll, _vp, _sz, _vp]),
     "mllmcu_f32_to_f16_rows": (_i, [_vp, _vp, _i, _i, _ll, _ll, _vp]),
     "mllmcu_argmax": (_i, [_vp, _i, _i, _vp, _vp]),
+    "mllmcu_argmax_ids": (_i, [_vp, _i, _i, _vp, _vp]),
 }
 
 _lib = None

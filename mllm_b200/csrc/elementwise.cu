@@ -253,7 +253,7 @@ MLLMCU_API int mllmcu_f32_to_f16_rows(const float *src, void *dst, int rows, int
 
 // ------------------------------------------------------------------- argmax
 // LlmTextGenerator greedy (Generate.cpp:46-53): first maximum wins.
-__global__ void __launch_bounds__(1024) k_argmax(const float *__restrict__ x, int n, int *__restrict__ out) {
+__global__ void __launch_bounds__(1024) k_argmax(const float *__restrict__ x, int n, int *__restrict__ out, float *__restrict__ out_f) {
     const float *xr = x + (size_t)blockIdx.x * n;
     float best = -INFINITY;
     int bi = 0x7fffffff;
@@ -281,12 +281,22 @@ __global__ void __launch_bounds__(1024) k_argmax(const float *__restrict__ x, in
             const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
             if (ov > best || (ov == best && oi < bi)) { best = ov; bi = oi; }
         }
-        if (threadIdx.x == 0) out[blockIdx.x] = (bi == 0x7fffffff) ? 0 : bi;
+        if (threadIdx.x == 0) {
+            const int r = (bi == 0x7fffffff) ? 0 : bi;
+            if (out) out[blockIdx.x] = r;
+            if (out_f) out_f[blockIdx.x] = (float)r;
+        }
     }
 }
 MLLMCU_API int mllmcu_argmax(const float *logits, int rows, int n, int *out, void *stream) {
     if (rows <= 0 || n <= 0) return -1;
-    k_argmax<<<rows, 1024, 0, (cudaStream_t)stream>>>(logits, n, out);
+    k_argmax<<<rows, 1024, 0, (cudaStream_t)stream>>>(logits, n, out, nullptr);
+    CU_LAUNCH_CHECK();
+    return 0;
+}
+MLLMCU_API int mllmcu_argmax_ids(const float *logits, int rows, int n, float *ids_out, void *stream) {
+    if (rows <= 0 || n <= 0) return -1;
+    k_argmax<<<rows, 1024, 0, (cudaStream_t)stream>>>(logits, n, nullptr, ids_out);
     CU_LAUNCH_CHECK();
     return 0;
 }

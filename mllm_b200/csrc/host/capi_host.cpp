@@ -149,3 +149,54 @@ HAPI int mllm_cuda_run_op(const char **keys, const float *vals, int n_params, co
         o.copyToHost(out_host);
     })
 }
+
+HAPI void *mllm_cuda_stream() {
+    try { return backend()->stream(); } catch (...) { return nullptr; }
+}
+
+// One request with inputs already resident in HBM (what bench.py's `value` times): ids are uploaded
+// BEFORE the timed region; prefill of S tokens, then n_decode single-token steps whose input is the
+// previous step's on-device argmax (mllmcu_argmax_ids) -- no host<->device traffic inside the region.
+// Device time (CUDA events on the backend stream) of the two phases is returned in ms.
+// tokens_out (host, optional): the B*n_decode greedy tokens, copied back after the timed region.
+HAPI int mllm_cuda_llama_request_device(void *hv, const float *ids_host, int B, int S, int n_decode, float *ms_prefill,
+                                        float *ms_decode, int *tokens_out) {
+    GUARD({
+        auto *h = (HostModel *)hv;
+        CUDABackend *bn = h->model->backend();
+        const int V = h->model->config().vocab;
+        Tensor ids(B, 1, S, 1, bn);
+        ids.setName("input_ids");
+        ids.copyFromHost(ids_host);
+        Tensor toks(1, 1, n_decode > 0 ? n_decode : 1, B, bn); // fp32 ids, row per step
+        void *e0, *e1, *e2;
+        MLLMCU_CHECK(mllmcu_event_create(&e0));
+        MLLMCU_CHECK(mllmcu_event_create(&e1));
+        MLLMCU_CHECK(mllmcu_event_create(&e2));
+        bn->sync();
+        MLLMCU_CHECK(mllmcu_event_record(e0, bn->stream()));
+        Tensor lg = h->model->forward(ids);
+        if (n_decode > 0) MLLMCU_CHECK(mllmcu_argmax_ids(lg.devPtr<float>(), B, V, toks.devPtr<float>(), bn->stream()));
+        MLLMCU_CHECK(mllmcu_event_record(e1, bn->stream()));
+        for (int step = 1; step < n_decode; step++) {
+            Tensor cur(bn);
+            cur.setName("input_ids");
+            cur.shallowCopyFrom(toks, step - 1, 1); // [1,1,1,B] row = B token ids
+            cur.reshapeKeepStrides(B, 1, 1, 1);
+            cur.reshape(B, 1, 1, 1);
+            Tensor l2 = h->model->forward(cur);
+            MLLMCU_CHECK(mllmcu_argmax_ids(l2.devPtr<float>(), B, V, toks.devPtr<float>() + (size_t)step * B, bn->stream()));
+        }
+        MLLMCU_CHECK(mllmcu_event_record(e2, bn->stream()));
+        MLLMCU_CHECK(mllmcu_event_sync(e2));
+        MLLMCU_CHECK(mllmcu_event_elapsed_ms(e0, e1, ms_prefill));
+        MLLMCU_CHECK(mllmcu_event_elapsed_ms(e1, e2, ms_decode));
+        mllmcu_event_destroy(e0); mllmcu_event_destroy(e1); mllmcu_event_destroy(e2);
+        if (tokens_out && n_decode > 0) {
+            std::vector<float> t((size_t)n_decode * B);
+            toks.copyToHost(t.data());
+            for (int s = 0; s < n_decode; s++)
+                for (int b = 0; b < B; b++) tokens_out[(size_t)b * n_decode + s] = (int)t[(size_t)s * B + b];
+        }
+    })
+}

@@ -45,3 +45,18 @@ MLLMCU_API int mllmcu_stream_create(void **stream) {
 }
 MLLMCU_API int mllmcu_stream_destroy(void *stream) { CU_TRY(cudaStreamDestroy((cudaStream_t)stream)); return 0; }
 MLLMCU_API int mllmcu_stream_sync(void *stream) { CU_TRY(cudaStreamSynchronize((cudaStream_t)stream)); return 0; }
+
+// ---- CUDA events on the caller's stream (device-side timing for Module::profiling-style numbers)
+MLLMCU_API int mllmcu_event_create(void **ev) {
+    cudaEvent_t e;
+    CU_TRY(cudaEventCreate(&e));
+    *ev = (void *)e;
+    return 0;
+}
+MLLMCU_API int mllmcu_event_destroy(void *ev) { CU_TRY(cudaEventDestroy((cudaEvent_t)ev)); return 0; }
+MLLMCU_API int mllmcu_event_record(void *ev, void *stream) { CU_TRY(cudaEventRecord((cudaEvent_t)ev, (cudaStream_t)stream)); return 0; }
+MLLMCU_API int mllmcu_event_sync(void *ev) { CU_TRY(cudaEventSynchronize((cudaEvent_t)ev)); return 0; }
+MLLMCU_API int mllmcu_event_elapsed_ms(void *start, void *stop, float *ms) {
+    CU_TRY(cudaEventElapsedTime(ms, (cudaEvent_t)start, (cudaEvent_t)stop));
+    return 0;
+}
