@@ -87,6 +87,30 @@ size_t mllmcu_linear_workspace_bytes(int M, int K);
 int mllmcu_linear(int wtype, const void *W, const float *x, const float *bias, void *y, int M, int N, int K, int ldx,
                   int ldy, int out_f16, void *ws, size_t ws_bytes, void *stream);
 
+/* ---- Fused decode Linear (M <= 8 rows): one launch = [RMSNorm ->] Q8_0 quantise -> nW (<=3) block-quantised
+ * Linears sharing the input -> epilogue.  It is the same arithmetic, in the same order, as the separate
+ * calls mllmcu_rmsnorm -> mllmcu_linear (-> mllmcu_add | mllmcu_silu + mllmcu_mul), so results are
+ * bit-identical to that sequence; the fusion only removes launches and HBM round trips of the graph
+ * RMSNorm -> {q,k,v}_proj / {gate,up}_proj -> SiLU*mul, o_proj / down_proj -> +residual
+ * (models/llama/modeling_llama.hpp:29-68, models/transformer/modeling_transformer.hpp:132-212).
+ *   W[i]: [Ns[i]][K/32] block_q4_0 (host array of nW device pointers); bias: host array of nW device
+ *   pointers (entries or the array itself may be NULL); x: [M][K] fp32, row stride ldx;
+ *   norm_w: RMSNorm weight [K] or NULL (no norm); eps: RMSNorm epsilon;
+ *   epilogue 0: y[m][n] = W.x (+bias), outputs of the nW matrices concatenated along n;
+ *            1: same + residual[m][n] (row stride ldr);
+ *            2: nW == 2, y[m][n] = silu(W0.x)[n] * (W1.x)[n];
+ *   y row stride ldy, fp32 or (out_f16) fp16; pdl != 0 launches with programmatic dependent launch so the
+ *   weight prefetch of this kernel overlaps the tail of the previous kernel on the stream.
+ * Returns MLLMCU_ENOSUP when the shape is outside this path (caller then uses mllmcu_linear). */
+int mllmcu_gemv_fused(int wtype, const void *const *W, const int *Ns, const float *const *bias, int nW, const float *x,
+                      int ldx, int M, int K, const float *norm_w, float eps, int epilogue, const float *residual, int ldr,
+                      void *y, int ldy, int out_f16, int pdl, void *stream);
+
+/* Self-test of the branch-free IEEE division used for Q8_0 scales inside the fused kernels: counts fp32 bit
+ * patterns amax in [lo, hi] for which (127/amax, amax/127) differ from IEEE division.  *mismatch_dev (device,
+ * zero-initialised by the caller) receives the count; 0 is the only acceptable answer. */
+int mllmcu_selftest_div(uint32_t lo, uint32_t hi, unsigned long long *mismatch_dev, void *stream);
+
 /* ---- RMSNorm: CPURMSNorm::execute (op/CPURMSNorm.cpp:31-95): double sum of
  * squares, y = (x * rsqrt) * w  (or * (1+w) when add_unit_offset). */
 int mllmcu_rmsnorm(const float *x, const float *w, float *y, int rows, int dim, float eps, int add_unit_offset, void *stream);

@@ -41,6 +41,8 @@ SYMBOLS = {
     "mllmcu_block_isums_q4_0_q8_0": (_i, [_vp, _vp, _vp, _i, _i, _i, _vp]),
     "mllmcu_linear_workspace_bytes": (_sz, [_i, _i]),
     "mllmcu_linear": (_i, [_i, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _vp, _sz, _vp]),
+    "mllmcu_gemv_fused": (_i, [_i, _vp, _vp, _vp, _i, _vp, _i, _i, _i, _vp, _f, _i, _vp, _i, _vp, _i, _i, _i, _vp]),
+    "mllmcu_selftest_div": (_i, [C.c_uint32, C.c_uint32, _vp, _vp]),
     "mllmcu_rmsnorm": (_i, [_vp, _vp, _vp, _i, _i, _f, _i, _vp]),
     "mllmcu_layernorm": (_i, [_vp, _vp, _vp, _vp, _i, _i, _f, _vp]),
     "mllmcu_rope": (_i, [_i, _vp, _vp, _i, _i, _i, _i, _i, _i, _vp, _vp, _i, _i, _ll, _ll, _vp]),
@@ -221,3 +223,21 @@ def argmax(logits):
     out = torch.empty((rows,), dtype=torch.int32, device=logits.device)
     check(lib().mllmcu_argmax(_ptr(logits), rows, n, _ptr(out), _stream()), "argmax")
     return out
+
+
+def gemv_fused(Ws, x, norm_w=None, eps=1e-6, biases=None, epilogue=0, residual=None, out_f16=False, pdl=False):
+    """Fused decode Linear; Ws: list of cuda uint8 [N_i, K/32*18]; x cuda fp32 [M,K]. Returns y [M, sum N] (or [M, N0] for epilogue 2)."""
+    import torch
+    M, K = x.shape
+    nW = len(Ws)
+    Wp = (C.c_void_p * nW)(*[w.data_ptr() for w in Ws])
+    Ns = (C.c_int * nW)(*[w.shape[0] for w in Ws])
+    bp = None
+    if biases is not None:
+        bp = (C.c_void_p * nW)(*[(b.data_ptr() if b is not None else None) for b in biases])
+    NT = Ws[0].shape[0] if epilogue == 2 else sum(w.shape[0] for w in Ws)
+    y = torch.empty((M, NT), dtype=torch.float16 if out_f16 else torch.float32, device=x.device)
+    rc = lib().mllmcu_gemv_fused(TYPE_Q4_0, Wp, Ns, bp, nW, _ptr(x), x.stride(0), M, K, _ptr(norm_w), eps, epilogue,
+                                 _ptr(residual), residual.stride(0) if residual is not None else 0, _ptr(y), NT, int(out_f16), int(pdl), _stream())
+    check(rc, "gemv_fused")
+    return y

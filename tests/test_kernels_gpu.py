@@ -251,3 +251,74 @@ def test_argmax_first_max_wins(cu):
     x[1, 0] = 50.0
     x[2, 31999] = 60.0
     assert cu.argmax(x).cpu().tolist() == [777, 0, 31999]
+
+
+# ---------------------------------------------------------------- fused decode Linear (TMA-staged GEMV)
+def _q4(oracle, rng, n, k, scale=0.02):
+    return oracle.quantize_q4_0((rng.standard_normal((n, k)) * scale).astype(np.float32))
+
+
+@pytest.mark.parametrize("M,N,K", [(1, 4096, 4096), (1, 64, 256), (2, 1000, 2048), (8, 72, 1024), (3, 4096, 11008), (1, 136, 5504)])
+def test_gemv_fused_plain_bit_equal_to_linear(cu, oracle, M, N, K):
+    """Same arithmetic, same order as mllmcu_linear's GEMV: bit-identical; and within tolerance of the oracle."""
+    rng = np.random.default_rng(N + K + M)
+    W = _q4(oracle, rng, N, K)
+    x = act_rows(rng, M, K)
+    b = (rng.standard_normal(N) * 0.02).astype(np.float32)
+    y = cu.gemv_fused([dev(W)], dev(x), biases=[dev(b)]).cpu().numpy()
+    y_lin = cu.linear(dev(W), dev(x), dev(b)).cpu().numpy()
+    assert np.array_equal(bits(y), bits(y_lin))
+    lin_check(y, oracle.linear(W, x, b))
+
+
+@pytest.mark.parametrize("M", [1, 4])
+def test_gemv_fused_rmsnorm_qkv(cu, oracle, M):
+    """RMSNorm -> q/k/v projections in one launch == rmsnorm kernel then three Linears."""
+    rng = np.random.default_rng(M)
+    K, Nq, Nkv = 2048, 2048, 256
+    Ws = [_q4(oracle, rng, n, K) for n in (Nq, Nkv, Nkv)]
+    bs = [(rng.standard_normal(n) * 0.02).astype(np.float32) for n in (Nq, Nkv, Nkv)]
+    x = (rng.standard_normal((M, K)) * 2).astype(np.float32)
+    w = (1 + 0.02 * rng.standard_normal(K)).astype(np.float32)
+    y = cu.gemv_fused([dev(v) for v in Ws], dev(x), norm_w=dev(w), eps=1e-5, biases=[dev(v) for v in bs]).cpu().numpy()
+    xn = cu.rmsnorm(dev(x), dev(w), 1e-5)
+    want = np.concatenate([cu.linear(dev(Wi), xn, dev(bi)).cpu().numpy() for Wi, bi in zip(Ws, bs)], axis=1)
+    # the fused prologue sums squares in compensated fp32, the stand-alone kernel in double: same float mean
+    assert np.array_equal(bits(y), bits(want))
+    xo = oracle.only.rmsnorm(x, w, 1e-5)
+    lin_check(y, np.concatenate([oracle.linear(Wi, xo, bi) for Wi, bi in zip(Ws, bs)], axis=1))
+
+
+def test_gemv_fused_residual_and_silu_mul(cu, oracle):
+    rng = np.random.default_rng(12)
+    M, K, F = 2, 1024, 2816
+    x = (rng.standard_normal((M, K))).astype(np.float32)
+    w = (1 + 0.02 * rng.standard_normal(K)).astype(np.float32)
+    Wg, Wu, Wd = _q4(oracle, rng, F, K), _q4(oracle, rng, F, K), _q4(oracle, rng, K, F)
+    act = cu.gemv_fused([dev(Wg), dev(Wu)], dev(x), norm_w=dev(w), eps=1e-6, epilogue=2)
+    xn = cu.rmsnorm(dev(x), dev(w), 1e-6)
+    want_act = cu.silu_mul(cu.linear(dev(Wg), xn), cu.linear(dev(Wu), xn))
+    assert np.array_equal(bits(act.cpu().numpy()), bits(want_act.cpu().numpy()))
+    out = cu.gemv_fused([dev(Wd)], act, epilogue=1, residual=dev(x)).cpu().numpy()
+    want = cu.add(cu.linear(dev(Wd), want_act), dev(x)).cpu().numpy()
+    assert np.array_equal(bits(out), bits(want))
+    xo = oracle.only.rmsnorm(x, w, 1e-6)
+    a_o = oracle.silu(oracle.linear(Wg, xo)) * oracle.linear(Wu, xo)
+    lin_check(out, oracle.linear(Wd, a_o) + x)
+
+
+def test_gemv_fused_rejects_unsupported(cu, oracle):
+    import torch
+    rng = np.random.default_rng(1)
+    W = dev(_q4(oracle, rng, 32, 96))
+    with pytest.raises(cu.MllmcuError):
+        cu.gemv_fused([W], torch.zeros((1, 96), device="cuda"))  # K % 128 != 0 -> MLLMCU_ENOSUP
+
+
+def test_fast_division_is_ieee_exhaustive(cu):
+    """Every non-negative fp32 bit pattern (0 .. +inf): the fused kernels' Q8_0 scale arithmetic == IEEE division."""
+    import torch
+    bad = torch.zeros(1, dtype=torch.int64, device="cuda")
+    cu.check(cu.lib().mllmcu_selftest_div(0, 0x7F800000, bad.data_ptr(), cu._stream()))
+    torch.cuda.synchronize()
+    assert int(bad.item()) == 0
