@@ -63,6 +63,15 @@ int mllmcu_event_record(void *ev, void *stream);
 int mllmcu_event_sync(void *ev);
 int mllmcu_event_elapsed_ms(void *start, void *stop, float *ms);
 
+/* ---- CUDA graphs.  A decode step is ~200 small launches; the backend captures the step once
+ * (begin_capture .. end_capture on its stream, thread-local mode) and replays it per token.  The
+ * reference has no counterpart: its CPU ops are called directly (CPUBackend::runOp, CPUBackend.cpp:314-405). */
+int mllmcu_graph_begin_capture(void *stream);
+int mllmcu_graph_end_capture(void *stream, void **graph_exec);
+int mllmcu_graph_abort_capture(void *stream);
+int mllmcu_graph_launch(void *graph_exec, void *stream);
+int mllmcu_graph_destroy(void *graph_exec);
+
 /* ---- quantize_row_q8_0 (ggml/QuantizeQ8.cpp:57-189, AVX2 body) for `rows`
  * fp32 rows of length k (row stride ldx floats) -> rows x k/32 native
  * block_q8_0 (34 B each).  Bytes are identical to the reference's. */
@@ -162,6 +171,25 @@ int mllmcu_argmax(const float *logits, int rows, int n, int *out, void *stream);
 /* same, writing the winning index as an fp32 token id (mllm feeds token ids as fp32,
  * tokenizers/Tokenizer.hpp:78-101) so the next step's input never leaves the device */
 int mllmcu_argmax_ids(const float *logits, int rows, int n, float *ids_out, void *stream);
+
+/* ---- single-token decode step, graph-replayable: per-step scalars live in device memory.
+ * ctl[0] = position of the token being consumed (== KV length before its append).
+ * mllmcu_decode_embed: CPUEmbedding Q4_0 gather (op/CPUEmbedding.cpp:66-81) and ctl[0] += 1 (ctl may be NULL). */
+int mllmcu_decode_embed(const void *table, const float *ids, float *out, int n_ids, int hidden, int *ctl, void *stream);
+/* q_rope + k_rope (op/CPURoPE.cpp:200-372) on the fused q|k|v projection rows qkv[B][ld] (q rotated in place)
+ * and k_cache / v_cache append in fp16 at cache row ctl[0] (op/CPUKVCache.cpp:137-247). */
+int mllmcu_decode_rope_kv(int rope_type, float *qkv, int ld, int B, int Hq, int Hkv, int D, int rot_dim, const float *sin_t,
+                          const float *cos_t, int tdim, const int *ctl, void *kcache, void *vcache, long long kv_bstride,
+                          int cache_limit, int pdl, void *stream);
+/* flash_attention_2_forward, decode (Sq == 1) over ctl[0]+1 cached keys (compute/FlashAttention2.hpp:1212-2284),
+ * split over keys with the merge done by the last CTA to finish.  D in {32, 64, 128}.  ws must be zeroed once. */
+int mllmcu_decode_attn_nsplit(int B, int Hq);
+size_t mllmcu_decode_attn_workspace_bytes(int B, int Hq, int D);
+int mllmcu_decode_attn(const float *q, int ldq, const void *k, const void *v, float *o, int ldo, const int *ctl, int B, int Hq,
+                       int Hkv, int D, long long kv_bstride, void *ws, size_t ws_bytes, int pdl, void *stream);
+/* greedy pick (Generate.cpp:46-53): ids_out[b] fp32 and, when tok_log != NULL, tok_log[ctl[0]*rows + b] (ctl[0] < log_rows) */
+int mllmcu_decode_argmax(const float *logits, int rows, int n, float *ids_out, int *tok_log, const int *ctl, int log_rows,
+                         void *stream);
 
 #ifdef __cplusplus
 }

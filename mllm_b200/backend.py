@@ -33,6 +33,8 @@ def lib():
         L.mllm_cuda_llama_forward.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
         L.mllm_cuda_llama_generate.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p]
         L.mllm_cuda_stream.restype = C.c_void_p
+        L.mllm_cuda_llama_last_step_fused.argtypes = [C.c_void_p]
+        L.mllm_cuda_llama_set_eager_decode.argtypes = [C.c_void_p, C.c_int]
         L.mllm_cuda_llama_request_device.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_float),
                                                      C.POINTER(C.c_float), C.c_void_p]
         L.mllm_cuda_run_op.argtypes = [C.POINTER(C.c_char_p), C.c_void_p, C.c_int, C.c_char_p, C.c_char_p, C.POINTER(C.c_void_p),
@@ -104,6 +106,14 @@ class LlamaModel:
         a, b = C.c_float(0), C.c_float(0)
         _check(lib().mllm_cuda_llama_request_device(self.h, _p(ids), B, S, n_decode, C.byref(a), C.byref(b), _p(toks)))
         return a.value, b.value, toks[:, :n_decode]
+
+    def last_step_fused(self):
+        """True when the last forward ran as the fused, graph-replayed decode step."""
+        return bool(lib().mllm_cuda_llama_last_step_fused(self.h))
+
+    def set_eager_decode(self, on):
+        """Force the op-by-op path for S == 1 (parity tests compare it with the fused step)."""
+        _check(lib().mllm_cuda_llama_set_eager_decode(self.h, int(bool(on))))
 
     def last_forward_ms(self):
         return float(lib().mllm_cuda_llama_last_forward_ms(self.h))

@@ -25,17 +25,28 @@ def _newer(target, sources):
 
 
 def build_kernels(force=False, verbose=False):
-    os.makedirs(LIB, exist_ok=True)
+    """One object per .cu (compiled in parallel, rebuilt only when it or a shared header changed), then one link."""
+    from concurrent.futures import ThreadPoolExecutor
+    os.makedirs(os.path.join(LIB, "obj"), exist_ok=True)
     srcs = sorted(glob.glob(os.path.join(HERE, "csrc", "*.cu")))
-    deps = srcs + glob.glob(os.path.join(HERE, "csrc", "*.cuh")) + [os.path.join(ROOT, "include", "mllmcu.h")]
+    hdrs = glob.glob(os.path.join(HERE, "csrc", "*.cuh")) + [os.path.join(ROOT, "include", "mllmcu.h")]
     out = os.path.join(LIB, "libmllmcu.so")
-    if not force and not _newer(out, deps):
-        return out
-    cmd = [NVCC, "-O3", "-std=c++17", *ARCH, "-lineinfo", "-Xcompiler", "-fPIC,-fvisibility=hidden", "-shared",
-           "-I", os.path.join(ROOT, "include"), "-o", out, *srcs, "-lcuda"]
+    base = [NVCC, "-O3", "-std=c++17", *ARCH, "-lineinfo", "-Xcompiler", "-fPIC,-fvisibility=hidden", "-I", os.path.join(ROOT, "include")]
     if verbose:
-        cmd.insert(1, "-Xptxas=-v")
-    subprocess.run(cmd, check=True)
+        base.insert(1, "-Xptxas=-v")
+
+    def one(src):
+        obj = os.path.join(LIB, "obj", os.path.basename(src)[:-3] + ".o")
+        if force or _newer(obj, [src] + hdrs):
+            subprocess.run(base + ["-c", src, "-o", obj], check=True)
+            return obj, True
+        return obj, False
+
+    with ThreadPoolExecutor(max_workers=min(8, len(srcs))) as ex:
+        res = list(ex.map(one, srcs))
+    objs = [o for o, _ in res]
+    if force or any(c for _, c in res) or _newer(out, objs):
+        subprocess.run([NVCC, *ARCH, "-shared", "-o", out, *objs, "-lcuda"], check=True)
     return out
 
 

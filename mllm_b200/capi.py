@@ -37,6 +37,11 @@ SYMBOLS = {
     "mllmcu_event_record": (_i, [_vp, _vp]),
     "mllmcu_event_sync": (_i, [_vp]),
     "mllmcu_event_elapsed_ms": (_i, [_vp, _vp, C.POINTER(_f)]),
+    "mllmcu_graph_begin_capture": (_i, [_vp]),
+    "mllmcu_graph_end_capture": (_i, [_vp, C.POINTER(_vp)]),
+    "mllmcu_graph_abort_capture": (_i, [_vp]),
+    "mllmcu_graph_launch": (_i, [_vp, _vp]),
+    "mllmcu_graph_destroy": (_i, [_vp]),
     "mllmcu_quantize_q8_0": (_i, [_vp, _vp, _i, _i, _i, _vp]),
     "mllmcu_block_isums_q4_0_q8_0": (_i, [_vp, _vp, _vp, _i, _i, _i, _vp]),
     "mllmcu_linear_workspace_bytes": (_sz, [_i, _i]),
@@ -56,6 +61,12 @@ SYMBOLS = {
     "mllmcu_f32_to_f16_rows": (_i, [_vp, _vp, _i, _i, _ll, _ll, _vp]),
     "mllmcu_argmax": (_i, [_vp, _i, _i, _vp, _vp]),
     "mllmcu_argmax_ids": (_i, [_vp, _i, _i, _vp, _vp]),
+    "mllmcu_decode_embed": (_i, [_vp, _vp, _vp, _i, _i, _vp, _vp]),
+    "mllmcu_decode_rope_kv": (_i, [_i, _vp, _i, _i, _i, _i, _i, _i, _vp, _vp, _i, _vp, _vp, _vp, C.c_longlong, _i, _i, _vp]),
+    "mllmcu_decode_attn_nsplit": (_i, [_i, _i]),
+    "mllmcu_decode_attn_workspace_bytes": (_sz, [_i, _i, _i]),
+    "mllmcu_decode_attn": (_i, [_vp, _i, _vp, _vp, _vp, _i, _vp, _i, _i, _i, _i, C.c_longlong, _vp, _sz, _i, _vp]),
+    "mllmcu_decode_argmax": (_i, [_vp, _i, _i, _vp, _vp, _vp, _i, _vp]),
 }
 
 _lib = None
@@ -241,3 +252,48 @@ def gemv_fused(Ws, x, norm_w=None, eps=1e-6, biases=None, epilogue=0, residual=N
                                  _ptr(residual), residual.stride(0) if residual is not None else 0, _ptr(y), NT, int(out_f16), int(pdl), _stream())
     check(rc, "gemv_fused")
     return y
+
+
+# ---------------------------------------------------------------- decode-step kernels (graph-replayable)
+def decode_embed(table, ids, hidden, ctl=None):
+    import torch
+    n = ids.numel()
+    out = torch.empty((n, hidden), dtype=torch.float32, device=table.device)
+    check(lib().mllmcu_decode_embed(_ptr(table), _ptr(ids), _ptr(out), n, hidden, _ptr(ctl), _stream()), "decode_embed")
+    return out
+
+
+def decode_rope_kv(rope_type, qkv, Hq, Hkv, D, sin_t, cos_t, ctl, kcache, vcache, rot=None, pdl=False):
+    """qkv cuda fp32 [B, (Hq+2Hkv)*D] (q rotated in place); caches cuda fp16 [B, limit, Hkv, D]; ctl cuda int32 [>=1]."""
+    B = qkv.shape[0]
+    rot = D if rot is None else rot
+    check(lib().mllmcu_decode_rope_kv(rope_type, _ptr(qkv), qkv.stride(0), B, Hq, Hkv, D, rot, _ptr(sin_t), _ptr(cos_t), sin_t.shape[1],
+                                      _ptr(ctl), _ptr(kcache), _ptr(vcache), kcache.stride(0), kcache.shape[1], int(pdl), _stream()), "decode_rope_kv")
+
+
+_attn_ws = {}
+
+
+def decode_attn(q, ldq, kcache, vcache, ctl, Hq, D, pdl=False):
+    """q cuda fp32 rows (head h at column h*D, row stride ldq); caches fp16 [B, limit, Hkv, D]; KV length = ctl[0]+1. Returns [B, Hq*D]."""
+    import torch
+    B, Hkv = kcache.shape[0], kcache.shape[2]
+    need = lib().mllmcu_decode_attn_workspace_bytes(B, Hq, D)
+    key = (q.device.index, B, Hq, D)
+    ws = _attn_ws.get(key)
+    if ws is None:
+        ws = torch.zeros(need, dtype=torch.uint8, device=q.device)
+        _attn_ws[key] = ws
+    o = torch.empty((B, Hq * D), dtype=torch.float32, device=q.device)
+    check(lib().mllmcu_decode_attn(_ptr(q), ldq, _ptr(kcache), _ptr(vcache), _ptr(o), Hq * D, _ptr(ctl), B, Hq, Hkv, D, kcache.stride(0),
+                                   _ptr(ws), ws.numel(), int(pdl), _stream()), "decode_attn")
+    return o
+
+
+def decode_argmax(logits, ctl=None, tok_log=None):
+    import torch
+    rows, n = logits.shape
+    ids = torch.empty((rows,), dtype=torch.float32, device=logits.device)
+    check(lib().mllmcu_decode_argmax(_ptr(logits), rows, n, _ptr(ids), _ptr(tok_log), _ptr(ctl), tok_log.shape[0] if tok_log is not None else 0,
+                                     _stream()), "decode_argmax")
+    return ids

@@ -81,6 +81,12 @@ public:
         return MLLM_NO_ERROR;
     }
     ErrorCode free(vector<shared_ptr<Tensor>>, vector<shared_ptr<Tensor>>) override { weight_.free(); biasT_.free(); return MLLM_NO_ERROR; }
+    bool fuseInfo(FuseInfo &f) override {
+        if (!weight_.allocated()) return false;
+        f.weight = weight_.rawDevPtr(); f.wtype = (int)weight_.dtype(); f.in = in_; f.out = out_;
+        f.bias = bias_ ? biasT_.devPtr<float>() : nullptr;
+        return true;
+    }
 
 private:
     int in_, out_;
@@ -114,6 +120,12 @@ public:
         MLLMCU_CHECK(mllmcu_rmsnorm(in[0]->devPtr<float>(), weight_.devPtr<float>(), out[0]->devPtr<float>(), rows, in[0]->dimension(), eps_, unit_, b->stream()));
         b->kernel_launches++;
         return MLLM_NO_ERROR;
+    }
+
+    bool fuseInfo(FuseInfo &f) override {
+        if (!weight_.allocated()) return false;
+        f.norm_w = weight_.devPtr<float>(); f.eps = eps_; f.unit_offset = unit_; f.in = n_;
+        return true;
     }
 
 private:
@@ -204,6 +216,13 @@ public:
         return MLLM_NO_ERROR;
     }
     void clearCache() override { h_cnt_ = 0; }
+    bool fuseInfo(FuseInfo &f) override {
+        if (!tab_) return false;
+        f.sin_t = tab_->sin_t.devPtr<float>(); f.cos_t = tab_->cos_t.devPtr<float>();
+        f.rope_type = pose_type_; f.rot_dim = ishape_; f.pos = h_cnt_; f.pos_max = pos_max_;
+        return true;
+    }
+    void advance(int tokens) override { h_cnt_ += tokens; }
 
 private:
     void build(RopeTables &t) {
@@ -285,6 +304,13 @@ public:
     }
     int getCacheSeqLen() override { return seq_; }
     void clearCache() override { seq_ = 0; }
+    bool fuseInfo(FuseInfo &f) override {
+        if (!cache_.allocated()) return false;
+        f.cache = cache_.rawDevPtr(); f.cache_bstride = cache_.batchStride(); f.cache_limit = limit_; f.cache_len = seq_;
+        f.cache_batch = cache_.batch(); f.cache_heads = H_ * n_rep_; f.cache_dim = D_;
+        return true;
+    }
+    void advance(int tokens) override { seq_ += tokens; }
 
 private:
     typedef char *__fp16_ptr;
@@ -331,6 +357,12 @@ public:
         MLLMCU_CHECK(mllmcu_embedding_q4_0(weight_.rawDevPtr(), in[0]->devPtr<float>(), out[0]->devPtr<float>(), n, hidden_, b->stream()));
         b->kernel_launches++;
         return MLLM_NO_ERROR;
+    }
+
+    bool fuseInfo(FuseInfo &f) override {
+        if (!weight_.allocated()) return false;
+        f.weight = weight_.rawDevPtr(); f.wtype = (int)weight_.dtype(); f.in = vocab_; f.out = hidden_;
+        return true;
     }
 
 private:

@@ -2,6 +2,8 @@
 // models/llama/modeling_llama.hpp:29-115 and models/transformer/modeling_transformer.hpp:132-212
 // issue through Layer::run / Tensor::runFunc.
 #include "Module.hpp"
+#include <cstdlib>
+#include <iostream>
 
 namespace mllm {
 
@@ -23,6 +25,8 @@ static OpParam P(std::initializer_list<std::pair<const string, float>> l) { retu
 
 LlamaModel::LlamaModel(CUDABackend *bn, const LlamaConfig &cfg) : cfg_(cfg), fn_(&st_) {
     st_.backend = bn;
+    static int instances = 0;
+    if (instances++ > 0) st_.tag = "@" + std::to_string(instances);
     const LlamaNames nm = LlamaNames::make(cfg.rope_type);
     const int H = cfg.hidden, D = cfg.head_dim();
     embedding_ = Layer(&st_, EMBEDDING, nm.embd, P({{"hidden_size", (float)H}, {"vocab_size", (float)cfg.vocab}}));
@@ -89,6 +93,9 @@ Tensor LlamaModel::block_forward(Block &b, int idx, Tensor in) {
 
 Tensor LlamaModel::forward(Tensor ids, float *dump) {
     CUDABackend *bn = st_.backend;
+    last_fused_ = false;
+    if (!bn->doTrace && !dump && ids.sequence() == 1 && ids.contiguous() && decode_plan_usable(ids.batch()))
+        return decode_step(ids.devPtr<float>(), ids.batch(), false);
     Tensor x = embedding_(ids);
     const size_t hs = x.cntSize();
     if (dump && !bn->doTrace) MLLMCU_CHECK(mllmcu_memcpy_d2d(dump, x.rawDevPtr(), hs, bn->stream()));
@@ -118,6 +125,183 @@ void LlamaModel::clear_kvcache() { // LLaMAModel::clear_kvcache (modeling_llama.
         for (Layer *l : {&b.k_cache, &b.v_cache, &b.q_rope, &b.k_rope})
             if (l->op()) l->op()->clearCache();
     }
+}
+
+// ===================================================================== decode plan
+struct LlamaModel::DecodePlan {
+    struct L {
+        FuseInfo n1, n2, q, k, v, o, gate, up, down, rope, kc, vc;
+        Op *advance[4]; // q_rope, k_rope, k_cache, v_cache
+    };
+    int B = 0;
+    vector<L> layers;
+    FuseInfo embd, norm, head;
+    Tensor x, x2, qkv, ao, g, logits, ids, ctl, tok_log, attn_ws;
+    size_t attn_ws_bytes = 0;
+    int dev_pos = -2;          // value ctl[0] holds in stream order (-2: unknown)
+    int ctl_host = 0;          // staging for the H2D of ctl[0]
+    bool warmed[2] = {false, false};
+    void *graph[2] = {nullptr, nullptr};
+    bool unsupported = false, use_graph = true, use_pdl = true;
+    int launches = 0;
+    ~DecodePlan() {
+        for (void *g : graph) if (g) mllmcu_graph_destroy(g);
+    }
+};
+
+LlamaModel::~LlamaModel() = default;
+
+static bool env_on(const char *k) {
+    const char *e = getenv(k);
+    return e && e[0] && e[0] != '0';
+}
+
+bool LlamaModel::decode_plan_usable(int B) {
+    static const bool eager = env_on("MLLM_CUDA_EAGER_DECODE");
+    if (eager || force_eager_ || B < 1 || B > 8) return false;
+    if (plan_ && plan_->unsupported) return false;
+    const int H = cfg_.hidden, D = cfg_.head_dim();
+    if (H % 128 || cfg_.ffn % 128 || (D != 32 && D != 64 && D != 128)) return false;
+    if (!(plan_ && plan_->B == B)) {
+        // (re)build: collect the device state of every op on the path
+        auto p = std::make_unique<DecodePlan>();
+        p->B = B;
+        p->layers.resize(cfg_.layers);
+        auto get = [](Layer &l, FuseInfo &f) { return l.op() && l.op()->fuseInfo(f); };
+        bool ok = get(embedding_, p->embd) && get(norm_, p->norm) && get(lm_head_, p->head);
+        for (int i = 0; ok && i < cfg_.layers; i++) {
+            Block &b = blocks_[i];
+            auto &l = p->layers[i];
+            ok = get(b.norm1, l.n1) && get(b.norm2, l.n2) && get(b.q, l.q) && get(b.k, l.k) && get(b.v, l.v) && get(b.o, l.o) &&
+                 get(b.gate, l.gate) && get(b.up, l.up) && get(b.down, l.down) && get(b.q_rope, l.rope) && get(b.k_cache, l.kc) &&
+                 get(b.v_cache, l.vc);
+            if (!ok) break;
+            for (const FuseInfo *f : {&l.q, &l.k, &l.v, &l.o, &l.gate, &l.up, &l.down}) ok = ok && f->wtype == MLLM_TYPE_Q4_0;
+            ok = ok && !l.n1.unit_offset && !l.n2.unit_offset && l.kc.cache_batch == B && l.vc.cache_batch == B && l.kc.cache_dim == D &&
+                 l.kc.cache_heads == cfg_.kv_heads && l.rope.rot_dim % 2 == 0;
+            l.advance[0] = b.q_rope.op(); l.advance[1] = b.k_rope.op(); l.advance[2] = b.k_cache.op(); l.advance[3] = b.v_cache.op();
+        }
+        ok = ok && p->head.wtype == MLLM_TYPE_Q4_0 && p->embd.wtype == MLLM_TYPE_Q4_0 && !p->norm.unit_offset;
+        if (!ok) return false; // caches not allocated yet (no prefill so far) or a dtype outside the fused kernels
+        CUDABackend *bn = st_.backend;
+        const int QKV = (cfg_.heads + 2 * cfg_.kv_heads) * D;
+        p->x = Tensor(B, 1, 1, H, bn); p->x2 = Tensor(B, 1, 1, H, bn);
+        p->qkv = Tensor(B, 1, 1, QKV, bn); p->ao = Tensor(B, 1, 1, cfg_.heads * D, bn);
+        p->g = Tensor(B, 1, 1, cfg_.ffn, bn); p->logits = Tensor(B, 1, 1, cfg_.vocab, bn);
+        p->ids = Tensor(B, 1, 1, 1, bn); p->ctl = Tensor(1, 1, 1, 4, bn);
+        p->tok_log = Tensor(1, 1, cfg_.cache_limit + 1, B, bn);
+        p->attn_ws_bytes = mllmcu_decode_attn_workspace_bytes(B, cfg_.heads, D);
+        p->attn_ws = Tensor(1, 1, 1, (int)((p->attn_ws_bytes + 3) / 4), bn);
+        MLLMCU_CHECK(mllmcu_memset(p->attn_ws.rawDevPtr(), 0, p->attn_ws.cntSize(), bn->stream()));
+        MLLMCU_CHECK(mllmcu_memset(p->ctl.rawDevPtr(), 0, 16, bn->stream()));
+        p->use_graph = !env_on("MLLM_CUDA_NO_GRAPH");
+        p->use_pdl = !env_on("MLLM_CUDA_NO_PDL");
+        p->launches = 3 + 6 * cfg_.layers;
+        plan_ = std::move(p);
+    }
+    // per-step state: every RoPE counter and cache length must agree (they do on the LLaMA path)
+    const int len = blocks_[0].k_cache.op()->getCacheSeqLen();
+    for (auto &b : blocks_) {
+        FuseInfo r;
+        if (b.k_cache.op()->getCacheSeqLen() != len || b.v_cache.op()->getCacheSeqLen() != len) return false;
+        if (!b.q_rope.op()->fuseInfo(r) || r.pos != len) return false;
+        if (!b.k_rope.op()->fuseInfo(r) || r.pos != len) return false;
+    }
+    return true;
+}
+
+float *LlamaModel::decode_ids() { return plan_ ? plan_->ids.devPtr<float>() : nullptr; }
+const int *LlamaModel::decode_tok_log() { return plan_ ? plan_->tok_log.devPtr<int>() : nullptr; }
+
+// the kernel sequence of one token; returns false if a fused kernel refuses the shape (rc == -2)
+bool LlamaModel::issue_step(DecodePlan &p, bool pick, bool pdl_on) {
+    CUDABackend *bn = st_.backend;
+    void *st = bn->stream();
+    const int B = p.B, H = cfg_.hidden, D = cfg_.head_dim(), Hq = cfg_.heads, Hkv = cfg_.kv_heads, F = cfg_.ffn;
+    const int QKV = (Hq + 2 * Hkv) * D, pdl = pdl_on ? 1 : 0;
+    int *ctl = p.ctl.devPtr<int>();
+    float *x = p.x.devPtr<float>(), *x2 = p.x2.devPtr<float>(), *qkv = p.qkv.devPtr<float>(), *ao = p.ao.devPtr<float>(), *g = p.g.devPtr<float>();
+    auto gemv = [&](std::initializer_list<const FuseInfo *> ws, const float *in, int K, const FuseInfo *norm, int epi, const float *res, int ldr,
+                    float *out, int ldy) -> bool {
+        const void *W[3]; int N[3]; const float *bias[3]; int n = 0;
+        for (const FuseInfo *f : ws) { W[n] = f->weight; N[n] = f->out; bias[n] = f->bias; n++; }
+        const int rc = mllmcu_gemv_fused(MLLM_TYPE_Q4_0, W, N, bias, n, in, K, B, K, norm ? norm->norm_w : nullptr, norm ? norm->eps : 0.f, epi, res, ldr,
+                                         out, ldy, 0, pdl, st);
+        if (rc == -2) return false;
+        MLLMCU_CHECK(rc);
+        return true;
+    };
+    MLLMCU_CHECK(mllmcu_decode_embed(p.embd.weight, p.ids.devPtr<float>(), x, B, H, ctl, st));
+    for (auto &l : p.layers) {
+        if (!gemv({&l.q, &l.k, &l.v}, x, H, &l.n1, 0, nullptr, 0, qkv, QKV)) return false;
+        MLLMCU_CHECK(mllmcu_decode_rope_kv(l.rope.rope_type, qkv, QKV, B, Hq, Hkv, D, l.rope.rot_dim, l.rope.sin_t, l.rope.cos_t, l.rope.rot_dim, ctl,
+                                           l.kc.cache, l.vc.cache, l.kc.cache_bstride, l.kc.cache_limit, pdl, st));
+        MLLMCU_CHECK(mllmcu_decode_attn(qkv, QKV, l.kc.cache, l.vc.cache, ao, Hq * D, ctl, B, Hq, Hkv, D, l.kc.cache_bstride, p.attn_ws.rawDevPtr(),
+                                        p.attn_ws_bytes, pdl, st));
+        if (!gemv({&l.o}, ao, Hq * D, nullptr, 1, x, H, x2, H)) return false;
+        if (!gemv({&l.gate, &l.up}, x2, H, &l.n2, 2, nullptr, 0, g, F)) return false;
+        if (!gemv({&l.down}, g, F, nullptr, 1, x2, H, x, H)) return false;
+    }
+    if (!gemv({&p.head}, x, H, &p.norm, 0, nullptr, 0, p.logits.devPtr<float>(), cfg_.vocab)) return false;
+    if (pick)
+        MLLMCU_CHECK(mllmcu_decode_argmax(p.logits.devPtr<float>(), B, cfg_.vocab, p.ids.devPtr<float>(), p.tok_log.devPtr<int>(), ctl,
+                                          cfg_.cache_limit + 1, st));
+    return true;
+}
+
+Tensor LlamaModel::decode_step(const float *ids_dev, int B, bool pick) {
+    CUDABackend *bn = st_.backend;
+    DecodePlan &p = *plan_;
+    void *st = bn->stream();
+    const int len = blocks_[0].k_cache.op()->getCacheSeqLen();
+    if (len + 1 > cfg_.cache_limit) { // same refusal as CUDAKVCache::reshape (CPUKVCache.cpp:121-126)
+        std::cerr << "\n[ERROR]: Current tokens exceed cache limit: " << len + 1 << ">" << cfg_.cache_limit << ";"
+                  << "\n         Please set args `--limits` >" << cfg_.cache_limit << std::endl;
+        throw std::runtime_error("[mllm-cuda] KV cache limit exceeded");
+    }
+    if (len + 1 > p.layers[0].rope.pos_max) throw std::runtime_error("[mllm-cuda] RoPE: position exceeds max_position_embeddings");
+    if (ids_dev != p.ids.devPtr<float>()) MLLMCU_CHECK(mllmcu_memcpy_d2d(p.ids.rawDevPtr(), ids_dev, sizeof(float) * B, st));
+    if (p.dev_pos != len - 1) { // the embed kernel pre-increments
+        p.ctl_host = len - 1;
+        MLLMCU_CHECK(mllmcu_memcpy_h2d(p.ctl.rawDevPtr(), &p.ctl_host, sizeof(int), st));
+        p.dev_pos = len - 1;
+    }
+    const int gi = pick ? 1 : 0;
+    bool ran = false;
+    if (p.use_graph && !p.graph[gi] && p.warmed[gi]) {
+        // second step of this flavour: every kernel attribute is configured, capture the sequence
+        for (int attempt = 0; attempt < 2 && !p.graph[gi]; attempt++) {
+            MLLMCU_CHECK(mllmcu_graph_begin_capture(st));
+            bool ok = false;
+            try { ok = issue_step(p, pick, p.use_pdl); } catch (...) { mllmcu_graph_abort_capture(st); throw; }
+            void *ge = nullptr;
+            if (!ok) { mllmcu_graph_abort_capture(st); break; }
+            if (mllmcu_graph_end_capture(st, &ge) == 0) p.graph[gi] = ge;
+            else if (p.use_pdl) p.use_pdl = false; // retry the capture with plain stream order
+            else { p.use_graph = false; break; }
+        }
+    }
+    if (p.graph[gi]) {
+        MLLMCU_CHECK(mllmcu_graph_launch(p.graph[gi], st));
+        ran = true;
+    } else {
+        ran = issue_step(p, pick, p.use_pdl);
+        p.warmed[gi] = true;
+    }
+    if (!ran) { // a kernel refused the shape mid-step: forget the plan and redo the token op by op
+        p.unsupported = true;
+        p.dev_pos = -2;
+        Tensor ids(B, 1, 1, 1, bn);
+        ids.setName("input_ids");
+        MLLMCU_CHECK(mllmcu_memcpy_d2d(ids.rawDevPtr(), p.ids.rawDevPtr(), sizeof(float) * B, st));
+        return forward(ids);
+    }
+    p.dev_pos = len;
+    for (auto &l : p.layers)
+        for (Op *o : l.advance) o->advance(1);
+    bn->kernel_launches += p.launches - (pick ? 0 : 1);
+    last_fused_ = true;
+    return p.logits;
 }
 
 } // namespace mllm

@@ -13,6 +13,7 @@ struct ModuleState { // Module::doLoad / doTrace / loader (mllm/Module.hpp)
     CUDABackend *backend = nullptr;
     ParamLoader *loader = nullptr;
     bool doLoad = false;
+    string tag; // suffix making this module's activation names unique inside the backend (two models may be loaded at once)
 };
 
 class Layer { // mllm/Layer.hpp:30-222
@@ -27,7 +28,7 @@ public:
             op_->load(*st_->loader);
             loaded_ = true;
         }
-        return st_->backend->runOp(op_.get(), inputs, {"out-" + name_}, false); // part 4
+        return st_->backend->runOp(op_.get(), inputs, {"out-" + name_ + st_->tag}, false); // part 4
     }
     Op *op() { return op_.get(); }
 
@@ -80,8 +81,24 @@ public:
     void clear_kvcache();
     const LlamaConfig &config() const { return cfg_; }
     CUDABackend *backend() { return st_.backend; }
+    ~LlamaModel();
+
+    // ---- fused single-token step (Module.cpp, "decode plan"): the S == 1 forward as ~6 launches per block
+    // (qkv GEMV with RMSNorm prologue, RoPE + KV append, attention, o GEMV + residual, gate/up GEMV with
+    // RMSNorm prologue and silu*mul epilogue, down GEMV + residual), captured once in a CUDA graph.
+    // forward() takes it automatically when the shapes qualify; MLLM_CUDA_EAGER_DECODE=1 forces op-by-op.
+    bool decode_plan_usable(int B);
+    Tensor decode_step(const float *ids_dev, int B, bool pick_on_device);
+    float *decode_ids();         // device fp32 [B]: input of the next step (written by the on-device pick)
+    const int *decode_tok_log(); // device int32 [cache_limit][B]: token picked after consuming position p
+    bool last_step_fused() const { return last_fused_; }
+    void set_eager_decode(bool on) { force_eager_ = on; }
 
 private:
+    struct DecodePlan;
+    std::unique_ptr<DecodePlan> plan_;
+    bool last_fused_ = false, force_eager_ = false;
+    bool issue_step(DecodePlan &p, bool pick, bool pdl);
     struct Block {
         Layer norm1, norm2, q, k, v, o, q_rope, k_rope, k_cache, v_cache, gate, up, down, silu;
     };

@@ -178,14 +178,21 @@ HAPI int mllm_cuda_llama_request_device(void *hv, const float *ids_host, int B, 
         Tensor lg = h->model->forward(ids);
         if (n_decode > 0) MLLMCU_CHECK(mllmcu_argmax_ids(lg.devPtr<float>(), B, V, toks.devPtr<float>(), bn->stream()));
         MLLMCU_CHECK(mllmcu_event_record(e1, bn->stream()));
+        std::vector<char> fused((size_t)(n_decode > 0 ? n_decode : 1), 0);
+        const float *cur_ids = toks.devPtr<float>(); // ids consumed by the next step
         for (int step = 1; step < n_decode; step++) {
-            Tensor cur(bn);
+            if (h->model->decode_plan_usable(B)) { // fused step + on-device pick: one graph launch per token
+                h->model->decode_step(cur_ids, B, true);
+                cur_ids = h->model->decode_ids();
+                fused[step] = 1;
+                continue;
+            }
+            Tensor cur(B, 1, 1, 1, bn);
             cur.setName("input_ids");
-            cur.shallowCopyFrom(toks, step - 1, 1); // [1,1,1,B] row = B token ids
-            cur.reshapeKeepStrides(B, 1, 1, 1);
-            cur.reshape(B, 1, 1, 1);
+            MLLMCU_CHECK(mllmcu_memcpy_d2d(cur.rawDevPtr(), cur_ids, sizeof(float) * B, bn->stream()));
             Tensor l2 = h->model->forward(cur);
             MLLMCU_CHECK(mllmcu_argmax_ids(l2.devPtr<float>(), B, V, toks.devPtr<float>() + (size_t)step * B, bn->stream()));
+            cur_ids = toks.devPtr<float>() + (size_t)step * B;
         }
         MLLMCU_CHECK(mllmcu_event_record(e2, bn->stream()));
         MLLMCU_CHECK(mllmcu_event_sync(e2));
@@ -195,8 +202,20 @@ HAPI int mllm_cuda_llama_request_device(void *hv, const float *ids_host, int B, 
         if (tokens_out && n_decode > 0) {
             std::vector<float> t((size_t)n_decode * B);
             toks.copyToHost(t.data());
+            std::vector<int> log;
+            const int *log_dev = h->model->decode_tok_log();
+            if (log_dev) {
+                log.resize((size_t)(h->model->config().cache_limit + 1) * B);
+                MLLMCU_CHECK(mllmcu_memcpy_d2h(log.data(), log_dev, log.size() * sizeof(int), bn->stream()));
+                bn->sync();
+            }
             for (int s = 0; s < n_decode; s++)
-                for (int b = 0; b < B; b++) tokens_out[(size_t)b * n_decode + s] = (int)t[(size_t)s * B + b];
+                for (int b = 0; b < B; b++) // step s consumed position S+s-1; its pick is logged under that position
+                    tokens_out[(size_t)b * n_decode + s] = fused[s] ? log[(size_t)(S + s - 1) * B + b] : (int)t[(size_t)s * B + b];
         }
     })
 }
+
+// 1 when the last forward() of this model ran as the fused (graph) decode step, 0 when it ran op by op
+HAPI int mllm_cuda_llama_last_step_fused(void *hv) { return ((HostModel *)hv)->model->last_step_fused() ? 1 : 0; }
+HAPI int mllm_cuda_llama_set_eager_decode(void *hv, int on) { GUARD({ ((HostModel *)hv)->model->set_eager_decode(on != 0); }) }

@@ -127,6 +127,22 @@ private:
     bool is_view_ = false;
 };
 
+// What the backend's decode-step fuser reads from an op it folds into a fused launch (device pointers
+// stay owned by the op).  No reference counterpart: the CPU backend executes ops one by one.
+struct FuseInfo {
+    const void *weight = nullptr; // Linear / Embedding: quantised rows in the .mllm layout
+    int wtype = 0, in = 0, out = 0;
+    const float *bias = nullptr;
+    const float *norm_w = nullptr; // RMSNorm
+    float eps = 0.f;
+    int unit_offset = 0;
+    const float *sin_t = nullptr, *cos_t = nullptr; // RoPE tables [pos_max][rot_dim]
+    int rope_type = 0, rot_dim = 0, pos = 0, pos_max = 0;
+    void *cache = nullptr; // KVCache fp16 [B][limit][H][D]
+    long long cache_bstride = 0;
+    int cache_limit = 0, cache_len = 0, cache_batch = 0, cache_heads = 0, cache_dim = 0;
+};
+
 // ---- mllm/Op.hpp:20-148
 class Op {
 public:
@@ -139,6 +155,8 @@ public:
     virtual ErrorCode free(vector<shared_ptr<Tensor>> inputs, vector<shared_ptr<Tensor>> outputs) { return MLLM_NO_ERROR; }
     virtual int getCacheSeqLen() { return -1; }
     virtual void clearCache() {}
+    virtual bool fuseInfo(FuseInfo &) { return false; } // decode-step fusion hook (CUDA backend only)
+    virtual void advance(int tokens) {}                 // a fused launch consumed `tokens` positions on this op's behalf
     Backend *backend() const { return backend_; }
     const string &name() const { return name_; }
     OpType &type() { return type_; }

@@ -60,3 +60,36 @@ MLLMCU_API int mllmcu_event_elapsed_ms(void *start, void *stop, float *ms) {
     CU_TRY(cudaEventElapsedTime(ms, (cudaEvent_t)start, (cudaEvent_t)stop));
     return 0;
 }
+
+// ---- CUDA graphs: a decode step is ~200 small launches; the backend captures it once and
+// replays it per token (host dispatch, not the kernels, bounds the eager loop otherwise).
+MLLMCU_API int mllmcu_graph_begin_capture(void *stream) {
+    CU_TRY(cudaStreamBeginCapture((cudaStream_t)stream, cudaStreamCaptureModeThreadLocal));
+    return 0;
+}
+MLLMCU_API int mllmcu_graph_end_capture(void *stream, void **graph_exec) {
+    cudaGraph_t g = nullptr;
+    CU_TRY(cudaStreamEndCapture((cudaStream_t)stream, &g));
+    cudaGraphExec_t e = nullptr;
+    cudaError_t rc = cudaGraphInstantiate(&e, g, 0);
+    cudaGraphDestroy(g);
+    CU_TRY(rc);
+    *graph_exec = (void *)e;
+    return 0;
+}
+// abandon a capture after an error inside it (leaves the stream usable)
+MLLMCU_API int mllmcu_graph_abort_capture(void *stream) {
+    cudaGraph_t g = nullptr;
+    cudaStreamEndCapture((cudaStream_t)stream, &g);
+    if (g) cudaGraphDestroy(g);
+    cudaGetLastError();
+    return 0;
+}
+MLLMCU_API int mllmcu_graph_launch(void *graph_exec, void *stream) {
+    CU_TRY(cudaGraphLaunch((cudaGraphExec_t)graph_exec, (cudaStream_t)stream));
+    return 0;
+}
+MLLMCU_API int mllmcu_graph_destroy(void *graph_exec) {
+    if (graph_exec) CU_TRY(cudaGraphExecDestroy((cudaGraphExec_t)graph_exec));
+    return 0;
+}

@@ -50,6 +50,7 @@ CONFIGS = {
     "qwen1.5-1.8b": dict(vocab=151936, hidden=2048, layers=24, heads=16, kv_heads=16, ffn=5504, rope_type=ROPE_HF, rope_theta=1000000.0, rms_eps=1e-6, qkv_bias=1),
     # small graphs with the same structure, for parity tests the CPU oracle finishes in seconds
     "toy-llama": dict(vocab=512, hidden=256, layers=2, heads=4, kv_heads=4, ffn=512, rope_type=ROPE_LLAMA, rope_theta=10000.0, rms_eps=1e-6, qkv_bias=0),
+    "toy-d128": dict(vocab=320, hidden=256, layers=2, heads=2, kv_heads=1, ffn=512, rope_type=ROPE_LLAMA, rope_theta=10000.0, rms_eps=1e-6, qkv_bias=0),
     "toy-gqa": dict(vocab=384, hidden=256, layers=3, heads=8, kv_heads=2, ffn=768, rope_type=ROPE_HF, rope_theta=10000.0, rms_eps=1e-5, qkv_bias=1),
 }
 
