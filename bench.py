@@ -149,38 +149,56 @@ def cpu_arm(cfg, path, prefill, decode, reps=1):
 
 # ----------------------------------------------------------------------------- GPU arm
 def gemv_roofline(cfg, peaks):
-    """Time the decode Linear (activation quantise + GEMV kernels) for every Linear shape of one decode step, live,
-    with CUDA events on the launching stream; weights rotate over buffers larger than L2 (cold HBM reads)."""
+    """The dominant kernel of the request is the decode Linear, k_gemv_tma (fused activation quantise + Q4_0 GEMV).
+    Every Linear launch of one decode step (qkv, o, gate|up, down per block + lm_head) is timed live: the launches are
+    captured in a CUDA graph (device time, not ctypes dispatch), weights rotate over buffers larger than L2 (cold HBM
+    reads), CUDA events on the stream the graph is launched on.  achieved = algorithmic weight bytes / launch time,
+    launch-weighted over the step."""
     import torch
     from mllm_b200 import capi
     H, F, V, D = cfg["hidden"], cfg["ffn"], cfg["vocab"], cfg["head_dim"]
-    shapes = [("qkvo", H, H, 2 * cfg["layers"] + 2 * cfg["layers"] * cfg["kv_heads"] // cfg["heads"]),
-              ("gate_up", F, H, 2 * cfg["layers"]), ("down", H, F, cfg["layers"]), ("lm_head", V, H, 1)]
-    x_cache, total_t, total_b, per = {}, 0.0, 0.0, {}
-    for tag, N, K, count in shapes:
-        wbytes = N * (K // 32) * 18
-        nbuf = max(2, int(160e6 // wbytes) + 1)
-        bufs = [torch.randint(0, 255, (N, K // 32 * 18), dtype=torch.uint8, device="cuda") for _ in range(nbuf)]
-        x = x_cache.setdefault(K, torch.randn((1, K), device="cuda"))
-        for b in bufs[:2]:
-            capi.linear(b, x)
-        reps = max(3 * nbuf, 24)
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        torch.cuda.synchronize()
-        e0.record()
-        for i in range(reps):
-            capi.linear(bufs[i % nbuf], x)
-        e1.record()
-        torch.cuda.synchronize()
+    kvd = cfg["kv_heads"] * D
+    L = cfg["layers"]
+    shapes = [("qkv", [H, kvd, kvd], H, 0, True, L), ("o", [H], H, 1, False, L), ("gate_up", [F, F], H, 2, True, L),
+              ("down", [H], F, 1, False, L), ("lm_head", [V], H, 0, True, 1)]
+    total_t, total_b, per = 0.0, 0.0, {}
+    for tag, Ns, K, epi, norm, count in shapes:
+        wbytes = sum(Ns) * (K // 32) * 18
+        nbuf = max(2, int(200e6 // wbytes) + 1)
+        bufs = [[torch.randint(0, 255, (n, K // 32 * 18), dtype=torch.uint8, device="cuda") for n in Ns] for _ in range(nbuf)]
+        x = torch.randn((1, K), device="cuda")
+        nw = torch.ones(K, device="cuda") if norm else None
+        res = torch.randn((1, Ns[0]), device="cuda") if epi == 1 else None
+
+        def call(ws):
+            capi.gemv_fused(ws, x, norm_w=nw, epilogue=epi, residual=res, pdl=True)
+        for i in range(3):
+            call(bufs[i % nbuf])
+        reps = 4 * nbuf
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g, stream=side):
+                for i in range(reps):
+                    call(bufs[i % nbuf])
+            g.replay()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            torch.cuda.synchronize()
+            e0.record()
+            g.replay()
+            e1.record()
+            torch.cuda.synchronize()
         t = e0.elapsed_time(e1) / reps * 1e-3
-        per[tag] = {"N": N, "K": K, "us": round(t * 1e6, 2), "GBs": round(wbytes / t / 1e9, 1), "launches_per_step": count}
+        per[tag] = {"N": sum(Ns) if epi != 2 else Ns[0], "K": K, "us": round(t * 1e6, 2), "GBs": round(wbytes / t / 1e9, 1), "launches_per_step": count,
+                    "bytes": wbytes}
         total_t += t * count
         total_b += wbytes * count
-        del bufs
+        del bufs, g
     achieved = total_b / total_t / 1e9
     peak = peaks.get("hbm_gbs", 6650.0)
     return {"bound": "hbm", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s", "frac": round(achieved / peak, 4),
-            "traffic": None, "kernel": "k_gemv (decode Linear: Q8_0 activation quantise + Q4_0 GEMV), launch-weighted over one decode step",
+            "traffic": None, "kernel": "k_gemv_tma (decode Linear: fused RMSNorm/Q8_0 prologue + Q4_0 GEMV), launch-weighted over one decode step",
             "peak_source": "measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in peaks else "fallback 6650",
             "per_shape": per}
 
