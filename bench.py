@@ -147,6 +147,23 @@ def cpu_arm(cfg, path, prefill, decode, reps=1):
             "prefill_tok_s": prefill / tp, "decode_tok_s": decode / td if decode else None, "seconds": tp + td}
 
 
+# ----------------------------------------------------------------------------- ranks
+def max_over_ranks(values, world, device):
+    """Each rank times its own replica; the job's time is the slowest rank's (no collective on the data path)."""
+    if world == 1:
+        return [float(v) for v in values]
+    import torch
+    import torch.distributed as dist
+    t = torch.tensor(values, device=device, dtype=torch.float64)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return [float(v) for v in t.tolist()]
+
+
+def job_tokens_per_s(tokens_per_replica, world, ms):
+    """Whole-job throughput of `world` independent replicas that each processed tokens_per_replica in <= ms."""
+    return tokens_per_replica * world / ms * 1e3
+
+
 # ----------------------------------------------------------------------------- GPU arm
 def gemv_roofline(cfg, peaks):
     """The dominant kernel of the request is the decode Linear, k_gemv_tma (fused activation quantise + Q4_0 GEMV).
@@ -257,23 +274,17 @@ def gpu_arm(args, rank, world, local_rank):
         model.generate(ids, DECODE)
         e2e_ms.append((time.perf_counter() - w0) * 1e3)
     clocks = sampler.stop()
-    if world > 1:
-        import torch.distributed as dist
-        t = torch.tensor([total_ms, float(np.mean(e2e_ms))], device="cuda", dtype=torch.float64)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        total_ms, e2e_mean = t[0].item(), t[1].item()
-    else:
-        e2e_mean = float(np.mean(e2e_ms))
+    total_ms, e2e_mean = max_over_ranks([total_ms, float(np.mean(e2e_ms))], world, "cuda")
     if rank != 0:
         return
     ms_per_step = total_ms / args.steps
-    toks = (PREFILL + DECODE) * world
+    toks = (PREFILL + DECODE) * world  # == job_tokens_per_s numerator
     roof = gemv_roofline(cfg, peaks)
     wbytes = mf.decode_weight_bytes(cfg)
     kv_bytes = 2 * cfg["layers"] * (PREFILL + DECODE / 2) * cfg["kv_heads"] * cfg["head_dim"] * 2
     dec_ms = float(np.mean(td)) / DECODE
     out = {
-        "metric": METRIC, "value": round(toks / ms_per_step * 1e3, 2), "unit": "tok/s", "n_gpus": world, "steps": args.steps,
+        "metric": METRIC, "value": round(job_tokens_per_s(PREFILL + DECODE, world, ms_per_step), 2), "unit": "tok/s", "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": round(ms_per_step, 3), "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "int8 block dot (Q4_0 x Q8_0) + fp32 accumulate, fp16 KV", "data": "synthetic",
         "config": {"workload": "LLaMA-2-7B Q4_0 (BASELINE configs[1]): prefill 512 + greedy decode 256, batch 1, cache limit 1024, "
@@ -284,7 +295,7 @@ def gpu_arm(args, rank, world, local_rank):
                         "GBs": round((wbytes + kv_bytes) / (dec_ms * 1e-3) / 1e9, 1),
                         "frac_of_hbm_peak": round((wbytes + kv_bytes) / (dec_ms * 1e-3) / 1e9 / peaks.get("hbm_gbs", 6650.0), 4)},
         "prefill": {"ms": round(float(np.mean(tp)), 3), "int8_TOPs": round(2 * (wbytes / 0.5625) * PREFILL / (float(np.mean(tp)) * 1e-3) / 1e12, 1)},
-        "e2e": {"value": round(toks / e2e_mean * 1e3, 2), "unit": "tok/s", "h2d_bytes_per_step": (PREFILL + DECODE - 1) * 4,
+        "e2e": {"value": round(job_tokens_per_s(PREFILL + DECODE, world, e2e_mean), 2), "unit": "tok/s", "h2d_bytes_per_step": (PREFILL + DECODE - 1) * 4,
                 "d2h_bytes_per_step": DECODE * cfg["vocab"] * 4, "ms_per_step": round(e2e_mean, 2)},
         "gpu_launches": int(launches), "clocks": clocks, "roofline": roof,
     }
