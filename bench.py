@@ -297,7 +297,7 @@ def gpu_arm(args, rank, world, local_rank):
         "prefill": {"ms": round(float(np.mean(tp)), 3), "int8_TOPs": round(2 * (wbytes / 0.5625) * PREFILL / (float(np.mean(tp)) * 1e-3) / 1e12, 1)},
         "e2e": {"value": round(job_tokens_per_s(PREFILL + DECODE, world, e2e_mean), 2), "unit": "tok/s", "h2d_bytes_per_step": (PREFILL + DECODE - 1) * 4,
                 "d2h_bytes_per_step": DECODE * cfg["vocab"] * 4, "ms_per_step": round(e2e_mean, 2)},
-        "gpu_launches": int(launches), "clocks": clocks, "roofline": roof,
+        "decode_mode": model.decode_mode(), "gpu_launches": int(launches), "clocks": clocks, "roofline": roof,
     }
     if not args.no_cpu:
         try:

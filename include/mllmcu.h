@@ -191,6 +191,49 @@ int mllmcu_decode_attn(const float *q, int ldq, const void *k, const void *v, fl
 int mllmcu_decode_argmax(const float *logits, int rows, int n, float *ids_out, int *tok_log, const int *ctl, int log_rows,
                          void *stream);
 
+/* ---- the whole decode step as ONE persistent kernel (decode_step.cu).  The caller describes the step as a list
+ * of fused Linears ("jobs", same fusion vocabulary as mllmcu_gemv_fused: optional RMSNorm prologue, epilogue
+ * 0 plain / 1 + residual / 2 silu(gate)*up); a job with post = 1 is followed by RoPE + KV append + decode
+ * attention of block `layer` (mllmcu_decode_rope_kv / mllmcu_decode_attn semantics, reading the job's output
+ * q|k|v rows in desc.qkv and writing desc.ao).  Weights stream through per-warp TMA rings that run ahead across
+ * job boundaries; activations cross jobs through a grid barrier.  create() copies the tables to the device
+ * (cudaMalloc: the plan owns ~100 KB) and returns MLLMCU_ENOSUP when a shape does not fit the kernel (the
+ * caller then chains the per-op kernels).  Replaces, per token, the reference's whole op sequence of
+ * LLaMAModel::Forward (models/llama/modeling_llama.hpp:98-115) for S == 1. */
+typedef struct mllmcu_step_job {
+    const void *W[3];
+    const float *bias[3];
+    int N[3];
+    int nW;
+    int K;
+    int epi;
+    int post;
+    int layer;
+    const float *x;
+    int ldx;
+    const float *norm_w;
+    float eps;
+    const float *residual;
+    int ldr;
+    float *y;
+    int ldy;
+} mllmcu_step_job;
+typedef struct mllmcu_step_desc {
+    int B, Hq, Hkv, D, rope_type, rot_dim, tdim, cache_limit, n_layers;
+    const float *sin_t, *cos_t;
+    long long kv_bstride;
+    void *const *kcache; /* host array [n_layers] of device pointers */
+    void *const *vcache;
+    float *qkv;
+    int ldqkv;
+    float *ao;
+    int ldao;
+    const int *ctl;
+} mllmcu_step_desc;
+int mllmcu_decode_step_create(const mllmcu_step_desc *desc, const mllmcu_step_job *jobs, int njobs, void **plan);
+int mllmcu_decode_step_launch(void *plan, void *stream);
+int mllmcu_decode_step_destroy(void *plan);
+
 #ifdef __cplusplus
 }
 #endif

@@ -35,6 +35,8 @@ def lib():
         L.mllm_cuda_stream.restype = C.c_void_p
         L.mllm_cuda_llama_last_step_fused.argtypes = [C.c_void_p]
         L.mllm_cuda_llama_set_eager_decode.argtypes = [C.c_void_p, C.c_int]
+        L.mllm_cuda_llama_decode_mode.argtypes = [C.c_void_p]
+        L.mllm_cuda_llama_set_step_kernel.argtypes = [C.c_void_p, C.c_int]
         L.mllm_cuda_llama_request_device.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_float),
                                                      C.POINTER(C.c_float), C.c_void_p]
         L.mllm_cuda_run_op.argtypes = [C.POINTER(C.c_char_p), C.c_void_p, C.c_int, C.c_char_p, C.c_char_p, C.POINTER(C.c_void_p),
@@ -110,6 +112,14 @@ class LlamaModel:
     def last_step_fused(self):
         """True when the last forward ran as the fused, graph-replayed decode step."""
         return bool(lib().mllm_cuda_llama_last_step_fused(self.h))
+
+    def decode_mode(self):
+        """0 no plan, 1 chained fused kernels, 2 persistent step kernel; +4 replayed from a CUDA graph, +8 PDL edges."""
+        return int(lib().mllm_cuda_llama_decode_mode(self.h))
+
+    def set_step_kernel(self, on):
+        """Opt in to the persistent whole-step decode kernel (decode_step.cu) instead of the chained fused kernels."""
+        _check(lib().mllm_cuda_llama_set_step_kernel(self.h, int(bool(on))))
 
     def set_eager_decode(self, on):
         """Force the op-by-op path for S == 1 (parity tests compare it with the fused step)."""

@@ -67,6 +67,9 @@ SYMBOLS = {
     "mllmcu_decode_attn_workspace_bytes": (_sz, [_i, _i, _i]),
     "mllmcu_decode_attn": (_i, [_vp, _i, _vp, _vp, _vp, _i, _vp, _i, _i, _i, _i, C.c_longlong, _vp, _sz, _i, _vp]),
     "mllmcu_decode_argmax": (_i, [_vp, _i, _i, _vp, _vp, _vp, _i, _vp]),
+    "mllmcu_decode_step_create": (_i, [_vp, _vp, _i, C.POINTER(_vp)]),
+    "mllmcu_decode_step_launch": (_i, [_vp, _vp]),
+    "mllmcu_decode_step_destroy": (_i, [_vp]),
 }
 
 _lib = None

@@ -144,8 +144,10 @@ struct LlamaModel::DecodePlan {
     void *graph[2] = {nullptr, nullptr};
     bool unsupported = false, use_graph = true, use_pdl = true;
     int launches = 0;
+    void *step = nullptr; // persistent whole-step kernel (mllmcu_decode_step_*), when the shapes fit it
     ~DecodePlan() {
         for (void *g : graph) if (g) mllmcu_graph_destroy(g);
+        if (step) mllmcu_decode_step_destroy(step);
     }
 };
 
@@ -197,6 +199,10 @@ bool LlamaModel::decode_plan_usable(int B) {
         p->use_graph = !env_on("MLLM_CUDA_NO_GRAPH");
         p->use_pdl = !env_on("MLLM_CUDA_NO_PDL");
         p->launches = 3 + 6 * cfg_.layers;
+        // the persistent whole-step kernel is opt-in: on B200 its grid barriers + in-order per-warp rings currently lose
+        // to the PDL-chained persistent GEMVs (2.2 vs 1.7 ms/token on the 7B, profiles/r01_step_kernel_phases.txt)
+        if ((env_on("MLLM_CUDA_STEP_KERNEL") || want_step_kernel_) && B <= 4) build_step_kernel(*p);
+        if (p->step) p->launches = 3;
         plan_ = std::move(p);
     }
     // per-step state: every RoPE counter and cache length must agree (they do on the LLaMA path)
@@ -210,8 +216,55 @@ bool LlamaModel::decode_plan_usable(int B) {
     return true;
 }
 
+int LlamaModel::decode_mode() const {
+    if (!plan_ || plan_->unsupported) return 0;
+    int m = plan_->step ? 2 : 1;
+    if (plan_->graph[0] || plan_->graph[1]) m += 4;
+    if (plan_->use_pdl && !plan_->step) m += 8;
+    return m;
+}
 float *LlamaModel::decode_ids() { return plan_ ? plan_->ids.devPtr<float>() : nullptr; }
 const int *LlamaModel::decode_tok_log() { return plan_ ? plan_->tok_log.devPtr<int>() : nullptr; }
+
+// describe the step to the persistent kernel: per block qkv (RMSNorm prologue; rope + KV append + attention follow),
+// o (+ residual), gate|up (RMSNorm prologue, silu*mul), down (+ residual); then final norm + lm_head
+void LlamaModel::build_step_kernel(DecodePlan &p) {
+    const int B = p.B, H = cfg_.hidden, D = cfg_.head_dim(), Hq = cfg_.heads, Hkv = cfg_.kv_heads, F = cfg_.ffn;
+    const int QKV = (Hq + 2 * Hkv) * D;
+    float *x = p.x.devPtr<float>(), *x2 = p.x2.devPtr<float>(), *qkv = p.qkv.devPtr<float>(), *ao = p.ao.devPtr<float>(), *g = p.g.devPtr<float>();
+    vector<mllmcu_step_job> jobs;
+    vector<void *> kc, vc;
+    auto job = [&](std::initializer_list<const FuseInfo *> ws, const float *in, int K, const FuseInfo *norm, int epi, const float *res, int ldr,
+                   float *out, int ldy, int post, int layer) {
+        mllmcu_step_job j = {};
+        int n = 0;
+        for (const FuseInfo *f : ws) { j.W[n] = f->weight; j.N[n] = f->out; j.bias[n] = f->bias; n++; }
+        j.nW = n; j.K = K; j.epi = epi; j.post = post; j.layer = layer; j.x = in; j.ldx = K;
+        j.norm_w = norm ? norm->norm_w : nullptr; j.eps = norm ? norm->eps : 0.f; j.residual = res; j.ldr = ldr; j.y = out; j.ldy = ldy;
+        jobs.push_back(j);
+    };
+    int li = 0;
+    for (auto &l : p.layers) {
+        job({&l.q, &l.k, &l.v}, x, H, &l.n1, 0, nullptr, 0, qkv, QKV, 1, li);
+        job({&l.o}, ao, Hq * D, nullptr, 1, x, H, x2, H, 0, li);
+        job({&l.gate, &l.up}, x2, H, &l.n2, 2, nullptr, 0, g, F, 0, li);
+        job({&l.down}, g, F, nullptr, 1, x2, H, x, H, 0, li);
+        kc.push_back(l.kc.cache);
+        vc.push_back(l.vc.cache);
+        li++;
+    }
+    job({&p.head}, x, H, &p.norm, 0, nullptr, 0, p.logits.devPtr<float>(), cfg_.vocab, 0, 0);
+    const FuseInfo &r = p.layers[0].rope;
+    mllmcu_step_desc d = {};
+    d.B = B; d.Hq = Hq; d.Hkv = Hkv; d.D = D; d.rope_type = r.rope_type; d.rot_dim = r.rot_dim; d.tdim = r.rot_dim;
+    d.cache_limit = p.layers[0].kc.cache_limit; d.n_layers = cfg_.layers; d.sin_t = r.sin_t; d.cos_t = r.cos_t;
+    d.kv_bstride = p.layers[0].kc.cache_bstride; d.kcache = kc.data(); d.vcache = vc.data();
+    d.qkv = qkv; d.ldqkv = QKV; d.ao = ao; d.ldao = Hq * D; d.ctl = p.ctl.devPtr<int>();
+    st_.backend->sync(); // create() uses synchronous copies on the default stream
+    const int rc = mllmcu_decode_step_create(&d, jobs.data(), (int)jobs.size(), &p.step);
+    if (rc == -2) { p.step = nullptr; return; } // shapes outside the kernel: keep the chained launches
+    MLLMCU_CHECK(rc);
+}
 
 // the kernel sequence of one token; returns false if a fused kernel refuses the shape (rc == -2)
 bool LlamaModel::issue_step(DecodePlan &p, bool pick, bool pdl_on) {
@@ -232,6 +285,13 @@ bool LlamaModel::issue_step(DecodePlan &p, bool pick, bool pdl_on) {
         return true;
     };
     MLLMCU_CHECK(mllmcu_decode_embed(p.embd.weight, p.ids.devPtr<float>(), x, B, H, ctl, st));
+    if (p.step) {
+        MLLMCU_CHECK(mllmcu_decode_step_launch(p.step, st));
+        if (pick)
+            MLLMCU_CHECK(mllmcu_decode_argmax(p.logits.devPtr<float>(), B, cfg_.vocab, p.ids.devPtr<float>(), p.tok_log.devPtr<int>(), ctl,
+                                              cfg_.cache_limit + 1, st));
+        return true;
+    }
     for (auto &l : p.layers) {
         if (!gemv({&l.q, &l.k, &l.v}, x, H, &l.n1, 0, nullptr, 0, qkv, QKV)) return false;
         MLLMCU_CHECK(mllmcu_decode_rope_kv(l.rope.rope_type, qkv, QKV, B, Hq, Hkv, D, l.rope.rot_dim, l.rope.sin_t, l.rope.cos_t, l.rope.rot_dim, ctl,

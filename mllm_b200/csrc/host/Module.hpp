@@ -93,12 +93,16 @@ public:
     const int *decode_tok_log(); // device int32 [cache_limit][B]: token picked after consuming position p
     bool last_step_fused() const { return last_fused_; }
     void set_eager_decode(bool on) { force_eager_ = on; }
+    void set_step_kernel(bool on) { want_step_kernel_ = on; plan_.reset(); } // persistent whole-step kernel (opt-in)
+    // 0: no plan, 1: chained fused kernels, 2: persistent step kernel; +4 when replayed from a CUDA graph, +8 with PDL edges
+    int decode_mode() const;
 
 private:
     struct DecodePlan;
     std::unique_ptr<DecodePlan> plan_;
-    bool last_fused_ = false, force_eager_ = false;
+    bool last_fused_ = false, force_eager_ = false, want_step_kernel_ = false;
     bool issue_step(DecodePlan &p, bool pick, bool pdl);
+    void build_step_kernel(DecodePlan &p);
     struct Block {
         Layer norm1, norm2, q, k, v, o, q_rope, k_rope, k_cache, v_cache, gate, up, down, silu;
     };

@@ -219,3 +219,5 @@ HAPI int mllm_cuda_llama_request_device(void *hv, const float *ids_host, int B, 
 // 1 when the last forward() of this model ran as the fused (graph) decode step, 0 when it ran op by op
 HAPI int mllm_cuda_llama_last_step_fused(void *hv) { return ((HostModel *)hv)->model->last_step_fused() ? 1 : 0; }
 HAPI int mllm_cuda_llama_set_eager_decode(void *hv, int on) { GUARD({ ((HostModel *)hv)->model->set_eager_decode(on != 0); }) }
+HAPI int mllm_cuda_llama_decode_mode(void *hv) { return ((HostModel *)hv)->model->decode_mode(); }
+HAPI int mllm_cuda_llama_set_step_kernel(void *hv, int on) { GUARD({ ((HostModel *)hv)->model->set_step_kernel(on != 0); }) }

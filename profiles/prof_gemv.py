@@ -8,7 +8,7 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from mllm_b200 import capi  # noqa: E402
 
 which = sys.argv[1] if len(sys.argv) > 1 else "down"
-Ns, K, epi = {"down": ([4096], 11008, 1), "gateup": ([11008] * 2, 4096, 2), "o": ([4096], 4096, 1)}[which]
+Ns, K, epi = {"down": ([4096], 11008, 1), "gateup": ([11008] * 2, 4096, 2), "o": ([4096], 4096, 1), "lm_head": ([32000], 4096, 0)}[which]
 bufs = [[torch.randint(0, 255, (n, K // 32 * 18), dtype=torch.uint8, device="cuda") for n in Ns] for _ in range(6)]
 x = torch.randn((1, K), device="cuda")
 nw = torch.ones(K, device="cuda")

@@ -162,6 +162,14 @@ def test_device_resident_request_tokens_match_oracle(be, oracle, tmp_path_factor
     n0 = be.kernel_launches()
     _, _, toks = gpu.request_device(ids, horizon)
     assert toks[0].tolist() == want
+    assert gpu.decode_mode() == 1 + 4 + 8  # chained fused kernels, replayed from a CUDA graph with PDL edges
+    # the persistent whole-step kernel (opt-in) produces the same tokens
+    gpu.clear_kvcache()
+    gpu.set_step_kernel(True)
+    _, _, toks = gpu.request_device(ids, horizon)
+    assert toks[0].tolist() == want
+    assert gpu.decode_mode() == 2 + 4
+    gpu.set_step_kernel(False)
     assert be.kernel_launches() > n0
     # again after clear_kvcache: the graph is replayed from a rewound position
     gpu.clear_kvcache()
