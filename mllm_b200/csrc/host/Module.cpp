@@ -152,6 +152,11 @@ struct LlamaModel::DecodePlan {
 };
 
 LlamaModel::~LlamaModel() = default;
+void LlamaModel::set_step_kernel(bool on) {
+    want_step_kernel_ = on;
+    st_.backend->sync();
+    plan_.reset();
+}
 
 static bool env_on(const char *k) {
     const char *e = getenv(k);

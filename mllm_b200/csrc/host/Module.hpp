@@ -93,7 +93,7 @@ public:
     const int *decode_tok_log(); // device int32 [cache_limit][B]: token picked after consuming position p
     bool last_step_fused() const { return last_fused_; }
     void set_eager_decode(bool on) { force_eager_ = on; }
-    void set_step_kernel(bool on) { want_step_kernel_ = on; plan_.reset(); } // persistent whole-step kernel (opt-in)
+    void set_step_kernel(bool on); // persistent whole-step kernel (opt-in); drops the current plan
     // 0: no plan, 1: chained fused kernels, 2: persistent step kernel; +4 when replayed from a CUDA graph, +8 with PDL edges
     int decode_mode() const;
 
