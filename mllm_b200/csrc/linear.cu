@@ -207,9 +207,17 @@ MLLMCU_API int mllmcu_block_isums_q4_0_q8_0(const void *W, const void *xq, int32
 // ------------------------------------------------------------------ entry
 static inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
+// tensor-core prefill path (gemm_tc.cu)
+size_t gemm_tc_workspace_bytes(int M, int K);
+bool gemm_tc_supported(int wtype, int M, int N, int K);
+int launch_gemm_q4_0_tc(const void *W, const float *x, int ldx, const float *bias, void *y, int M, int N, int K, int ldy, int out_f16,
+                        void *ws, cudaStream_t st);
+
 MLLMCU_API size_t mllmcu_linear_workspace_bytes(int M, int K) {
     if (M <= 0 || K <= 0) return 0;
-    return align_up((size_t)M * K, 256) + align_up((size_t)M * (K / QK) * sizeof(float), 256);
+    const size_t a = align_up((size_t)M * K, 256) + align_up((size_t)M * (K / QK) * sizeof(float), 256);
+    const size_t b = gemm_tc_workspace_bytes(M, K);
+    return a > b ? a : b;
 }
 
 template <int WT>
@@ -232,6 +240,7 @@ MLLMCU_API int mllmcu_linear(int wtype, const void *W, const float *x, const flo
     if (wtype != 2 && wtype != 8) return -2;
     if (ws == nullptr || ws_bytes < mllmcu_linear_workspace_bytes(M, K)) return -3;
     cudaStream_t st = (cudaStream_t)stream;
+    if (gemm_tc_supported(wtype, M, N, K) && !((uintptr_t)W & 15)) return launch_gemm_q4_0_tc(W, x, ldx, bias, y, M, N, K, ldy, out_f16, ws, st);
     int8_t *xq = (int8_t *)ws;
     float *xd = (float *)((char *)ws + align_up((size_t)M * K, 256));
     int rc = launch_quantize_q8_0_split(x, xq, xd, M, K, ldx, st);

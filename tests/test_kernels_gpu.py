@@ -78,6 +78,51 @@ def test_linear_q4_0(cu, oracle, M, N, K, bias):
     lin_check(y, oracle.linear(W, x, b))
 
 
+@pytest.mark.parametrize("M,N,K", [(9, 128, 64), (128, 128, 256), (130, 256, 512), (300, 384, 2048), (512, 128, 11008), (33, 512, 4096)])
+@pytest.mark.parametrize("bias", [False, True])
+def test_linear_q4_0_tensor_core_path(cu, oracle, M, N, K, bias):
+    """Prefill shapes that take the tcgen05 kernel (M > 8, N % 128 == 0, K % 64 == 0): per-block integer sums come out of
+    the tensor core exactly (fp16 integers, fp32 accumulate), so the result obeys the same bar as the CUDA-core path."""
+    rng = np.random.default_rng(M + N + K)
+    W = oracle.quantize_q4_0((rng.standard_normal((N, K)) * 0.02).astype(np.float32))
+    x = act_rows(rng, M, K)
+    b = (rng.standard_normal(N) * 0.02).astype(np.float32) if bias else None
+    y = cu.linear(dev(W), dev(x), dev(b) if bias else None).cpu().numpy()
+    lin_check(y, oracle.linear(W, x, b))
+
+
+def test_linear_tensor_core_block_sums_exact(cu, oracle):
+    """With d_w = d_x = 1 the output IS the sum of integer block sums: must equal the integer arithmetic exactly."""
+    rng = np.random.default_rng(5)
+    M, N, K = 256, 256, 1024
+    blocks = rng.integers(0, 256, (N, K // 32, 18), dtype=np.uint8)
+    one = np.float16(1.0).view(np.uint16)
+    blocks[:, :, 0] = one & 0xFF
+    blocks[:, :, 1] = one >> 8
+    W = blocks.reshape(N, -1)
+    q = rng.integers(-127, 128, (M, K)).astype(np.float32)
+    q[:, ::32] = 127.0  # amax = 127 in every block -> d_x = 1, q8 = the integers themselves
+    y = cu.linear(dev(W), dev(q)).cpu().numpy()
+    qs = blocks[:, :, 2:]
+    w = np.concatenate([(qs & 0x0F).astype(np.int64) - 8, (qs >> 4).astype(np.int64) - 8], axis=2).reshape(N, K)
+    want = q.astype(np.int64) @ w.T
+    assert np.array_equal(y.astype(np.int64), want) and np.all(y == np.round(y))
+
+
+def test_linear_tensor_core_fp16_out_strided(cu, oracle):
+    import torch
+    rng = np.random.default_rng(8)
+    M, N, K, ld = 40, 128, 512, 160
+    W = oracle.quantize_q4_0((rng.standard_normal((N, K)) * 0.05).astype(np.float32))
+    x = act_rows(rng, M, K)
+    out = torch.zeros((M + 2, ld), dtype=torch.float16, device="cuda")
+    cu.linear(dev(W), dev(x), out_f16=True, out=out[1:], ldy=ld)
+    got = out.cpu().numpy()
+    want = oracle.linear(W, x, out_fp16=True).view(np.float16).astype(np.float32)
+    assert np.all(got[0] == 0) and np.all(got[M + 1] == 0) and np.all(got[:, N:] == 0)
+    assert np.abs(got[1:M + 1, :N].astype(np.float32) - want).max() <= 1e-3 * np.abs(want).max()
+
+
 def test_linear_q4_0_golden(cu, golden):
     y = cu.linear(dev(golden["q4_blocks"]), dev(golden["q8_x"]), dev(golden["lin_bias"])).cpu().numpy()
     lin_check(y, golden["lin_y_bias"])
