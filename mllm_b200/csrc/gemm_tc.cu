@@ -16,7 +16,7 @@
 //   warp 0      : TMEM alloc, single-thread MMA issue, tcgen05.commit -> mbarriers
 //   warps 1-4   : loaders -- Q4_0 rows -> exact fp16 (q-8) into the canonical no-swizzle K-major core-matrix
 //                 layout (generic-proxy stores + fence.proxy.async), fp16 activation rows, d_w / d_x rings
-//   warps 5-12  : epilogue -- tcgen05.ld (32 lanes x 64 columns per warp), scale, accumulate in registers,
+//   warps 5-20  : epilogue -- tcgen05.ld (32 lanes x 32 columns per warp), scale, accumulate in registers,
 //                 finally bias and store
 // Pipelines: 4 smem stages of 2 Q blocks, 4 TMEM buffers; all hand-offs through mbarriers.
 #include "common.cuh"
@@ -28,7 +28,8 @@
 #define TC_NS 4   // shared-memory stages
 #define TC_ND 4   // TMEM accumulator buffers (one Q block each)
 #define TC_SR 16  // scale ring depth in Q blocks (> TC_NS*TC_KB + TC_ND: loaders never lap the epilogue)
-#define TC_THREADS (13 * 32)
+#define TC_EPI_WARPS 16 // 4 TMEM lane quarters x 4 column quarters of 32
+#define TC_THREADS ((5 + TC_EPI_WARPS) * 32) // 21 warps; registers are granted per 4 warps, so the budget is 80 per thread
 #define TC_STAGE_BYTES (2 * TC_KB * 4 * TC_BM * 16) // A + B: KB blocks x 4 16-byte K chunks x 128 rows
 #define TC_OPER_BYTES (TC_KB * 4 * TC_BM * 16)
 
@@ -94,16 +95,23 @@ static __device__ __forceinline__ void tc_ld32(uint32_t taddr, uint32_t (&r)[32]
 static __device__ __forceinline__ void tc_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
 // ------------------------------------------------------------------ activation quantisation for this kernel
-// Q8_0 values (bytes identical to quantize_row_q8_0) stored as fp16 integers qh[rows][k], scales d[rows][nb] fp32.
-__global__ void k_quantize_q8_0_f16(const float *__restrict__ x, __half *__restrict__ qh, float *__restrict__ d, int rows, int nb, int ldx) {
+// Q8_0 values (bytes identical to quantize_row_q8_0) stored as fp16 integers, already in the shared-memory image the
+// GEMM wants: for every 128-row tile, 16-byte chunks of 8 consecutive k ordered [k chunk][row] -- so the A operand of
+// a pipeline stage (8 chunks x 128 rows) is ONE contiguous 16 KB range and moves with a single bulk copy.
+//   qt[((mt * K/8 + kc) * 128 + r) * 8 + e]   row = mt*128 + r, k = kc*8 + e;   dt[(mt * nb + b) * 128 + r] = d_x
+// Rows beyond `rows` in the last tile are written as zeros.
+__global__ void k_quantize_q8_0_f16_tiled(const float *__restrict__ x, __half *__restrict__ qt, float *__restrict__ dt, int rows, int rows_pad,
+                                          int nb, int ldx) {
     const int lane = threadIdx.x & 31;
     const long long wid = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-    if (wid >= (long long)rows * nb) return;
-    const int r = (int)(wid / nb), b = (int)(wid % nb);
-    const float v = x[(size_t)r * ldx + (size_t)b * QK + lane];
+    if (wid >= (long long)rows_pad * nb) return;
+    const int row = (int)(wid / nb), b = (int)(wid % nb);
+    const int mt = row >> 7, r = row & 127;
+    const float v = row < rows ? x[(size_t)row * ldx + (size_t)b * QK + lane] : 0.f;
     const float amax = warp_max(fabsf(v));
-    qh[((size_t)r * nb + b) * QK + lane] = __int2half_rn(q8_0_quant(v, amax));
-    if (lane == 0) d[(size_t)r * nb + b] = __half2float(q8_0_scale(amax));
+    const size_t kc = (size_t)b * 4 + (lane >> 3);
+    qt[(((size_t)mt * nb * 4 + kc) * 128 + r) * 8 + (lane & 7)] = __int2half_rn(q8_0_quant(v, amax));
+    if (lane == 0) dt[((size_t)mt * nb + b) * 128 + r] = __half2float(q8_0_scale(amax));
 }
 
 // 4 bytes holding values 0..15 -> two half2 (value - 8), exact: 0x6400 | v is the fp16 1024 + v
@@ -117,10 +125,11 @@ static __device__ __forceinline__ void nib4_to_h4(uint32_t x, uint32_t &h01, uin
 
 #define TC_SMEM_SCALES (TC_NS * TC_STAGE_BYTES)
 #define TC_SMEM_BARS (TC_SMEM_SCALES + 2 * TC_SR * 128 * 4)
-#define TC_SMEM_TOTAL (TC_SMEM_BARS + 256)
+#define TC_SMEM_WST (TC_SMEM_BARS + 256)          // raw weight staging: [2 groups][128 rows][144 bytes]
+#define TC_SMEM_TOTAL (TC_SMEM_WST + 2 * 128 * 144)
 
 __global__ void __launch_bounds__(TC_THREADS, 1)
-k_gemm_q4_0_tc(const uint8_t *__restrict__ W, const __half *__restrict__ qh, const float *__restrict__ dx, const float *__restrict__ bias,
+k_gemm_q4_0_tc(const uint8_t *__restrict__ W, const __half *__restrict__ qt, const float *__restrict__ dt, const float *__restrict__ bias,
                void *__restrict__ y, int M, int N, int K, int ldy, int out_f16) {
     extern __shared__ __align__(1024) uint8_t smem[];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -138,8 +147,8 @@ k_gemm_q4_0_tc(const uint8_t *__restrict__ W, const __half *__restrict__ qh, con
 
     if (warp == 0) {
         if (lane == 0) {
-            for (int s = 0; s < TC_NS; s++) { tc_mbar_init(FULL(s), 128); tc_mbar_init(EMPTY(s), 1); }
-            for (int s = 0; s < TC_ND; s++) { tc_mbar_init(DFULL(s), 1); tc_mbar_init(DFREE(s), 8); }
+            for (int s = 0; s < TC_NS; s++) { tc_mbar_init(FULL(s), 129); tc_mbar_init(EMPTY(s), 1); } // 128 loader rows + the A bulk copy
+            for (int s = 0; s < TC_ND; s++) { tc_mbar_init(DFULL(s), 1); tc_mbar_init(DFREE(s), TC_EPI_WARPS); }
             asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         }
         __syncwarp();
@@ -176,105 +185,120 @@ k_gemm_q4_0_tc(const uint8_t *__restrict__ W, const __half *__restrict__ qh, con
             }
         }
     } else if (warp <= 4) {
-        // ---------------- loaders: one operand row per thread
+        // ---------------- loaders: one weight row per thread; thread 0 also starts the A bulk copy of each stage
         const int r = tid - 32;
-        const int n = n0 + r, m = m0 + r;
-        const uint8_t *wrow = W + (size_t)n * rowb;
-        for (int c = 0; c < nchunks; c++) {
-            const int s = c % TC_NS;
-            tc_mbar_wait(EMPTY(s), (uint32_t)(((c / TC_NS) & 1) ^ 1));
-            uint8_t *sa = smem + (size_t)s * TC_STAGE_BYTES, *sb = sa + TC_OPER_BYTES;
-            // weights: 2 blocks = 36 bytes = 9 words (4-byte aligned because c * 36 and the row length are)
-            const uint32_t *wp = (const uint32_t *)(wrow + (size_t)c * (TC_KB * 18));
-            uint32_t w[9];
+        const int n = n0 + r;
+        const uint4 *wrow = (const uint4 *)(W + (size_t)n * rowb);
+        const __half *qtile = qt + (size_t)blockIdx.y * nb * 4 * 128 * 8;
+        const float *dtile = dt + (size_t)blockIdx.y * nb * 128;
+        const int ngroups = nb / 8; // 8 Q blocks = 144 bytes of a weight row = 9 aligned 16-byte loads
+        // raw weights go global -> shared with per-thread async copies one 8-block group ahead (each thread only ever
+        // reads back its own row, so no cross-thread synchronisation is needed)
+        uint8_t *wst = smem + TC_SMEM_WST + (size_t)r * 144;
+        auto fetch = [&](int g) {
+            const uint32_t dst = tc_smem_u32(wst + (size_t)(g & 1) * (128 * 144));
 #pragma unroll
-            for (int i = 0; i < 9; i++) w[i] = __ldg(wp + i);
-            uint32_t q[2][4];
-#pragma unroll
-            for (int j = 0; j < 4; j++) { q[0][j] = __byte_perm(w[j], w[j + 1], 0x5432); q[1][j] = w[5 + j]; }
-            const float d0 = __half2float(__ushort_as_half((unsigned short)(w[0] & 0xffffu)));
-            const float d1 = __half2float(__ushort_as_half((unsigned short)(w[4] >> 16)));
-#pragma unroll
-            for (int blk = 0; blk < 2; blk++) {
-                uint32_t lo[4], hi[4];
-#pragma unroll
-                for (int j = 0; j < 4; j++) { lo[j] = q[blk][j] & 0x0F0F0F0Fu; hi[j] = (q[blk][j] >> 4) & 0x0F0F0F0Fu; }
-                uint4 ch[4]; // elements 0-7, 8-15 (low nibbles of bytes 0-7, 8-15), 16-23, 24-31 (high nibbles)
-                nib4_to_h4(lo[0], ch[0].x, ch[0].y); nib4_to_h4(lo[1], ch[0].z, ch[0].w);
-                nib4_to_h4(lo[2], ch[1].x, ch[1].y); nib4_to_h4(lo[3], ch[1].z, ch[1].w);
-                nib4_to_h4(hi[0], ch[2].x, ch[2].y); nib4_to_h4(hi[1], ch[2].z, ch[2].w);
-                nib4_to_h4(hi[2], ch[3].x, ch[3].y); nib4_to_h4(hi[3], ch[3].z, ch[3].w);
-#pragma unroll
-                for (int kc = 0; kc < 4; kc++) *(uint4 *)(sb + ((size_t)(blk * 4 + kc) * TC_BN + r) * 16) = ch[kc];
-            }
-            const int b0 = c * TC_KB;
-            dwS[(b0 % TC_SR) * 128 + r] = d0;
-            dwS[((b0 + 1) % TC_SR) * 128 + r] = d1;
-            // activations: 64 fp16 integers = 8 chunks of 16 bytes
-            if (m < M) {
-                const uint4 *ap = (const uint4 *)(qh + (size_t)m * K + (size_t)c * (TC_KB * QK));
-#pragma unroll
-                for (int j = 0; j < 8; j++) *(uint4 *)(sa + ((size_t)j * TC_BM + r) * 16) = __ldg(ap + j);
-                dxS[(b0 % TC_SR) * 128 + r] = dx[(size_t)m * nb + b0];
-                dxS[((b0 + 1) % TC_SR) * 128 + r] = dx[(size_t)m * nb + b0 + 1];
+            for (int i = 0; i < 9; i++)
+                asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + 16u * i), "l"(wrow + (size_t)g * 9 + i) : "memory");
+            asm volatile("cp.async.commit_group;" ::: "memory");
+        };
+        fetch(0);
+        for (int g = 0; g < ngroups; g++) {
+            if (g + 1 < ngroups) {
+                fetch(g + 1);
+                asm volatile("cp.async.wait_group 1;" ::: "memory");
             } else {
-                const uint4 z = make_uint4(0, 0, 0, 0);
-#pragma unroll
-                for (int j = 0; j < 8; j++) *(uint4 *)(sa + ((size_t)j * TC_BM + r) * 16) = z;
-                dxS[(b0 % TC_SR) * 128 + r] = 0.f;
-                dxS[((b0 + 1) % TC_SR) * 128 + r] = 0.f;
+                asm volatile("cp.async.wait_group 0;" ::: "memory");
             }
-            asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); // generic-proxy stores -> visible to the tensor core
-            tc_mbar_arrive(FULL(s));
+            const uint32_t *cw = (const uint32_t *)(wst + (size_t)(g & 1) * (128 * 144));
+            float sxc[8];
+#pragma unroll
+            for (int i = 0; i < 8; i++) sxc[i] = dtile[(size_t)(g * 8 + i) * 128 + r];
+#pragma unroll
+            for (int cc = 0; cc < 4; cc++) {
+                const int c = g * 4 + cc, s = c % TC_NS, b0 = c * TC_KB;
+                tc_mbar_wait(EMPTY(s), (uint32_t)(((c / TC_NS) & 1) ^ 1));
+                uint8_t *sa = smem + (size_t)s * TC_STAGE_BYTES, *sb = sa + TC_OPER_BYTES;
+                if (r == 0) { // activations of this stage: one contiguous 16 KB image
+                    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(FULL(s)), "r"((uint32_t)TC_OPER_BYTES) : "memory");
+                    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(tc_smem_u32(sa)),
+                                 "l"(qtile + (size_t)c * (TC_KB * 4) * 128 * 8), "r"((uint32_t)TC_OPER_BYTES), "r"(FULL(s))
+                                 : "memory");
+                }
+                const float sx0 = sxc[2 * cc], sx1 = sxc[2 * cc + 1];
+                uint32_t w[9]; // 2 blocks = 36 bytes = 9 words
+#pragma unroll
+                for (int i = 0; i < 9; i++) w[i] = cw[9 * cc + i];
+                uint32_t q[2][4];
+#pragma unroll
+                for (int j = 0; j < 4; j++) { q[0][j] = __byte_perm(w[j], w[j + 1], 0x5432); q[1][j] = w[5 + j]; }
+                const float d0 = __half2float(__ushort_as_half((unsigned short)(w[0] & 0xffffu)));
+                const float d1 = __half2float(__ushort_as_half((unsigned short)(w[4] >> 16)));
+#pragma unroll
+                for (int blk = 0; blk < 2; blk++) {
+                    uint32_t lo[4], hi[4];
+#pragma unroll
+                    for (int j = 0; j < 4; j++) { lo[j] = q[blk][j] & 0x0F0F0F0Fu; hi[j] = (q[blk][j] >> 4) & 0x0F0F0F0Fu; }
+                    uint4 ch[4]; // elements 0-7, 8-15 (low nibbles of bytes 0-7, 8-15), 16-23, 24-31 (high nibbles)
+                    nib4_to_h4(lo[0], ch[0].x, ch[0].y); nib4_to_h4(lo[1], ch[0].z, ch[0].w);
+                    nib4_to_h4(lo[2], ch[1].x, ch[1].y); nib4_to_h4(lo[3], ch[1].z, ch[1].w);
+                    nib4_to_h4(hi[0], ch[2].x, ch[2].y); nib4_to_h4(hi[1], ch[2].z, ch[2].w);
+                    nib4_to_h4(hi[2], ch[3].x, ch[3].y); nib4_to_h4(hi[3], ch[3].z, ch[3].w);
+#pragma unroll
+                    for (int kc = 0; kc < 4; kc++) *(uint4 *)(sb + ((size_t)(blk * 4 + kc) * TC_BN + r) * 16) = ch[kc];
+                }
+                dwS[(b0 % TC_SR) * 128 + r] = d0;
+                dwS[((b0 + 1) % TC_SR) * 128 + r] = d1;
+                dxS[(b0 % TC_SR) * 128 + r] = sx0;
+                dxS[((b0 + 1) % TC_SR) * 128 + r] = sx1;
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); // generic-proxy stores -> visible to the tensor core
+                tc_mbar_arrive(FULL(s));
+            }
         }
     } else {
-        // ---------------- epilogue: TMEM lane quarter = warp % 4, 64 of the 128 columns per warp
-        const int q = warp & 3, hc = (warp - 5) >> 2;
+        // ---------------- epilogue: TMEM lane quarter = warp % 4, 32 of the 128 columns per warp
+        const int q = warp & 3, cq = (warp - 5) >> 2;
         const int r = 32 * q + lane, m = m0 + r;
-        float acc[64];
+        float2 acc[16]; // columns 2j, 2j+1 of this warp's 32
 #pragma unroll
-        for (int j = 0; j < 64; j++) acc[j] = 0.f;
+        for (int j = 0; j < 16; j++) acc[j] = make_float2(0.f, 0.f);
         for (int b = 0; b < nb; b++) {
             const int buf = b % TC_ND;
             tc_mbar_wait(DFULL(buf), (uint32_t)((b / TC_ND) & 1));
             tc_fence_after();
-            const uint32_t taddr = tmem_base + ((uint32_t)(32 * q) << 16) + (uint32_t)(buf * TC_BN + hc * 64);
-            uint32_t v0[32], v1[32];
-            tc_ld32(taddr, v0);
-            tc_ld32(taddr + 32, v1);
+            uint32_t v[32];
+            tc_ld32(tmem_base + ((uint32_t)(32 * q) << 16) + (uint32_t)(buf * TC_BN + cq * 32), v);
+            const float sx = dxS[(b % TC_SR) * 128 + r];
+            const float4 *dwp = (const float4 *)(dwS + (b % TC_SR) * 128 + cq * 32);
             tc_wait_ld();
             tc_fence_before();
             __syncwarp();
             if (lane == 0) tc_mbar_arrive(DFREE(buf)); // accumulator drained: the next block may overwrite it
-            const float sx = dxS[(b % TC_SR) * 128 + r];
-            const float4 *dwp = (const float4 *)(dwS + (b % TC_SR) * 128 + hc * 64);
+            const float2 sx2 = make_float2(sx, sx);
+            // packed fp32x2: one FMUL2 (d_w * d_x, rounded as the reference's product) + one FFMA2 per element pair
 #pragma unroll
             for (int j4 = 0; j4 < 8; j4++) {
                 const float4 wv = dwp[j4];
-                acc[4 * j4 + 0] = fmaf(__fmul_rn(wv.x, sx), __uint_as_float(v0[4 * j4 + 0]), acc[4 * j4 + 0]);
-                acc[4 * j4 + 1] = fmaf(__fmul_rn(wv.y, sx), __uint_as_float(v0[4 * j4 + 1]), acc[4 * j4 + 1]);
-                acc[4 * j4 + 2] = fmaf(__fmul_rn(wv.z, sx), __uint_as_float(v0[4 * j4 + 2]), acc[4 * j4 + 2]);
-                acc[4 * j4 + 3] = fmaf(__fmul_rn(wv.w, sx), __uint_as_float(v0[4 * j4 + 3]), acc[4 * j4 + 3]);
-            }
-#pragma unroll
-            for (int j4 = 0; j4 < 8; j4++) {
-                const float4 wv = dwp[8 + j4];
-                acc[32 + 4 * j4 + 0] = fmaf(__fmul_rn(wv.x, sx), __uint_as_float(v1[4 * j4 + 0]), acc[32 + 4 * j4 + 0]);
-                acc[32 + 4 * j4 + 1] = fmaf(__fmul_rn(wv.y, sx), __uint_as_float(v1[4 * j4 + 1]), acc[32 + 4 * j4 + 1]);
-                acc[32 + 4 * j4 + 2] = fmaf(__fmul_rn(wv.z, sx), __uint_as_float(v1[4 * j4 + 2]), acc[32 + 4 * j4 + 2]);
-                acc[32 + 4 * j4 + 3] = fmaf(__fmul_rn(wv.w, sx), __uint_as_float(v1[4 * j4 + 3]), acc[32 + 4 * j4 + 3]);
+                acc[2 * j4] = __ffma2_rn(__fmul2_rn(make_float2(wv.x, wv.y), sx2), make_float2(__uint_as_float(v[4 * j4]), __uint_as_float(v[4 * j4 + 1])), acc[2 * j4]);
+                acc[2 * j4 + 1] = __ffma2_rn(__fmul2_rn(make_float2(wv.z, wv.w), sx2), make_float2(__uint_as_float(v[4 * j4 + 2]), __uint_as_float(v[4 * j4 + 3])), acc[2 * j4 + 1]);
             }
         }
         if (m < M) {
-            const int nc = n0 + hc * 64;
+            const int nc = n0 + cq * 32;
             if (out_f16) {
                 __half *yp = (__half *)y + (size_t)m * ldy + nc;
 #pragma unroll
-                for (int j = 0; j < 64; j++) yp[j] = __float2half_rn(bias ? acc[j] + bias[nc + j] : acc[j]);
+                for (int j = 0; j < 16; j++) {
+                    yp[2 * j] = __float2half_rn(bias ? acc[j].x + bias[nc + 2 * j] : acc[j].x);
+                    yp[2 * j + 1] = __float2half_rn(bias ? acc[j].y + bias[nc + 2 * j + 1] : acc[j].y);
+                }
             } else {
                 float *yp = (float *)y + (size_t)m * ldy + nc;
 #pragma unroll
-                for (int j = 0; j < 64; j++) yp[j] = bias ? acc[j] + bias[nc + j] : acc[j];
+                for (int j = 0; j < 16; j++) {
+                    yp[2 * j] = bias ? acc[j].x + bias[nc + 2 * j] : acc[j].x;
+                    yp[2 * j + 1] = bias ? acc[j].y + bias[nc + 2 * j + 1] : acc[j].y;
+                }
             }
         }
     }
@@ -285,30 +309,33 @@ k_gemm_q4_0_tc(const uint8_t *__restrict__ W, const __half *__restrict__ qh, con
     }
 }
 
-// qh/dx scratch: rows x K fp16 + rows x K/32 fp32
+// scratch: tile-major fp16 activations (rows padded to 128) + tile-major scales
 size_t gemm_tc_workspace_bytes(int M, int K) {
-    return ((size_t)M * K * 2 + 255) / 256 * 256 + ((size_t)M * (K / QK) * 4 + 255) / 256 * 256;
+    const size_t mp = ((size_t)M + TC_BM - 1) / TC_BM * TC_BM;
+    return (mp * K * 2 + 255) / 256 * 256 + (mp * (K / QK) * 4 + 255) / 256 * 256;
 }
 bool gemm_tc_supported(int wtype, int M, int N, int K) {
     static int off = -1;
     if (off < 0) { const char *e = getenv("MLLMCU_NO_TC_GEMM"); off = (e && e[0] == '1') ? 1 : 0; }
-    return !off && wtype == 2 && M > 8 && N % TC_BN == 0 && K % (TC_KB * QK) == 0;
+    // K % 256: weight rows are read in 144-byte (8-block) groups that must start 16-byte aligned
+    return !off && wtype == 2 && M > 8 && N % TC_BN == 0 && K % 256 == 0;
 }
 int launch_gemm_q4_0_tc(const void *W, const float *x, int ldx, const float *bias, void *y, int M, int N, int K, int ldy, int out_f16,
                         void *ws, cudaStream_t st) {
-    __half *qh = (__half *)ws;
-    float *dx = (float *)((char *)ws + ((size_t)M * K * 2 + 255) / 256 * 256);
+    const int mp = (M + TC_BM - 1) / TC_BM * TC_BM;
+    __half *qt = (__half *)ws;
+    float *dt = (float *)((char *)ws + ((size_t)mp * K * 2 + 255) / 256 * 256);
     const int nb = K / QK;
-    const long long warps = (long long)M * nb;
-    k_quantize_q8_0_f16<<<(unsigned)((warps + 7) / 8), 256, 0, st>>>(x, qh, dx, M, nb, ldx);
+    const long long warps = (long long)mp * nb;
+    k_quantize_q8_0_f16_tiled<<<(unsigned)((warps + 7) / 8), 256, 0, st>>>(x, qt, dt, M, mp, nb, ldx);
     CU_LAUNCH_CHECK();
     static bool configured = false;
     if (!configured) {
         CU_TRY(cudaFuncSetAttribute(k_gemm_q4_0_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_TOTAL));
         configured = true;
     }
-    const dim3 grid(N / TC_BN, (M + TC_BM - 1) / TC_BM);
-    k_gemm_q4_0_tc<<<grid, TC_THREADS, TC_SMEM_TOTAL, st>>>((const uint8_t *)W, qh, dx, bias, y, M, N, K, ldy, out_f16);
+    const dim3 grid(N / TC_BN, mp / TC_BM);
+    k_gemm_q4_0_tc<<<grid, TC_THREADS, TC_SMEM_TOTAL, st>>>((const uint8_t *)W, qt, dt, bias, y, M, N, K, ldy, out_f16);
     CU_LAUNCH_CHECK();
     return 0;
 }
