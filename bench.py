@@ -11,6 +11,7 @@ A step = one request: clear the KV cache, prefill 512 synthetic tokens, then 256
 `--impl reference` times only the CPU arm.  N>1: one replica per GPU, no collective ("weak").
 """
 import argparse
+import faulthandler
 import json
 import os
 import subprocess
@@ -22,6 +23,7 @@ import numpy as np
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
+faulthandler.enable()  # a native crash leaves a Python traceback on stderr instead of a silent exit
 
 from mllm_b200 import mllm_file as mf  # noqa: E402
 
@@ -300,10 +302,16 @@ def gpu_arm(args, rank, world, local_rank):
         "decode_mode": model.decode_mode(), "gpu_launches": int(launches), "clocks": clocks, "roofline": roof,
     }
     if not args.no_cpu:
+        # the CPU arm is a reported baseline: it runs in its own process so that nothing it does (OpenMP runtime, a crash,
+        # a stall) can take the GPU line down
         try:
-            out["cpu_baseline"] = cpu_arm(cfg, path, args.cpu_prefill, args.cpu_decode)
-        except Exception as e:  # the CPU arm is a reported baseline; never let it take the GPU line down
-            out["cpu_baseline"] = {"error": str(e)}
+            r = subprocess.run([sys.executable, os.path.abspath(__file__), "--impl", "reference", "--steps", "1", "--warmup", "0",
+                                "--cpu-prefill", str(args.cpu_prefill), "--cpu-decode", str(args.cpu_decode)],
+                               capture_output=True, text=True, timeout=900, env=dict(os.environ, RANK="0", WORLD_SIZE="1", LOCAL_RANK="0"))
+            line = [l for l in r.stdout.splitlines() if l.startswith("{")][-1]
+            out["cpu_baseline"] = json.loads(line)["cpu_baseline"]
+        except Exception as e:
+            out["cpu_baseline"] = {"error": repr(e)[:300]}
     print(json.dumps(out), flush=True)
 
 

@@ -187,6 +187,11 @@ int mllmcu_decode_attn_nsplit(int B, int Hq);
 size_t mllmcu_decode_attn_workspace_bytes(int B, int Hq, int D);
 int mllmcu_decode_attn(const float *q, int ldq, const void *k, const void *v, float *o, int ldo, const int *ctl, int B, int Hq,
                        int Hkv, int D, long long kv_bstride, void *ws, size_t ws_bytes, int pdl, void *stream);
+/* the same with q_rope / k_rope / k_cache / v_cache fused in (full rotary only: rot_dim == D == tdim): qkv holds the raw
+ * q|k|v projection rows and is not modified; k (rotated) and v are appended in fp16 at cache row ctl[0] */
+int mllmcu_decode_attn_rope(int rope_type, const float *qkv, int ld, void *kcache, void *vcache, float *o, int ldo, const int *ctl,
+                            int B, int Hq, int Hkv, int D, const float *sin_t, const float *cos_t, int tdim, long long kv_bstride,
+                            int cache_limit, void *ws, size_t ws_bytes, int pdl, void *stream);
 /* greedy pick (Generate.cpp:46-53): ids_out[b] fp32 and, when tok_log != NULL, tok_log[ctl[0]*rows + b] (ctl[0] < log_rows) */
 int mllmcu_decode_argmax(const float *logits, int rows, int n, float *ids_out, int *tok_log, const int *ctl, int log_rows,
                          void *stream);

@@ -66,6 +66,7 @@ SYMBOLS = {
     "mllmcu_decode_attn_nsplit": (_i, [_i, _i]),
     "mllmcu_decode_attn_workspace_bytes": (_sz, [_i, _i, _i]),
     "mllmcu_decode_attn": (_i, [_vp, _i, _vp, _vp, _vp, _i, _vp, _i, _i, _i, _i, C.c_longlong, _vp, _sz, _i, _vp]),
+    "mllmcu_decode_attn_rope": (_i, [_i, _vp, _i, _vp, _vp, _vp, _i, _vp, _i, _i, _i, _i, _vp, _vp, _i, C.c_longlong, _i, _vp, _sz, _i, _vp]),
     "mllmcu_decode_argmax": (_i, [_vp, _i, _i, _vp, _vp, _vp, _i, _vp]),
     "mllmcu_decode_step_create": (_i, [_vp, _vp, _i, C.POINTER(_vp)]),
     "mllmcu_decode_step_launch": (_i, [_vp, _vp]),
@@ -290,6 +291,23 @@ def decode_attn(q, ldq, kcache, vcache, ctl, Hq, D, pdl=False):
     o = torch.empty((B, Hq * D), dtype=torch.float32, device=q.device)
     check(lib().mllmcu_decode_attn(_ptr(q), ldq, _ptr(kcache), _ptr(vcache), _ptr(o), Hq * D, _ptr(ctl), B, Hq, Hkv, D, kcache.stride(0),
                                    _ptr(ws), ws.numel(), int(pdl), _stream()), "decode_attn")
+    return o
+
+
+def decode_attn_rope(rope_type, qkv, kcache, vcache, ctl, Hq, D, sin_t, cos_t, pdl=False):
+    """Fused q/k RoPE + KV append + decode attention on raw q|k|v rows [B, (Hq+2Hkv)*D]. Returns [B, Hq*D]."""
+    import torch
+    B, Hkv = kcache.shape[0], kcache.shape[2]
+    need = lib().mllmcu_decode_attn_workspace_bytes(B, Hq, D)
+    key = (qkv.device.index, B, Hq, D)
+    ws = _attn_ws.get(key)
+    if ws is None:
+        ws = torch.zeros(need, dtype=torch.uint8, device=qkv.device)
+        _attn_ws[key] = ws
+    o = torch.empty((B, Hq * D), dtype=torch.float32, device=qkv.device)
+    check(lib().mllmcu_decode_attn_rope(rope_type, _ptr(qkv), qkv.stride(0), _ptr(kcache), _ptr(vcache), _ptr(o), Hq * D, _ptr(ctl), B, Hq, Hkv, D,
+                                        _ptr(sin_t), _ptr(cos_t), sin_t.shape[1], kcache.stride(0), kcache.shape[1], _ptr(ws), ws.numel(), int(pdl),
+                                        _stream()), "decode_attn_rope")
     return o
 
 

@@ -14,6 +14,7 @@
 //                     fp32 q, fp16 K/V) split over keys, partials merged by the last CTA to finish
 //   k_argmax (elementwise.cu) with token log: greedy pick (Generate.cpp:46-53)
 #include "common.cuh"
+#include <stdlib.h>
 
 static __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 static __device__ __forceinline__ void pdl_launch() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
@@ -131,11 +132,44 @@ static __device__ __forceinline__ void h8_to_f(const uint4 &u, float *f) {
     }
 }
 
+// Optional fused RoPE + KV append (ROPE = true, full rotary only): q/k/v are the raw q|k|v projection row(s);
+// q is rotated in registers, and the group that owns key `pos` (the token being decoded) rotates k, rounds k and v to
+// fp16 exactly as the cache stores them, uses those values, and -- for the first q head of each kv head -- appends
+// them to the cache.  Saves the separate rope/append launch; arithmetic identical to k_decode_rope_kv.
+struct RopeArgs {
+    int type, tdim, limit;
+    const float *sin_t, *cos_t;
+    const float *kv_src; // q|k|v rows (same row stride as q): k of kv head j at (Hq + j) * D, v at (Hq + Hkv + j) * D
+    __half *kc, *vc;     // writable cache bases
+};
+
+// rotate the 16 dims [sub*16, sub*16+16) of one head held by this lane; `x` raw values.  LPK lanes hold the head.
 template <int D>
+static __device__ __forceinline__ void rope16(float (&x)[16], int type, int sub, const float *sn, const float *cs) {
+    constexpr int LPK = D / 16;
+    if (type == 2) { // pairs (2i, 2i+1): both in this lane
+#pragma unroll
+        for (int i = 0; i < 16; i += 2) {
+            const float a = x[i], bb = x[i + 1];
+            x[i] = __fsub_rn(__fmul_rn(a, cs[i]), __fmul_rn(bb, sn[i]));
+            x[i + 1] = __fadd_rn(__fmul_rn(a, sn[i]), __fmul_rn(bb, cs[i]));
+        }
+    } else { // pairs (d, d + D/2): the partner lives LPK/2 lanes away
+        const bool upper = sub >= LPK / 2;
+#pragma unroll
+        for (int i = 0; i < 16; i++) {
+            const float other = __shfl_xor_sync(0xffffffffu, x[i], LPK / 2);
+            // lower half: a*cos - b*sin (a = own, b = partner); upper half: a*sin + b*cos (a = partner, b = own)
+            x[i] = upper ? __fadd_rn(__fmul_rn(other, sn[i]), __fmul_rn(x[i], cs[i])) : __fsub_rn(__fmul_rn(x[i], cs[i]), __fmul_rn(other, sn[i]));
+        }
+    }
+}
+
+template <int D, bool ROPE>
 __global__ void __launch_bounds__(128) k_attn_decode(const float *__restrict__ q, int ldq, const __half *__restrict__ k,
                                                      const __half *__restrict__ v, float *__restrict__ o, int ldo, float *__restrict__ ws,
                                                      unsigned *__restrict__ tickets, const int *__restrict__ ctl, int Hq, int Hkv,
-                                                     long long kvb, int nsplit) {
+                                                     long long kvb, int nsplit, const RopeArgs ra) {
     constexpr int LPK = D / 16, KPW = 32 / LPK;
     __shared__ float sm[4][D + 2];
     __shared__ int s_last;
@@ -144,7 +178,8 @@ __global__ void __launch_bounds__(128) k_attn_decode(const float *__restrict__ q
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int sp = blockIdx.x % nsplit, h = (blockIdx.x / nsplit) % Hq, b = blockIdx.x / (nsplit * Hq);
     const int kvh = h / (Hq / Hkv);
-    const int Sk = ctl[0] + 1;
+    const int pos = ctl[0];
+    const int Sk = pos + 1;
     const int chunk = (Sk + nsplit - 1) / nsplit;
     const int c_begin = sp * chunk, c_end = min(Sk, c_begin + chunk);
     const int g = lane / LPK, sub = lane % LPK;
@@ -156,6 +191,22 @@ __global__ void __launch_bounds__(128) k_attn_decode(const float *__restrict__ q
 #pragma unroll
         for (int i = 0; i < 4; i++) { const float4 t = qp[i]; qv[4 * i] = t.x; qv[4 * i + 1] = t.y; qv[4 * i + 2] = t.z; qv[4 * i + 3] = t.w; }
     }
+    // table row of this position for the lane's 16 dims (loaded where used: keeping 32 values live across the key loop costs occupancy)
+    auto load_sincos = [&](float (&sn)[16], float (&cs)[16]) {
+        const float4 *sp4 = (const float4 *)(ra.sin_t + (size_t)pos * ra.tdim + sub * 16), *cp4 = (const float4 *)(ra.cos_t + (size_t)pos * ra.tdim + sub * 16);
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+            const float4 a = sp4[i], c = cp4[i];
+            sn[4 * i] = a.x; sn[4 * i + 1] = a.y; sn[4 * i + 2] = a.z; sn[4 * i + 3] = a.w;
+            cs[4 * i] = c.x; cs[4 * i + 1] = c.y; cs[4 * i + 2] = c.z; cs[4 * i + 3] = c.w;
+        }
+    };
+    if (ROPE) {
+        if (pos < 0 || pos >= ra.limit) return; // the host refuses such a step; never touch memory outside the cache
+        float sn[16], cs[16];
+        load_sincos(sn, cs);
+        rope16<D>(qv, ra.type, sub, sn, cs);
+    }
 #pragma unroll
     for (int i = 0; i < 16; i++) acc[i] = 0.f;
     float m = -INFINITY, l = 0.f;
@@ -166,9 +217,40 @@ __global__ void __launch_bounds__(128) k_attn_decode(const float *__restrict__ q
     for (int c0 = c_begin + warp * KPW; c0 < c_end; c0 += 4 * KPW) { // warp-uniform trip count
         const int c = c0 + g;
         const bool ok = c < c_end;
-        const size_t off = (size_t)(ok ? c : c_begin) * rs;
-        const uint4 k0 = *(const uint4 *)(kb + off), k1 = *(const uint4 *)(kb + off + 8);
-        const uint4 v0 = *(const uint4 *)(vb + off), v1 = *(const uint4 *)(vb + off + 8);
+        const bool fresh = ROPE && ((c0 + KPW > pos) && (c0 <= pos)); // warp-uniform: this pass contains the new token's key
+        const size_t off = (size_t)((ok && !(ROPE && c == pos)) ? c : c_begin) * rs;
+        uint4 k0 = *(const uint4 *)(kb + off), k1 = *(const uint4 *)(kb + off + 8);
+        uint4 v0 = *(const uint4 *)(vb + off), v1 = *(const uint4 *)(vb + off + 8);
+        if (fresh) { // every lane takes part in the shuffles of rope16; only the owning group keeps the result
+            float kx[16], vx[16];
+            const float4 *kp = (const float4 *)(ra.kv_src + (size_t)b * ldq + (size_t)(Hq + kvh) * D + sub * 16);
+            const float4 *vp = (const float4 *)(ra.kv_src + (size_t)b * ldq + (size_t)(Hq + Hkv + kvh) * D + sub * 16);
+#pragma unroll
+            for (int i = 0; i < 4; i++) {
+                const float4 t = kp[i], u = vp[i];
+                kx[4 * i] = t.x; kx[4 * i + 1] = t.y; kx[4 * i + 2] = t.z; kx[4 * i + 3] = t.w;
+                vx[4 * i] = u.x; vx[4 * i + 1] = u.y; vx[4 * i + 2] = u.z; vx[4 * i + 3] = u.w;
+            }
+            {
+                float sn[16], cs[16];
+                load_sincos(sn, cs);
+                rope16<D>(kx, ra.type, sub, sn, cs);
+            }
+            if (ok && c == pos) {
+                __half2 *kh = (__half2 *)&k0, *kh1 = (__half2 *)&k1, *vh = (__half2 *)&v0, *vh1 = (__half2 *)&v1;
+#pragma unroll
+                for (int i = 0; i < 4; i++) {
+                    kh[i] = __floats2half2_rn(kx[2 * i], kx[2 * i + 1]); kh1[i] = __floats2half2_rn(kx[8 + 2 * i], kx[8 + 2 * i + 1]);
+                    vh[i] = __floats2half2_rn(vx[2 * i], vx[2 * i + 1]); vh1[i] = __floats2half2_rn(vx[8 + 2 * i], vx[8 + 2 * i + 1]);
+                }
+                if (h % (Hq / Hkv) == 0) { // one writer per kv head
+                    __half *kd = ra.kc + (size_t)b * kvb + (size_t)pos * rs + (size_t)kvh * D + sub * 16;
+                    __half *vd = ra.vc + (size_t)b * kvb + (size_t)pos * rs + (size_t)kvh * D + sub * 16;
+                    *(uint4 *)kd = k0; *(uint4 *)(kd + 8) = k1;
+                    *(uint4 *)vd = v0; *(uint4 *)(vd + 8) = v1;
+                }
+            }
+        }
         float kf[16], vf[16];
         h8_to_f(k0, kf); h8_to_f(k1, kf + 8);
         float s = 0.f;
@@ -259,8 +341,10 @@ __global__ void __launch_bounds__(128) k_attn_decode(const float *__restrict__ q
 }
 
 MLLMCU_API int mllmcu_decode_attn_nsplit(int B, int Hq) {
-    // ~2 CTAs of 4 warps per SM in one wave; a split of fewer than ~16 keys is not worth a CTA
-    int n = (2 * 148) / (B * Hq);
+    // ~2 CTAs of 4 warps per SM (swept on B200: 1x 1.70, 2x 1.66, 4x 1.82 ms per 7B decode step)
+    static int mult = 0;
+    if (mult == 0) { const char *e = getenv("MLLMCU_ATTN_SPLIT_MULT"); mult = (e && e[0]) ? atoi(e) : 2; if (mult < 1) mult = 1; }
+    int n = (mult * 148) / (B * Hq);
     if (n < 1) n = 1;
     if (n > 32) n = 32;
     return n;
@@ -270,9 +354,9 @@ MLLMCU_API size_t mllmcu_decode_attn_workspace_bytes(int B, int Hq, int D) {
     return rows * mllmcu_decode_attn_nsplit(B, Hq) * (D + 2) * sizeof(float) + rows * sizeof(unsigned) + 256;
 }
 
-template <int D>
+template <int D, bool ROPE>
 static int launch_attn_decode(const float *q, int ldq, const __half *k, const __half *v, float *o, int ldo, float *ws, unsigned *tickets,
-                              const int *ctl, int B, int Hq, int Hkv, long long kvb, int nsplit, int pdl, cudaStream_t st) {
+                              const int *ctl, int B, int Hq, int Hkv, long long kvb, int nsplit, const RopeArgs &ra, int pdl, cudaStream_t st) {
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)(B * Hq * nsplit));
     cfg.blockDim = dim3(128);
@@ -282,14 +366,12 @@ static int launch_attn_decode(const float *q, int ldq, const __half *k, const __
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
     cfg.numAttrs = pdl ? 1 : 0;
-    CU_TRY(cudaLaunchKernelEx(&cfg, k_attn_decode<D>, q, ldq, k, v, o, ldo, ws, tickets, ctl, Hq, Hkv, kvb, nsplit));
+    CU_TRY(cudaLaunchKernelEx(&cfg, k_attn_decode<D, ROPE>, q, ldq, k, v, o, ldo, ws, tickets, ctl, Hq, Hkv, kvb, nsplit, ra));
     return 0;
 }
 
-// q [B][ldq] fp32 (head h at h*D), o [B][ldo]; K/V fp16 at b*kv_bstride + s*Hkv*D + h*D; the KV length is ctl[0]+1.
-// ws: mllmcu_decode_attn_workspace_bytes, zero-initialised once (the ticket counters live at its end and reset themselves).
-MLLMCU_API int mllmcu_decode_attn(const float *q, int ldq, const void *k, const void *v, float *o, int ldo, const int *ctl, int B, int Hq,
-                                  int Hkv, int D, long long kv_bstride, void *ws, size_t ws_bytes, int pdl, void *stream) {
+static int decode_attn_common(const float *q, int ldq, const void *k, const void *v, float *o, int ldo, const int *ctl, int B, int Hq, int Hkv,
+                              int D, long long kv_bstride, void *ws, size_t ws_bytes, const RopeArgs *ra, int pdl, void *stream) {
     if (B <= 0 || Hq <= 0 || Hkv <= 0 || Hq % Hkv || (ldq & 3) || ((uintptr_t)q & 15) || ((uintptr_t)k & 15) || ((uintptr_t)v & 15)) return -1;
     if (D != 32 && D != 64 && D != 128) return -2;
     if ((kv_bstride & 7) || ((Hkv * D) & 7)) return -2;
@@ -298,9 +380,34 @@ MLLMCU_API int mllmcu_decode_attn(const float *q, int ldq, const void *k, const 
     float *wsf = (float *)ws;
     unsigned *tickets = (unsigned *)(wsf + (size_t)B * Hq * nsplit * (D + 2));
     cudaStream_t st = (cudaStream_t)stream;
-    if (D == 128) return launch_attn_decode<128>(q, ldq, (const __half *)k, (const __half *)v, o, ldo, wsf, tickets, ctl, B, Hq, Hkv, kv_bstride, nsplit, pdl, st);
-    if (D == 64) return launch_attn_decode<64>(q, ldq, (const __half *)k, (const __half *)v, o, ldo, wsf, tickets, ctl, B, Hq, Hkv, kv_bstride, nsplit, pdl, st);
-    return launch_attn_decode<32>(q, ldq, (const __half *)k, (const __half *)v, o, ldo, wsf, tickets, ctl, B, Hq, Hkv, kv_bstride, nsplit, pdl, st);
+    const __half *kh = (const __half *)k, *vh = (const __half *)v;
+    RopeArgs none = {};
+    if (ra) {
+        if (D == 128) return launch_attn_decode<128, true>(q, ldq, kh, vh, o, ldo, wsf, tickets, ctl, B, Hq, Hkv, kv_bstride, nsplit, *ra, pdl, st);
+        if (D == 64) return launch_attn_decode<64, true>(q, ldq, kh, vh, o, ldo, wsf, tickets, ctl, B, Hq, Hkv, kv_bstride, nsplit, *ra, pdl, st);
+        return launch_attn_decode<32, true>(q, ldq, kh, vh, o, ldo, wsf, tickets, ctl, B, Hq, Hkv, kv_bstride, nsplit, *ra, pdl, st);
+    }
+    if (D == 128) return launch_attn_decode<128, false>(q, ldq, kh, vh, o, ldo, wsf, tickets, ctl, B, Hq, Hkv, kv_bstride, nsplit, none, pdl, st);
+    if (D == 64) return launch_attn_decode<64, false>(q, ldq, kh, vh, o, ldo, wsf, tickets, ctl, B, Hq, Hkv, kv_bstride, nsplit, none, pdl, st);
+    return launch_attn_decode<32, false>(q, ldq, kh, vh, o, ldo, wsf, tickets, ctl, B, Hq, Hkv, kv_bstride, nsplit, none, pdl, st);
+}
+
+// q [B][ldq] fp32 (head h at h*D), o [B][ldo]; K/V fp16 at b*kv_bstride + s*Hkv*D + h*D; the KV length is ctl[0]+1.
+// ws: mllmcu_decode_attn_workspace_bytes, zero-initialised once (the ticket counters live at its end and reset themselves).
+MLLMCU_API int mllmcu_decode_attn(const float *q, int ldq, const void *k, const void *v, float *o, int ldo, const int *ctl, int B, int Hq,
+                                  int Hkv, int D, long long kv_bstride, void *ws, size_t ws_bytes, int pdl, void *stream) {
+    return decode_attn_common(q, ldq, k, v, o, ldo, ctl, B, Hq, Hkv, D, kv_bstride, ws, ws_bytes, nullptr, pdl, stream);
+}
+
+// Same with q_rope / k_rope / k_cache / v_cache fused in: qkv [B][ld] holds the RAW q|k|v projection rows; the kernel rotates q
+// in registers, rotates k, appends k and v (fp16) at cache row ctl[0] and attends over ctl[0]+1 keys.  Full rotary only
+// (rot_dim == D == tdim); qkv is not modified.
+MLLMCU_API int mllmcu_decode_attn_rope(int rope_type, const float *qkv, int ld, void *kcache, void *vcache, float *o, int ldo, const int *ctl,
+                                       int B, int Hq, int Hkv, int D, const float *sin_t, const float *cos_t, int tdim, long long kv_bstride,
+                                       int cache_limit, void *ws, size_t ws_bytes, int pdl, void *stream) {
+    if ((rope_type != 2 && rope_type != 4) || tdim != D || ((uintptr_t)sin_t & 15) || ((uintptr_t)cos_t & 15)) return -2;
+    RopeArgs ra = {rope_type, tdim, cache_limit, sin_t, cos_t, qkv, (__half *)kcache, (__half *)vcache};
+    return decode_attn_common(qkv, ld, kcache, vcache, o, ldo, ctl, B, Hq, Hkv, D, kv_bstride, ws, ws_bytes, &ra, pdl, stream);
 }
 
 // ------------------------------------------------------------------ greedy pick with token log

@@ -203,7 +203,7 @@ bool LlamaModel::decode_plan_usable(int B) {
         MLLMCU_CHECK(mllmcu_memset(p->ctl.rawDevPtr(), 0, 16, bn->stream()));
         p->use_graph = !env_on("MLLM_CUDA_NO_GRAPH");
         p->use_pdl = !env_on("MLLM_CUDA_NO_PDL");
-        p->launches = 3 + 6 * cfg_.layers;
+        p->launches = 3 + (p->layers[0].rope.rot_dim == D ? 5 : 6) * cfg_.layers;
         // the persistent whole-step kernel is opt-in: on B200 its grid barriers + in-order per-warp rings currently lose
         // to the PDL-chained persistent GEMVs (2.2 vs 1.7 ms/token on the 7B, profiles/r01_step_kernel_phases.txt)
         if ((env_on("MLLM_CUDA_STEP_KERNEL") || want_step_kernel_) && B <= 4) build_step_kernel(*p);
@@ -299,10 +299,17 @@ bool LlamaModel::issue_step(DecodePlan &p, bool pick, bool pdl_on) {
     }
     for (auto &l : p.layers) {
         if (!gemv({&l.q, &l.k, &l.v}, x, H, &l.n1, 0, nullptr, 0, qkv, QKV)) return false;
-        MLLMCU_CHECK(mllmcu_decode_rope_kv(l.rope.rope_type, qkv, QKV, B, Hq, Hkv, D, l.rope.rot_dim, l.rope.sin_t, l.rope.cos_t, l.rope.rot_dim, ctl,
-                                           l.kc.cache, l.vc.cache, l.kc.cache_bstride, l.kc.cache_limit, pdl, st));
-        MLLMCU_CHECK(mllmcu_decode_attn(qkv, QKV, l.kc.cache, l.vc.cache, ao, Hq * D, ctl, B, Hq, Hkv, D, l.kc.cache_bstride, p.attn_ws.rawDevPtr(),
-                                        p.attn_ws_bytes, pdl, st));
+        static const bool no_rope_fusion = env_on("MLLM_CUDA_NO_ROPE_FUSION");
+        if (l.rope.rot_dim == D && !no_rope_fusion) { // full rotary: RoPE and the KV append ride inside the attention kernel
+            MLLMCU_CHECK(mllmcu_decode_attn_rope(l.rope.rope_type, qkv, QKV, l.kc.cache, l.vc.cache, ao, Hq * D, ctl, B, Hq, Hkv, D, l.rope.sin_t,
+                                                 l.rope.cos_t, l.rope.rot_dim, l.kc.cache_bstride, l.kc.cache_limit, p.attn_ws.rawDevPtr(),
+                                                 p.attn_ws_bytes, pdl, st));
+        } else {
+            MLLMCU_CHECK(mllmcu_decode_rope_kv(l.rope.rope_type, qkv, QKV, B, Hq, Hkv, D, l.rope.rot_dim, l.rope.sin_t, l.rope.cos_t, l.rope.rot_dim,
+                                               ctl, l.kc.cache, l.vc.cache, l.kc.cache_bstride, l.kc.cache_limit, pdl, st));
+            MLLMCU_CHECK(mllmcu_decode_attn(qkv, QKV, l.kc.cache, l.vc.cache, ao, Hq * D, ctl, B, Hq, Hkv, D, l.kc.cache_bstride,
+                                            p.attn_ws.rawDevPtr(), p.attn_ws_bytes, pdl, st));
+        }
         if (!gemv({&l.o}, ao, Hq * D, nullptr, 1, x, H, x2, H)) return false;
         if (!gemv({&l.gate, &l.up}, x2, H, &l.n2, 2, nullptr, 0, g, F)) return false;
         if (!gemv({&l.down}, g, F, nullptr, 1, x2, H, x, H)) return false;

@@ -77,6 +77,38 @@ def test_decode_attention(cu, oracle, B, Sk, Hq, Hkv, D):
             assert np.abs(o[b].reshape(1, Hq, D) - want).max() <= 1e-5 * max(1.0, np.abs(want).max()), (rep, b)
 
 
+@pytest.mark.parametrize("rtype,B,Sk,Hq,Hkv,D", [(2, 1, 1, 4, 4, 64), (4, 1, 37, 8, 2, 64), (2, 1, 700, 32, 32, 128), (4, 2, 130, 4, 2, 128),
+                                                  (4, 1, 9, 2, 1, 32), (2, 3, 65, 8, 8, 128)])
+def test_decode_attention_with_fused_rope_and_append(cu, oracle, rtype, B, Sk, Hq, Hkv, D):
+    """mllmcu_decode_attn_rope == mllmcu_decode_rope_kv + mllmcu_decode_attn: same cache bytes (bit-exact), same output as the oracle."""
+    import torch
+    rng = np.random.default_rng(Sk * 3 + Hq + rtype)
+    limit, pos = Sk + 3, Sk - 1
+    s, c = oracle.only.rope_tables(rtype, limit, D, 10000.0)
+    qkv = rng.standard_normal((B, (Hq + 2 * Hkv) * D)).astype(np.float32)
+    k = rng.standard_normal((B, limit, Hkv, D)).astype(np.float16)
+    v = rng.standard_normal((B, limit, Hkv, D)).astype(np.float16)
+    k[:, pos:] = 0
+    v[:, pos:] = 0
+    ctl = torch.tensor([pos, 0, 0, 0], dtype=torch.int32, device="cuda")
+    # reference composition on the device
+    k1, v1, x1 = dev(k), dev(v), dev(qkv)
+    cu.decode_rope_kv(rtype, x1, Hq, Hkv, D, dev(s), dev(c), ctl, k1, v1)
+    o1 = cu.decode_attn(x1, x1.stride(0), k1, v1, ctl, Hq, D).cpu().numpy()
+    # fused
+    k2, v2, x2 = dev(k), dev(v), dev(qkv)
+    o2 = cu.decode_attn_rope(rtype, x2, k2, v2, ctl, Hq, D, dev(s), dev(c)).cpu().numpy()
+    assert np.array_equal(k1.cpu().numpy().view(np.uint16), k2.cpu().numpy().view(np.uint16))
+    assert np.array_equal(v1.cpu().numpy().view(np.uint16), v2.cpu().numpy().view(np.uint16))
+    assert np.array_equal(bits(x2.cpu().numpy()), bits(qkv))  # raw projection untouched
+    assert np.abs(o2 - o1).max() <= 2e-6 * max(1.0, np.abs(o1).max())
+    kc, vc = k1.cpu().numpy(), v1.cpu().numpy()
+    for b in range(B):
+        qr = oracle.only.rope_apply(rtype, qkv[b, :Hq * D].reshape(1, Hq, D), pos, s, c)
+        want = oracle.flash_attn_f16kv(qr, kc[b, :Sk].view(np.uint16), vc[b, :Sk].view(np.uint16))
+        assert np.abs(o2[b].reshape(1, Hq, D) - want).max() <= 1e-5 * max(1.0, np.abs(want).max())
+
+
 def test_decode_attention_golden(cu, golden):
     import torch
     q, k, v = golden["fa_dec_q"], golden["fa_dec_k"].view(np.float16), golden["fa_dec_v"].view(np.float16)
