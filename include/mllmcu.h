@@ -115,6 +115,39 @@ int mllmcu_gemv_fused(int wtype, const void *const *W, const int *Ns, const floa
                       int ldx, int M, int K, const float *norm_w, float eps, int epilogue, const float *residual, int ldr,
                       void *y, int ldy, int out_f16, int pdl, void *stream);
 
+/* mllmcu_gemv_fused described by a struct, with two extras for the chained decode step (neither changes results):
+ *  - replicas: the 148 CTAs of a launch all read the same activation row, which sits in a handful of L2 slices; when the
+ *    producer stores `y_reps` copies (element stride y_rep_stride) and the consumer is told `x_reps` / x_rep_stride, CTA c
+ *    reads copy c % x_reps and the L2 broadcast spreads over x_reps times more slices (same for the RMSNorm weight);
+ *  - L2 look-ahead: while the kernel streams its own weights it asks L2 to fetch n_pf (<= 8) byte ranges (16-byte aligned,
+ *    sizes multiples of 16) that LATER launches will stream, paced with its own row groups. */
+typedef struct mllmcu_gemv_desc {
+    int wtype, nW;
+    const void *W[3];
+    int N[3];
+    const float *bias[3];
+    const float *x;
+    int ldx, M, K;
+    const float *norm_w;
+    float eps;
+    int epilogue;
+    const float *residual;
+    int ldr;
+    void *y;
+    int ldy, out_f16, pdl;
+    int x_reps, norm_reps, y_reps;             /* 0 or 1: a single copy */
+    long long x_rep_stride, norm_rep_stride, y_rep_stride; /* elements between copies */
+    int n_pf;
+    const void *pf_ptr[8];
+    size_t pf_bytes[8];
+} mllmcu_gemv_desc;
+int mllmcu_gemv_fused_ex(const mllmcu_gemv_desc *d, void *stream);
+
+/* development aid (MLLMCU_GEMV_PROF=1): 64 %globaltimer slots {entry, dependency wait passed, prologue done, exit, 4 spare, then per warp w: [8+2w] activation
+ * loads landed, [9+2w] quantisation done} of CTA 0 for the
+ * last n mllmcu_gemv_fused launches, oldest first; returns the number of launches copied */
+int mllmcu_gemv_prof_read(unsigned long long *host_out, int n_launches);
+
 /* Self-test of the branch-free IEEE division used for Q8_0 scales inside the fused kernels: counts fp32 bit
  * patterns amax in [lo, hi] for which (127/amax, amax/127) differ from IEEE division.  *mismatch_dev (device,
  * zero-initialised by the caller) receives the count; 0 is the only acceptable answer. */

@@ -47,6 +47,8 @@ SYMBOLS = {
     "mllmcu_linear_workspace_bytes": (_sz, [_i, _i]),
     "mllmcu_linear": (_i, [_i, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _vp, _sz, _vp]),
     "mllmcu_gemv_fused": (_i, [_i, _vp, _vp, _vp, _i, _vp, _i, _i, _i, _vp, _f, _i, _vp, _i, _vp, _i, _i, _i, _vp]),
+    "mllmcu_gemv_fused_ex": (_i, [_vp, _vp]),
+    "mllmcu_gemv_prof_read": (_i, [_vp, _i]),
     "mllmcu_selftest_div": (_i, [C.c_uint32, C.c_uint32, _vp, _vp]),
     "mllmcu_rmsnorm": (_i, [_vp, _vp, _vp, _i, _i, _f, _i, _vp]),
     "mllmcu_layernorm": (_i, [_vp, _vp, _vp, _vp, _i, _i, _f, _vp]),
@@ -238,6 +240,40 @@ def argmax(logits):
     out = torch.empty((rows,), dtype=torch.int32, device=logits.device)
     check(lib().mllmcu_argmax(_ptr(logits), rows, n, _ptr(out), _stream()), "argmax")
     return out
+
+
+class GemvDesc(C.Structure):
+    """mllmcu_gemv_desc (include/mllmcu.h)"""
+    _fields_ = [("wtype", C.c_int), ("nW", C.c_int), ("W", C.c_void_p * 3), ("N", C.c_int * 3), ("bias", C.c_void_p * 3), ("x", C.c_void_p),
+                ("ldx", C.c_int), ("M", C.c_int), ("K", C.c_int), ("norm_w", C.c_void_p), ("eps", C.c_float), ("epilogue", C.c_int),
+                ("residual", C.c_void_p), ("ldr", C.c_int), ("y", C.c_void_p), ("ldy", C.c_int), ("out_f16", C.c_int), ("pdl", C.c_int),
+                ("x_reps", C.c_int), ("norm_reps", C.c_int), ("y_reps", C.c_int), ("x_rep_stride", C.c_longlong),
+                ("norm_rep_stride", C.c_longlong), ("y_rep_stride", C.c_longlong), ("n_pf", C.c_int), ("pf_ptr", C.c_void_p * 8),
+                ("pf_bytes", C.c_size_t * 8)]
+
+
+def gemv_fused_ex(Ws, x, y, norm_w=None, eps=1e-6, epilogue=0, residual=None, pdl=False, x_reps=1, norm_reps=1, y_reps=1, lookahead=()):
+    """Descriptor form of gemv_fused.  x: cuda fp32 [x_reps, M, K]; norm_w: [norm_reps, K]; y: preallocated [y_reps, M, N];
+    residual: [M, N] (copy 0); lookahead: (device pointer, bytes) pairs for the L2 look-ahead."""
+    d = GemvDesc()
+    d.wtype, d.nW = TYPE_Q4_0, len(Ws)
+    for i, w in enumerate(Ws):
+        d.W[i], d.N[i] = w.data_ptr(), w.shape[0]
+    M, K = x.shape[-2], x.shape[-1]
+    d.x, d.ldx, d.M, d.K = x.data_ptr(), K, M, K
+    if norm_w is not None:
+        d.norm_w, d.eps, d.norm_reps, d.norm_rep_stride = norm_w.data_ptr(), eps, norm_reps, K
+    d.epilogue = epilogue
+    if residual is not None:
+        d.residual, d.ldr = residual.data_ptr(), residual.stride(-2)
+    NT = y.shape[-1]
+    d.y, d.ldy, d.out_f16, d.pdl = y.data_ptr(), NT, int(y.element_size() == 2), int(pdl)
+    d.x_reps, d.x_rep_stride, d.y_reps, d.y_rep_stride = x_reps, M * K, y_reps, M * NT
+    d.n_pf = len(lookahead)
+    for i, (ptr, nbytes) in enumerate(lookahead):
+        d.pf_ptr[i], d.pf_bytes[i] = ptr, nbytes
+    check(lib().mllmcu_gemv_fused_ex(C.byref(d), _stream()), "gemv_fused_ex")
+    return y
 
 
 def gemv_fused(Ws, x, norm_w=None, eps=1e-6, biases=None, epilogue=0, residual=None, out_f16=False, pdl=False):

@@ -128,6 +128,8 @@ void LlamaModel::clear_kvcache() { // LLaMAModel::clear_kvcache (modeling_llama.
 }
 
 // ===================================================================== decode plan
+struct DecodeLookahead { const void *ptr[8]; size_t bytes[8]; int n = 0; };
+
 struct LlamaModel::DecodePlan {
     struct L {
         FuseInfo n1, n2, q, k, v, o, gate, up, down, rope, kc, vc;
@@ -137,6 +139,10 @@ struct LlamaModel::DecodePlan {
     vector<L> layers;
     FuseInfo embd, norm, head;
     Tensor x, x2, qkv, ao, g, logits, ids, ctl, tok_log, attn_ws;
+    // activation replicas: x, x2 and g are stored `reps` times ([reps][B][width]) by their producers and every RMSNorm weight is
+    // copied `reps` times ([norm][reps][H]), so the CTAs of the consuming Linear spread their reads over more L2 slices
+    int reps = 1;
+    Tensor norm_rep;
     size_t attn_ws_bytes = 0;
     int dev_pos = -2;          // value ctl[0] holds in stream order (-2: unknown)
     int ctl_host = 0;          // staging for the H2D of ctl[0]
@@ -145,6 +151,9 @@ struct LlamaModel::DecodePlan {
     bool unsupported = false, use_graph = true, use_pdl = true;
     int launches = 0;
     void *step = nullptr; // persistent whole-step kernel (mllmcu_decode_step_*), when the shapes fit it
+    // L2 look-ahead: the byte ranges of LATER launches' weights that fused Linear number i asks L2 to fetch while it runs
+    vector<DecodeLookahead> lookahead;
+    bool lookahead_built = false;
     ~DecodePlan() {
         for (void *g : graph) if (g) mllmcu_graph_destroy(g);
         if (step) mllmcu_decode_step_destroy(step);
@@ -192,9 +201,22 @@ bool LlamaModel::decode_plan_usable(int B) {
         if (!ok) return false; // caches not allocated yet (no prefill so far) or a dtype outside the fused kernels
         CUDABackend *bn = st_.backend;
         const int QKV = (cfg_.heads + 2 * cfg_.kv_heads) * D;
-        p->x = Tensor(B, 1, 1, H, bn); p->x2 = Tensor(B, 1, 1, H, bn);
+        {
+            const char *e = getenv("MLLM_CUDA_ACT_REPLICAS");
+            p->reps = (e && e[0]) ? atoi(e) : 1; // measured on B200: copies do not shorten the prologue loads (profiles/r01_gemv_timeline.txt)
+            if (p->reps < 1) p->reps = 1;
+            if (p->reps > 16) p->reps = 16;
+        }
+        const int R = p->reps;
+        p->x = Tensor(R, 1, B, H, bn); p->x2 = Tensor(R, 1, B, H, bn);
         p->qkv = Tensor(B, 1, 1, QKV, bn); p->ao = Tensor(B, 1, 1, cfg_.heads * D, bn);
-        p->g = Tensor(B, 1, 1, cfg_.ffn, bn); p->logits = Tensor(B, 1, 1, cfg_.vocab, bn);
+        p->g = Tensor(R, 1, B, cfg_.ffn, bn); p->logits = Tensor(B, 1, 1, cfg_.vocab, bn);
+        p->norm_rep = Tensor(2 * cfg_.layers + 1, 1, R, H, bn);
+        for (int i = 0; i <= 2 * cfg_.layers; i++) {
+            const FuseInfo &n = i == 2 * cfg_.layers ? p->norm : (i % 2 ? p->layers[i / 2].n2 : p->layers[i / 2].n1);
+            for (int r = 0; r < R; r++)
+                MLLMCU_CHECK(mllmcu_memcpy_d2d(p->norm_rep.devPtr<float>() + ((size_t)i * R + r) * H, n.norm_w, sizeof(float) * H, bn->stream()));
+        }
         p->ids = Tensor(B, 1, 1, 1, bn); p->ctl = Tensor(1, 1, 1, 4, bn);
         p->tok_log = Tensor(1, 1, cfg_.cache_limit + 1, B, bn);
         p->attn_ws_bytes = mllmcu_decode_attn_workspace_bytes(B, cfg_.heads, D);
@@ -271,6 +293,41 @@ void LlamaModel::build_step_kernel(DecodePlan &p) {
     MLLMCU_CHECK(rc);
 }
 
+// Weights are streamed in a fixed cyclic order (layer 0 q,k,v,o,gate,up,down ... lm_head, then layer 0 again for the next
+// token).  Launch i is told to pull into L2 the part of that stream between the previous launch's frontier and
+// `lead` bytes past the end of its own weights, so the next launches find their rows in L2 while HBM keeps streaming
+// through launch gaps and prologues.  MLLM_CUDA_L2_LEAD_MB sets the lead (default 0 = off: no measurable gain so far).
+static void build_lookahead(const vector<vector<std::pair<const void *, size_t>>> &own, size_t lead, vector<DecodeLookahead> &out) {
+    struct Seg { const uint8_t *p; size_t bytes, start; };
+    vector<Seg> segs;
+    vector<size_t> end_of; // stream offset where launch i's own weights end
+    size_t total = 0;
+    for (auto &launch : own) {
+        for (auto &w : launch) { segs.push_back({(const uint8_t *)w.first, w.second, total}); total += w.second; }
+        end_of.push_back(total);
+    }
+    out.assign(own.size(), DecodeLookahead());
+    if (lead == 0 || total == 0) return;
+    if (total < 4 * lead) lead = (total / 4) & ~(size_t)15; // toy models: never ask for more than a quarter of the stream
+    if (lead == 0) return;
+    size_t frontier = lead; // absolute position (not wrapped) the previous launch -- the last one of the previous token -- reached
+    size_t si = 0;          // segment holding `frontier % total`
+    for (size_t i = 0; i < own.size(); i++) {
+        const size_t target = end_of[i] + lead;
+        DecodeLookahead &la = out[i];
+        while (frontier < target && la.n < 8) {
+            const size_t pos = frontier % total;
+            while (!(segs[si].start <= pos && pos < segs[si].start + segs[si].bytes)) si = (si + 1) % segs.size();
+            const size_t off = pos - segs[si].start;
+            const size_t take = std::min(segs[si].bytes - off, target - frontier);
+            la.ptr[la.n] = segs[si].p + off;
+            la.bytes[la.n] = take;
+            la.n++;
+            frontier += take;
+        }
+    }
+}
+
 // the kernel sequence of one token; returns false if a fused kernel refuses the shape (rc == -2)
 bool LlamaModel::issue_step(DecodePlan &p, bool pick, bool pdl_on) {
     CUDABackend *bn = st_.backend;
@@ -279,12 +336,42 @@ bool LlamaModel::issue_step(DecodePlan &p, bool pick, bool pdl_on) {
     const int QKV = (Hq + 2 * Hkv) * D, pdl = pdl_on ? 1 : 0;
     int *ctl = p.ctl.devPtr<int>();
     float *x = p.x.devPtr<float>(), *x2 = p.x2.devPtr<float>(), *qkv = p.qkv.devPtr<float>(), *ao = p.ao.devPtr<float>(), *g = p.g.devPtr<float>();
-    auto gemv = [&](std::initializer_list<const FuseInfo *> ws, const float *in, int K, const FuseInfo *norm, int epi, const float *res, int ldr,
-                    float *out, int ldy) -> bool {
-        const void *W[3]; int N[3]; const float *bias[3]; int n = 0;
-        for (const FuseInfo *f : ws) { W[n] = f->weight; N[n] = f->out; bias[n] = f->bias; n++; }
-        const int rc = mllmcu_gemv_fused(MLLM_TYPE_Q4_0, W, N, bias, n, in, K, B, K, norm ? norm->norm_w : nullptr, norm ? norm->eps : 0.f, epi, res, ldr,
-                                         out, ldy, 0, pdl, st);
+    if (!p.lookahead_built) {
+        vector<vector<std::pair<const void *, size_t>>> own;
+        auto bytes_of = [](const FuseInfo &f) { return (size_t)f.out * (size_t)(f.in / 32) * 18; };
+        for (auto &l : p.layers) {
+            own.push_back({{l.q.weight, bytes_of(l.q)}, {l.k.weight, bytes_of(l.k)}, {l.v.weight, bytes_of(l.v)}});
+            own.push_back({{l.o.weight, bytes_of(l.o)}});
+            own.push_back({{l.gate.weight, bytes_of(l.gate)}, {l.up.weight, bytes_of(l.up)}});
+            own.push_back({{l.down.weight, bytes_of(l.down)}});
+        }
+        own.push_back({{p.head.weight, bytes_of(p.head)}});
+        const char *e = getenv("MLLM_CUDA_L2_LEAD_MB");
+        const size_t lead = (size_t)((e && e[0]) ? atoi(e) : 0) << 20; // off: within run-to-run noise on the 7B (profiles/r01_gemv_timeline.txt)
+        build_lookahead(own, lead, p.lookahead);
+        p.lookahead_built = true;
+    }
+    size_t launch_no = 0;
+    const int R = p.reps;
+    // in_reps / out_reps: how many copies of the input row exist and how many of the output row to store; norm_idx picks the
+    // replicated RMSNorm weight (2 * layer, 2 * layer + 1, or 2 * layers for the final norm)
+    auto gemv = [&](std::initializer_list<const FuseInfo *> ws, const float *in, int K, int in_reps, const FuseInfo *norm, int norm_idx, int epi,
+                    const float *res, int ldr, float *out, int ldy, int out_reps) -> bool {
+        mllmcu_gemv_desc d = {};
+        d.wtype = MLLM_TYPE_Q4_0;
+        for (const FuseInfo *f : ws) { d.W[d.nW] = f->weight; d.N[d.nW] = f->out; d.bias[d.nW] = f->bias; d.nW++; }
+        d.x = in; d.ldx = K; d.M = B; d.K = K;
+        if (norm) {
+            d.norm_w = p.norm_rep.devPtr<float>() + (size_t)norm_idx * R * H;
+            d.eps = norm->eps; d.norm_reps = R; d.norm_rep_stride = H;
+        }
+        d.epilogue = epi; d.residual = res; d.ldr = ldr; d.y = out; d.ldy = ldy; d.pdl = pdl;
+        d.x_reps = in_reps; d.x_rep_stride = (long long)B * K;
+        d.y_reps = out_reps; d.y_rep_stride = (long long)B * ldy;
+        const DecodeLookahead &la = p.lookahead[launch_no++];
+        d.n_pf = la.n;
+        for (int i = 0; i < la.n; i++) { d.pf_ptr[i] = la.ptr[i]; d.pf_bytes[i] = la.bytes[i]; }
+        const int rc = mllmcu_gemv_fused_ex(&d, st);
         if (rc == -2) return false;
         MLLMCU_CHECK(rc);
         return true;
@@ -298,7 +385,8 @@ bool LlamaModel::issue_step(DecodePlan &p, bool pick, bool pdl_on) {
         return true;
     }
     for (auto &l : p.layers) {
-        if (!gemv({&l.q, &l.k, &l.v}, x, H, &l.n1, 0, nullptr, 0, qkv, QKV)) return false;
+        const int li = (int)(&l - &p.layers[0]);
+        if (!gemv({&l.q, &l.k, &l.v}, x, H, li == 0 ? 1 : R, &l.n1, 2 * li, 0, nullptr, 0, qkv, QKV, 1)) return false; // the embedding wrote one copy
         static const bool no_rope_fusion = env_on("MLLM_CUDA_NO_ROPE_FUSION");
         if (l.rope.rot_dim == D && !no_rope_fusion) { // full rotary: RoPE and the KV append ride inside the attention kernel
             MLLMCU_CHECK(mllmcu_decode_attn_rope(l.rope.rope_type, qkv, QKV, l.kc.cache, l.vc.cache, ao, Hq * D, ctl, B, Hq, Hkv, D, l.rope.sin_t,
@@ -310,11 +398,11 @@ bool LlamaModel::issue_step(DecodePlan &p, bool pick, bool pdl_on) {
             MLLMCU_CHECK(mllmcu_decode_attn(qkv, QKV, l.kc.cache, l.vc.cache, ao, Hq * D, ctl, B, Hq, Hkv, D, l.kc.cache_bstride,
                                             p.attn_ws.rawDevPtr(), p.attn_ws_bytes, pdl, st));
         }
-        if (!gemv({&l.o}, ao, Hq * D, nullptr, 1, x, H, x2, H)) return false;
-        if (!gemv({&l.gate, &l.up}, x2, H, &l.n2, 2, nullptr, 0, g, F)) return false;
-        if (!gemv({&l.down}, g, F, nullptr, 1, x2, H, x, H)) return false;
+        if (!gemv({&l.o}, ao, Hq * D, 1, nullptr, 0, 1, x, H, x2, H, R)) return false;
+        if (!gemv({&l.gate, &l.up}, x2, H, R, &l.n2, 2 * li + 1, 2, nullptr, 0, g, F, R)) return false;
+        if (!gemv({&l.down}, g, F, R, nullptr, 0, 1, x2, H, x, H, R)) return false;
     }
-    if (!gemv({&p.head}, x, H, &p.norm, 0, nullptr, 0, p.logits.devPtr<float>(), cfg_.vocab)) return false;
+    if (!gemv({&p.head}, x, H, R, &p.norm, 2 * cfg_.layers, 0, nullptr, 0, p.logits.devPtr<float>(), cfg_.vocab, 1)) return false;
     if (pick)
         MLLMCU_CHECK(mllmcu_decode_argmax(p.logits.devPtr<float>(), B, cfg_.vocab, p.ids.devPtr<float>(), p.tok_log.devPtr<int>(), ctl,
                                           cfg_.cache_limit + 1, st));

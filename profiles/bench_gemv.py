@@ -7,7 +7,7 @@ import torch
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from mllm_b200 import capi  # noqa: E402
 
-SHAPES = [("o/q 4096x4096", [4096], 4096, 0), ("qkv 3x4096x4096", [4096] * 3, 4096, 0), ("gate+up 2x11008x4096", [11008] * 2, 4096, 2),
+SHAPES = [("floor 296x4096 (1 row pair per SM)", [296], 4096, 0), ("o/q 4096x4096", [4096], 4096, 0), ("qkv 3x4096x4096", [4096] * 3, 4096, 0), ("gate+up 2x11008x4096", [11008] * 2, 4096, 2),
           ("down 4096x11008", [4096], 11008, 1), ("lm_head 32000x4096", [32000], 4096, 0)]
 
 

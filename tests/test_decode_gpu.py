@@ -223,3 +223,29 @@ def test_fused_step_cache_limit_is_an_error(be, tmp_path_factory):
     with pytest.raises(be.BackendError, match="cache limit"):
         gpu.forward(np.array([[1.0]], dtype=np.float32))
     gpu.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("M,reps", [(1, 4), (2, 3)])
+def test_gemv_descriptor_replicas_and_lookahead_do_not_change_results(cu, oracle, M, reps):
+    """mllmcu_gemv_fused_ex: reading one of `reps` copies of the input / norm weight, storing `reps` copies of the output and
+    prefetching other weights into L2 must give the bits of the plain mllmcu_gemv_fused launch."""
+    import torch
+    capi = cu
+    torch.manual_seed(5)
+    K, N = 512, 384
+    Wq = [dev(oracle.quantize_q4_0(np.random.default_rng(i).standard_normal((N, K)).astype(np.float32))) for i in range(2)]
+    other = torch.randint(0, 255, (1 << 20,), dtype=torch.uint8, device="cuda")
+    x = torch.randn((M, K), device="cuda")
+    nw = torch.rand(K, device="cuda") + 0.5
+    res = torch.randn((M, N), device="cuda")
+    xr = x.unsqueeze(0).repeat(reps, 1, 1).contiguous()
+    nwr = nw.unsqueeze(0).repeat(reps, 1).contiguous()
+    la = [(other.data_ptr(), 65536), (other.data_ptr() + 131072, 4096 * 3 + 48)]
+    for kw, nWs in ((dict(epilogue=0), 2), (dict(epilogue=1, residual=res), 1), (dict(epilogue=2), 2)):
+        ref = capi.gemv_fused(Wq[:nWs], x, norm_w=nw, **kw)
+        y = torch.full((reps, M, ref.shape[1]), float("nan"), device="cuda")
+        capi.gemv_fused_ex(Wq[:nWs], xr, y, norm_w=nwr, x_reps=reps, norm_reps=reps, y_reps=reps, lookahead=la, **kw)
+        torch.cuda.synchronize()
+        for r in range(reps):
+            assert torch.equal(y[r], ref), (kw, r)
