@@ -119,6 +119,9 @@ int mllmcu_gemv_fused(int wtype, const void *const *W, const int *Ns, const floa
  *  - replicas: the 148 CTAs of a launch all read the same activation row, which sits in a handful of L2 slices; when the
  *    producer stores `y_reps` copies (element stride y_rep_stride) and the consumer is told `x_reps` / x_rep_stride, CTA c
  *    reads copy c % x_reps and the L2 broadcast spreads over x_reps times more slices (same for the RMSNorm weight);
+ *  - pdl == 2: like pdl == 1, but the kernel lets its dependents start only after its OWN dependency wait has passed, so
+ *    everything launched behind it may assume that whatever ran before it (the embedding kernel bumping the position
+ *    counter) is complete even ahead of their own waits;
  *  - L2 look-ahead: while the kernel streams its own weights it asks L2 to fetch n_pf (<= 8) byte ranges (16-byte aligned,
  *    sizes multiples of 16) that LATER launches will stream, paced with its own row groups. */
 typedef struct mllmcu_gemv_desc {
@@ -147,6 +150,10 @@ int mllmcu_gemv_fused_ex(const mllmcu_gemv_desc *d, void *stream);
  * loads landed, [9+2w] quantisation done} of CTA 0 for the
  * last n mllmcu_gemv_fused launches, oldest first; returns the number of launches copied */
 int mllmcu_gemv_prof_read(unsigned long long *host_out, int n_launches);
+
+/* development aid (MLLMCU_ATTN_PROF=1): 8 %globaltimer slots per mllmcu_decode_attn_rope launch, oldest first: CTA 0 {entry,
+ * dependency wait passed, q rotated, key loop done, partial stored, ticket taken}, merging CTA of row 0 {merge start, output stored} */
+int mllmcu_decode_attn_prof_read(unsigned long long *host_out, int n_launches);
 
 /* Self-test of the branch-free IEEE division used for Q8_0 scales inside the fused kernels: counts fp32 bit
  * patterns amax in [lo, hi] for which (127/amax, amax/127) differ from IEEE division.  *mismatch_dev (device,

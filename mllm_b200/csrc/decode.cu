@@ -113,7 +113,7 @@ MLLMCU_API int mllmcu_decode_rope_kv(int rope_type, float *qkv, int ld, int B, i
 }
 
 // ------------------------------------------------------------------ decode attention
-// One CTA (4 warps) per (batch row, q head, key split).  Inside a warp a group of LPK = D/16 lanes
+// One CTA (ATTN_WARPS warps) per (batch row, q head, key split).  Inside a warp a group of LPK = D/16 lanes
 // owns one key: each lane holds 16 of the D dims (two 16-byte fp16 loads per K row and per V row),
 // the score is a 16-FMA partial + log2(LPK) shuffles, and every group runs its own online softmax
 // (m, l, acc[16]) so nothing in the key loop is warp-wide.  Groups are merged by shuffles, warps
@@ -141,7 +141,22 @@ struct RopeArgs {
     const float *sin_t, *cos_t;
     const float *kv_src; // q|k|v rows (same row stride as q): k of kv head j at (Hq + j) * D, v at (Hq + Hkv + j) * D
     __half *kc, *vc;     // writable cache bases
+    unsigned long long *prof; // development aid (MLLMCU_ATTN_PROF=1): 8 %globaltimer slots per launch
+    int early;                // ctl[0] is final before the dependency resolves: position, K/V rows and the table row are read ahead of the wait
 };
+
+// ---- thread-block cluster helpers: the key splits of one (row, head) form a cluster and merge through rank 0's shared memory
+static __device__ __forceinline__ uint32_t smem_addr_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+static __device__ __forceinline__ uint32_t cluster_map_rank(uint32_t saddr, uint32_t rank) {
+    uint32_t r;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(saddr), "r"(rank));
+    return r;
+}
+static __device__ __forceinline__ void cluster_st_f32(uint32_t addr, float v) { asm volatile("st.shared::cluster.f32 [%0], %1;" ::"r"(addr), "f"(v) : "memory"); }
+static __device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
 
 // rotate the 16 dims [sub*16, sub*16+16) of one head held by this lane; `x` raw values.  LPK lanes hold the head.
 template <int D>
@@ -165,33 +180,67 @@ static __device__ __forceinline__ void rope16(float (&x)[16], int type, int sub,
     }
 }
 
-template <int D, bool ROPE>
-__global__ void __launch_bounds__(128) k_attn_decode(const float *__restrict__ q, int ldq, const __half *__restrict__ k,
-                                                     const __half *__restrict__ v, float *__restrict__ o, int ldo, float *__restrict__ ws,
-                                                     unsigned *__restrict__ tickets, const int *__restrict__ ctl, int Hq, int Hkv,
-                                                     long long kvb, int nsplit, const RopeArgs ra) {
-    constexpr int LPK = D / 16, KPW = 32 / LPK;
-    __shared__ float sm[4][D + 2];
+#define ATTN_PROF_RING 4096
+static unsigned long long *g_attn_prof = nullptr;
+static int g_attn_prof_on = -1, g_attn_prof_n = 0;
+#define ATTN_WARPS 4 // warps per CTA: 128 threads x <= 200 registers sit beside a resident Linear CTA (512 x 64) on the same SM
+#define ATTN_NB 6    // key passes whose K/V loads are in flight together (registers: 4 x uint4 per pass): 96 keys per CTA before any refill
+#define ATTN_MAXS 16 // splits merged from registers in one L2 round trip (more: a second pass over the workspace)
+
+template <int D, bool ROPE, bool CLUSTER>
+__global__ void __launch_bounds__(ATTN_WARPS * 32) k_attn_decode(const float *__restrict__ q, int ldq, const __half *__restrict__ k,
+                                                                const __half *__restrict__ v, float *__restrict__ o, int ldo, float *__restrict__ ws,
+                                                                unsigned *__restrict__ tickets, const int *__restrict__ ctl, int Hq, int Hkv,
+                                                                long long kvb, int nsplit, const RopeArgs ra) {
+    constexpr int LPK = D / 16, KPW = 32 / LPK, NW = ATTN_WARPS, KPP = NW * KPW, NB = ATTN_NB;
+    __shared__ float sm[NW][D + 2];
     __shared__ int s_last;
-    pdl_wait();
-    pdl_launch();
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int sp = blockIdx.x % nsplit, h = (blockIdx.x / nsplit) % Hq, b = blockIdx.x / (nsplit * Hq);
     const int kvh = h / (Hq / Hkv);
-    const int pos = ctl[0];
-    const int Sk = pos + 1;
-    const int chunk = (Sk + nsplit - 1) / nsplit;
-    const int c_begin = sp * chunk, c_end = min(Sk, c_begin + chunk);
+    const size_t rs = (size_t)Hkv * D;
+#define ATTN_STAMP(k) do { if (ROPE && ra.prof && blockIdx.x == 0 && tid == 0) { unsigned long long t_; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t_)); ra.prof[k] = t_; } } while (0)
+    ATTN_STAMP(0);
+    pdl_launch();
     const int g = lane / LPK, sub = lane % LPK;
     const float scale = __fdiv_rn(1.0f, __fsqrt_rn((float)D));
-
-    float qv[16], acc[16];
-    {
-        const float4 *qp = (const float4 *)(q + (size_t)b * ldq + (size_t)h * D + sub * 16);
+    const __half *kb = k + (size_t)b * kvb + (size_t)kvh * D + sub * 16;
+    const __half *vb = v + (size_t)b * kvb + (size_t)kvh * D + sub * 16;
+    const bool early = ROPE && ra.early; // kernel-uniform
+    // [c_begin, c_end): this split's keys; [c_begin, e_end): those already in the cache (with ROPE the last key, `pos`, is the
+    // token being decoded: it is rotated and appended by warp 0 of the split that owns it, apart from the cached keys)
+    int pos = 0, c_begin = 0, c_end = 0, e_end = 0;
+    auto take_pos = [&]() {
+        pos = ctl[0];
+        const int Sk = pos + 1, chunk = (Sk + nsplit - 1) / nsplit;
+        c_begin = sp * chunk;
+        c_end = min(Sk, c_begin + chunk);
+        e_end = ROPE ? min(c_end, pos) : c_end;
+    };
+    // K/V rows of NB passes are in flight together; lanes past the end read the split's first row (finite values, masked later)
+    uint4 kk[NB][2], vv[NB][2];
 #pragma unroll
-        for (int i = 0; i < 4; i++) { const float4 t = qp[i]; qv[4 * i] = t.x; qv[4 * i + 1] = t.y; qv[4 * i + 2] = t.z; qv[4 * i + 3] = t.w; }
-    }
-    // table row of this position for the lane's 16 dims (loaded where used: keeping 32 values live across the key loop costs occupancy)
+    for (int j = 0; j < NB; j++) kk[j][0] = kk[j][1] = vv[j][0] = vv[j][1] = make_uint4(0u, 0u, 0u, 0u);
+    auto load_k = [&](int j, int c0) {
+        const int c = c0 + g;
+        const size_t off = (size_t)(c < e_end ? c : c_begin) * rs;
+        kk[j][0] = *(const uint4 *)(kb + off); kk[j][1] = *(const uint4 *)(kb + off + 8);
+    };
+    auto load_v = [&](int j, int c0) {
+        const int c = c0 + g;
+        const size_t off = (size_t)(c < e_end ? c : c_begin) * rs;
+        vv[j][0] = *(const uint4 *)(vb + off); vv[j][1] = *(const uint4 *)(vb + off + 8);
+    };
+    auto issue_loads = [&](int cb0) {
+#pragma unroll
+        for (int j = 0; j < NB; j++) {
+            const int c0 = cb0 + j * KPP;
+            if (c0 >= e_end) break; // warp-uniform
+            load_k(j, c0);
+            load_v(j, c0);
+        }
+    };
+    // table row of this position for the lane's 16 dims (shared by q and the new key)
     auto load_sincos = [&](float (&sn)[16], float (&cs)[16]) {
         const float4 *sp4 = (const float4 *)(ra.sin_t + (size_t)pos * ra.tdim + sub * 16), *cp4 = (const float4 *)(ra.cos_t + (size_t)pos * ra.tdim + sub * 16);
 #pragma unroll
@@ -201,74 +250,153 @@ __global__ void __launch_bounds__(128) k_attn_decode(const float *__restrict__ q
             cs[4 * i] = c.x; cs[4 * i + 1] = c.y; cs[4 * i + 2] = c.z; cs[4 * i + 3] = c.w;
         }
     };
-    if (ROPE) {
-        if (pos < 0 || pos >= ra.limit) return; // the host refuses such a step; never touch memory outside the cache
-        float sn[16], cs[16];
-        load_sincos(sn, cs);
-        rope16<D>(qv, ra.type, sub, sn, cs);
+    float qsn[16], qcs[16];
+    bool bad_pos = false;
+    if (early) {
+        // The caller guarantees ctl[0] is final (an earlier kernel of the chain triggered its dependents only after ITS wait), and
+        // the cache rows of earlier tokens were complete before this step began: position, K/V rows and the table row are all
+        // read while the q|k|v projection in front is still running.
+        take_pos();
+        bad_pos = pos < 0 || pos >= ra.limit;
+        if (!bad_pos) {
+            issue_loads(c_begin + warp * KPW);
+            load_sincos(qsn, qcs);
+            for (int c = c_begin + NB * KPP + tid; c < e_end; c += NW * 32) { // keys beyond the register window: into L2
+                const __half *kr = k + (size_t)b * kvb + (size_t)c * rs + (size_t)kvh * D, *vr = v + (size_t)b * kvb + (size_t)c * rs + (size_t)kvh * D;
+                asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(kr), "r"(D * 2) : "memory");
+                asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(vr), "r"(D * 2) : "memory");
+            }
+        }
+    } else if (ROPE) {
+        // ctl[0] may still be the previous token's position while the embedding kernel of this step is in flight: only ask L2
+        // for this CTA's slice of the cache (a slice that is off by one key prefetches a neighbour row, nothing more)
+        const int p0 = min(max(ctl[0], 0), ra.limit - 1);
+        const int ch0 = (p0 + nsplit) / nsplit, cb = sp * ch0, ce = min(p0, cb + ch0);
+        for (int c = cb + tid; c < ce; c += NW * 32) {
+            const __half *kr = k + (size_t)b * kvb + (size_t)c * rs + (size_t)kvh * D, *vr = v + (size_t)b * kvb + (size_t)c * rs + (size_t)kvh * D;
+            asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(kr), "r"(D * 2) : "memory");
+            asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(vr), "r"(D * 2) : "memory");
+        }
     }
+    pdl_wait();
+    ATTN_STAMP(1);
+    if (!early) {
+        take_pos();
+        bad_pos = ROPE && (pos < 0 || pos >= ra.limit);
+    }
+    if (bad_pos) { // the host refuses such a step; never touch memory outside the cache (uniform over the grid)
+        if (CLUSTER) cluster_sync_all();
+        return;
+    }
+    const int first = c_begin + warp * KPW;
+    if (!early) {
+        issue_loads(first);
+        if (ROPE) load_sincos(qsn, qcs);
+    }
+
+    float qv[16], acc[16];
+    {
+        const float4 *qp = (const float4 *)(q + (size_t)b * ldq + (size_t)h * D + sub * 16);
+#pragma unroll
+        for (int i = 0; i < 4; i++) { const float4 t = qp[i]; qv[4 * i] = t.x; qv[4 * i + 1] = t.y; qv[4 * i + 2] = t.z; qv[4 * i + 3] = t.w; }
+    }
+    // the raw k and v of the new token, fetched together with q by the one warp that will need them
+    const bool fresh = ROPE && warp == 0 && pos >= c_begin && pos < c_end; // warp-uniform
+    float kx[16], vx[16];
+    if (fresh) {
+        const float4 *kp = (const float4 *)(ra.kv_src + (size_t)b * ldq + (size_t)(Hq + kvh) * D + sub * 16);
+        const float4 *vp = (const float4 *)(ra.kv_src + (size_t)b * ldq + (size_t)(Hq + Hkv + kvh) * D + sub * 16);
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+            const float4 t = kp[i], u = vp[i];
+            kx[4 * i] = t.x; kx[4 * i + 1] = t.y; kx[4 * i + 2] = t.z; kx[4 * i + 3] = t.w;
+            vx[4 * i] = u.x; vx[4 * i + 1] = u.y; vx[4 * i + 2] = u.z; vx[4 * i + 3] = u.w;
+        }
+    }
+    if (ROPE) rope16<D>(qv, ra.type, sub, qsn, qcs);
 #pragma unroll
     for (int i = 0; i < 16; i++) acc[i] = 0.f;
     float m = -INFINITY, l = 0.f;
-    const size_t rs = (size_t)Hkv * D;
-    const __half *kb = k + (size_t)b * kvb + (size_t)kvh * D + sub * 16;
-    const __half *vb = v + (size_t)b * kvb + (size_t)kvh * D + sub * 16;
-#pragma unroll 2
-    for (int c0 = c_begin + warp * KPW; c0 < c_end; c0 += 4 * KPW) { // warp-uniform trip count
-        const int c = c0 + g;
-        const bool ok = c < c_end;
-        const bool fresh = ROPE && ((c0 + KPW > pos) && (c0 <= pos)); // warp-uniform: this pass contains the new token's key
-        const size_t off = (size_t)((ok && !(ROPE && c == pos)) ? c : c_begin) * rs;
-        uint4 k0 = *(const uint4 *)(kb + off), k1 = *(const uint4 *)(kb + off + 8);
-        uint4 v0 = *(const uint4 *)(vb + off), v1 = *(const uint4 *)(vb + off + 8);
-        if (fresh) { // every lane takes part in the shuffles of rope16; only the owning group keeps the result
-            float kx[16], vx[16];
-            const float4 *kp = (const float4 *)(ra.kv_src + (size_t)b * ldq + (size_t)(Hq + kvh) * D + sub * 16);
-            const float4 *vp = (const float4 *)(ra.kv_src + (size_t)b * ldq + (size_t)(Hq + Hkv + kvh) * D + sub * 16);
+    if (ROPE && ra.prof && blockIdx.x == 0 && tid == 0) { unsigned long long t_; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t_)); ra.prof[2] = t_ + (qv[0] == 1.2345e-30f ? 1 : 0); }
+    if (fresh) {
+        // every group of the warp rotates the key (the shuffles of rope16 need whole groups); group 0 keeps it as its first key.
+        // k and v are rounded to fp16 exactly as the cache stores them, and appended by the first q head of each kv head.
+        rope16<D>(kx, ra.type, sub, qsn, qcs);
+        uint4 k0, k1, v0, v1;
+        __half2 *kh = (__half2 *)&k0, *kh1 = (__half2 *)&k1, *vh = (__half2 *)&v0, *vh1 = (__half2 *)&v1;
 #pragma unroll
-            for (int i = 0; i < 4; i++) {
-                const float4 t = kp[i], u = vp[i];
-                kx[4 * i] = t.x; kx[4 * i + 1] = t.y; kx[4 * i + 2] = t.z; kx[4 * i + 3] = t.w;
-                vx[4 * i] = u.x; vx[4 * i + 1] = u.y; vx[4 * i + 2] = u.z; vx[4 * i + 3] = u.w;
-            }
-            {
-                float sn[16], cs[16];
-                load_sincos(sn, cs);
-                rope16<D>(kx, ra.type, sub, sn, cs);
-            }
-            if (ok && c == pos) {
-                __half2 *kh = (__half2 *)&k0, *kh1 = (__half2 *)&k1, *vh = (__half2 *)&v0, *vh1 = (__half2 *)&v1;
-#pragma unroll
-                for (int i = 0; i < 4; i++) {
-                    kh[i] = __floats2half2_rn(kx[2 * i], kx[2 * i + 1]); kh1[i] = __floats2half2_rn(kx[8 + 2 * i], kx[8 + 2 * i + 1]);
-                    vh[i] = __floats2half2_rn(vx[2 * i], vx[2 * i + 1]); vh1[i] = __floats2half2_rn(vx[8 + 2 * i], vx[8 + 2 * i + 1]);
-                }
-                if (h % (Hq / Hkv) == 0) { // one writer per kv head
-                    __half *kd = ra.kc + (size_t)b * kvb + (size_t)pos * rs + (size_t)kvh * D + sub * 16;
-                    __half *vd = ra.vc + (size_t)b * kvb + (size_t)pos * rs + (size_t)kvh * D + sub * 16;
-                    *(uint4 *)kd = k0; *(uint4 *)(kd + 8) = k1;
-                    *(uint4 *)vd = v0; *(uint4 *)(vd + 8) = v1;
-                }
-            }
+        for (int i = 0; i < 4; i++) {
+            kh[i] = __floats2half2_rn(kx[2 * i], kx[2 * i + 1]); kh1[i] = __floats2half2_rn(kx[8 + 2 * i], kx[8 + 2 * i + 1]);
+            vh[i] = __floats2half2_rn(vx[2 * i], vx[2 * i + 1]); vh1[i] = __floats2half2_rn(vx[8 + 2 * i], vx[8 + 2 * i + 1]);
         }
-        float kf[16], vf[16];
+        if (g == 0 && h % (Hq / Hkv) == 0) { // one writer per kv head
+            __half *kd = ra.kc + (size_t)b * kvb + (size_t)pos * rs + (size_t)kvh * D + sub * 16;
+            __half *vd = ra.vc + (size_t)b * kvb + (size_t)pos * rs + (size_t)kvh * D + sub * 16;
+            *(uint4 *)kd = k0; *(uint4 *)(kd + 8) = k1;
+            *(uint4 *)vd = v0; *(uint4 *)(vd + 8) = v1;
+        }
+        float kf[16];
         h8_to_f(k0, kf); h8_to_f(k1, kf + 8);
         float s = 0.f;
 #pragma unroll
         for (int i = 0; i < 16; i++) s = fmaf(qv[i], kf[i], s);
 #pragma unroll
         for (int x = 1; x < LPK; x <<= 1) s += __shfl_xor_sync(0xffffffffu, s, x);
-        if (ok) {
-            h8_to_f(v0, vf); h8_to_f(v1, vf + 8);
-            const float m_new = fmaxf(m, s);
-            const float sc = expf((m - m_new) * scale);
-            const float p = expf((s - m_new) * scale);
-            l = fmaf(l, sc, p);
-#pragma unroll
-            for (int i = 0; i < 16; i++) acc[i] = fmaf(p, vf[i], acc[i] * sc);
-            m = m_new;
+        if (g == 0) { // first key of this group: weight exp(0) = 1
+            m = s; l = 1.0f;
+            h8_to_f(v0, acc); h8_to_f(v1, acc + 8);
         }
     }
+    for (int cb0 = first; cb0 < e_end; cb0 += NB * KPP) { // warp-uniform trip count
+        // scores of the NB passes first (independent chains), then ONE softmax rescale for the batch
+        float sj[NB];
+#pragma unroll
+        for (int j = 0; j < NB; j++) {
+            float kf[16];
+            h8_to_f(kk[j][0], kf); h8_to_f(kk[j][1], kf + 8);
+            float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+#pragma unroll
+            for (int i = 0; i < 4; i++) {
+                s0 = fmaf(qv[i], kf[i], s0); s1 = fmaf(qv[4 + i], kf[4 + i], s1);
+                s2 = fmaf(qv[8 + i], kf[8 + i], s2); s3 = fmaf(qv[12 + i], kf[12 + i], s3);
+            }
+            sj[j] = (s0 + s1) + (s2 + s3);
+            const int cn0 = cb0 + (j + NB) * KPP;
+            if (cn0 < e_end) load_k(j, cn0); // this slot's K is consumed: refill it with the pass NB ahead (warp-uniform)
+        }
+#pragma unroll
+        for (int x = 1; x < LPK; x <<= 1)
+#pragma unroll
+            for (int j = 0; j < NB; j++) sj[j] += __shfl_xor_sync(0xffffffffu, sj[j], x);
+        float bm = -INFINITY;
+#pragma unroll
+        for (int j = 0; j < NB; j++) {
+            if (cb0 + j * KPP + g >= e_end) sj[j] = -INFINITY;
+            bm = fmaxf(bm, sj[j]);
+        }
+        const float m_new = fmaxf(m, bm);
+        const float sc = (m == -INFINITY) ? 0.f : expf((m - m_new) * scale);
+        float pj[NB], psum = 0.f;
+#pragma unroll
+        for (int j = 0; j < NB; j++) {
+            pj[j] = (sj[j] == -INFINITY) ? 0.f : expf((sj[j] - m_new) * scale);
+            psum += pj[j];
+        }
+        l = fmaf(l, sc, psum);
+#pragma unroll
+        for (int i = 0; i < 16; i++) acc[i] *= sc;
+#pragma unroll
+        for (int j = 0; j < NB; j++) {
+            float vf[16];
+            h8_to_f(vv[j][0], vf); h8_to_f(vv[j][1], vf + 8);
+#pragma unroll
+            for (int i = 0; i < 16; i++) acc[i] = fmaf(pj[j], vf[i], acc[i]);
+            const int cn0 = cb0 + (j + NB) * KPP;
+            if (cn0 < e_end) load_v(j, cn0);
+        }
+        m = m_new;
+    }
+    if (ROPE && ra.prof && blockIdx.x == 0 && tid == 0) { unsigned long long t_; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t_)); ra.prof[3] = t_ + (acc[0] == 1.2345e-30f ? 1 : 0); }
     // ---- merge the KPW key groups of the warp (lanes with equal `sub`)
 #pragma unroll
     for (int x = LPK; x < 32; x <<= 1) {
@@ -290,13 +418,13 @@ __global__ void __launch_bounds__(128) k_attn_decode(const float *__restrict__ q
         for (int i = 0; i < 16; i++) sm[warp][2 + sub * 16 + i] = acc[i];
     }
     __syncthreads();
-    // ---- merge the 4 warps: thread t < D owns output dim t
+    // ---- merge the warps: thread t < D owns output dim t
     float mt = -INFINITY, lt = 0.f, at = 0.f;
     if (tid < D) {
 #pragma unroll
-        for (int w = 0; w < 4; w++) mt = fmaxf(mt, sm[w][0]);
+        for (int w = 0; w < NW; w++) mt = fmaxf(mt, sm[w][0]);
 #pragma unroll
-        for (int w = 0; w < 4; w++) {
+        for (int w = 0; w < NW; w++) {
             const float mw = sm[w][0];
             const float f = (mw == -INFINITY) ? 0.f : expf((mw - mt) * scale);
             lt = fmaf(sm[w][1], f, lt);
@@ -309,37 +437,93 @@ __global__ void __launch_bounds__(128) k_attn_decode(const float *__restrict__ q
         return;
     }
     const size_t row = (size_t)b * Hq + h;
+    if (CLUSTER) {
+        // the nsplit CTAs of this (row, head) are one cluster (rank == sp): partials go straight into rank 0's shared memory,
+        // one cluster barrier orders them, rank 0 merges -- no global round trip, no ticket
+        __shared__ float part[8][D + 2];
+        const uint32_t dst = cluster_map_rank(smem_addr_u32(&part[sp][0]), 0);
+        if (tid < D) {
+            if (tid == 0) { cluster_st_f32(dst, mt); cluster_st_f32(dst + 4, lt); }
+            cluster_st_f32(dst + 8 + tid * 4, at);
+        }
+        ATTN_STAMP(4);
+        cluster_sync_all();
+        ATTN_STAMP(5);
+        if (sp != 0) return;
+        if (ROPE && ra.prof && row == 0 && tid == 0) { unsigned long long t_; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t_)); ra.prof[6] = t_; }
+        if (tid < D) {
+            float mm = -INFINITY, ll = 0.f, aa = 0.f;
+            for (int s2 = 0; s2 < nsplit; s2++) mm = fmaxf(mm, part[s2][0]);
+            for (int s2 = 0; s2 < nsplit; s2++) {
+                const float ms = part[s2][0];
+                const float f = (ms == -INFINITY) ? 0.f : expf((ms - mm) * scale);
+                ll = fmaf(part[s2][1], f, ll);
+                aa = fmaf(part[s2][2 + tid], f, aa);
+            }
+            op[tid] = aa * (1.0f / ll);
+        }
+        if (ROPE && ra.prof && row == 0 && tid == 0) { unsigned long long t_; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t_)); ra.prof[7] = t_; }
+        return;
+    }
     float *wp = ws + (row * nsplit + sp) * (D + 2);
     if (tid < D) {
         if (tid == 0) { wp[0] = mt; wp[1] = lt; }
         wp[2 + tid] = at;
     }
-    __threadfence();
     __syncthreads();
+    ATTN_STAMP(4);
     if (tid == 0) {
-        const unsigned t = atomicAdd(&tickets[row], 1u);
+        // release the CTA's partial (ordered before this point by the barrier) and acquire the others' in one atomic
+        unsigned t;
+        asm volatile("atom.acq_rel.gpu.global.add.u32 %0, [%1], 1;" : "=r"(t) : "l"(tickets + row) : "memory");
         s_last = (t == (unsigned)nsplit - 1u);
         if (s_last) tickets[row] = 0; // ready for the next launch
     }
     __syncthreads();
+    ATTN_STAMP(5);
     if (!s_last) return;
-    __threadfence();
+    if (ROPE && ra.prof && row == 0 && tid == 0) { unsigned long long t_; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t_)); ra.prof[6] = t_; }
     if (tid < D) {
         const float *wr = ws + row * nsplit * (D + 2);
-        float mm = -INFINITY;
-        for (int s = 0; s < nsplit; s++) mm = fmaxf(mm, __ldcg(wr + (size_t)s * (D + 2)));
-        float ll = 0.f, aa = 0.f;
-        for (int s = 0; s < nsplit; s++) {
-            const float ms = __ldcg(wr + (size_t)s * (D + 2));
-            if (ms == -INFINITY) continue;
-            const float f = expf((ms - mm) * scale);
-            ll = fmaf(__ldcg(wr + (size_t)s * (D + 2) + 1), f, ll);
-            aa = fmaf(__ldcg(wr + (size_t)s * (D + 2) + 2 + tid), f, aa);
+        float mm = -INFINITY, ll = 0.f, aa = 0.f;
+        if (nsplit <= ATTN_MAXS) { // every partial in flight at once
+            float ms[ATTN_MAXS], ls[ATTN_MAXS], as[ATTN_MAXS];
+#pragma unroll
+            for (int s = 0; s < ATTN_MAXS; s++) {
+                const bool on = s < nsplit;
+                const float *r = wr + (size_t)(on ? s : 0) * (D + 2);
+                ms[s] = on ? __ldcg(r) : -INFINITY;
+                ls[s] = __ldcg(r + 1);
+                as[s] = __ldcg(r + 2 + tid);
+            }
+#pragma unroll
+            for (int s = 0; s < ATTN_MAXS; s++) mm = fmaxf(mm, ms[s]);
+#pragma unroll
+            for (int s = 0; s < ATTN_MAXS; s++) {
+                const float f = (ms[s] == -INFINITY) ? 0.f : expf((ms[s] - mm) * scale);
+                ll = fmaf(ls[s], f, ll);
+                aa = fmaf(as[s], f, aa);
+            }
+        } else {
+            for (int s = 0; s < nsplit; s++) mm = fmaxf(mm, __ldcg(wr + (size_t)s * (D + 2)));
+            for (int s = 0; s < nsplit; s++) {
+                const float ms = __ldcg(wr + (size_t)s * (D + 2));
+                if (ms == -INFINITY) continue;
+                const float f = expf((ms - mm) * scale);
+                ll = fmaf(__ldcg(wr + (size_t)s * (D + 2) + 1), f, ll);
+                aa = fmaf(__ldcg(wr + (size_t)s * (D + 2) + 2 + tid), f, aa);
+            }
         }
         op[tid] = aa * (1.0f / ll);
     }
+    if (ROPE && ra.prof && row == 0 && tid == 0) { unsigned long long t_; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t_)); ra.prof[7] = t_; }
 }
 
+static bool attn_use_cluster() {
+    static int on = -1;
+    if (on < 0) { const char *e = getenv("MLLMCU_ATTN_NO_CLUSTER"); on = (e && e[0] && e[0] != '0') ? 0 : 1; }
+    return on == 1;
+}
 MLLMCU_API int mllmcu_decode_attn_nsplit(int B, int Hq) {
     // ~2 CTAs of 4 warps per SM (swept on B200: 1x 1.70, 2x 1.66, 4x 1.82 ms per 7B decode step)
     static int mult = 0;
@@ -347,6 +531,7 @@ MLLMCU_API int mllmcu_decode_attn_nsplit(int B, int Hq) {
     int n = (mult * 148) / (B * Hq);
     if (n < 1) n = 1;
     if (n > 32) n = 32;
+    if (attn_use_cluster() && n > 8) n = 8; // the splits of one head form a thread-block cluster (portable maximum 8)
     return n;
 }
 MLLMCU_API size_t mllmcu_decode_attn_workspace_bytes(int B, int Hq, int D) {
@@ -359,14 +544,27 @@ static int launch_attn_decode(const float *q, int ldq, const __half *k, const __
                               const int *ctl, int B, int Hq, int Hkv, long long kvb, int nsplit, const RopeArgs &ra, int pdl, cudaStream_t st) {
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)(B * Hq * nsplit));
-    cfg.blockDim = dim3(128);
+    cfg.blockDim = dim3(ATTN_WARPS * 32);
     cfg.stream = st;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cudaLaunchAttribute attr[2];
+    int na = 0;
+    if (pdl) {
+        attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[na].val.programmaticStreamSerializationAllowed = 1;
+        na++;
+    }
+    const bool cluster = attn_use_cluster() && nsplit > 1 && nsplit <= 8;
+    if (cluster) {
+        attr[na].id = cudaLaunchAttributeClusterDimension;
+        attr[na].val.clusterDim.x = (unsigned)nsplit;
+        attr[na].val.clusterDim.y = 1;
+        attr[na].val.clusterDim.z = 1;
+        na++;
+    }
     cfg.attrs = attr;
-    cfg.numAttrs = pdl ? 1 : 0;
-    CU_TRY(cudaLaunchKernelEx(&cfg, k_attn_decode<D, ROPE>, q, ldq, k, v, o, ldo, ws, tickets, ctl, Hq, Hkv, kvb, nsplit, ra));
+    cfg.numAttrs = na;
+    if (cluster) CU_TRY(cudaLaunchKernelEx(&cfg, k_attn_decode<D, ROPE, true>, q, ldq, k, v, o, ldo, ws, tickets, ctl, Hq, Hkv, kvb, nsplit, ra));
+    else CU_TRY(cudaLaunchKernelEx(&cfg, k_attn_decode<D, ROPE, false>, q, ldq, k, v, o, ldo, ws, tickets, ctl, Hq, Hkv, kvb, nsplit, ra));
     return 0;
 }
 
@@ -406,8 +604,28 @@ MLLMCU_API int mllmcu_decode_attn_rope(int rope_type, const float *qkv, int ld, 
                                        int B, int Hq, int Hkv, int D, const float *sin_t, const float *cos_t, int tdim, long long kv_bstride,
                                        int cache_limit, void *ws, size_t ws_bytes, int pdl, void *stream) {
     if ((rope_type != 2 && rope_type != 4) || tdim != D || ((uintptr_t)sin_t & 15) || ((uintptr_t)cos_t & 15)) return -2;
-    RopeArgs ra = {rope_type, tdim, cache_limit, sin_t, cos_t, qkv, (__half *)kcache, (__half *)vcache};
+    RopeArgs ra = {rope_type, tdim, cache_limit, sin_t, cos_t, qkv, (__half *)kcache, (__half *)vcache, nullptr, pdl == 2 ? 1 : 0};
+    if (g_attn_prof_on < 0) {
+        const char *e = getenv("MLLMCU_ATTN_PROF");
+        g_attn_prof_on = (e && e[0] == '1') ? 1 : 0;
+        if (g_attn_prof_on && (cudaMalloc(&g_attn_prof, ATTN_PROF_RING * 8 * 8) != cudaSuccess || cudaMemset(g_attn_prof, 0, ATTN_PROF_RING * 8 * 8) != cudaSuccess)) g_attn_prof_on = 0;
+    }
+    if (g_attn_prof_on) { ra.prof = g_attn_prof + (size_t)(g_attn_prof_n % ATTN_PROF_RING) * 8; g_attn_prof_n++; }
     return decode_attn_common(qkv, ld, kcache, vcache, o, ldo, ctl, B, Hq, Hkv, D, kv_bstride, ws, ws_bytes, &ra, pdl, stream);
+}
+
+// development aid: the last n fused-rope attention launches' stamps, oldest first (MLLMCU_ATTN_PROF=1): CTA 0 {entry, dependency
+// wait passed, q rotated, key loop done, partial stored, ticket taken}, then the merging CTA of row 0 {merge start, output stored}
+MLLMCU_API int mllmcu_decode_attn_prof_read(unsigned long long *host_out, int n_launches) {
+    if (g_attn_prof_on != 1 || !host_out || n_launches <= 0) return 0;
+    if (cudaDeviceSynchronize() != cudaSuccess) return 0;
+    int n = n_launches < g_attn_prof_n ? n_launches : g_attn_prof_n;
+    if (n > ATTN_PROF_RING) n = ATTN_PROF_RING;
+    for (int i = 0; i < n; i++) {
+        const int slot = (g_attn_prof_n - n + i) % ATTN_PROF_RING;
+        if (cudaMemcpy(host_out + (size_t)i * 8, g_attn_prof + (size_t)slot * 8, 64, cudaMemcpyDeviceToHost) != cudaSuccess) return i;
+    }
+    return n;
 }
 
 // ------------------------------------------------------------------ greedy pick with token log

@@ -356,7 +356,7 @@ bool LlamaModel::issue_step(DecodePlan &p, bool pick, bool pdl_on) {
     // in_reps / out_reps: how many copies of the input row exist and how many of the output row to store; norm_idx picks the
     // replicated RMSNorm weight (2 * layer, 2 * layer + 1, or 2 * layers for the final norm)
     auto gemv = [&](std::initializer_list<const FuseInfo *> ws, const float *in, int K, int in_reps, const FuseInfo *norm, int norm_idx, int epi,
-                    const float *res, int ldr, float *out, int ldy, int out_reps) -> bool {
+                    const float *res, int ldr, float *out, int ldy, int out_reps, bool late_trigger = false) -> bool {
         mllmcu_gemv_desc d = {};
         d.wtype = MLLM_TYPE_Q4_0;
         for (const FuseInfo *f : ws) { d.W[d.nW] = f->weight; d.N[d.nW] = f->out; d.bias[d.nW] = f->bias; d.nW++; }
@@ -365,7 +365,7 @@ bool LlamaModel::issue_step(DecodePlan &p, bool pick, bool pdl_on) {
             d.norm_w = p.norm_rep.devPtr<float>() + (size_t)norm_idx * R * H;
             d.eps = norm->eps; d.norm_reps = R; d.norm_rep_stride = H;
         }
-        d.epilogue = epi; d.residual = res; d.ldr = ldr; d.y = out; d.ldy = ldy; d.pdl = pdl;
+        d.epilogue = epi; d.residual = res; d.ldr = ldr; d.y = out; d.ldy = ldy; d.pdl = (pdl && late_trigger) ? 2 : pdl;
         d.x_reps = in_reps; d.x_rep_stride = (long long)B * K;
         d.y_reps = out_reps; d.y_rep_stride = (long long)B * ldy;
         const DecodeLookahead &la = p.lookahead[launch_no++];
@@ -386,12 +386,15 @@ bool LlamaModel::issue_step(DecodePlan &p, bool pick, bool pdl_on) {
     }
     for (auto &l : p.layers) {
         const int li = (int)(&l - &p.layers[0]);
-        if (!gemv({&l.q, &l.k, &l.v}, x, H, li == 0 ? 1 : R, &l.n1, 2 * li, 0, nullptr, 0, qkv, QKV, 1)) return false; // the embedding wrote one copy
+        // Layer 0's projection releases its dependents only after its own wait: from then on every kernel of the step starts
+        // with the embedding kernel (which bumps ctl[0]) complete, so the attention kernels may read the position, their K/V
+        // rows and the RoPE table row ahead of THEIR waits (pdl == 2 below).
+        if (!gemv({&l.q, &l.k, &l.v}, x, H, li == 0 ? 1 : R, &l.n1, 2 * li, 0, nullptr, 0, qkv, QKV, 1, li == 0)) return false; // the embedding wrote one copy
         static const bool no_rope_fusion = env_on("MLLM_CUDA_NO_ROPE_FUSION");
         if (l.rope.rot_dim == D && !no_rope_fusion) { // full rotary: RoPE and the KV append ride inside the attention kernel
             MLLMCU_CHECK(mllmcu_decode_attn_rope(l.rope.rope_type, qkv, QKV, l.kc.cache, l.vc.cache, ao, Hq * D, ctl, B, Hq, Hkv, D, l.rope.sin_t,
                                                  l.rope.cos_t, l.rope.rot_dim, l.kc.cache_bstride, l.kc.cache_limit, p.attn_ws.rawDevPtr(),
-                                                 p.attn_ws_bytes, pdl, st));
+                                                 p.attn_ws_bytes, pdl ? 2 : 0, st));
         } else {
             MLLMCU_CHECK(mllmcu_decode_rope_kv(l.rope.rope_type, qkv, QKV, B, Hq, Hkv, D, l.rope.rot_dim, l.rope.sin_t, l.rope.cos_t, l.rope.rot_dim,
                                                ctl, l.kc.cache, l.vc.cache, l.kc.cache_bstride, l.kc.cache_limit, pdl, st));

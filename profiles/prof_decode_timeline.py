@@ -7,6 +7,7 @@ import sys
 import numpy as np
 
 os.environ["MLLMCU_GEMV_PROF"] = "1"
+os.environ["MLLMCU_ATTN_PROF"] = "1"
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import bench  # noqa: E402
 from mllm_b200 import backend, capi, mllm_file as mf  # noqa: E402
@@ -22,6 +23,8 @@ n = 129
 buf = np.zeros((n, 64), dtype=np.uint64)
 got = capi.lib().mllmcu_gemv_prof_read(buf.ctypes.data_as(C.c_void_p), n)
 assert got == n
+ab = np.zeros((32, 8), dtype=np.uint64)
+assert capi.lib().mllmcu_decode_attn_prof_read(ab.ctypes.data_as(C.c_void_p), 32) == 32
 t0 = int(buf[0, 0])
 names = ["qkv", "o", "gate|up", "down"]
 tot = dict(gap=0.0, pro=0.0, stream=0.0)
@@ -31,6 +34,10 @@ for i in range(n):
     nm = names[i % 4] if i < 128 else "lm_head"
     if 8 <= i < 16 or i >= 124:
         print(f"{nm:8s} entry {e[0]:8.2f} wait-done {e[1]:8.2f} prologue-done {e[2]:8.2f} exit {e[3]:8.2f} | prev exit -> wait-done {e[1] - prev:6.2f}  prologue {e[2] - e[1]:5.2f}  stream {e[3] - e[2]:5.2f}")
+    if (8 <= i < 16 or i >= 124) and i % 4 == 0 and i < 128:
+        a = [(int(v) - t0) / 1e3 for v in ab[i // 4]]
+        print(f"  attn   entry {a[0]:8.2f} wait-done {a[1]:8.2f} q-rotated {a[2]:8.2f} keys-done {a[3]:8.2f} partial-stored {a[4]:8.2f} ticket {a[5]:8.2f}"
+              f" | merge-start {a[6]:8.2f} out-stored {a[7]:8.2f}   (qkv exit {e[3]:8.2f})")
     if 4 <= i < 128:
         tot["gap"] += e[1] - prev
         tot["pro"] += e[2] - e[1]

@@ -59,7 +59,16 @@ bufs = dict(qkv=torch.empty((1, 1, QKV), device="cuda"), x=torch.randn((R, 1, H)
 bufs["x"][:] = bufs["x"][0]
 
 
+SAME = len(sys.argv) > 3 and sys.argv[3] == "same"  # every launch the same kernel variant (o-type): is the prologue I-cache bound?
+
+
 def step():
+    if SAME:
+        for li, L in enumerate(layers):
+            for j, w in enumerate(("q", "k", "v", "o")):
+                src, dst = (bufs["x"], bufs["x2"]) if j % 2 == 0 else (bufs["x2"], bufs["x"])
+                capi.gemv_fused_ex([L[w]], src, dst, epilogue=1, residual=src[0], pdl=True, x_reps=R, y_reps=R)
+        return
     for li, L in enumerate(layers):
         capi.gemv_fused_ex([L["q"], L["k"], L["v"]], bufs["x"], bufs["qkv"], norm_w=nwr, pdl=True, x_reps=R, norm_reps=R, lookahead=PLAN[4 * li])
         capi.gemv_fused_ex([L["o"]], bufs["qkv"][:, :, :H], bufs["x2"], epilogue=1, residual=bufs["x"][0], pdl=True, y_reps=R, lookahead=PLAN[4 * li + 1])
