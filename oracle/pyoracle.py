@@ -19,6 +19,8 @@ _ref = None
 
 Q4_0, Q8_0 = 2, 8  # mllm/Types.hpp:64-68 DataType values
 Q4_0_BYTES, Q8_0_BYTES = 18, 34
+Q4_K, Q6_K = 12, 14
+Q4_K_BYTES, Q6_K_BYTES, Q8_K_BYTES = 144, 210, 292
 
 
 def build():
@@ -126,6 +128,73 @@ class Lib:
             self.fn("flash_attn_f16kv")(_p(q), _p(k), _p(v), _p(o), Sq, Sk, Hq, Hkv, D, int(causal), threads)
         return o
 
+    # ---- rows a4/a5/a7/a15/a17: available with both prefixes (restatement and compiled reference)
+    def quantize_q8_K(self, x):
+        x = np.ascontiguousarray(x, dtype=np.float32)
+        rows, k = x.reshape(-1, x.shape[-1]).shape
+        out = np.zeros((rows, k // 256 * Q8_K_BYTES), dtype=np.uint8)
+        f = self.fn("quantize_row_q8_K")
+        xr = x.reshape(rows, k)
+        for r in range(rows):
+            f(_p(xr[r]), _p(out[r]), C.c_int(k))
+        return out
+
+    def dequantize_kq(self, w, k, wtype=Q4_K):
+        bs = Q4_K_BYTES if wtype == Q4_K else Q6_K_BYTES
+        w = np.ascontiguousarray(w, dtype=np.uint8).reshape(-1, k // 256 * bs)
+        out = np.empty((w.shape[0], k), dtype=np.float32)
+        f = self.fn("dequantize_row_q4_K" if wtype == Q4_K else "dequantize_row_q6_K")
+        for r in range(w.shape[0]):
+            f(_p(w[r]), _p(out[r]), C.c_int(k))
+        return out
+
+    def vec_dot_kq(self, wrow, xrow, k, wtype=Q4_K):
+        s = C.c_float(0)
+        if wtype == Q4_K:
+            self.fn("vec_dot_q4_K_q8_K")(C.c_int(k), C.byref(s), _p(wrow), _p(xrow))
+        elif self.prefix == "orc_":
+            self.fn("vec_dot_q6_K_q8_K")(C.c_int(k), C.byref(s), _p(wrow), _p(xrow), None)
+        else:
+            self.fn("vec_dot_q6_K_q8_K")(C.c_int(k), C.byref(s), _p(wrow), _p(xrow))
+        return np.float32(s.value)
+
+    def linear_kq(self, W, x, bias=None, wtype=Q4_K):
+        x = np.ascontiguousarray(x, dtype=np.float32)
+        M, K = x.shape
+        N = W.shape[0]
+        y = np.empty((M, N), dtype=np.float32)
+        b = _p(np.ascontiguousarray(bias, dtype=np.float32)) if bias is not None else None
+        rc = self.fn("linear_kq")(C.c_int(wtype), _p(W), _p(x), b, _p(y), M, N, K, K, N)
+        assert rc == 0
+        return y
+
+    def softmax(self, x, causal=False, old_dim=0):
+        """x [outer, S, n] -> CPUSoftMax over the last dim"""
+        x = np.ascontiguousarray(x, dtype=np.float32)
+        outer, S, n = x.shape
+        y = np.empty_like(x)
+        self.fn("softmax")(_p(x), _p(y), outer, S, n, int(causal), old_dim)
+        return y
+
+    def gelu_table(self, kind):
+        t = np.empty(65536, dtype=np.uint16)
+        if self.prefix == "orc_":
+            self.fn("gelu_table")(kind, _p(t))
+        else:
+            self.fn("gelu_table")(kind, _p(t))
+        return t
+
+    def conv2d_valid(self, x, w, bias, stride):
+        x = np.ascontiguousarray(x, dtype=np.float32)
+        w = np.ascontiguousarray(w, dtype=np.float32)
+        B, Cc, H, W = x.shape
+        O, _, kh, kw = w.shape
+        sh, sw = stride
+        y = np.empty((B, O, (H - kh) // sh + 1, (W - kw) // sw + 1), dtype=np.float32)
+        b = _p(np.ascontiguousarray(bias, dtype=np.float32)) if bias is not None else None
+        self.fn("conv2d_valid")(_p(x), _p(w), b, _p(y), B, Cc, H, W, O, kh, kw, sh, sw)
+        return y
+
 
 class PortOnly:
     """Functions that exist only in the restatement (no compilable reference twin)."""
@@ -172,6 +241,65 @@ class PortOnly:
         out = np.empty(k // 32, dtype=np.int32)
         self.L.orc_block_isums_q4_0_q8_0(k, _p(wrow), _p(xrow), _p(out))
         return out
+
+    def gelu(self, table, x):
+        x = np.ascontiguousarray(x, dtype=np.float32)
+        y = np.empty_like(x)
+        self.L.orc_gelu_lookup(_p(table), _p(x), _p(y), C.c_size_t(x.size))
+        return y
+
+    def mrope_tables(self, pos, dim, base, sections):
+        pos = np.ascontiguousarray(pos, dtype=np.float32)  # [3, S]
+        S = pos.shape[1]
+        sec = np.ascontiguousarray(sections, dtype=np.int32)
+        s = np.empty((S, dim), dtype=np.float32)
+        c = np.empty((S, dim), dtype=np.float32)
+        self.L.orc_mrope_tables(_p(pos), S, dim, C.c_float(base), _p(sec), sec.size, _p(s), _p(c))
+        return s, c
+
+    def rope_vision(self, x, angles):
+        x = np.ascontiguousarray(x, dtype=np.float32)
+        angles = np.ascontiguousarray(angles, dtype=np.float32)
+        S, H, D = x.shape
+        out = np.empty_like(x)
+        self.L.orc_rope_vision(_p(x), _p(angles), _p(out), S, H, D)
+        return out
+
+    def conv3d_valid(self, x, w, bias, stride, channels_last=False):
+        x = np.ascontiguousarray(x, dtype=np.float32)
+        w = np.ascontiguousarray(w, dtype=np.float32)
+        B, Cc, T, H, W = x.shape
+        O, _, kt, kh, kw = w.shape
+        st, sh, sw = stride
+        ot, oh, ow = (T - kt) // st + 1, (H - kh) // sh + 1, (W - kw) // sw + 1
+        y = np.empty((B, ot, oh, ow, O) if channels_last else (B, O, ot, oh, ow), dtype=np.float32)
+        b = _p(np.ascontiguousarray(bias, dtype=np.float32)) if bias is not None else None
+        self.L.orc_conv3d_valid(_p(x), _p(w), b, _p(y), B, Cc, T, H, W, O, kt, kh, kw, st, sh, sw, int(channels_last))
+        return y
+
+    def q4_0_4x4_pack(self, rows, k):
+        rows = np.ascontiguousarray(rows, dtype=np.uint8)
+        out = np.empty_like(rows)
+        self.L.orc_q4_0_4x4_pack(_p(rows), _p(out), rows.shape[0], k)
+        return out
+
+    def q4_0_4x4_unpack(self, packed, nrow, k):
+        packed = np.ascontiguousarray(packed, dtype=np.uint8)
+        out = np.empty((nrow, k // 32 * Q4_0_BYTES), dtype=np.uint8)
+        self.L.orc_q4_0_4x4_unpack(_p(packed), _p(out), nrow, k)
+        return out
+
+    def block_isums_q4_K_q8_K(self, wrow, xrow, k):
+        a = np.empty(k // 256, dtype=np.int32)
+        b = np.empty(k // 256, dtype=np.int32)
+        self.L.orc_block_isums_q4_K_q8_K(k, _p(wrow), _p(xrow), _p(a), _p(b))
+        return a, b
+
+    def block_lanes_q6_K_q8_K(self, wrow, xrow, k):
+        lanes = np.empty((k // 256, 8), dtype=np.int32)
+        s = C.c_float(0)
+        self.L.orc_vec_dot_q6_K_q8_K(C.c_int(k), C.byref(s), _p(wrow), _p(xrow), _p(lanes))
+        return lanes
 
     def fp32_to_fp16_bits(self, x):
         x = np.ascontiguousarray(x, dtype=np.float32)
