@@ -32,6 +32,9 @@ extern "C" {
 #define MLLMCU_TYPE_F16 1
 #define MLLMCU_TYPE_Q4_0 2
 #define MLLMCU_TYPE_Q8_0 8
+#define MLLMCU_TYPE_Q4_K 12
+#define MLLMCU_TYPE_Q6_K 14
+#define MLLMCU_TYPE_Q4_0_4_4 19
 /* RoPEType values, identical to mllm/Types.hpp RoPEType */
 #define MLLMCU_ROPE_LLAMA 2
 #define MLLMCU_ROPE_HF 4
@@ -91,6 +94,11 @@ int mllmcu_block_isums_q4_0_q8_0(const void *W, const void *xq_blocks, int32_t *
  * cache slice (Matmul.cpp:262-268).
  *   wtype: MLLMCU_TYPE_Q4_0 | MLLMCU_TYPE_Q8_0;  W: [N][K/32] native blocks,
  *   x: [M][K] fp32 row stride ldx;  y: [M][N] row stride ldy (elements).
+ * wtype MLLMCU_TYPE_Q4_K | MLLMCU_TYPE_Q6_K (K % 256 == 0): the k-quant path -- rows quantised to block_q8_K
+ * (quantize_row_q8_K, ggml/QuantizeQ8.cpp:216-266, bytes identical), vec_dot_q4_K_q8_K / vec_dot_q6_K_q8_K
+ * (ggml/VecDotQ4.cpp:32-345, ggml/VecDotQ6.cpp:32-262): per super-block the same two exact integers
+ * (sum scale*dot, sum min*bsum) times d = d_x*fp16(d_w), dmin = -d_x*fp16(dmin_w).  W: [N][K/256] block_q4_K (144 B,
+ * 16-byte aligned rows) or block_q6_K (210 B).
  * ws: scratch of at least mllmcu_linear_workspace_bytes(M,K). */
 size_t mllmcu_linear_workspace_bytes(int M, int K);
 int mllmcu_linear(int wtype, const void *W, const float *x, const float *bias, void *y, int M, int N, int K, int ldx,
@@ -200,6 +208,71 @@ int mllmcu_embedding_q4_0(const void *table, const float *ids, float *out, int n
 size_t mllmcu_flash_attn_workspace_bytes(int B, int Sq, int Hq, int D);
 int mllmcu_flash_attn_f16kv(const float *q, const void *k, const void *v, float *o, int B, int Sq, int Sk, int Hq,
                             int Hkv, int D, int causal, long long kv_bstride, void *ws, size_t ws_bytes, void *stream);
+
+/* ---- quantize_row_q8_K (ggml/QuantizeQ8.cpp:216-266): rows x k/256 native block_q8_K (292 B: float d, 256 int8,
+ * 16 int16 group sums).  Bytes identical to the reference's (an all-zero super-block gets zero group sums, which the
+ * reference leaves unwritten).  x rows 16-byte aligned, ldx % 4 == 0. */
+int mllmcu_quantize_q8_K(const float *x, void *y_blocks, int rows, int k, int ldx, void *stream);
+/* the two exact integers vec_dot_q4_K_q8_K forms per super-block (ggml/VecDotQ4.cpp:220-283):
+ * sumi[n][m][i] = sum_sb scale_sb * (q4_sb . q8_sb), summ[n][m][i] = sum_sb min_sb * (bsums[2sb] + bsums[2sb+1]).
+ * Test/diagnostic entry point. */
+int mllmcu_block_isums_q4_K_q8_K(const void *W, const void *xq_blocks, int32_t *sumi, int32_t *summ, int M, int N, int K, void *stream);
+
+/* ---- Q4_0_4_4 weights (block_q4_0x4, mllm/DataType.hpp:104-107; make_block_q4_0x4 + quantize_q4_0_nr_bl,
+ * ggml/GemmPack.cpp:45-60, :308-344; consumed by gemv/gemm_q4_0_4x4_q8_0 when W.dtype == MLLM_TYPE_Q4_0_4_4,
+ * compute/Matmul.cpp:158-217): rewritten ONCE at load into plain block_q4_0 rows (same nibbles, same scales), after which
+ * the tensor is an ordinary MLLMCU_TYPE_Q4_0 weight.  nrow % 4 == 0; packed != rows. */
+int mllmcu_q4_0_4x4_to_q4_0(const void *packed, void *rows, int nrow, int k, void *stream);
+
+/* ---- GELU / QuickGELU through the reference's fp16 table: mllm_vec_gelu_f32 / mllm_vec_gelu_quick_f32
+ * (ggml/Quantize.hpp:101-133): y = fp32(table[fp16 bits of x]); table_f16 = the 65536-entry table built as
+ * init_table_gelu_f16 / init_table_gelu_quick_f16 build it (host, once), resident on the device. */
+int mllmcu_gelu_table(const float *x, float *y, size_t n, const void *table_f16, void *stream);
+
+/* ---- Softmax over the last dim with the causal mask of the eager attention spelling: CPUSoftMax::execute
+ * (op/CPUSoftMax.cpp:29-66) + mllm_vec_soft_max_f32 (compute/ActivationFunction.cpp:29-80).  x,y: [outer][S][n];
+ * row s sees (causal && S > 1) ? s + 1 + old_dim : n entries, the rest of the row is written 0.  Bit-identical to
+ * the AVX2 build of the reference for the vector part (same polynomial exp, same summation order). */
+int mllmcu_softmax(const float *x, float *y, int outer, int S, int n, int causal, int old_dim, void *stream);
+/* x / s, IEEE division (q / sqrt(D) of the eager spelling; CPUdivintFunction, op/CPUBinaryFunc.hpp) */
+int mllmcu_div_scalar(const float *x, float s, float *y, size_t n, void *stream);
+
+/* ---- M-RoPE: CPUMultimodalRoPE (op/CPUMultimodalRoPE.cpp:25-331).  The per-call tables ([S][dim], sections of the
+ * t/h/w axes already gathered, built on the host as multimodal_sinusoidal_position_embedding + apply_multimodal_
+ * rotary_pos_emb do) are applied rotate-half with table row s: exactly mllmcu_rope(MLLMCU_ROPE_HF, ..., pos0 = 0). */
+int mllmcu_rope_mrope(const float *x, void *out, int B, int S, int H, int D, int rot_dim, const float *sin_t, const float *cos_t,
+                      int tdim, int out_f16, long long out_bstride, long long out_sstride, void *stream);
+/* ---- ViT 2-D rotary: CPUVisionRoPEFuncFunction::rope_hf (op/CPUVisionRoPEFunc.hpp:27-90).  x,out [B][S][H][D];
+ * cos_or_null == NULL: angles_or_sin holds rotary_pos_emb [S][D/2] and sin/cos are evaluated on the device (<= 2 ulp from
+ * libm's); otherwise the two pointers hold host-built sin and cos [S][D/2] and the result is bit-identical. */
+int mllmcu_rope_vision(const float *x, const float *angles_or_sin, const float *cos_or_null, void *out, int B, int S, int H, int D,
+                       int out_f16, void *stream);
+
+/* ---- strided 4-D copy, the device form of the reference's physical data movers (CPUtransposeFunction
+ * op/CPUTransposeFunc.hpp:127-149, CPUcatFunction, CPUsplitFunction, KV head replication op/CPUKVCache.cpp:137-247):
+ * dst[sum i_j*ds[j]] = src[sum i_j*ss[j]] for i in n[0] x n[1] x n[2] x n[3]; strides in elements of elem_bytes (2 | 4).
+ * n, ss, ds are HOST arrays of 4. */
+int mllmcu_copy_strided(const void *src, void *dst, int elem_bytes, const int *n, const long long *ss, const long long *ds, void *stream);
+
+/* ---- fp32 GEMM C[b][m][n] = sum_k A[b][m*lda + k] * B[b][n*ldbn + k*ldbk] + bias[n]  (batch strides in elements):
+ * the fp32 mat_mul of the eager attention spelling (CPUMatmul::execute, op/CPUMatmul.cpp:63-83: Q.K^T with ldbn = row
+ * stride of K, ldbk = 1; P.V with ldbn = 1, ldbk = row stride of V) and Linears whose weights stay F32. */
+int mllmcu_sgemm(const float *A, long long lda, long long strideA, const float *B, long long ldbn, long long ldbk, long long strideB,
+                 const float *bias, float *C, long long ldc, long long strideC, int M, int N, int K, int batch, void *stream);
+/* ---- patch-embed convolutions, VALID padding: conv2d_fp32_VALID / conv3d_fp32_VALID (compute/Convolution.cpp:35-90,
+ * :179-240) as an implicit GEMM (receptive fields gathered while loading tiles).  x [B][C][H][W] (mllm BSHD with
+ * S = channel), w [O][C][kh][kw], y [B][O][oh][ow], or with channels_last [B][oh*ow][O] -- the flatten(2).transpose the ViT
+ * graphs apply next.  3-D: x [B][C][T][H][W], w [O][C][kt][kh][kw], y BCTHW or (channels_last) BTHWC. */
+int mllmcu_conv2d_valid(const float *x, const float *w, const float *bias, float *y, int B, int C, int H, int W, int O, int kh, int kw,
+                        int sh, int sw, int channels_last, void *stream);
+int mllmcu_conv3d_valid(const float *x, const float *w, const float *bias, float *y, int B, int C, int T, int H, int W, int O, int kt,
+                        int kh, int kw, int st, int sh, int sw, int channels_last, void *stream);
+
+/* ---- flash attention with fp32 K/V (no cache): the vision towers' attention (flash_attention_2_forward fp32 variant,
+ * compute/FlashAttention2.hpp:87-1210; models/vit/modeling_vit.hpp:42-45).  D in {32, 64, 80, 128}; workspace as
+ * mllmcu_flash_attn_workspace_bytes. */
+int mllmcu_flash_attn_f32kv(const float *q, const float *k, const float *v, float *o, int B, int Sq, int Sk, int Hq, int Hkv, int D,
+                            int causal, long long kv_bstride, void *ws, size_t ws_bytes, void *stream);
 
 /* ---- fp32 -> fp16 RNE rows (KV-cache append of a tensor that is not produced
  * by a Linear/RoPE writing in place). dst row stride ld_dst, src row stride ld_src (elements) */

@@ -11,6 +11,8 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "lib", "libmllmcu.so")
 
 TYPE_F32, TYPE_F16, TYPE_Q4_0, TYPE_Q8_0 = 0, 1, 2, 8
+TYPE_Q4_K, TYPE_Q6_K, TYPE_Q4_0_4_4 = 12, 14, 19
+Q4_K_BYTES, Q6_K_BYTES, Q8_K_BYTES = 144, 210, 292
 ROPE_LLAMA, ROPE_HF = 2, 4
 Q4_0_BYTES, Q8_0_BYTES = 18, 34
 
@@ -61,6 +63,19 @@ SYMBOLS = {
     "mllmcu_embedding_q4_0": (_i, [_vp, _vp, _vp, _i, _i, _vp]),
     "mllmcu_flash_attn_workspace_bytes": (_sz, [_i, _i, _i, _i]),
     "mllmcu_flash_attn_f16kv": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _ll, _vp, _sz, _vp]),
+    "mllmcu_quantize_q8_K": (_i, [_vp, _vp, _i, _i, _i, _vp]),
+    "mllmcu_block_isums_q4_K_q8_K": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _vp]),
+    "mllmcu_q4_0_4x4_to_q4_0": (_i, [_vp, _vp, _i, _i, _vp]),
+    "mllmcu_gelu_table": (_i, [_vp, _vp, _sz, _vp, _vp]),
+    "mllmcu_softmax": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _vp]),
+    "mllmcu_div_scalar": (_i, [_vp, _f, _vp, _sz, _vp]),
+    "mllmcu_rope_mrope": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _vp, _vp, _i, _i, _ll, _ll, _vp]),
+    "mllmcu_rope_vision": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _vp]),
+    "mllmcu_copy_strided": (_i, [_vp, _vp, _i, _vp, _vp, _vp, _vp]),
+    "mllmcu_sgemm": (_i, [_vp, _ll, _ll, _vp, _ll, _ll, _ll, _vp, _vp, _ll, _ll, _i, _i, _i, _i, _vp]),
+    "mllmcu_conv2d_valid": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _vp]),
+    "mllmcu_conv3d_valid": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _vp]),
+    "mllmcu_flash_attn_f32kv": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _ll, _vp, _sz, _vp]),
     "mllmcu_f32_to_f16_rows": (_i, [_vp, _vp, _i, _i, _ll, _ll, _vp]),
     "mllmcu_argmax": (_i, [_vp, _i, _i, _vp, _vp]),
     "mllmcu_argmax_ids": (_i, [_vp, _i, _i, _vp, _vp]),
@@ -232,6 +247,126 @@ def flash_attn_f16kv(q, k, v, causal=True, kv_bstride=None):
     ws = _workspace(need, q.device)
     check(lib().mllmcu_flash_attn_f16kv(_ptr(q), _ptr(k), _ptr(v), _ptr(o), B, Sq, Sk, Hq, Hkv, D, int(causal), kv_bstride,
                                         _ptr(ws), ws.numel(), _stream()), "flash_attn")
+    return o
+
+
+# ---------------------------------------------------------------- rows a4/a5/a7/a10/a11/a15/a17/a18
+def quantize_q8_K(x):
+    """x: cuda fp32 [rows,k] -> cuda uint8 [rows, k/256*292] native block_q8_K."""
+    import torch
+    rows, k = x.shape
+    y = torch.zeros((rows, k // 256 * Q8_K_BYTES), dtype=torch.uint8, device=x.device)
+    check(lib().mllmcu_quantize_q8_K(_ptr(x), _ptr(y), rows, k, x.stride(0), _stream()), "quantize_q8_K")
+    return y
+
+
+def block_isums_q4_K_q8_K(W, xq, K):
+    import torch
+    N, M = W.shape[0], xq.shape[0]
+    a = torch.empty((N, M, K // 256), dtype=torch.int32, device=W.device)
+    b = torch.empty_like(a)
+    check(lib().mllmcu_block_isums_q4_K_q8_K(_ptr(W), _ptr(xq), _ptr(a), _ptr(b), M, N, K, _stream()), "block_isums_q4_K")
+    return a, b
+
+
+def q4_0_4x4_to_q4_0(packed, nrow, k):
+    import torch
+    out = torch.empty((nrow, k // 32 * Q4_0_BYTES), dtype=torch.uint8, device=packed.device)
+    check(lib().mllmcu_q4_0_4x4_to_q4_0(_ptr(packed), _ptr(out), nrow, k, _stream()), "q4_0_4x4_to_q4_0")
+    return out
+
+
+def gelu_table(x, table):
+    import torch
+    y = torch.empty_like(x)
+    check(lib().mllmcu_gelu_table(_ptr(x), _ptr(y), x.numel(), _ptr(table), _stream()), "gelu_table")
+    return y
+
+
+def softmax(x, causal=False, old_dim=0):
+    """x cuda fp32 [outer, S, n]"""
+    import torch
+    outer, S, n = x.shape
+    y = torch.empty_like(x)
+    check(lib().mllmcu_softmax(_ptr(x), _ptr(y), outer, S, n, int(causal), old_dim, _stream()), "softmax")
+    return y
+
+
+def div_scalar(x, s):
+    import torch
+    y = torch.empty_like(x)
+    check(lib().mllmcu_div_scalar(_ptr(x), s, _ptr(y), x.numel(), _stream()), "div_scalar")
+    return y
+
+
+def rope_mrope(x, sin_t, cos_t, out_f16=False):
+    import torch
+    B, S, H, D = x.shape
+    out = torch.empty((B, S, H, D), dtype=torch.float16 if out_f16 else torch.float32, device=x.device)
+    check(lib().mllmcu_rope_mrope(_ptr(x), _ptr(out), B, S, H, D, D, _ptr(sin_t), _ptr(cos_t), sin_t.shape[1], int(out_f16),
+                                  S * H * D, H * D, _stream()), "rope_mrope")
+    return out
+
+
+def rope_vision(x, angles=None, sin_t=None, cos_t=None):
+    import torch
+    B, S, H, D = x.shape
+    out = torch.empty_like(x)
+    a0 = angles if angles is not None else sin_t
+    check(lib().mllmcu_rope_vision(_ptr(x), _ptr(a0), _ptr(cos_t), _ptr(out), B, S, H, D, 0, _stream()), "rope_vision")
+    return out
+
+
+def copy_strided(src, dst, n, ss, ds):
+    n_ = (C.c_int * 4)(*n)
+    ss_ = (C.c_longlong * 4)(*ss)
+    ds_ = (C.c_longlong * 4)(*ds)
+    check(lib().mllmcu_copy_strided(_ptr(src), _ptr(dst), src.element_size(), n_, ss_, ds_, _stream()), "copy_strided")
+    return dst
+
+
+def sgemm(A, B, bias=None, b_is_kn=False):
+    """A cuda fp32 [batch, M, K]; B [batch, N, K] (or [batch, K, N] with b_is_kn) -> C [batch, M, N]"""
+    import torch
+    batch, M, K = A.shape
+    N = B.shape[2] if b_is_kn else B.shape[1]
+    Cm = torch.empty((batch, M, N), dtype=torch.float32, device=A.device)
+    ldbn, ldbk = (1, N) if b_is_kn else (K, 1)
+    check(lib().mllmcu_sgemm(_ptr(A), K, M * K, _ptr(B), ldbn, ldbk, B.stride(0), _ptr(bias), _ptr(Cm), N, M * N, M, N, K, batch, _stream()), "sgemm")
+    return Cm
+
+
+def conv2d_valid(x, w, bias, stride, channels_last=False):
+    import torch
+    B, Cc, H, W = x.shape
+    O, _, kh, kw = w.shape
+    oh, ow = (H - kh) // stride[0] + 1, (W - kw) // stride[1] + 1
+    y = torch.empty((B, oh * ow, O) if channels_last else (B, O, oh, ow), dtype=torch.float32, device=x.device)
+    check(lib().mllmcu_conv2d_valid(_ptr(x), _ptr(w), _ptr(bias), _ptr(y), B, Cc, H, W, O, kh, kw, stride[0], stride[1], int(channels_last), _stream()), "conv2d")
+    return y
+
+
+def conv3d_valid(x, w, bias, stride, channels_last=False):
+    import torch
+    B, Cc, T, H, W = x.shape
+    O, _, kt, kh, kw = w.shape
+    ot, oh, ow = (T - kt) // stride[0] + 1, (H - kh) // stride[1] + 1, (W - kw) // stride[2] + 1
+    y = torch.empty((B, ot, oh, ow, O) if channels_last else (B, O, ot, oh, ow), dtype=torch.float32, device=x.device)
+    check(lib().mllmcu_conv3d_valid(_ptr(x), _ptr(w), _ptr(bias), _ptr(y), B, Cc, T, H, W, O, kt, kh, kw, stride[0], stride[1], stride[2],
+                                    int(channels_last), _stream()), "conv3d")
+    return y
+
+
+def flash_attn_f32kv(q, k, v, causal=False):
+    """q cuda fp32 [B,Sq,Hq,D]; k,v cuda fp32 [B,Sk,Hkv,D]"""
+    import torch
+    B, Sq, Hq, D = q.shape
+    Sk, Hkv = k.shape[1], k.shape[2]
+    o = torch.empty_like(q)
+    need = lib().mllmcu_flash_attn_workspace_bytes(B, Sq, Hq, D)
+    ws = _workspace(need, q.device)
+    check(lib().mllmcu_flash_attn_f32kv(_ptr(q), _ptr(k), _ptr(v), _ptr(o), B, Sq, Sk, Hq, Hkv, D, int(causal), k.stride(0),
+                                        _ptr(ws), ws.numel(), _stream()), "flash_attn_f32kv")
     return o
 
 

@@ -20,13 +20,22 @@
 // (2 * Sk * Hkv * D * 2 bytes per sequence).
 #include "common.cuh"
 
-template <int D>
-__global__ void __launch_bounds__(128) k_attn_splitk(const float *__restrict__ q, const __half *__restrict__ k,
-                                                     const __half *__restrict__ v, float *__restrict__ o, float *__restrict__ ws,
+static __device__ __forceinline__ float kv_to_f32(__half h) { return __half2float(h); }
+static __device__ __forceinline__ float kv_to_f32(float f) { return f; }
+
+// KT = __half (the KV cache) or float (ViT blocks, whose K/V never enter a cache: models/vit/modeling_vit.hpp:42-45,
+// flash_attention_2_forward's fp32 variant, compute/FlashAttention2.hpp:87-1210).  D need not be a multiple of 32
+// (Qwen2-VL's ViT has D = 80): then D/4 lanes carry 4 elements each and the rest idle.
+template <int D, typename KT>
+__global__ void __launch_bounds__(128) k_attn_splitk(const float *__restrict__ q, const KT *__restrict__ k,
+                                                     const KT *__restrict__ v, float *__restrict__ o, float *__restrict__ ws,
                                                      int B, int Sq, int Sk, int Hq, int Hkv, int causal, long long kvb,
                                                      int nsplit, int chunk) {
-    constexpr int E = D / 32;
+    constexpr int E = (D % 32 == 0) ? D / 32 : 4;
+    constexpr int ACT = D / E; // lanes that hold data
     const int lane = threadIdx.x & 31;
+    const bool live = lane < ACT;
+    const int lo = live ? lane * E : 0;
     const long long wid = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     const long long total = (long long)B * Sq * Hq * nsplit;
     if (wid >= total) return;
@@ -41,19 +50,19 @@ __global__ void __launch_bounds__(128) k_attn_splitk(const float *__restrict__ q
     const int c_end = min(last + 1, c_begin + chunk);
 
     float qv[E];
-    const float *qp = q + (((size_t)b * Sq + r) * Hq + h) * D + lane * E;
+    const float *qp = q + (((size_t)b * Sq + r) * Hq + h) * D + lo;
 #pragma unroll
-    for (int e = 0; e < E; e++) qv[e] = qp[e];
+    for (int e = 0; e < E; e++) qv[e] = live ? qp[e] : 0.f;
     float acc[E];
 #pragma unroll
     for (int e = 0; e < E; e++) acc[e] = 0.f;
     float m = -INFINITY, l = 0.f;
-    const __half *kb = k + (size_t)b * kvb + (size_t)kvh * D + lane * E;
-    const __half *vb = v + (size_t)b * kvb + (size_t)kvh * D + lane * E;
+    const KT *kb = k + (size_t)b * kvb + (size_t)kvh * D + lo;
+    const KT *vb = v + (size_t)b * kvb + (size_t)kvh * D + lo;
     const size_t rs = (size_t)Hkv * D;
     for (int c = c_begin; c < c_end; c++) {
         float kf[E], vf[E];
-        if (E == 4) {
+        if (E == 4 && sizeof(KT) == 2) {
             const uint2 kk = *(const uint2 *)(kb + (size_t)c * rs);
             const uint2 vv = *(const uint2 *)(vb + (size_t)c * rs);
             const __half2 *k2 = (const __half2 *)&kk, *v2 = (const __half2 *)&vv;
@@ -64,7 +73,7 @@ __global__ void __launch_bounds__(128) k_attn_splitk(const float *__restrict__ q
             t = __half22float2(v2[1]); vf[2] = t.x; vf[3] = t.y;
         } else {
 #pragma unroll
-            for (int e = 0; e < E; e++) { kf[e] = __half2float(kb[(size_t)c * rs + e]); vf[e] = __half2float(vb[(size_t)c * rs + e]); }
+            for (int e = 0; e < E; e++) { kf[e] = kv_to_f32(kb[(size_t)c * rs + e]); vf[e] = kv_to_f32(vb[(size_t)c * rs + e]); }
         }
         float s = 0.f;
 #pragma unroll
@@ -79,22 +88,29 @@ __global__ void __launch_bounds__(128) k_attn_splitk(const float *__restrict__ q
         m = m_new;
     }
     if (nsplit == 1) {
-        float *op = o + (((size_t)b * Sq + r) * Hq + h) * D + lane * E;
+        float *op = o + (((size_t)b * Sq + r) * Hq + h) * D + lo;
         const float inv = 1.0f / l;
+        if (live) {
 #pragma unroll
-        for (int e = 0; e < E; e++) op[e] = acc[e] * inv;
+            for (int e = 0; e < E; e++) op[e] = acc[e] * inv;
+        }
     } else {
         float *wp = ws + (size_t)wid * (D + 2);
         if (lane == 0) { wp[0] = m; wp[1] = l; }
+        if (live) {
 #pragma unroll
-        for (int e = 0; e < E; e++) wp[2 + lane * E + e] = acc[e];
+            for (int e = 0; e < E; e++) wp[2 + lo + e] = acc[e];
+        }
     }
 }
 
 template <int D>
 __global__ void k_attn_merge(const float *__restrict__ ws, float *__restrict__ o, long long rows, int nsplit) {
-    constexpr int E = D / 32;
+    constexpr int E = (D % 32 == 0) ? D / 32 : 4;
+    constexpr int ACT = D / E;
     const int lane = threadIdx.x & 31;
+    const bool live = lane < ACT;
+    const int lo = live ? lane * E : 0;
     const long long row = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (row >= rows) return;
     const float scale = __fdiv_rn(1.0f, __fsqrt_rn((float)D));
@@ -110,12 +126,14 @@ __global__ void k_attn_merge(const float *__restrict__ ws, float *__restrict__ o
         const float f = expf((ms - m) * scale);
         l = fmaf(wp[1], f, l);
 #pragma unroll
-        for (int e = 0; e < E; e++) acc[e] = fmaf(wp[2 + lane * E + e], f, acc[e]);
+        for (int e = 0; e < E; e++) acc[e] = fmaf(wp[2 + lo + e], f, acc[e]);
     }
     const float inv = 1.0f / l;
-    float *op = o + (size_t)row * D + lane * E;
+    float *op = o + (size_t)row * D + lo;
+    if (live) {
 #pragma unroll
-    for (int e = 0; e < E; e++) op[e] = acc[e] * inv;
+        for (int e = 0; e < E; e++) op[e] = acc[e] * inv;
+    }
 }
 
 static int pick_nsplit(int B, int Sq, int Hq, int Sk) {
@@ -138,15 +156,15 @@ MLLMCU_API size_t mllmcu_flash_attn_workspace_bytes(int B, int Sq, int Hq, int D
     return (size_t)rows * ns * (D + 2) * sizeof(float) + 256;
 }
 
-template <int D>
-static int launch_attn(const float *q, const __half *k, const __half *v, float *o, int B, int Sq, int Sk, int Hq, int Hkv,
+template <int D, typename KT>
+static int launch_attn(const float *q, const KT *k, const KT *v, float *o, int B, int Sq, int Sk, int Hq, int Hkv,
                        int causal, long long kvb, float *ws, size_t ws_bytes, cudaStream_t st) {
     int nsplit = pick_nsplit(B, Sq, Hq, Sk);
     const long long rows = (long long)B * Sq * Hq;
     if (nsplit > 1 && (ws == nullptr || ws_bytes < (size_t)rows * nsplit * (D + 2) * sizeof(float))) nsplit = 1;
     const int chunk = (Sk + nsplit - 1) / nsplit;
     const long long warps = rows * nsplit;
-    k_attn_splitk<D><<<(unsigned)((warps + 3) / 4), 128, 0, st>>>(q, k, v, o, ws, B, Sq, Sk, Hq, Hkv, causal, kvb, nsplit, chunk);
+    k_attn_splitk<D, KT><<<(unsigned)((warps + 3) / 4), 128, 0, st>>>(q, k, v, o, ws, B, Sq, Sk, Hq, Hkv, causal, kvb, nsplit, chunk);
     CU_LAUNCH_CHECK();
     if (nsplit > 1) {
         k_attn_merge<D><<<(unsigned)((rows + 3) / 4), 128, 0, st>>>(ws, o, rows, nsplit);
@@ -161,10 +179,26 @@ MLLMCU_API int mllmcu_flash_attn_f16kv(const float *q, const void *k, const void
     if (causal && Sq > Sk) return -1;
     cudaStream_t st = (cudaStream_t)stream;
     switch (D) {
-    case 64: return launch_attn<64>(q, (const __half *)k, (const __half *)v, o, B, Sq, Sk, Hq, Hkv, causal, kv_bstride, (float *)ws, ws_bytes, st);
-    case 128: return launch_attn<128>(q, (const __half *)k, (const __half *)v, o, B, Sq, Sk, Hq, Hkv, causal, kv_bstride, (float *)ws, ws_bytes, st);
-    case 96: return launch_attn<96>(q, (const __half *)k, (const __half *)v, o, B, Sq, Sk, Hq, Hkv, causal, kv_bstride, (float *)ws, ws_bytes, st);
-    case 32: return launch_attn<32>(q, (const __half *)k, (const __half *)v, o, B, Sq, Sk, Hq, Hkv, causal, kv_bstride, (float *)ws, ws_bytes, st);
+    case 64: return launch_attn<64, __half>(q, (const __half *)k, (const __half *)v, o, B, Sq, Sk, Hq, Hkv, causal, kv_bstride, (float *)ws, ws_bytes, st);
+    case 128: return launch_attn<128, __half>(q, (const __half *)k, (const __half *)v, o, B, Sq, Sk, Hq, Hkv, causal, kv_bstride, (float *)ws, ws_bytes, st);
+    case 96: return launch_attn<96, __half>(q, (const __half *)k, (const __half *)v, o, B, Sq, Sk, Hq, Hkv, causal, kv_bstride, (float *)ws, ws_bytes, st);
+    case 32: return launch_attn<32, __half>(q, (const __half *)k, (const __half *)v, o, B, Sq, Sk, Hq, Hkv, causal, kv_bstride, (float *)ws, ws_bytes, st);
+    default: return -2;
+    }
+}
+
+// fp32 K/V (no cache): the attention of the vision towers -- CLIP ViT-L/14 (D 64), Qwen2-VL ViT (D 80) -- and of any graph
+// that calls flash_attention_2_forward on fp32 tensors.  k,v: element (b,s,h,d) at b*kv_bstride + s*Hkv*D + h*D + d.
+MLLMCU_API int mllmcu_flash_attn_f32kv(const float *q, const float *k, const float *v, float *o, int B, int Sq, int Sk, int Hq,
+                                       int Hkv, int D, int causal, long long kv_bstride, void *ws, size_t ws_bytes, void *stream) {
+    if (B <= 0 || Sq <= 0 || Sk <= 0 || Hq <= 0 || Hkv <= 0 || Hq % Hkv) return -1;
+    if (causal && Sq > Sk) return -1;
+    cudaStream_t st = (cudaStream_t)stream;
+    switch (D) {
+    case 64: return launch_attn<64, float>(q, k, v, o, B, Sq, Sk, Hq, Hkv, causal, kv_bstride, (float *)ws, ws_bytes, st);
+    case 80: return launch_attn<80, float>(q, k, v, o, B, Sq, Sk, Hq, Hkv, causal, kv_bstride, (float *)ws, ws_bytes, st);
+    case 128: return launch_attn<128, float>(q, k, v, o, B, Sq, Sk, Hq, Hkv, causal, kv_bstride, (float *)ws, ws_bytes, st);
+    case 32: return launch_attn<32, float>(q, k, v, o, B, Sq, Sk, Hq, Hkv, causal, kv_bstride, (float *)ws, ws_bytes, st);
     default: return -2;
     }
 }

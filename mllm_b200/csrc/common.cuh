@@ -58,3 +58,24 @@ static __device__ __forceinline__ uint4 ld_stream_u4(const void *p) {
     asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
     return r;
 }
+
+// mllm_v_expf (compute/ActivationFunction.hpp:96-141) per element: same fused / unfused operations as the AVX2 and
+// AVX-512 vector bodies, so results are bit-identical to theirs.
+static __device__ __forceinline__ float v_expf(float x) {
+    const float r = 0x1.8p23f;
+    const float z = __fmaf_rn(x, 0x1.715476p+0f, r);
+    const float n = __fsub_rn(z, r);
+    const float b = __fmaf_rn(-n, 0x1.7f7d1cp-20f, __fmaf_rn(-n, 0x1.62e4p-1f, x));
+    const uint32_t e = __float_as_uint(z) << 23;
+    const float k = __uint_as_float(e + __float_as_uint(1.0f));
+    const bool c = fabsf(n) > 126.0f;
+    const float u = __fmul_rn(b, b);
+    const float j = __fmaf_rn(__fmaf_rn(__fmaf_rn(0x1.0e4020p-7f, b, 0x1.573e2ep-5f), u, __fmaf_rn(0x1.555e66p-3f, b, 0x1.fffdb6p-2f)), u,
+                              __fmul_rn(0x1.ffffecp-1f, b));
+    if (!c) return __fmaf_rn(j, k, k);
+    const uint32_t g = (n <= 0.0f) ? 0x82000000u : 0u;
+    const float s1 = __uint_as_float(g + 0x7f000000u);
+    const float s2 = __uint_as_float(e - g);
+    if (fabsf(n) > 192.0f) return __fmul_rn(s1, s1);
+    return __fmul_rn(__fmaf_rn(s2, j, s2), s1);
+}

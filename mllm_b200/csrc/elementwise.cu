@@ -143,28 +143,15 @@ MLLMCU_API int mllmcu_rope(int rope_type, const float *x, void *out, int B, int 
     return 0;
 }
 
+MLLMCU_API int mllmcu_rope_mrope(const float *x, void *out, int B, int S, int H, int D, int rot_dim, const float *sin_t, const float *cos_t,
+                                 int tdim, int out_f16, long long obs, long long oss, void *stream) {
+    return mllmcu_rope(4, x, out, B, S, H, D, rot_dim, 0, sin_t, cos_t, tdim, out_f16, obs, oss, stream);
+}
+
 // --------------------------------------------------------------------- SiLU
 // mllm_v_expf / mllm_v_silu (compute/ActivationFunction.hpp:96-141) restated per
 // element with the same fused / unfused operations, so results are bit-identical
 // to the AVX2 (and AVX-512) vector bodies.
-static __device__ __forceinline__ float v_expf(float x) {
-    const float r = 0x1.8p23f;
-    const float z = __fmaf_rn(x, 0x1.715476p+0f, r);
-    const float n = __fsub_rn(z, r);
-    const float b = __fmaf_rn(-n, 0x1.7f7d1cp-20f, __fmaf_rn(-n, 0x1.62e4p-1f, x));
-    const uint32_t e = __float_as_uint(z) << 23;
-    const float k = __uint_as_float(e + __float_as_uint(1.0f));
-    const bool c = fabsf(n) > 126.0f;
-    const float u = __fmul_rn(b, b);
-    const float j = __fmaf_rn(__fmaf_rn(__fmaf_rn(0x1.0e4020p-7f, b, 0x1.573e2ep-5f), u, __fmaf_rn(0x1.555e66p-3f, b, 0x1.fffdb6p-2f)), u,
-                              __fmul_rn(0x1.ffffecp-1f, b));
-    if (!c) return __fmaf_rn(j, k, k);
-    const uint32_t g = (n <= 0.0f) ? 0x82000000u : 0u;
-    const float s1 = __uint_as_float(g + 0x7f000000u);
-    const float s2 = __uint_as_float(e - g);
-    if (fabsf(n) > 192.0f) return __fmul_rn(s1, s1);
-    return __fmul_rn(__fmaf_rn(s2, j, s2), s1);
-}
 static __device__ __forceinline__ float silu_f(float x) {
     return __fdiv_rn(x, __fadd_rn(1.0f, v_expf(__fsub_rn(0.0f, x))));
 }

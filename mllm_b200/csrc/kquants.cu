@@ -1,0 +1,373 @@
+// kquants.cu -- k-quant Linear: Q4_K / Q6_K weights x Q8_K activations.
+// Reference: mat_mul generic path (compute/Matmul.cpp:104-115 row quantisation to vec_dot_type Q8_K, :223-276 vec_dot
+// loop) with quantize_row_q8_K (ggml/QuantizeQ8.cpp:216-266), vec_dot_q4_K_q8_K (ggml/VecDotQ4.cpp:32-345, AVX2 body
+// :220-283) and vec_dot_q6_K_q8_K (ggml/VecDotQ6.cpp:32-262).
+//
+// Weights stay in the .mllm file's native super-blocks (block_q4_K 144 B, block_q6_K 210 B per 256 weights,
+// mllm/DataType.hpp:93-98, :123-128).  Activations are quantised once per call into native block_q8_K (292 B: float d,
+// 256 x int8, 16 x int16 group sums), bytes identical to the reference's.  Per super-block the kernels form the same
+// two exact integers the reference forms -- sum_sb scale_sb * (q . q8) and sum_sb min_sb * bsum_sb -- and apply
+// d = d_x * fp16(d_w), dmin = -d_x * fp16(dmin_w) with one fp32 FMA each; only the order of the fp32 accumulation over
+// super-blocks differs from the 8 AVX lanes (tolerance in the tests).
+#include "common.cuh"
+
+#define QK_K 256
+#define Q4K_BYTES 144
+#define Q6K_BYTES 210
+#define Q8K_BYTES 292
+
+// nearest_int (ggml/Quantize.hpp:174-180)
+static __device__ __forceinline__ int nearest_int_dev(float f) {
+    const float v = __fadd_rn(f, 12582912.f);
+    return (int)(__float_as_uint(v) & 0x007fffffu) - 0x00400000;
+}
+
+// ------------------------------------------------------------ quantize_row_q8_K
+// one warp per super-block, lane l owns elements 8l..8l+7
+__global__ void __launch_bounds__(128) k_quantize_q8_K(const float *__restrict__ x, uint8_t *__restrict__ y, long long nblk, int nb, int ldx) {
+    const int lane = threadIdx.x & 31;
+    const long long blk = (long long)blockIdx.x * 4 + (threadIdx.x >> 5);
+    if (blk >= nblk) return;
+    const long long row = blk / nb;
+    const int b = (int)(blk % nb);
+    const float *xp = x + (size_t)row * ldx + (size_t)b * QK_K + lane * 8;
+    const float4 v0 = *(const float4 *)xp, v1 = *(const float4 *)(xp + 4);
+    const float v[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
+    // first element with the largest |x| decides the sign of the scale (strict > in the reference's scan)
+    float amax = 0.f, mx = 0.f;
+    int idx = 0x7fffffff;
+#pragma unroll
+    for (int j = 0; j < 8; j++) {
+        const float ax = fabsf(v[j]);
+        if (ax > amax) { amax = ax; mx = v[j]; idx = lane * 8 + j; }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const float oa = __shfl_xor_sync(0xffffffffu, amax, o);
+        const float om = __shfl_xor_sync(0xffffffffu, mx, o);
+        const int oi = __shfl_xor_sync(0xffffffffu, idx, o);
+        if (oa > amax || (oa == amax && oi < idx)) { amax = oa; mx = om; idx = oi; }
+    }
+    uint8_t *out = y + (size_t)blk * Q8K_BYTES;
+    int q[8];
+    float d = 0.f;
+    if (amax == 0.f) {
+#pragma unroll
+        for (int j = 0; j < 8; j++) q[j] = 0;
+    } else {
+        const float iscale = __fdiv_rn(-128.f, mx);
+#pragma unroll
+        for (int j = 0; j < 8; j++) q[j] = min(127, nearest_int_dev(__fmul_rn(iscale, v[j])));
+        d = __fdiv_rn(1.f, iscale);
+    }
+    int s = 0;
+#pragma unroll
+    for (int j = 0; j < 8; j++) s += q[j];
+    const int s2 = s + __shfl_xor_sync(0xffffffffu, s, 1);
+    uint32_t w0 = 0, w1 = 0;
+#pragma unroll
+    for (int j = 0; j < 4; j++) { w0 |= (uint32_t)(q[j] & 0xFF) << (8 * j); w1 |= (uint32_t)(q[4 + j] & 0xFF) << (8 * j); }
+    *(uint32_t *)(out + 4 + lane * 8) = w0; // blocks are 292 B apart: only 4-byte alignment is guaranteed
+    *(uint32_t *)(out + 8 + lane * 8) = w1;
+    if ((lane & 1) == 0) *(int16_t *)(out + 260 + (lane >> 1) * 2) = (int16_t)s2; // all-zero block: 0 (the reference leaves it unwritten)
+    if (lane == 0) *(float *)out = d;
+}
+
+MLLMCU_API int mllmcu_quantize_q8_K(const float *x, void *y_blocks, int rows, int k, int ldx, void *stream) {
+    if (rows <= 0 || k <= 0 || k % QK_K || ldx % 4 || ((uintptr_t)x & 15) || ((uintptr_t)y_blocks & 3)) return -1;
+    const long long nblk = (long long)rows * (k / QK_K);
+    k_quantize_q8_K<<<(unsigned)((nblk + 3) / 4), 128, 0, (cudaStream_t)stream>>>(x, (uint8_t *)y_blocks, nblk, k / QK_K, ldx);
+    CU_LAUNCH_CHECK();
+    return 0;
+}
+
+// ------------------------------------------------------------ weight decode
+// get_scale_min_k4 (ggml/QuantizeQ4.cpp:177-184)
+static __device__ __forceinline__ void q4k_scale_min(const uint8_t *q, int j, int &sc, int &mn) {
+    if (j < 4) { sc = q[j] & 63; mn = q[j + 4] & 63; }
+    else { sc = (q[j + 4] & 0xF) | ((q[j - 4] >> 6) << 4); mn = (q[j + 4] >> 4) | ((q[j] >> 6) << 4); }
+}
+// the 32 weights of chunk c (elements 32c..32c+31) of a super-block as 8 words of int8
+//   Q4_K: values 0..15 (the min term carries the offset); Q6_K: values -32..31
+template <int WT>
+static __device__ __forceinline__ void kq_chunk_words(const uint8_t *blk, int c, int *w) {
+    if (WT == 12) {
+        const uint4 *p = (const uint4 *)(blk + 16 + (c >> 1) * 32);
+        const uint4 a = p[0], b = p[1];
+        const uint32_t r[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+#pragma unroll
+        for (int j = 0; j < 8; j++) w[j] = (int)((c & 1) ? ((r[j] >> 4) & 0x0F0F0F0Fu) : (r[j] & 0x0F0F0F0Fu));
+    } else {
+        const int n = c >> 2, g = c & 3;
+        const uint16_t *ql = (const uint16_t *)(blk + n * 64 + ((g & 1) ? 32 : 0));
+        const uint16_t *qh = (const uint16_t *)(blk + 128 + n * 32);
+#pragma unroll
+        for (int j = 0; j < 8; j++) {
+            const uint32_t l = (uint32_t)ql[2 * j] | ((uint32_t)ql[2 * j + 1] << 16);
+            const uint32_t h = (uint32_t)qh[2 * j] | ((uint32_t)qh[2 * j + 1] << 16);
+            const uint32_t nib = (g >= 2) ? ((l >> 4) & 0x0F0F0F0Fu) : (l & 0x0F0F0F0Fu);
+            const uint32_t hi = ((h >> (2 * g)) & 0x03030303u) << 4;
+            w[j] = (int)__vsub4(nib | hi, 0x20202020u);
+        }
+    }
+}
+
+// ------------------------------------------------------------------- GEMV
+// M <= 8 rows (decode).  One warp per output row; lane l takes chunk l%8 of super-block l/8 + 4*it, the 8 lanes of a
+// super-block add their integers (exactly what the reference sums) before the fp32 FMA.
+template <int WT, int M>
+__global__ void __launch_bounds__(128) k_gemv_kq(const uint8_t *__restrict__ W, const uint8_t *__restrict__ xq, const float *__restrict__ bias,
+                                                 void *y, int N, int nb, int ldy, int out_f16) {
+    constexpr int BS = (WT == 12) ? Q4K_BYTES : Q6K_BYTES;
+    const int lane = threadIdx.x & 31;
+    const int n = blockIdx.x * 4 + (threadIdx.x >> 5);
+    if (n >= N) return;
+    const uint8_t *row = W + (size_t)n * nb * BS;
+    const int c = lane & 7;
+    float acc[M], accm[M];
+#pragma unroll
+    for (int m = 0; m < M; m++) { acc[m] = 0.f; accm[m] = 0.f; }
+    for (int i0 = 0; i0 < nb; i0 += 4) {
+        const int i = i0 + (lane >> 3);
+        const bool on = i < nb;
+        const uint8_t *blk = row + (size_t)(on ? i : 0) * BS;
+        int w[8];
+        kq_chunk_words<WT>(blk, c, w);
+        int sc0, sc1 = 0, mn = 0;
+        float dw, dminw = 0.f;
+        if (WT == 12) {
+            q4k_scale_min(blk + 4, c, sc0, mn);
+            dw = __half2float(*(const __half *)blk);
+            dminw = __half2float(*(const __half *)(blk + 2));
+        } else {
+            sc0 = (int)(int8_t)blk[192 + 2 * c];
+            sc1 = (int)(int8_t)blk[192 + 2 * c + 1];
+            dw = __half2float(*(const __half *)(blk + 208));
+        }
+#pragma unroll
+        for (int m = 0; m < M; m++) {
+            const uint8_t *xb = xq + ((size_t)m * nb + (on ? i : 0)) * Q8K_BYTES;
+            const int *a = (const int *)(xb + 4 + c * 32);
+            int vi, vm = 0;
+            if (WT == 12) {
+                int is = 0;
+#pragma unroll
+                for (int j = 0; j < 8; j++) is = __dp4a(w[j], a[j], is);
+                vi = sc0 * is;
+                const int16_t *bs = (const int16_t *)(xb + 260);
+                vm = mn * ((int)bs[2 * c] + (int)bs[2 * c + 1]);
+            } else {
+                int i0s = 0, i1s = 0;
+#pragma unroll
+                for (int j = 0; j < 4; j++) { i0s = __dp4a(w[j], a[j], i0s); i1s = __dp4a(w[4 + j], a[4 + j], i1s); }
+                vi = sc0 * i0s + sc1 * i1s;
+            }
+            if (!on) { vi = 0; vm = 0; }
+#pragma unroll
+            for (int o = 1; o < 8; o <<= 1) {
+                vi += __shfl_xor_sync(0xffffffffu, vi, o);
+                if (WT == 12) vm += __shfl_xor_sync(0xffffffffu, vm, o);
+            }
+            if (c == 0 && on) {
+                const float dx = *(const float *)xb;
+                acc[m] = fmaf(__fmul_rn(dx, dw), (float)vi, acc[m]);
+                if (WT == 12) accm[m] = fmaf(__fmul_rn(-dx, dminw), (float)vm, accm[m]);
+            }
+        }
+    }
+#pragma unroll
+    for (int m = 0; m < M; m++) {
+        float v = warp_sum(acc[m]);
+        if (WT == 12) v = __fadd_rn(v, warp_sum(accm[m]));
+        if (lane == 0) {
+            if (bias) v = __fadd_rn(v, bias[n]);
+            if (out_f16) ((__half *)y)[(size_t)m * ldy + n] = __float2half_rn(v);
+            else ((float *)y)[(size_t)m * ldy + n] = v;
+        }
+    }
+}
+
+// ------------------------------------------------------------------- GEMM
+// 64x64 output tile per CTA of 256 threads (4x4 per thread); one 32-element chunk per step, integer accumulators carried
+// across the 8 chunks of a super-block and folded into fp32 once per super-block.
+template <int WT>
+__global__ void __launch_bounds__(256) k_gemm_kq(const uint8_t *__restrict__ W, const uint8_t *__restrict__ xq, const float *__restrict__ bias,
+                                                 void *y, int M, int N, int nb, int ldy, int out_f16) {
+    constexpr int BM = 64, BN = 64;
+    constexpr int BS = (WT == 12) ? Q4K_BYTES : Q6K_BYTES;
+    __shared__ int sA[BM][9];
+    __shared__ int sB[BN][9];
+    __shared__ int sAbs[BM];           // bsums pair of the chunk
+    __shared__ int sBsc[BN][2], sBmn[BN];
+    __shared__ float sAd[BM], sBd[BN], sBdm[BN];
+    const int m0 = blockIdx.y * BM, n0 = blockIdx.x * BN;
+    const int t = threadIdx.x, tx = t & 15, ty = t >> 4;
+    float acc[4][4], accm[4][4];
+    int iacc[4][4], macc[4][4];
+#pragma unroll
+    for (int i = 0; i < 4; i++)
+#pragma unroll
+        for (int j = 0; j < 4; j++) { acc[i][j] = 0.f; accm[i][j] = 0.f; iacc[i][j] = 0; macc[i][j] = 0; }
+    for (int sbk = 0; sbk < nb; sbk++) {
+        for (int c = 0; c < 8; c++) {
+            if (t < 128) { // activations: 64 rows x 2 halves of 4 words
+                const int r = t >> 1, h = t & 1;
+                int4 v = make_int4(0, 0, 0, 0);
+                if (m0 + r < M) {
+                    const uint8_t *xb = xq + ((size_t)(m0 + r) * nb + sbk) * Q8K_BYTES;
+                    const int *a = (const int *)(xb + 4 + c * 32 + h * 16);
+                    v = make_int4(a[0], a[1], a[2], a[3]);
+                    if (h == 0) {
+                        const int16_t *bs = (const int16_t *)(xb + 260);
+                        sAbs[r] = (int)bs[2 * c] + (int)bs[2 * c + 1];
+                        if (c == 0) sAd[r] = *(const float *)xb;
+                    }
+                } else if (h == 0) { sAbs[r] = 0; if (c == 0) sAd[r] = 0.f; }
+                sA[r][h * 4 + 0] = v.x; sA[r][h * 4 + 1] = v.y; sA[r][h * 4 + 2] = v.z; sA[r][h * 4 + 3] = v.w;
+            } else if (t < 192) { // weights: one row's chunk per thread
+                const int r = t - 128;
+                int w[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+                int sc0 = 0, sc1 = 0, mn = 0;
+                if (n0 + r < N) {
+                    const uint8_t *blk = W + ((size_t)(n0 + r) * nb + sbk) * BS;
+                    kq_chunk_words<WT>(blk, c, w);
+                    if (WT == 12) {
+                        q4k_scale_min(blk + 4, c, sc0, mn);
+                        sc1 = sc0;
+                        if (c == 0) { sBd[r] = __half2float(*(const __half *)blk); sBdm[r] = __half2float(*(const __half *)(blk + 2)); }
+                    } else {
+                        sc0 = (int)(int8_t)blk[192 + 2 * c];
+                        sc1 = (int)(int8_t)blk[192 + 2 * c + 1];
+                        if (c == 0) { sBd[r] = __half2float(*(const __half *)(blk + 208)); sBdm[r] = 0.f; }
+                    }
+                } else if (c == 0) { sBd[r] = 0.f; sBdm[r] = 0.f; }
+#pragma unroll
+                for (int j = 0; j < 8; j++) sB[r][j] = w[j];
+                sBsc[r][0] = sc0; sBsc[r][1] = sc1; sBmn[r] = mn;
+            }
+            __syncthreads();
+            int lo[4][4], hi[4][4];
+#pragma unroll
+            for (int i = 0; i < 4; i++)
+#pragma unroll
+                for (int j = 0; j < 4; j++) { lo[i][j] = 0; hi[i][j] = 0; }
+#pragma unroll
+            for (int w = 0; w < 8; w++) {
+                int a[4], bb[4];
+#pragma unroll
+                for (int i = 0; i < 4; i++) a[i] = sA[ty * 4 + i][w];
+#pragma unroll
+                for (int j = 0; j < 4; j++) bb[j] = sB[tx * 4 + j][w];
+#pragma unroll
+                for (int i = 0; i < 4; i++)
+#pragma unroll
+                    for (int j = 0; j < 4; j++) {
+                        if (w < 4) lo[i][j] = __dp4a(a[i], bb[j], lo[i][j]);
+                        else hi[i][j] = __dp4a(a[i], bb[j], hi[i][j]);
+                    }
+            }
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+                const int s0 = sBsc[tx * 4 + j][0], s1 = sBsc[tx * 4 + j][1], mn = sBmn[tx * 4 + j];
+#pragma unroll
+                for (int i = 0; i < 4; i++) {
+                    iacc[i][j] += s0 * lo[i][j] + s1 * hi[i][j];
+                    if (WT == 12) macc[i][j] += mn * sAbs[ty * 4 + i];
+                }
+            }
+            if (c == 7) {
+#pragma unroll
+                for (int i = 0; i < 4; i++)
+#pragma unroll
+                    for (int j = 0; j < 4; j++) {
+                        const float dx = sAd[ty * 4 + i];
+                        acc[i][j] = fmaf(__fmul_rn(dx, sBd[tx * 4 + j]), (float)iacc[i][j], acc[i][j]);
+                        if (WT == 12) accm[i][j] = fmaf(__fmul_rn(-dx, sBdm[tx * 4 + j]), (float)macc[i][j], accm[i][j]);
+                        iacc[i][j] = 0; macc[i][j] = 0;
+                    }
+            }
+            __syncthreads();
+        }
+    }
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+        const int m = m0 + ty * 4 + i;
+        if (m >= M) continue;
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            const int n = n0 + tx * 4 + j;
+            if (n >= N) continue;
+            float v = acc[i][j];
+            if (WT == 12) v = __fadd_rn(v, accm[i][j]);
+            if (bias) v = __fadd_rn(v, bias[n]);
+            if (out_f16) ((__half *)y)[(size_t)m * ldy + n] = __float2half_rn(v);
+            else ((float *)y)[(size_t)m * ldy + n] = v;
+        }
+    }
+}
+
+size_t kq_workspace_bytes(int M, int K) { return (K % QK_K) ? 0 : (size_t)M * (K / QK_K) * Q8K_BYTES + 256; }
+
+template <int WT>
+static int launch_kq(const uint8_t *W, const uint8_t *xq, const float *bias, void *y, int M, int N, int nb, int ldy, int out_f16, cudaStream_t st) {
+    if (M <= 8) {
+        const dim3 grid((N + 3) / 4), block(128);
+        switch (M) {
+#define CASE(m) case m: k_gemv_kq<WT, m><<<grid, block, 0, st>>>(W, xq, bias, y, N, nb, ldy, out_f16); break;
+            CASE(1) CASE(2) CASE(3) CASE(4) CASE(5) CASE(6) CASE(7) CASE(8)
+#undef CASE
+        }
+    } else {
+        const dim3 grid((N + 63) / 64, (M + 63) / 64);
+        k_gemm_kq<WT><<<grid, 256, 0, st>>>(W, xq, bias, y, M, N, nb, ldy, out_f16);
+    }
+    CU_LAUNCH_CHECK();
+    return 0;
+}
+
+// called by mllmcu_linear for wtype 12 (Q4_K) / 14 (Q6_K)
+int launch_linear_kq(int wtype, const void *W, const float *x, const float *bias, void *y, int M, int N, int K, int ldx, int ldy, int out_f16,
+                     void *ws, cudaStream_t st) {
+    if (K % QK_K || ldx % 4 || ((uintptr_t)x & 15)) return -1;
+    if (wtype == 12 && ((uintptr_t)W & 15)) return -1;
+    if (wtype == 14 && ((uintptr_t)W & 1)) return -1;
+    const int rc = mllmcu_quantize_q8_K(x, ws, M, K, ldx, st);
+    if (rc) return rc;
+    return wtype == 12 ? launch_kq<12>((const uint8_t *)W, (const uint8_t *)ws, bias, y, M, N, K / QK_K, ldy, out_f16, st)
+                       : launch_kq<14>((const uint8_t *)W, (const uint8_t *)ws, bias, y, M, N, K / QK_K, ldy, out_f16, st);
+}
+
+// ------------------------------------------------- exact integers per super-block (test / diagnostic hook)
+// sumi[n][m][i] = sum_sb scale_sb * (q4 . q8), summ[n][m][i] = sum_sb min_sb * (bsums[2sb] + bsums[2sb+1])
+__global__ void k_block_isums_q4_K(const uint8_t *__restrict__ W, const uint8_t *__restrict__ xq, int32_t *__restrict__ sumi, int32_t *__restrict__ summ,
+                                   int M, int N, int nb) {
+    const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= (long long)M * N * nb) return;
+    const int i = (int)(idx % nb);
+    const int m = (int)((idx / nb) % M);
+    const int n = (int)(idx / ((long long)nb * M));
+    const uint8_t *blk = W + ((size_t)n * nb + i) * Q4K_BYTES;
+    const uint8_t *xb = xq + ((size_t)m * nb + i) * Q8K_BYTES;
+    const int16_t *bs = (const int16_t *)(xb + 260);
+    int si = 0, sm = 0;
+    for (int c = 0; c < 8; c++) {
+        int w[8], sc, mn, is = 0;
+        kq_chunk_words<12>(blk, c, w);
+        q4k_scale_min(blk + 4, c, sc, mn);
+        const int *a = (const int *)(xb + 4 + c * 32);
+#pragma unroll
+        for (int j = 0; j < 8; j++) is = __dp4a(w[j], a[j], is);
+        si += sc * is;
+        sm += mn * ((int)bs[2 * c] + (int)bs[2 * c + 1]);
+    }
+    sumi[idx] = si;
+    summ[idx] = sm;
+}
+MLLMCU_API int mllmcu_block_isums_q4_K_q8_K(const void *W, const void *xq_blocks, int32_t *sumi, int32_t *summ, int M, int N, int K, void *stream) {
+    if (K % QK_K || M <= 0 || N <= 0 || ((uintptr_t)W & 15)) return -1;
+    const int nb = K / QK_K;
+    const long long tot = (long long)M * N * nb;
+    k_block_isums_q4_K<<<(unsigned)((tot + 127) / 128), 128, 0, (cudaStream_t)stream>>>((const uint8_t *)W, (const uint8_t *)xq_blocks, sumi, summ, M, N, nb);
+    CU_LAUNCH_CHECK();
+    return 0;
+}

@@ -213,11 +213,17 @@ bool gemm_tc_supported(int wtype, int M, int N, int K);
 int launch_gemm_q4_0_tc(const void *W, const float *x, int ldx, const float *bias, void *y, int M, int N, int K, int ldy, int out_f16,
                         void *ws, cudaStream_t st);
 
+// k-quant weights (kquants.cu)
+size_t kq_workspace_bytes(int M, int K);
+int launch_linear_kq(int wtype, const void *W, const float *x, const float *bias, void *y, int M, int N, int K, int ldx, int ldy, int out_f16,
+                     void *ws, cudaStream_t st);
+
 MLLMCU_API size_t mllmcu_linear_workspace_bytes(int M, int K) {
     if (M <= 0 || K <= 0) return 0;
-    const size_t a = align_up((size_t)M * K, 256) + align_up((size_t)M * (K / QK) * sizeof(float), 256);
-    const size_t b = gemm_tc_workspace_bytes(M, K);
-    return a > b ? a : b;
+    size_t a = align_up((size_t)M * K, 256) + align_up((size_t)M * (K / QK) * sizeof(float), 256);
+    const size_t b = gemm_tc_workspace_bytes(M, K), c = kq_workspace_bytes(M, K);
+    if (b > a) a = b;
+    return c > a ? c : a;
 }
 
 template <int WT>
@@ -237,9 +243,10 @@ static int launch_gemv(int M, const uint8_t *W, const int8_t *xq, const float *x
 MLLMCU_API int mllmcu_linear(int wtype, const void *W, const float *x, const float *bias, void *y, int M, int N, int K,
                              int ldx, int ldy, int out_f16, void *ws, size_t ws_bytes, void *stream) {
     if (M <= 0 || N <= 0 || K <= 0 || K % QK) return -1;
-    if (wtype != 2 && wtype != 8) return -2;
+    if (wtype != 2 && wtype != 8 && wtype != 12 && wtype != 14) return -2;
     if (ws == nullptr || ws_bytes < mllmcu_linear_workspace_bytes(M, K)) return -3;
     cudaStream_t st = (cudaStream_t)stream;
+    if (wtype == 12 || wtype == 14) return launch_linear_kq(wtype, W, x, bias, y, M, N, K, ldx, ldy, out_f16, ws, st);
     if (gemm_tc_supported(wtype, M, N, K) && !((uintptr_t)W & 15)) return launch_gemm_q4_0_tc(W, x, ldx, bias, y, M, N, K, ldy, out_f16, ws, st);
     int8_t *xq = (int8_t *)ws;
     float *xd = (float *)((char *)ws + align_up((size_t)M * K, 256));
