@@ -234,7 +234,7 @@ int mllmcu_gelu_table(const float *x, float *y, size_t n, const void *table_f16,
  * row s sees (causal && S > 1) ? s + 1 + old_dim : n entries, the rest of the row is written 0.  Bit-identical to
  * the AVX2 build of the reference for the vector part (same polynomial exp, same summation order). */
 int mllmcu_softmax(const float *x, float *y, int outer, int S, int n, int causal, int old_dim, void *stream);
-/* x / s, IEEE division (q / sqrt(D) of the eager spelling; CPUdivintFunction, op/CPUBinaryFunc.hpp) */
+/* x / s, IEEE division (q / sqrt(D) of the eager spelling; CPUdivFunction, op/CPUBinaryFunc.hpp) */
 int mllmcu_div_scalar(const float *x, float s, float *y, size_t n, void *stream);
 
 /* ---- M-RoPE: CPUMultimodalRoPE (op/CPUMultimodalRoPE.cpp:25-331).  The per-call tables ([S][dim], sections of the

@@ -140,15 +140,16 @@ class LlamaModel:
             pass
 
 
-def run_op(params, name, inputs, path=""):
+def run_op(params, name, inputs, path="", shapes=None):
     """One op through Backend::opCreate + runOp (the test/cpu/CPUTest.hpp per-op pattern).
-    params: dict OpParam (must hold 'type'); inputs: list of fp32 arrays shaped [b,h,s,d]."""
+    params: dict OpParam (must hold 'type'); inputs: list of fp32 arrays shaped [b,h,s,d] -- or, with `shapes`
+    (a list of logical (b,h,s,d) per input), arrays already in BSHD memory order."""
     init_backend()
     keys = (C.c_char_p * len(params))(*[k.encode() for k in params])
     vals = np.array(list(params.values()), dtype=np.float32)
     ins = [np.ascontiguousarray(a, dtype=np.float32) for a in inputs]
     ptrs = (C.c_void_p * len(ins))(*[a.ctypes.data for a in ins])
-    shapes = np.array([a.shape for a in ins], dtype=np.int32)
+    shapes = np.array([a.shape for a in ins] if shapes is None else shapes, dtype=np.int32)
     out = np.empty(1 << 24, dtype=np.float32)
     oshape = np.zeros(4, dtype=np.int32)
     _check(lib().mllm_cuda_run_op(keys, _p(vals), len(params), name.encode(), path.encode(), ptrs, _p(shapes), len(ins), _p(out), _p(oshape)))

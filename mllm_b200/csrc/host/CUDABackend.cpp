@@ -26,16 +26,17 @@ size_t dtype_block_bytes(DataType t) {
     switch (t) {
     case MLLM_TYPE_F32: case MLLM_TYPE_I32: return 4;
     case MLLM_TYPE_F16: return 2;
-    case MLLM_TYPE_Q4_0: return 18;
+    case MLLM_TYPE_Q4_0: case MLLM_TYPE_Q4_0_4_4: return 18; // Q4_0_4_4: 72 B per 4 interleaved blocks (DataType.hpp:104-107)
     case MLLM_TYPE_Q8_0: return 34;
     case MLLM_TYPE_Q4_K: return 144;
+    case MLLM_TYPE_Q6_K: return 210;
     default: throw std::runtime_error("[mllm-cuda] unsupported dtype");
     }
 }
 int dtype_block_elems(DataType t) {
     switch (t) {
-    case MLLM_TYPE_Q4_0: case MLLM_TYPE_Q8_0: return 32;
-    case MLLM_TYPE_Q4_K: return 256;
+    case MLLM_TYPE_Q4_0: case MLLM_TYPE_Q8_0: case MLLM_TYPE_Q4_0_4_4: return 32;
+    case MLLM_TYPE_Q4_K: case MLLM_TYPE_Q6_K: return 256;
     default: return 1;
     }
 }

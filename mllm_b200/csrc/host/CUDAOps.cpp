@@ -13,6 +13,14 @@
 //   CPUviewFunction (op/CPUViewFunc.hpp)           -> CUDAView
 //   CPUclipFunction (op/CPUClipFunc.hpp)           -> CUDAClip
 //   CPUFlashAttention2Func (op/CPUFlashAttention2Func.hpp) -> CUDAFlashAttention2
+//   CPUGELU / CPUQuickGELU (op/CPUGELU.cpp, op/CPUQuickGELU.cpp) -> CUDAGelu
+//   CPUSoftMax (op/CPUSoftMax.cpp)                 -> CUDASoftMax
+//   CPUmmFunction (op/CPUMatmulFunc.hpp)           -> CUDAMatmulFunc
+//   CPUdivintFunction (op/CPUBinaryFunc.hpp)       -> CUDADivScalar
+//   CPUtransposeFunction (op/CPUTransposeFunc.hpp) -> CUDATranspose (HEAD <-> SEQUENCE, physical)
+//   CPUConvolution2D (op/CPUConvolution2D.cpp)     -> CUDAConvolution2D
+//   CPUMultimodalRoPE (op/CPUMultimodalRoPE.cpp)   -> CUDAMultimodalRoPE
+//   CPUVisionRoPEFuncFunction (op/CPUVisionRoPEFunc.hpp) -> CUDAVisionRoPEFunc
 #include "mllm_cuda.hpp"
 
 #include <cmath>
@@ -44,11 +52,28 @@ public:
         DataType dt = loader.getDataType(weight_.name());
         const bool absent = (dt == MLLM_TYPE_COUNT);
         if (absent) dt = Op::noLoadWeightsDtype();
-        if (dt != MLLM_TYPE_Q4_0 && dt != MLLM_TYPE_Q8_0)
+        if (dt != MLLM_TYPE_Q4_0 && dt != MLLM_TYPE_Q8_0 && dt != MLLM_TYPE_Q4_K && dt != MLLM_TYPE_Q6_K && dt != MLLM_TYPE_Q4_0_4_4)
             throw std::runtime_error("[mllm-cuda] Linear " + name() + ": weight dtype " + std::to_string((int)dt) + " not supported by the CUDA backend yet");
-        weight_.setDtype(dt);
-        weight_.alloc();
-        if (!absent) loader.load(&weight_);
+        if ((dt == MLLM_TYPE_Q4_K || dt == MLLM_TYPE_Q6_K) && in_ % 256) throw std::runtime_error("[mllm-cuda] Linear " + name() + ": k-quant weights need in_features % 256 == 0");
+        if (dt == MLLM_TYPE_Q4_0_4_4) {
+            // shipped *-q4_0_4_4.mllm: upload the 4-row-interleaved blocks, de-interleave once on the device into plain Q4_0 rows
+            // (same nibbles and scales; ggml/GemmPack.cpp:45-60), after which this is an ordinary Q4_0 Linear
+            if (out_ % 4) throw std::runtime_error("[mllm-cuda] Linear " + name() + ": Q4_0_4_4 needs out_features % 4 == 0");
+            Tensor packed(backend_);
+            packed.setName(weight_.name());
+            packed.reshape(1, 1, out_, in_);
+            packed.setDtype(MLLM_TYPE_Q4_0_4_4);
+            packed.alloc();
+            loader.load(&packed);
+            weight_.setDtype(MLLM_TYPE_Q4_0);
+            weight_.alloc();
+            MLLMCU_CHECK(mllmcu_q4_0_4x4_to_q4_0(packed.rawDevPtr(), weight_.rawDevPtr(), out_, in_, cb(backend_)->stream()));
+            cb(backend_)->sync();
+        } else {
+            weight_.setDtype(dt);
+            weight_.alloc();
+            if (!absent) loader.load(&weight_);
+        }
         if (bias_) {
             biasT_ = Tensor(backend_);
             biasT_.setName(name() + ".bias");
@@ -483,6 +508,290 @@ private:
     bool causal_;
 };
 
+
+// ------------------------------------------------------ GELU / QuickGELU
+// host-side fp16 <-> fp32 (IEEE, round-to-nearest-even) for building the lookup tables exactly as init_table_gelu_f16 does
+static float h2f(uint16_t h) {
+    const uint32_t sign = (uint32_t)(h & 0x8000) << 16;
+    uint32_t e = (h >> 10) & 0x1F, m = h & 0x3FF, u;
+    if (e == 0) {
+        if (m == 0) u = sign;
+        else { int sh = 0; while (!(m & 0x400)) { m <<= 1; sh++; } u = sign | ((uint32_t)(113 - sh) << 23) | ((m & 0x3FF) << 13); }
+    } else if (e == 31) u = sign | 0x7F800000u | (m << 13) | (m ? 0x400000u : 0);
+    else u = sign | ((e + 112) << 23) | (m << 13);
+    float f; memcpy(&f, &u, 4); return f;
+}
+static uint16_t f2h(float f) {
+    uint32_t u; memcpy(&u, &f, 4);
+    const uint16_t sign = (uint16_t)((u >> 16) & 0x8000);
+    u &= 0x7FFFFFFFu;
+    if (u >= 0x7F800000u) return sign | 0x7C00 | (u > 0x7F800000u ? (0x200 | ((u >> 13) & 0x3FF)) : 0);
+    if (u >= 0x477FF000u) return sign | 0x7C00; // rounds to >= 65520 -> inf
+    if (u < 0x33000001u) return sign;           // < 2^-25 (or exactly 2^-25, ties to even 0)
+    const int e = (int)(u >> 23) - 127;
+    uint32_t m = (u & 0x7FFFFFu) | 0x800000u;
+    int shift = e < -14 ? (13 + (-14 - e)) : 13;
+    uint32_t r = m >> shift, rem = m & ((1u << shift) - 1), halfv = 1u << (shift - 1);
+    if (rem > halfv || (rem == halfv && (r & 1))) r++;
+    if (e < -14) return sign | (uint16_t)r; // subnormal (r may carry into the smallest normal: same bits)
+    return sign | (uint16_t)(((uint32_t)(e + 15) << 10) + (r - 0x400));
+}
+
+class CUDAGelu final : public Op { // kind 0: mllm_vec_gelu_f32, 1: mllm_vec_gelu_quick_f32 (ggml/Quantize.hpp:74-133)
+public:
+    CUDAGelu(Backend *bn, string name, int kind) : Op(bn, name), kind_(kind) {}
+    ErrorCode reshape(vector<shared_ptr<Tensor>> in, vector<shared_ptr<Tensor>> out) override {
+        out[0]->reshape(in[0]->batch(), in[0]->head(), in[0]->sequence(), in[0]->dimension());
+        return MLLM_NO_ERROR;
+    }
+    ErrorCode execute(vector<shared_ptr<Tensor>> in, vector<shared_ptr<Tensor>> out) override {
+        auto *b = cb(backend_);
+        if (!table_.allocated()) { // built once per op, like the reference's lazily initialised static tables
+            std::vector<uint16_t> t(1 << 16);
+            for (int i = 0; i < (1 << 16); i++) {
+                const float x = h2f((uint16_t)i);
+                // gelu: g++ -O3 with FMA contracts 1 + (A*x)*x into one fma in the reference build (pinned by tests/golden)
+                const float g = kind_ == 0 ? 0.5f * x * (1.0f + tanhf(0.79788456080286535587989211986876f * x * std::fmaf(0.044715f * x, x, 1.0f)))
+                                           : x * (1.0f / (1.0f + expf(-1.702f * x)));
+                t[i] = f2h(g);
+            }
+            table_ = Tensor(1, 1, 1, 1 << 16, backend_, false);
+            table_.setDtype(MLLM_TYPE_F16);
+            table_.alloc();
+            table_.copyFromHost(t.data());
+        }
+        MLLMCU_CHECK(mllmcu_gelu_table(in[0]->devPtr<float>(), out[0]->devPtr<float>(), in[0]->count(), table_.rawDevPtr(), b->stream()));
+        b->kernel_launches++;
+        return MLLM_NO_ERROR;
+    }
+
+private:
+    int kind_;
+    Tensor table_;
+};
+
+// ---------------------------------------------------------------- SoftMax
+// CPUSoftMax (op/CPUSoftMax.cpp:29-66), axis = DIMENSION.  In this backend's BSHD memory a [B,H,S,D] score tensor has its
+// rows at (b, s, h): the kernel's row index only needs s for the causal length, so rows are visited as outer = B, S, n = D per
+// head by running one launch per head slice when H > 1 would break contiguity -- scores produced by CUDAMatmulFunc are stored
+// head-major ([B][H][S][D] dense, flagged through origin "bhsd"), which is what this op expects.
+class CUDASoftMax final : public Op {
+public:
+    CUDASoftMax(Backend *bn, string name, int axis, bool causal) : Op(bn, name), axis_(axis), causal_(causal) {}
+    ErrorCode reshape(vector<shared_ptr<Tensor>> in, vector<shared_ptr<Tensor>> out) override {
+        out[0]->reshape(in[0]->batch(), in[0]->head(), in[0]->sequence(), in[0]->dimension());
+        return MLLM_NO_ERROR;
+    }
+    ErrorCode execute(vector<shared_ptr<Tensor>> in, vector<shared_ptr<Tensor>> out) override {
+        auto *b = cb(backend_);
+        Tensor &x = *in[0];
+        if (axis_ != 3) throw std::runtime_error("[mllm-cuda] softmax: only axis = DIMENSION");
+        if (x.head() != 1) throw std::runtime_error("[mllm-cuda] softmax: scores must be [B*H,1,S,D] head-major rows (see CUDAMatmulFunc)");
+        const int old_dim = x.dimension() - x.sequence(); // CPUSoftMax.cpp:38-40
+        MLLMCU_CHECK(mllmcu_softmax(x.devPtr<float>(), out[0]->devPtr<float>(), x.batch(), x.sequence(), x.dimension(), causal_, old_dim < 0 ? 0 : old_dim, b->stream()));
+        b->kernel_launches++;
+        return MLLM_NO_ERROR;
+    }
+
+private:
+    int axis_;
+    bool causal_;
+};
+
+// x / scalar: Tensor::operator/(float) -> F_DIV -> CPUdivFunction (Tensor.cpp:445-450, op/CPUBinaryFunc.hpp)
+class CUDADivScalar final : public Op {
+public:
+    CUDADivScalar(Backend *bn, string name, float v) : Op(bn, name), v_(v) {}
+    ErrorCode reshape(vector<shared_ptr<Tensor>> in, vector<shared_ptr<Tensor>> out) override {
+        out[0]->reshape(in[0]->batch(), in[0]->head(), in[0]->sequence(), in[0]->dimension());
+        return MLLM_NO_ERROR;
+    }
+    ErrorCode execute(vector<shared_ptr<Tensor>> in, vector<shared_ptr<Tensor>> out) override {
+        auto *b = cb(backend_);
+        MLLMCU_CHECK(mllmcu_div_scalar(in[0]->devPtr<float>(), v_, out[0]->devPtr<float>(), in[0]->count(), b->stream()));
+        b->kernel_launches++;
+        return MLLM_NO_ERROR;
+    }
+
+private:
+    float v_;
+};
+
+// Tensor::mm (F_MM, op/CPUMatmulFunc.hpp) on fp32 operands laid out head-major: a [G,1,M,K] x b [G,1,N,K]^T (transpose1) or
+// b [G,1,K,N] -> [G,1,M,N], G = batch*heads.  The eager attention spelling reaches it after CUDATranspose (BSHD -> BHSD).
+class CUDAMatmulFunc final : public Op {
+public:
+    CUDAMatmulFunc(Backend *bn, string name, bool t1) : Op(bn, name), t1_(t1) {}
+    ErrorCode reshape(vector<shared_ptr<Tensor>> in, vector<shared_ptr<Tensor>> out) override {
+        Tensor &a = *in[0], &bm = *in[1];
+        if (a.head() != 1 || bm.head() != 1 || a.batch() != bm.batch()) throw std::runtime_error("[mllm-cuda] mm: operands must be [G,1,rows,cols]");
+        const int N = t1_ ? bm.sequence() : bm.dimension();
+        if ((t1_ ? bm.dimension() : bm.sequence()) != a.dimension()) throw std::runtime_error("[mllm-cuda] mm: inner dimensions differ");
+        out[0]->reshape(a.batch(), 1, a.sequence(), N);
+        return MLLM_NO_ERROR;
+    }
+    ErrorCode execute(vector<shared_ptr<Tensor>> in, vector<shared_ptr<Tensor>> out) override {
+        auto *b = cb(backend_);
+        Tensor &a = *in[0], &bm = *in[1], &c = *out[0];
+        const int M = a.sequence(), K = a.dimension(), N = c.dimension();
+        MLLMCU_CHECK(mllmcu_sgemm(a.devPtr<float>(), a.seqStride(), a.batchStride(), bm.devPtr<float>(), t1_ ? bm.seqStride() : 1, t1_ ? 1 : bm.seqStride(),
+                                  bm.batchStride(), nullptr, c.devPtr<float>(), c.seqStride(), c.batchStride(), M, N, K, a.batch(), b->stream()));
+        b->kernel_launches++;
+        return MLLM_NO_ERROR;
+    }
+
+private:
+    bool t1_;
+};
+
+// x.transpose(HEAD, SEQUENCE) as a physical copy (op/CPUTransposeFunc.hpp:127-149): BSHD [B,H,S,D] -> head-major rows,
+// returned as [B*H, 1, S, D] so the matmul / softmax ops above see dense per-head matrices.  Works on cache-slice views.
+class CUDATranspose final : public Op {
+public:
+    CUDATranspose(Backend *bn, string name) : Op(bn, name) {}
+    ErrorCode reshape(vector<shared_ptr<Tensor>> in, vector<shared_ptr<Tensor>> out) override {
+        out[0]->reshape(in[0]->batch() * in[0]->head(), 1, in[0]->sequence(), in[0]->dimension());
+        out[0]->setDtype(in[0]->dtype());
+        return MLLM_NO_ERROR;
+    }
+    ErrorCode execute(vector<shared_ptr<Tensor>> in, vector<shared_ptr<Tensor>> out) override {
+        auto *b = cb(backend_);
+        Tensor &x = *in[0];
+        const int n[4] = {x.batch(), x.head(), x.sequence(), x.dimension()};
+        const long long ss[4] = {x.batchStride(), x.dimension(), x.seqStride(), 1};
+        const long long ds[4] = {(long long)x.head() * x.sequence() * x.dimension(), (long long)x.sequence() * x.dimension(), x.dimension(), 1};
+        MLLMCU_CHECK(mllmcu_copy_strided(x.rawDevPtr(), out[0]->rawDevPtr(), x.dtype() == MLLM_TYPE_F16 ? 2 : 4, n, ss, ds, b->stream()));
+        b->kernel_launches++;
+        return MLLM_NO_ERROR;
+    }
+};
+
+// ------------------------------------------------------------ Convolution2D
+// CPUConvolution2D (op/CPUConvolution2D.cpp) VALID padding: input [B, H=height, S=channel, D=width] (NCHW bytes in BSHD), weight
+// name + ".weight" [O][C][kh][kw] F32, optional bias; output [B, H=oh, S=O, D=ow].
+class CUDAConvolution2D final : public Op {
+public:
+    CUDAConvolution2D(Backend *bn, string name, const OpParam &p)
+        : Op(bn, name), C_((int)p.at("in_channel")), O_((int)p.at("out_channel")), kh_((int)p.at("kernal_h")), kw_((int)p.at("kernal_w")),
+          sh_((int)p.at("stride_h")), sw_((int)p.at("stride_w")), pad_((int)getp(p, "padding", 1)), bias_((bool)getp(p, "bias", 1)) {
+        if (pad_ != 1) throw std::runtime_error("[mllm-cuda] Convolution2D: only VALID padding (the patch-embed case)"); // PaddingType VALID = 1 (Types.hpp)
+    }
+    ErrorCode reshape(vector<shared_ptr<Tensor>> in, vector<shared_ptr<Tensor>> out) override {
+        if (in[0]->sequence() != C_) throw std::runtime_error("[mllm-cuda] Convolution2D: channel mismatch");
+        out[0]->reshape(in[0]->batch(), (in[0]->head() - kh_) / sh_ + 1, O_, (in[0]->dimension() - kw_) / sw_ + 1);
+        return MLLM_NO_ERROR;
+    }
+    ErrorCode load(ParamLoader &loader) override {
+        w_ = Tensor(backend_);
+        w_.setName(name() + ".weight");
+        w_.reshape(O_, kh_, C_, kw_);
+        w_.setDtype(MLLM_TYPE_F32);
+        w_.alloc();
+        if (loader.getDataType(w_.name()) != MLLM_TYPE_COUNT) loader.load(&w_);
+        if (bias_) {
+            b_ = Tensor(backend_);
+            b_.setName(name() + ".bias");
+            b_.reshape(1, 1, 1, O_);
+            b_.setDtype(MLLM_TYPE_F32);
+            b_.alloc();
+            if (loader.getDataType(b_.name()) != MLLM_TYPE_COUNT) loader.load(&b_);
+        }
+        return MLLM_NO_ERROR;
+    }
+    ErrorCode execute(vector<shared_ptr<Tensor>> in, vector<shared_ptr<Tensor>> out) override {
+        auto *b = cb(backend_);
+        Tensor &x = *in[0];
+        MLLMCU_CHECK(mllmcu_conv2d_valid(x.devPtr<float>(), w_.devPtr<float>(), bias_ ? b_.devPtr<float>() : nullptr, out[0]->devPtr<float>(), x.batch(), C_,
+                                         x.head(), x.dimension(), O_, kh_, kw_, sh_, sw_, 0, b->stream()));
+        b->kernel_launches++;
+        return MLLM_NO_ERROR;
+    }
+
+private:
+    int C_, O_, kh_, kw_, sh_, sw_, pad_;
+    bool bias_;
+    Tensor w_, b_;
+};
+
+// ----------------------------------------------------------- MultimodalRoPE
+// CPUMultimodalRoPE (op/CPUMultimodalRoPE.cpp:25-331): inputs {x [B,H,S,D], position_ids [3,1,1,S]}.  The sin/cos tables are
+// rebuilt on the HOST from the ids exactly as multimodal_sinusoidal_position_embedding + apply_multimodal_rotary_pos_emb do
+// (same libm sinf/cosf, so the rotation is bit-identical to the reference), uploaded, and applied rotate-half by row s.
+class CUDAMultimodalRoPE final : public Op {
+public:
+    CUDAMultimodalRoPE(Backend *bn, string name, const OpParam &p) : Op(bn, name), theta_((float)p.at("rope_theta")) {
+        for (int i = 0;; i++) {
+            auto it = p.find("mrope_section_" + std::to_string(i));
+            if (it == p.end()) break;
+            sec_.push_back((int)it->second);
+        }
+        // {16,24,24} (configuration_qwen2_vl.hpp:48) covers the D/2 frequency columns the rotation reads; the rest of the table stays 0
+    }
+    ErrorCode reshape(vector<shared_ptr<Tensor>> in, vector<shared_ptr<Tensor>> out) override {
+        out[0]->reshape(in[0]->batch(), in[0]->head(), in[0]->sequence(), in[0]->dimension());
+        return MLLM_NO_ERROR;
+    }
+    ErrorCode execute(vector<shared_ptr<Tensor>> in, vector<shared_ptr<Tensor>> out) override {
+        auto *b = cb(backend_);
+        Tensor &x = *in[0], &pid = *in[1];
+        const int S = x.sequence(), D = x.dimension(), half = D / 2;
+        if (pid.batch() != 3 || pid.dimension() < S) throw std::runtime_error("[mllm-cuda] MultimodalRoPE: position_ids must be [3,1,1,S]");
+        std::vector<float> pos((size_t)3 * pid.dimension());
+        b->sync();
+        pid.copyToHost(pos.data());
+        std::vector<float> theta(half), sn((size_t)S * D, 0.f), cs((size_t)S * D, 0.f);
+        for (int i = 0; i < half; i++) theta[i] = (float)(1.0 / pow((double)theta_, 2.0 * i / D));
+        int start = 0;
+        for (size_t j = 0; j < sec_.size(); j++) {
+            const int axis = (int)(j % 3);
+            for (int c = start; c < start + sec_[j] && c < D; c++)
+                for (int s = 0; s < S; s++) {
+                    const float value = theta[c % half] * pos[(size_t)axis * pid.dimension() + s];
+                    cs[(size_t)s * D + c] = cosf(value) * 1.0f;
+                    sn[(size_t)s * D + c] = sinf(value) * 1.0f;
+                }
+            start += sec_[j];
+        }
+        if (!sin_.allocated() || sin_.sequence() < S) {
+            sin_ = Tensor(1, 1, S, D, backend_);
+            cos_ = Tensor(1, 1, S, D, backend_);
+        }
+        MLLMCU_CHECK(mllmcu_memcpy_h2d(sin_.rawDevPtr(), sn.data(), sn.size() * 4, b->stream()));
+        MLLMCU_CHECK(mllmcu_memcpy_h2d(cos_.rawDevPtr(), cs.data(), cs.size() * 4, b->stream()));
+        b->sync(); // the host vectors die at scope exit
+        Tensor &y = *out[0];
+        const int f16 = y.dtype() == MLLM_TYPE_F16;
+        MLLMCU_CHECK(mllmcu_rope_mrope(x.devPtr<float>(), y.rawDevPtr(), x.batch(), S, x.head(), D, D, sin_.devPtr<float>(), cos_.devPtr<float>(), D, f16,
+                                       y.batchStride(), y.seqStride(), b->stream()));
+        b->kernel_launches++;
+        return MLLM_NO_ERROR;
+    }
+
+private:
+    float theta_;
+    vector<int> sec_;
+    Tensor sin_, cos_;
+};
+
+// Tensor::apply_rotary_pos_emb_vision (F_APPLY_VISIOROPE, op/CPUVisionRoPEFunc.hpp:20-160): inputs {x [B,H,S,D], rotary_pos_emb
+// [1,1,S,D/2]}; sin/cos of the angles are taken on the device (<= 2 ulp from libm; mllmcu_rope_vision also accepts host tables).
+class CUDAVisionRoPEFunc final : public Op {
+public:
+    CUDAVisionRoPEFunc(Backend *bn, string name) : Op(bn, name) {}
+    ErrorCode reshape(vector<shared_ptr<Tensor>> in, vector<shared_ptr<Tensor>> out) override {
+        out[0]->reshape(in[0]->batch(), in[0]->head(), in[0]->sequence(), in[0]->dimension());
+        return MLLM_NO_ERROR;
+    }
+    ErrorCode execute(vector<shared_ptr<Tensor>> in, vector<shared_ptr<Tensor>> out) override {
+        auto *b = cb(backend_);
+        Tensor &x = *in[0];
+        if (in[1]->dimension() * 2 != x.dimension() || in[1]->sequence() != x.sequence()) throw std::runtime_error("[mllm-cuda] vision rope: rotary_pos_emb must be [1,1,S,D/2]");
+        MLLMCU_CHECK(mllmcu_rope_vision(x.devPtr<float>(), in[1]->devPtr<float>(), nullptr, out[0]->devPtr<float>(), x.batch(), x.sequence(), x.head(), x.dimension(), 0, b->stream()));
+        b->kernel_launches++;
+        return MLLM_NO_ERROR;
+    }
+};
+
 // ---------------------------------------------------------------- creators
 #define CREATOR(cls, expr)                                                                    \
     class cls##Creator : public CUDABackend::Creator {                                        \
@@ -507,6 +816,15 @@ static Op *make_clip(const OpParam &p, Backend *bn, const string &name) {
 }
 CREATOR(CUDAClip, make_clip(p, bn, name))
 CREATOR(CUDAFlashAttention2, new CUDAFlashAttention2(bn, name, (bool)getp(p, "causal_mask", 1)))
+CREATOR(CUDAGelu, new CUDAGelu(bn, name, 0))
+CREATOR(CUDAQuickGelu, new CUDAGelu(bn, name, 1))
+CREATOR(CUDASoftMax, new CUDASoftMax(bn, name, (int)getp(p, "axis", 3), (bool)getp(p, "do_causal_mask", 0)))
+CREATOR(CUDADivScalar, new CUDADivScalar(bn, name, getp(p, "data", 1.f)))
+CREATOR(CUDAMatmulFunc, new CUDAMatmulFunc(bn, name, (bool)getp(p, "transpose1", 0)))
+CREATOR(CUDATranspose, new CUDATranspose(bn, name))
+CREATOR(CUDAConvolution2D, new CUDAConvolution2D(bn, name, p))
+CREATOR(CUDAMultimodalRoPE, new CUDAMultimodalRoPE(bn, name, p))
+CREATOR(CUDAVisionRoPEFunc, new CUDAVisionRoPEFunc(bn, name))
 
 void CUDABackend::registerOps() { // CPUBackend::registerOps, CPUBackend.cpp:142-244
     addCreator(LINEAR, new CUDALinearCreator());
@@ -521,6 +839,15 @@ void CUDABackend::registerOps() { // CPUBackend::registerOps, CPUBackend.cpp:142
     addCreator(F_VIEW, new CUDAViewCreator());
     addCreator(F_CLIP, new CUDAClipCreator());
     addCreator(F_FA2, new CUDAFlashAttention2Creator());
+    addCreator(OP_GELU, new CUDAGeluCreator());
+    addCreator(QUICKGLUE, new CUDAQuickGeluCreator());
+    addCreator(SOFTMAX, new CUDASoftMaxCreator());
+    addCreator(F_DIV, new CUDADivScalarCreator());
+    addCreator(F_MM, new CUDAMatmulFuncCreator());
+    addCreator(F_TRANPOSE, new CUDATransposeCreator());
+    addCreator(CONVOLUTION2D, new CUDAConvolution2DCreator());
+    addCreator(MULTIMODALROPE, new CUDAMultimodalRoPECreator());
+    addCreator(F_APPLY_VISIOROPE, new CUDAVisionRoPEFuncCreator());
 }
 
 } // namespace mllm

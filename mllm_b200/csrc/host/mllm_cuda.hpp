@@ -34,14 +34,15 @@ enum BackendType { MLLM_CPU = 0, MLLM_OPENCL, MLLM_QNN, MLLM_XNNPACK, MLLM_CUDA 
 // ---- mllm/Types.hpp:54-61
 enum ErrorCode { MLLM_NO_ERROR = 0, OUT_OF_MEMORY = 1, NOT_SUPPORT = 2, COMPUTE_SIZE_ERROR = 3, NO_EXECUTION = 4, INVALID_VALUE = 5 };
 // ---- mllm/Types.hpp:63-96 (values used on this path)
-enum DataType { MLLM_TYPE_F32 = 0, MLLM_TYPE_F16 = 1, MLLM_TYPE_Q4_0 = 2, MLLM_TYPE_Q8_0 = 8, MLLM_TYPE_Q4_K = 12, MLLM_TYPE_I32 = 18, MLLM_TYPE_COUNT = 34 };
+enum DataType { MLLM_TYPE_F32 = 0, MLLM_TYPE_F16 = 1, MLLM_TYPE_Q4_0 = 2, MLLM_TYPE_Q8_0 = 8, MLLM_TYPE_Q4_K = 12, MLLM_TYPE_Q6_K = 14, MLLM_TYPE_Q8_K = 15, MLLM_TYPE_I32 = 18, MLLM_TYPE_Q4_0_4_4 = 19, MLLM_TYPE_COUNT = 34 };
 enum ChlType { BSHD = 0 };
 enum RoPEType { NONE = 0, PERSIMMONROPE = 1, LLAMAROPE = 2, HFHUBROPE = 4 };
 // ---- mllm/OpDefined.hpp:10-134 (numeric values must match: OpParam["type"] carries them)
 enum OpType {
     INVALID_VALUE_OP = 0, PARAMETER = 1, ADD = 2, SOFTMAX = 3, SILU = 4, MATMUL = 6, ROPE = 8, RMSNORM = 11, LINEAR = 14,
-    EMBEDDING = 17, MUL = 18, VIEW = 19, KVCACHE = 20, LAYERNORM = 26,
-    F_TTADD = 83, F_TTMUL = 85, F_VIEW = 91, F_CLIP = 94, F_FA2 = 110,
+    EMBEDDING = 17, MUL = 18, VIEW = 19, KVCACHE = 20, OP_GELU = 24, QUICKGLUE = 25, LAYERNORM = 26, CONVOLUTION2D = 29, CONVOLUTION3D = 30,
+    MULTIMODALROPE = 35, F_DIV = 81, F_TTADD = 83, F_TTMUL = 85, F_MM = 87, F_VIEW = 91, F_TRANPOSE = 92, F_CLIP = 94,
+    F_APPLY_VISIOROPE = 109, F_FA2 = 110,
 };
 typedef map<string, float> OpParam; // mllm/Types.hpp:21
 

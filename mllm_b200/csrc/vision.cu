@@ -96,7 +96,7 @@ MLLMCU_API int mllmcu_softmax(const float *x, float *y, int outer, int S, int n,
 }
 
 // ------------------------------------------------------- scalar division
-// q / sqrt(D) of the eager attention spelling (Tensor::operator/(float) -> CPUdivintFunction, op/CPUBinaryFunc.hpp)
+// q / sqrt(D) of the eager attention spelling (Tensor::operator/(float) -> CPUdivFunction, op/CPUBinaryFunc.hpp)
 __global__ void k_div_scalar(const float *__restrict__ x, float s, float *__restrict__ y, size_t n) {
     const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) y[i] = __fdiv_rn(x[i], s);

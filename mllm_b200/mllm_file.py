@@ -12,6 +12,7 @@ import numpy as np
 
 MAGIC = 20012
 F32, F16, Q4_0, Q8_0 = 0, 1, 2, 8
+Q4_K, Q6_K, Q4_0_4_4 = 12, 14, 19
 ROPE_LLAMA, ROPE_HF = 2, 4
 
 
@@ -65,9 +66,19 @@ def config(name, cache_limit=1024, max_pos=None):
 
 
 def tensor_list(cfg):
-    """[(name, rows, cols, dtype)] of every parameter, in file order."""
+    """[(name, rows, cols, dtype)] of every parameter, in file order.  cfg["wtype"] (default Q4_0) is the Linear dtype --
+    Q4_K for the LLaVA config, Q4_0_4_4 for the shipped interleaved files; the embedding table stays Q4_0 as the reference
+    quantizer forces (tools/quantizer/QuantWriter.cpp:32-35,133)."""
     n = Names(cfg["rope_type"])
     H, D = cfg["hidden"], cfg["head_dim"]
+    out = _tensor_list_q4_0(cfg, n, H, D)
+    wt = cfg.get("wtype", Q4_0)
+    if wt != Q4_0:
+        out = [(nm, r, c, (wt if (d == Q4_0 and nm != n.embed) else d)) for nm, r, c, d in out]
+    return out
+
+
+def _tensor_list_q4_0(cfg, n, H, D):
     out = [(n.embed, cfg["vocab"], H, Q4_0)]
     for L in range(cfg["layers"]):
         out.append((n.layer(L, "attn_norm"), 1, H, F32))
@@ -86,7 +97,57 @@ def tensor_list(cfg):
 
 
 def nbytes(rows, cols, dtype):
-    return rows * cols * 4 if dtype == F32 else rows * (cols // 32) * 18
+    if dtype == F32:
+        return rows * cols * 4
+    if dtype == Q4_K:
+        return rows * (cols // 256) * 144
+    if dtype == Q6_K:
+        return rows * (cols // 256) * 210
+    return rows * (cols // 32) * 18
+
+
+def quantize_q4_K_np(w):
+    """A simple min/max Q4_K quantiser (NOT the reference's make_qkx2 search): produces valid block_q4_K bytes
+    (mllm/DataType.hpp:93-98) for random-init model files; parity never depends on how the blocks were chosen, only on how
+    they are consumed."""
+    w = np.ascontiguousarray(w, dtype=np.float32)
+    rows, cols = w.shape
+    b = w.reshape(rows, cols // 256, 8, 32)
+    mn = np.minimum(b.min(axis=3), 0)
+    mx = b.max(axis=3)
+    dsb = (mx - mn) / 15.0
+    msb = -mn
+    d = (dsb.max(axis=2) / 63.0).astype(np.float16)
+    dm = (msb.max(axis=2) / 63.0).astype(np.float16)
+    df, dmf = d.astype(np.float32), dm.astype(np.float32)
+    with np.errstate(divide="ignore", invalid="ignore"):
+        sc = np.where(df[..., None] > 0, np.rint(dsb / df[..., None]), 0).clip(0, 63).astype(np.uint8)
+        m6 = np.where(dmf[..., None] > 0, np.rint(msb / dmf[..., None]), 0).clip(0, 63).astype(np.uint8)
+        eff = df[..., None] * sc
+        q = np.where(eff[..., None] > 0, np.rint((b + (dmf[..., None] * m6)[..., None]) / eff[..., None]), 0).clip(0, 15).astype(np.uint8)
+    out = np.zeros((rows, cols // 256, 144), dtype=np.uint8)
+    out[..., 0:2] = d.view(np.uint8).reshape(rows, cols // 256, 2)
+    out[..., 2:4] = dm.view(np.uint8).reshape(rows, cols // 256, 2)
+    # 6-bit packing, inverse of get_scale_min_k4 (ggml/QuantizeQ4.cpp:177-184)
+    for j in range(4):
+        out[..., 4 + j] = (sc[..., j] & 63) | ((sc[..., j + 4] >> 4) << 6)
+        out[..., 8 + j] = (m6[..., j] & 63) | ((m6[..., j + 4] >> 4) << 6)
+        out[..., 12 + j] = (sc[..., j + 4] & 0xF) | ((m6[..., j + 4] & 0xF) << 4)
+    for j in range(4):
+        out[..., 16 + 32 * j:16 + 32 * (j + 1)] = q[..., 2 * j, :] | (q[..., 2 * j + 1, :] << 4)
+    return out.reshape(rows, cols // 256 * 144)
+
+
+def pack_q4_0_4x4_np(rows_q4_0, cols):
+    """plain block_q4_0 rows -> block_q4_0x4 groups (make_block_q4_0x4, interleave 4, XOR 0x88; ggml/GemmPack.cpp:45-60, :308-344)"""
+    r = np.ascontiguousarray(rows_q4_0, dtype=np.uint8)
+    n, nb = r.shape[0], cols // 32
+    b = r.reshape(n // 4, 4, nb, 18)
+    out = np.empty((n // 4, nb, 72), dtype=np.uint8)
+    out[..., 0:8] = b[..., 0:2].transpose(0, 2, 1, 3).reshape(n // 4, nb, 8)
+    qs = b[..., 2:].reshape(n // 4, 4, nb, 4, 4)  # [g, row, x, chunk, byte]
+    out[..., 8:] = (qs.transpose(0, 2, 3, 1, 4) ^ 0x88).reshape(n // 4, nb, 64)
+    return out.reshape(n, nb * 18)
 
 
 def quantize_q4_0_np(w):
@@ -117,7 +178,9 @@ def random_tensors(cfg, seed=1234, quantize=None):
         if dt == F32:
             base = 1.0 if "norm" in name else 0.0
             t[name] = (base + 0.02 * rng.standard_normal(cols)).astype(np.float32)
-        else:
+        elif dt == Q4_K:
+            t[name] = quantize_q4_K_np((0.02 * rng.standard_normal((rows, cols))).astype(np.float32))
+        else:  # Q4_0, and Q4_0_4_4 (kept as plain rows here; write_model interleaves them for the file)
             t[name] = quantize((0.02 * rng.standard_normal((rows, cols))).astype(np.float32))
     return t
 
@@ -141,8 +204,10 @@ def write_mllm(path, tensors, dtypes):
 
 
 def write_model(path, cfg, tensors):
-    dt = {name: d for name, _, _, d in tensor_list(cfg)}
-    return write_mllm(path, {n: tensors[n] for n in dt}, dt)
+    tl = tensor_list(cfg)
+    dt = {name: d for name, _, _, d in tl}
+    cols = {name: c for name, _, c, _ in tl}
+    return write_mllm(path, {n: (pack_q4_0_4x4_np(tensors[n], cols[n]) if dt[n] == Q4_0_4_4 else tensors[n]) for n in dt}, dt)
 
 
 def read_mllm(path):
@@ -171,4 +236,4 @@ def model_bytes(cfg):
 
 def decode_weight_bytes(cfg):
     """Algorithmic HBM bytes of Linear weights read per decode step: every Linear incl. lm_head, not the embedding table."""
-    return sum(nbytes(r, c, d) for n, r, c, d in tensor_list(cfg) if d == Q4_0 and n != Names(cfg["rope_type"]).embed)
+    return sum(nbytes(r, c, d) for n, r, c, d in tensor_list(cfg) if d != F32 and n != Names(cfg["rope_type"]).embed)

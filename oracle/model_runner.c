@@ -16,7 +16,9 @@ void orc_embedding_q4_0(const void *table, const float *ids, float *out, int n_i
 int ref_linear(int wtype, const void *W, const float *x, const float *bias, void *y, int M, int N, int K, int ldx, int ldy, int out_fp16);
 void ref_silu(const float *x, float *y, size_t n);
 void ref_flash_attn_f16kv(const float *Q, const uint16_t *K, const uint16_t *V, float *O, int Sq, int Sk, int Hq, int Hkv, int D, int causal, int threads);
-#define K_LINEAR ref_linear
+int ref_linear_kq(int wtype, const void *W, const float *x, const float *bias, float *y, int M, int N, int K, int ldx, int ldy);
+#define K_LINEAR_Q0 ref_linear
+#define K_LINEAR_KQ ref_linear_kq
 static void k_silu(const float *x, float *y, size_t n) { ref_silu(x, y, n); }
 static void k_attn(const float *Q, const uint16_t *K, const uint16_t *V, float *O, int Sq, int Sk, int Hq, int Hkv, int D) {
     ref_flash_attn_f16kv(Q, K, V, O, Sq, Sk, Hq, Hkv, D, 1, omp_get_max_threads());
@@ -25,12 +27,27 @@ static void k_attn(const float *Q, const uint16_t *K, const uint16_t *V, float *
 int orc_linear(int wtype, const void *W, const float *x, const float *bias, void *y, int M, int N, int K, int ldx, int ldy, int out_fp16);
 void orc_silu(const float *x, float *y, size_t n, int vec_width);
 void orc_flash_attn_f16kv(const float *Q, const uint16_t *K, const uint16_t *V, float *O, int Sq, int Sk, int Hq, int Hkv, int D, int causal, size_t kv_ld);
-#define K_LINEAR orc_linear
+int orc_linear_kq(int wtype, const void *W, const float *x, const float *bias, float *y, int M, int N, int K, int ldx, int ldy);
+#define K_LINEAR_Q0 orc_linear
+#define K_LINEAR_KQ orc_linear_kq
 static void k_silu(const float *x, float *y, size_t n) { orc_silu(x, y, n, 8); }
 static void k_attn(const float *Q, const uint16_t *K, const uint16_t *V, float *O, int Sq, int Sk, int Hq, int Hkv, int D) {
     orc_flash_attn_f16kv(Q, K, V, O, Sq, Sk, Hq, Hkv, D, 1, (size_t)Hkv * D);
 }
 #endif
+
+uint16_t orc_fp32_to_fp16(float f);
+/* Linear of either weight family; k-quant results are fp32, the fp16 store of Matmul.cpp:262-268 is MLLM_FP32_TO_FP16(value + bias) */
+static int K_LINEAR(int wtype, const void *W, const float *x, const float *bias, void *y, int M, int N, int K, int ldx, int ldy, int out_fp16) {
+    if (wtype != 12 && wtype != 14) return K_LINEAR_Q0(wtype, W, x, bias, y, M, N, K, ldx, ldy, out_fp16);
+    if (!out_fp16) return K_LINEAR_KQ(wtype, W, x, bias, (float *)y, M, N, K, ldx, ldy);
+    float *tmp = (float *)malloc(sizeof(float) * (size_t)M * N);
+    int rc = K_LINEAR_KQ(wtype, W, x, bias, tmp, M, N, K, ldx, N);
+    for (int m = 0; m < M; m++)
+        for (int n = 0; n < N; n++) ((uint16_t *)y)[(size_t)m * ldy + n] = orc_fp32_to_fp16(tmp[(size_t)m * N + n]);
+    free(tmp);
+    return rc;
+}
 
 typedef struct {
     int vocab, hidden, layers, heads, kv_heads, head_dim, ffn, rope_type, cache_limit, max_batch, wtype, pos_max;

@@ -342,7 +342,8 @@ class ModelRunner:
         self.keep = tensors
         cache_limit = cache_limit or cfg["cache_limit"]
         ci = np.array([cfg["vocab"], cfg["hidden"], cfg["layers"], cfg["heads"], cfg["kv_heads"], cfg["head_dim"],
-                       cfg["ffn"], cfg["rope_type"], cache_limit, max_batch, Q4_0, cfg.get("pos_max", cache_limit)], dtype=np.int32)
+                       cfg["ffn"], cfg["rope_type"], cache_limit, max_batch, (Q4_K if cfg.get("wtype", Q4_0) == Q4_K else Q4_0),
+                       cfg.get("pos_max", cache_limit)], dtype=np.int32)
         cf = np.array([cfg["rope_theta"], cfg["rms_eps"]], dtype=np.float32)
         self.h = C.c_void_p(self.lib.mr_create(_p(ci), _p(cf)))
         for L in range(cfg["layers"]):
