@@ -103,6 +103,14 @@ int mllmcu_block_isums_q4_0_q8_0(const void *W, const void *xq_blocks, int32_t *
 size_t mllmcu_linear_workspace_bytes(int M, int K);
 int mllmcu_linear(int wtype, const void *W, const float *x, const float *bias, void *y, int M, int N, int K, int ldx,
                   int ldy, int out_f16, void *ws, size_t ws_bytes, void *stream);
+/* The same Linear when several Linears read ONE activation tensor back to back (q/k/v, gate/up: models/llama/
+ * modeling_llama.hpp:29-36, models/transformer/modeling_transformer.hpp:150-160): the reference's mat_mul re-quantises the
+ * row for every call (compute/Matmul.cpp:104-115); here flags bit 0 says "ws still holds the quantised image of exactly
+ * these activations (same x, M, K, ldx) written by the previous call", so the quantiser launch is skipped.  Only valid when
+ * mllmcu_linear_quant_kind() returned the same non-zero kind for both calls (0: this shape keeps no reusable image). */
+int mllmcu_linear_quant_kind(int wtype, int M, int N, int K, const void *W);
+int mllmcu_linear_ex(int wtype, const void *W, const float *x, const float *bias, void *y, int M, int N, int K,
+                     int ldx, int ldy, int out_f16, void *ws, size_t ws_bytes, int flags, void *stream);
 
 /* ---- Fused decode Linear (M <= 8 rows): one launch = [RMSNorm ->] Q8_0 quantise -> nW (<=3) block-quantised
  * Linears sharing the input -> epilogue.  It is the same arithmetic, in the same order, as the separate

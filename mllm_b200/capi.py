@@ -48,6 +48,8 @@ SYMBOLS = {
     "mllmcu_block_isums_q4_0_q8_0": (_i, [_vp, _vp, _vp, _i, _i, _i, _vp]),
     "mllmcu_linear_workspace_bytes": (_sz, [_i, _i]),
     "mllmcu_linear": (_i, [_i, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _vp, _sz, _vp]),
+    "mllmcu_linear_ex": (_i, [_i, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _vp, _sz, _i, _vp]),
+    "mllmcu_linear_quant_kind": (_i, [_i, _i, _i, _i, _vp]),
     "mllmcu_gemv_fused": (_i, [_i, _vp, _vp, _vp, _i, _vp, _i, _i, _i, _vp, _f, _i, _vp, _i, _vp, _i, _i, _i, _vp]),
     "mllmcu_gemv_fused_ex": (_i, [_vp, _vp]),
     "mllmcu_gemv_prof_read": (_i, [_vp, _i]),
@@ -158,8 +160,9 @@ def _workspace(nbytes, device):
     return t
 
 
-def linear(W, x, bias=None, wtype=TYPE_Q4_0, out_f16=False, out=None, ldy=None):
-    """x cuda fp32 [M,K]; W cuda uint8 [N, K/32*blk]; returns y [M,N] fp32 (or fp16)."""
+def linear(W, x, bias=None, wtype=TYPE_Q4_0, out_f16=False, out=None, ldy=None, reuse_quant=False):
+    """x cuda fp32 [M,K]; W cuda uint8 [N, K/32*blk]; returns y [M,N] fp32 (or fp16).
+    reuse_quant: the workspace still holds the quantised image of x from the previous call (mllmcu_linear_ex flag 1)."""
     import torch
     M, K = x.shape
     N = W.shape[0]
@@ -168,8 +171,10 @@ def linear(W, x, bias=None, wtype=TYPE_Q4_0, out_f16=False, out=None, ldy=None):
         ldy = N
     need = lib().mllmcu_linear_workspace_bytes(M, K)
     ws = _workspace(need, x.device)
-    check(lib().mllmcu_linear(wtype, _ptr(W), _ptr(x), _ptr(bias), _ptr(out), M, N, K, x.stride(0), ldy, int(out_f16),
-                              _ptr(ws), ws.numel(), _stream()), "linear")
+    if reuse_quant and lib().mllmcu_linear_quant_kind(wtype, M, N, K, _ptr(W)) == 0:
+        raise MllmcuError("linear: this shape keeps no reusable quantised image")
+    check(lib().mllmcu_linear_ex(wtype, _ptr(W), _ptr(x), _ptr(bias), _ptr(out), M, N, K, x.stride(0), ldy, int(out_f16),
+                                 _ptr(ws), ws.numel(), int(reuse_quant), _stream()), "linear")
     return out
 
 

@@ -19,6 +19,7 @@
 // merged by k_attn_merge.  Decode is HBM-bound on the KV read
 // (2 * Sk * Hkv * D * 2 bytes per sequence).
 #include "common.cuh"
+#include <stdlib.h>
 
 static __device__ __forceinline__ float kv_to_f32(__half h) { return __half2float(h); }
 static __device__ __forceinline__ float kv_to_f32(float f) { return f; }
@@ -173,11 +174,25 @@ static int launch_attn(const float *q, const KT *k, const KT *v, float *o, int B
     return 0;
 }
 
+// attention_tc.cu: tensor-core prefill kernels; return 1 when the shape is not theirs
+int attn_prefill_tc_f16(const float *q, const void *k, const void *v, float *o, int B, int Sq, int Sk, int Hq, int Hkv, int D, int causal,
+                        long long kvb, cudaStream_t st);
+int attn_prefill_tc_f32(const float *q, const void *k, const void *v, float *o, int B, int Sq, int Sk, int Hq, int Hkv, int D, int causal,
+                        long long kvb, cudaStream_t st);
+static bool use_tc() { // MLLM_CUDA_ATTN_TC=0 keeps every shape on the CUDA-core kernel (A/B measurements)
+    const char *e = getenv("MLLM_CUDA_ATTN_TC"); // read per call so one process can compare both
+    return !(e && e[0] == '0');
+}
+
 MLLMCU_API int mllmcu_flash_attn_f16kv(const float *q, const void *k, const void *v, float *o, int B, int Sq, int Sk, int Hq,
                                        int Hkv, int D, int causal, long long kv_bstride, void *ws, size_t ws_bytes, void *stream) {
     if (B <= 0 || Sq <= 0 || Sk <= 0 || Hq <= 0 || Hkv <= 0 || Hq % Hkv) return -1;
     if (causal && Sq > Sk) return -1;
     cudaStream_t st = (cudaStream_t)stream;
+    if (use_tc()) {
+        const int rc = attn_prefill_tc_f16(q, k, v, o, B, Sq, Sk, Hq, Hkv, D, causal, kv_bstride, st);
+        if (rc != 1) return rc;
+    }
     switch (D) {
     case 64: return launch_attn<64, __half>(q, (const __half *)k, (const __half *)v, o, B, Sq, Sk, Hq, Hkv, causal, kv_bstride, (float *)ws, ws_bytes, st);
     case 128: return launch_attn<128, __half>(q, (const __half *)k, (const __half *)v, o, B, Sq, Sk, Hq, Hkv, causal, kv_bstride, (float *)ws, ws_bytes, st);
@@ -194,6 +209,10 @@ MLLMCU_API int mllmcu_flash_attn_f32kv(const float *q, const float *k, const flo
     if (B <= 0 || Sq <= 0 || Sk <= 0 || Hq <= 0 || Hkv <= 0 || Hq % Hkv) return -1;
     if (causal && Sq > Sk) return -1;
     cudaStream_t st = (cudaStream_t)stream;
+    if (use_tc()) {
+        const int rc = attn_prefill_tc_f32(q, k, v, o, B, Sq, Sk, Hq, Hkv, D, causal, kv_bstride, st);
+        if (rc != 1) return rc;
+    }
     switch (D) {
     case 64: return launch_attn<64, float>(q, k, v, o, B, Sq, Sk, Hq, Hkv, causal, kv_bstride, (float *)ws, ws_bytes, st);
     case 80: return launch_attn<80, float>(q, k, v, o, B, Sq, Sk, Hq, Hkv, causal, kv_bstride, (float *)ws, ws_bytes, st);

@@ -309,10 +309,203 @@ k_gemm_q4_0_tc(const uint8_t *__restrict__ W, const __half *__restrict__ qt, con
     }
 }
 
-// scratch: tile-major fp16 activations (rows padded to 128) + tile-major scales
+
+// =====================================================================================================================
+// Scaled-operand kernel (default).  The per-block rescale above costs one FMUL + one FFMA per output element and Q block
+// on the CUDA cores (~2300 cycles per 128x128 tile and block against 128 cycles of tensor work).  This kernel moves the
+// scales INTO the operands instead, without giving up exactness of the products:
+//   a[m][k] = d_x[m][b] * q8[m][k]        (18 significant bits)  = a_hi + a_lo,  a_hi = fp16(a),       a_lo = a - a_hi   (exact)
+//   w[n][k] = d_w[n][b] * (q4[n][k] - 8)  (14 significant bits)  = w_hi + w_lo,  w_hi = fp16(w) (HMUL2), w_lo = fma(d, v, -w_hi) (exact)
+//   y[m][n] = sum_k a_hi w_hi + a_lo w_hi + a_hi w_lo            (three fp16 MMAs, fp32 accumulation over the whole K in TMEM)
+// Every product is exact in the fp32 accumulator; the dropped a_lo*w_lo term is <= 2^-22 of its product (an fp32 rounding).
+// q8 / d_x are still the bit-exact Q8_0 quantisation of the row, so the result is the reference's sum
+// sum_b d_w d_x isum_b evaluated in a different (and tighter: no per-block product rounding) fp32 order.
+// Layout per pipeline stage (one Q block, K = 32): [a_hi 8 KB][a_lo 8 KB][w_hi 8 KB][w_lo 8 KB], each the canonical
+// K-major no-swizzle core-matrix image ([4 k-chunks][128 rows][16 B]).  The activation side of a stage is one 16 KB bulk copy.
+//   warp 0: TMEM alloc + MMA issue (6 tcgen05.mma per block)   warps 1-4: weight unpack (one row per thread)
+//   warps 5-8: epilogue, once per tile (tcgen05.ld, bias, store)
+#define TS_NS 5
+#define TS_STAGE_BYTES (4 * 4 * 128 * 16) // 32 KB
+#define TS_THREADS (9 * 32)
+#define TS_SMEM_BARS (TS_NS * TS_STAGE_BYTES)
+#define TS_SMEM_WST (TS_SMEM_BARS + 256)
+#define TS_SMEM_TOTAL (TS_SMEM_WST + 2 * 128 * 144)
+
+// Q8_0 of the activation rows (bytes as quantize_row_q8_0), dequantised exactly and split into fp16 hi / lo planes, in the
+// stage image:  qt[((((mt * nb + b) * 2 + plane) * 4 + kc) * 128 + r) * 8 + e]   row = mt*128 + r, k = b*32 + kc*8 + e
+__global__ void k_quantize_q8_0_f16x2_tiled(const float *__restrict__ x, __half *__restrict__ qt, int rows, int rows_pad, int nb, int ldx) {
+    const int lane = threadIdx.x & 31;
+    const long long wid = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (wid >= (long long)rows_pad * nb) return;
+    const int row = (int)(wid / nb), b = (int)(wid % nb);
+    const int mt = row >> 7, r = row & 127;
+    const float v = row < rows ? x[(size_t)row * ldx + (size_t)b * QK + lane] : 0.f;
+    const float amax = warp_max(fabsf(v));
+    const float d = __half2float(q8_0_scale(amax));
+    const float a = __fmul_rn(d, (float)q8_0_quant(v, amax)); // exact: 11 x 7 significant bits
+    const __half hi = __float2half_rn(a);
+    const __half lo = __float2half_rn(__fsub_rn(a, __half2float(hi)));
+    const size_t base = ((((size_t)mt * nb + b) * 2) * 4 + (lane >> 3)) * 128 + r;
+    qt[base * 8 + (lane & 7)] = hi;
+    qt[(base + 4 * 128) * 8 + (lane & 7)] = lo;
+}
+
+// 4 bytes holding values 0..15 -> (v - 8) * d as hi / lo half2 pairs
+static __device__ __forceinline__ void nib4_scaled(uint32_t x, __half2 dd, uint32_t &h01, uint32_t &h23, uint32_t &l01, uint32_t &l23) {
+    const uint32_t a = __byte_perm(x, 0x64646464u, 0x4140), b = __byte_perm(x, 0x64646464u, 0x4342);
+    const __half2 off = __halves2half2(__ushort_as_half((unsigned short)0x6408), __ushort_as_half((unsigned short)0x6408)); // 1032
+    const __half2 va = __hsub2(*(const __half2 *)&a, off), vb = __hsub2(*(const __half2 *)&b, off);
+    const __half2 ha = __hmul2(va, dd), hb = __hmul2(vb, dd);
+    const __half2 la = __hfma2(va, dd, __hneg2(ha)), lb = __hfma2(vb, dd, __hneg2(hb));
+    h01 = *(const uint32_t *)&ha; h23 = *(const uint32_t *)&hb;
+    l01 = *(const uint32_t *)&la; l23 = *(const uint32_t *)&lb;
+}
+
+__global__ void __launch_bounds__(TS_THREADS, 1)
+k_gemm_q4_0_tcs(const uint8_t *__restrict__ W, const __half *__restrict__ qt, const float *__restrict__ bias, void *__restrict__ y, int M, int N,
+                int K, int ldy, int out_f16) {
+    extern __shared__ __align__(1024) uint8_t smem[];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int nb = K / QK, rowb = nb * 18;
+    const int n0 = blockIdx.x * TC_BN, m0 = blockIdx.y * TC_BM;
+    uint64_t *bars = (uint64_t *)(smem + TS_SMEM_BARS);
+    uint32_t *tmem_slot = (uint32_t *)(smem + TS_SMEM_BARS + 128);
+    const uint32_t bar0 = tc_smem_u32(bars);
+    auto FULL = [&](int s) { return bar0 + 8u * s; };
+    auto EMPTY = [&](int s) { return bar0 + 8u * (TS_NS + s); };
+    const uint32_t DFULL = bar0 + 8u * (2 * TS_NS);
+
+    if (warp == 0) {
+        if (lane == 0) {
+            for (int s = 0; s < TS_NS; s++) { tc_mbar_init(FULL(s), 129); tc_mbar_init(EMPTY(s), 1); }
+            tc_mbar_init(DFULL, 1);
+            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        }
+        __syncwarp();
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tc_smem_u32(tmem_slot)), "r"(128u) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            for (int b = 0; b < nb; b++) {
+                const int s = b % TS_NS;
+                tc_mbar_wait(FULL(s), (uint32_t)((b / TS_NS) & 1));
+                tc_fence_after();
+                const uint32_t ah = tc_smem_u32(smem + (size_t)s * TS_STAGE_BYTES), al = ah + 8192, wh = ah + 16384, wl = ah + 24576;
+#pragma unroll
+                for (int i = 0; i < 2; i++) { // K = 16 halves = two 16-byte core-matrix columns
+                    const uint32_t koff = (uint32_t)(2 * i) * (128 * 16);
+                    tc_mma_f16(tmem_base, tc_desc(ah + koff, 128 * 16, 128), tc_desc(wh + koff, 128 * 16, 128), TC_IDESC, (uint32_t)((b | i) != 0));
+                    tc_mma_f16(tmem_base, tc_desc(al + koff, 128 * 16, 128), tc_desc(wh + koff, 128 * 16, 128), TC_IDESC, 1u);
+                    tc_mma_f16(tmem_base, tc_desc(ah + koff, 128 * 16, 128), tc_desc(wl + koff, 128 * 16, 128), TC_IDESC, 1u);
+                }
+                tc_commit(EMPTY(s));
+            }
+            tc_commit(DFULL);
+        }
+    } else if (warp <= 4) {
+        const int r = tid - 32;
+        const uint4 *wrow = (const uint4 *)(W + (size_t)(n0 + r) * rowb);
+        const __half *qtile = qt + (size_t)blockIdx.y * nb * (2 * 4 * 128 * 8);
+        const int ngroups = nb / 8;
+        uint8_t *wst = smem + TS_SMEM_WST + (size_t)r * 144;
+        auto fetch = [&](int g) {
+            const uint32_t dst = tc_smem_u32(wst + (size_t)(g & 1) * (128 * 144));
+#pragma unroll
+            for (int i = 0; i < 9; i++)
+                asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + 16u * i), "l"(wrow + (size_t)g * 9 + i) : "memory");
+            asm volatile("cp.async.commit_group;" ::: "memory");
+        };
+        fetch(0);
+        for (int g = 0; g < ngroups; g++) {
+            if (g + 1 < ngroups) {
+                fetch(g + 1);
+                asm volatile("cp.async.wait_group 1;" ::: "memory");
+            } else {
+                asm volatile("cp.async.wait_group 0;" ::: "memory");
+            }
+            const uint32_t *cw = (const uint32_t *)(wst + (size_t)(g & 1) * (128 * 144));
+#pragma unroll
+            for (int cc = 0; cc < 4; cc++) {
+                uint32_t w[9]; // 2 blocks = 36 bytes = 9 words
+#pragma unroll
+                for (int i = 0; i < 9; i++) w[i] = cw[9 * cc + i];
+                uint32_t q[2][4];
+#pragma unroll
+                for (int j = 0; j < 4; j++) { q[0][j] = __byte_perm(w[j], w[j + 1], 0x5432); q[1][j] = w[5 + j]; }
+                const unsigned short dbits[2] = {(unsigned short)(w[0] & 0xffffu), (unsigned short)(w[4] >> 16)};
+#pragma unroll
+                for (int blk = 0; blk < 2; blk++) {
+                    const int b = g * 8 + cc * 2 + blk, s = b % TS_NS;
+                    tc_mbar_wait(EMPTY(s), (uint32_t)(((b / TS_NS) & 1) ^ 1));
+                    uint8_t *sa = smem + (size_t)s * TS_STAGE_BYTES, *sh = sa + 16384, *sl = sa + 24576;
+                    if (r == 0) { // activations of this block: one contiguous 16 KB image (hi plane, lo plane)
+                        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(FULL(s)), "r"(16384u) : "memory");
+                        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(tc_smem_u32(sa)),
+                                     "l"(qtile + (size_t)b * (2 * 4 * 128 * 8)), "r"(16384u), "r"(FULL(s))
+                                     : "memory");
+                    }
+                    const __half dh = __ushort_as_half(dbits[blk]);
+                    const __half2 dd = __halves2half2(dh, dh);
+                    uint32_t lo[4], hi[4];
+#pragma unroll
+                    for (int j = 0; j < 4; j++) { lo[j] = q[blk][j] & 0x0F0F0F0Fu; hi[j] = (q[blk][j] >> 4) & 0x0F0F0F0Fu; }
+                    uint4 ch[4], cl[4]; // elements 0-7, 8-15 (low nibbles of bytes 0-7, 8-15), 16-23, 24-31 (high nibbles)
+                    nib4_scaled(lo[0], dd, ch[0].x, ch[0].y, cl[0].x, cl[0].y); nib4_scaled(lo[1], dd, ch[0].z, ch[0].w, cl[0].z, cl[0].w);
+                    nib4_scaled(lo[2], dd, ch[1].x, ch[1].y, cl[1].x, cl[1].y); nib4_scaled(lo[3], dd, ch[1].z, ch[1].w, cl[1].z, cl[1].w);
+                    nib4_scaled(hi[0], dd, ch[2].x, ch[2].y, cl[2].x, cl[2].y); nib4_scaled(hi[1], dd, ch[2].z, ch[2].w, cl[2].z, cl[2].w);
+                    nib4_scaled(hi[2], dd, ch[3].x, ch[3].y, cl[3].x, cl[3].y); nib4_scaled(hi[3], dd, ch[3].z, ch[3].w, cl[3].z, cl[3].w);
+#pragma unroll
+                    for (int kc = 0; kc < 4; kc++) {
+                        *(uint4 *)(sh + ((size_t)kc * 128 + r) * 16) = ch[kc];
+                        *(uint4 *)(sl + ((size_t)kc * 128 + r) * 16) = cl[kc];
+                    }
+                    asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); // generic-proxy stores -> visible to the tensor core
+                    tc_mbar_arrive(FULL(s));
+                }
+            }
+        }
+    } else {
+        // epilogue: TMEM lane quarter = warp % 4; the whole 128-column accumulator, 32 columns at a time
+        const int q = warp & 3;
+        const int r = 32 * q + lane, m = m0 + r;
+        tc_mbar_wait(DFULL, 0u);
+        tc_fence_after();
+#pragma unroll 1
+        for (int cq = 0; cq < 4; cq++) {
+            uint32_t v[32];
+            tc_ld32(tmem_base + ((uint32_t)(32 * q) << 16) + (uint32_t)(cq * 32), v);
+            tc_wait_ld();
+            if (m < M) {
+                const int nc = n0 + cq * 32;
+                if (out_f16) {
+                    __half *yp = (__half *)y + (size_t)m * ldy + nc;
+#pragma unroll
+                    for (int j = 0; j < 32; j++) yp[j] = __float2half_rn(bias ? __uint_as_float(v[j]) + bias[nc + j] : __uint_as_float(v[j]));
+                } else {
+                    float *yp = (float *)y + (size_t)m * ldy + nc;
+#pragma unroll
+                    for (int j = 0; j < 32; j++) yp[j] = bias ? __uint_as_float(v[j]) + bias[nc + j] : __uint_as_float(v[j]);
+                }
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0) {
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(128u) : "memory");
+    }
+}
+
+// scratch: tile-major fp16 activations (rows padded to 128), two planes for the scaled-operand kernel
 size_t gemm_tc_workspace_bytes(int M, int K) {
     const size_t mp = ((size_t)M + TC_BM - 1) / TC_BM * TC_BM;
-    return (mp * K * 2 + 255) / 256 * 256 + (mp * (K / QK) * 4 + 255) / 256 * 256;
+    return (mp * K * 4 + 255) / 256 * 256 + (mp * (K / QK) * 4 + 255) / 256 * 256;
 }
 bool gemm_tc_supported(int wtype, int M, int N, int K) {
     static int off = -1;
@@ -320,15 +513,41 @@ bool gemm_tc_supported(int wtype, int M, int N, int K) {
     // K % 256: weight rows are read in 144-byte (8-block) groups that must start 16-byte aligned
     return !off && wtype == 2 && M > 8 && N % TC_BN == 0 && K % 256 == 0;
 }
+static bool tc_exact() { // MLLMCU_TC_EXACT=1: the per-block integer-sum kernel (read per call: tests compare both)
+    const char *ex = getenv("MLLMCU_TC_EXACT");
+    return ex && ex[0] == '1';
+}
+// which activation image the workspace holds after a call: 1 = hi/lo planes (scaled-operand kernel), 2 = integer fp16 + scales
+int gemm_tc_quant_kind() { return tc_exact() ? 2 : 1; }
+// skip_quant: the workspace already holds this kernel's image of the same activations (an earlier Linear on the same input)
 int launch_gemm_q4_0_tc(const void *W, const float *x, int ldx, const float *bias, void *y, int M, int N, int K, int ldy, int out_f16,
-                        void *ws, cudaStream_t st) {
+                        void *ws, int skip_quant, cudaStream_t st) {
     const int mp = (M + TC_BM - 1) / TC_BM * TC_BM;
     __half *qt = (__half *)ws;
+    if (!tc_exact()) {
+        const int nb = K / QK;
+        const long long warps = (long long)mp * nb;
+        if (!skip_quant) {
+            k_quantize_q8_0_f16x2_tiled<<<(unsigned)((warps + 7) / 8), 256, 0, st>>>(x, qt, M, mp, nb, ldx);
+            CU_LAUNCH_CHECK();
+        }
+        static bool configured_s = false;
+        if (!configured_s) {
+            CU_TRY(cudaFuncSetAttribute(k_gemm_q4_0_tcs, cudaFuncAttributeMaxDynamicSharedMemorySize, TS_SMEM_TOTAL));
+            configured_s = true;
+        }
+        const dim3 grid(N / TC_BN, mp / TC_BM);
+        k_gemm_q4_0_tcs<<<grid, TS_THREADS, TS_SMEM_TOTAL, st>>>((const uint8_t *)W, qt, bias, y, M, N, K, ldy, out_f16);
+        CU_LAUNCH_CHECK();
+        return 0;
+    }
     float *dt = (float *)((char *)ws + ((size_t)mp * K * 2 + 255) / 256 * 256);
     const int nb = K / QK;
     const long long warps = (long long)mp * nb;
-    k_quantize_q8_0_f16_tiled<<<(unsigned)((warps + 7) / 8), 256, 0, st>>>(x, qt, dt, M, mp, nb, ldx);
-    CU_LAUNCH_CHECK();
+    if (!skip_quant) {
+        k_quantize_q8_0_f16_tiled<<<(unsigned)((warps + 7) / 8), 256, 0, st>>>(x, qt, dt, M, mp, nb, ldx);
+        CU_LAUNCH_CHECK();
+    }
     static bool configured = false;
     if (!configured) {
         CU_TRY(cudaFuncSetAttribute(k_gemm_q4_0_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_TOTAL));

@@ -160,6 +160,7 @@ void CUDABackend::free_device(DeviceMemory &mem) {
     mem.handle = nullptr;
 }
 void CUDABackend::copy_from_host(const DeviceMemory &dest, const void *src) {
+    dropQuantTag();
     MLLMCU_CHECK(mllmcu_memcpy_h2d(dest.handle, src, dest.size_in_bytes, stream_));
     MLLMCU_CHECK(mllmcu_stream_sync(stream_));
 }
@@ -170,7 +171,12 @@ void CUDABackend::copy_to_host(void *dest, const DeviceMemory &src) {
 void CUDABackend::sync() { MLLMCU_CHECK(mllmcu_stream_sync(stream_)); }
 
 void *CUDABackend::workspace(size_t bytes) {
+    dropQuantTag();
+    return linearWorkspace(bytes);
+}
+void *CUDABackend::linearWorkspace(size_t bytes) {
     if (bytes > ws_bytes_) {
+        dropQuantTag();
         MLLMCU_CHECK(mllmcu_stream_sync(stream_));
         if (ws_) MLLMCU_CHECK(mllmcu_free(ws_));
         ws_bytes_ = (bytes + (8u << 20)) / (1u << 20) * (1u << 20);
@@ -254,6 +260,15 @@ vector<Tensor> CUDABackend::runOp(Op *op, vector<Tensor> inputs, vector<string> 
         }
     }
     op->execute(in, out);
+    if (qtag_.x) { // an op that wrote over the tagged activations invalidates their quantised image
+        const char *lo = (const char *)qtag_.x, *hi = lo + (size_t)qtag_.M * qtag_.ld * 4;
+        for (auto &o : out) {
+            if (!o->allocated()) continue;
+            const char *p = (const char *)o->rawDevPtr();
+            const char *q = p + (size_t)o->batch() * o->head() * o->sequence() * o->dimension() * 4;
+            if (p < hi && lo < q) dropQuantTag();
+        }
+    }
     return shells;
 }
 

@@ -95,13 +95,18 @@ public:
         const int nb = dense ? 1 : x.batch();
         const int M = dense ? x.batch() * x.sequence() : x.sequence();
         const size_t wsb = mllmcu_linear_workspace_bytes(M, in_);
-        void *ws = b->workspace(wsb);
+        void *ws = b->linearWorkspace(wsb);
+        const int kind = nb == 1 ? mllmcu_linear_quant_kind((int)weight_.dtype(), M, out_, in_, weight_.rawDevPtr()) : 0;
         for (int i = 0; i < nb; i++) {
             const float *xp = x.devPtr<float>() + (size_t)i * x.batchStride();
             char *yp = (char *)y.rawDevPtr() + (size_t)i * y.batchStride() * esz;
-            MLLMCU_CHECK(mllmcu_linear((int)weight_.dtype(), weight_.rawDevPtr(), xp, bias, yp, M, out_, in_, (int)x.seqStride(),
-                                       (int)y.seqStride(), f16, ws, b->workspaceBytes(), b->stream()));
-            b->kernel_launches += 2;
+            // q/k/v and gate/up read the same tensor: the second and third Linear reuse the first one's quantised image
+            const int reuse = b->quantTagMatches(xp, M, in_, (int)x.seqStride(), kind) ? 1 : 0;
+            MLLMCU_CHECK(mllmcu_linear_ex((int)weight_.dtype(), weight_.rawDevPtr(), xp, bias, yp, M, out_, in_, (int)x.seqStride(),
+                                          (int)y.seqStride(), f16, ws, b->workspaceBytes(), reuse, b->stream()));
+            if (kind) b->setQuantTag(xp, M, in_, (int)x.seqStride(), kind);
+            else b->dropQuantTag();
+            b->kernel_launches += 2 - reuse;
         }
         return MLLM_NO_ERROR;
     }

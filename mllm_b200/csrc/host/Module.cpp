@@ -92,6 +92,7 @@ Tensor LlamaModel::block_forward(Block &b, int idx, Tensor in) {
 }
 
 Tensor LlamaModel::forward(Tensor ids, float *dump) {
+    st_.backend->dropQuantTag();
     CUDABackend *bn = st_.backend;
     last_fused_ = false;
     if (!bn->doTrace && !dump && ids.sequence() == 1 && ids.contiguous() && decode_plan_usable(ids.batch()))
@@ -413,6 +414,7 @@ bool LlamaModel::issue_step(DecodePlan &p, bool pick, bool pdl_on) {
 }
 
 Tensor LlamaModel::decode_step(const float *ids_dev, int B, bool pick) {
+    st_.backend->dropQuantTag(); // the plan's kernels write outside runOp
     CUDABackend *bn = st_.backend;
     DecodePlan &p = *plan_;
     void *st = bn->stream();

@@ -239,6 +239,16 @@ public:
     // scratch shared by ops (activation quantisation, split-K partials); grows monotonically
     void *workspace(size_t bytes);
     size_t workspaceBytes() const { return ws_bytes_; }
+    // Several Linears reading one activation tensor back to back (q/k/v, gate/up) share its quantised image in the
+    // workspace (mllmcu_linear_ex flag 1).  The tag names what the workspace holds; it is dropped by any other workspace
+    // user, by a workspace reallocation, by an H2D copy and by any op whose output overlaps the tagged activations.
+    struct QuantTag { const void *x = nullptr; int M = 0, K = 0, ld = 0, kind = 0; };
+    void *linearWorkspace(size_t bytes);
+    bool quantTagMatches(const void *x, int M, int K, int ld, int kind) const {
+        return kind != 0 && qtag_.kind == kind && qtag_.x == x && qtag_.M == M && qtag_.K == K && qtag_.ld == ld;
+    }
+    void setQuantTag(const void *x, int M, int K, int ld, int kind) { qtag_ = QuantTag{x, M, K, ld, kind}; }
+    void dropQuantTag() { qtag_ = QuantTag{}; }
 
     // trace mode (Module::doTrace): runOp only calls reshape + setUp (CPUBackend.cpp:318-349)
     bool doTrace = false;
@@ -256,6 +266,7 @@ private:
     std::multimap<size_t, void *> free_list_; // stream-ordered arena: size class -> free blocks
     void *ws_ = nullptr;
     size_t ws_bytes_ = 0;
+    QuantTag qtag_;
 };
 
 [[noreturn]] void cuda_fail(int rc, const char *what, const char *file, int line);

@@ -210,8 +210,9 @@ static inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; 
 // tensor-core prefill path (gemm_tc.cu)
 size_t gemm_tc_workspace_bytes(int M, int K);
 bool gemm_tc_supported(int wtype, int M, int N, int K);
+int gemm_tc_quant_kind();
 int launch_gemm_q4_0_tc(const void *W, const float *x, int ldx, const float *bias, void *y, int M, int N, int K, int ldy, int out_f16,
-                        void *ws, cudaStream_t st);
+                        void *ws, int skip_quant, cudaStream_t st);
 
 // k-quant weights (kquants.cu)
 size_t kq_workspace_bytes(int M, int K);
@@ -240,14 +241,25 @@ static int launch_gemv(int M, const uint8_t *W, const int8_t *xq, const float *x
     return 0;
 }
 
+MLLMCU_API int mllmcu_linear_quant_kind(int wtype, int M, int N, int K, const void *W) {
+    return (gemm_tc_supported(wtype, M, N, K) && !((uintptr_t)W & 15)) ? gemm_tc_quant_kind() : 0;
+}
+
+MLLMCU_API int mllmcu_linear_ex(int wtype, const void *W, const float *x, const float *bias, void *y, int M, int N, int K,
+                                int ldx, int ldy, int out_f16, void *ws, size_t ws_bytes, int flags, void *stream);
 MLLMCU_API int mllmcu_linear(int wtype, const void *W, const float *x, const float *bias, void *y, int M, int N, int K,
                              int ldx, int ldy, int out_f16, void *ws, size_t ws_bytes, void *stream) {
+    return mllmcu_linear_ex(wtype, W, x, bias, y, M, N, K, ldx, ldy, out_f16, ws, ws_bytes, 0, stream);
+}
+
+MLLMCU_API int mllmcu_linear_ex(int wtype, const void *W, const float *x, const float *bias, void *y, int M, int N, int K,
+                                int ldx, int ldy, int out_f16, void *ws, size_t ws_bytes, int flags, void *stream) {
     if (M <= 0 || N <= 0 || K <= 0 || K % QK) return -1;
     if (wtype != 2 && wtype != 8 && wtype != 12 && wtype != 14) return -2;
     if (ws == nullptr || ws_bytes < mllmcu_linear_workspace_bytes(M, K)) return -3;
     cudaStream_t st = (cudaStream_t)stream;
     if (wtype == 12 || wtype == 14) return launch_linear_kq(wtype, W, x, bias, y, M, N, K, ldx, ldy, out_f16, ws, st);
-    if (gemm_tc_supported(wtype, M, N, K) && !((uintptr_t)W & 15)) return launch_gemm_q4_0_tc(W, x, ldx, bias, y, M, N, K, ldy, out_f16, ws, st);
+    if (gemm_tc_supported(wtype, M, N, K) && !((uintptr_t)W & 15)) return launch_gemm_q4_0_tc(W, x, ldx, bias, y, M, N, K, ldy, out_f16, ws, flags & 1, st);
     int8_t *xq = (int8_t *)ws;
     float *xd = (float *)((char *)ws + align_up((size_t)M * K, 256));
     int rc = launch_quantize_q8_0_split(x, xq, xd, M, K, ldx, st);

@@ -109,6 +109,55 @@ def test_linear_tensor_core_block_sums_exact(cu, oracle):
     assert np.array_equal(y.astype(np.int64), want) and np.all(y == np.round(y))
 
 
+def _with_env(name, val, fn):
+    import os
+    old = os.environ.get(name)
+    os.environ[name] = val
+    try:
+        return fn()
+    finally:
+        if old is None:
+            del os.environ[name]
+        else:
+            os.environ[name] = old
+
+
+@pytest.mark.parametrize("M,N,K", [(128, 128, 256), (300, 384, 2048), (512, 256, 11008)])
+def test_linear_tensor_core_both_kernels(cu, oracle, M, N, K):
+    """The scaled-operand kernel (default: scales folded into exactly-split fp16 operands, one accumulator over all of K)
+    and the per-block integer-sum kernel (MLLMCU_TC_EXACT=1) against the oracle and against each other."""
+    rng = np.random.default_rng(M + N + K + 1)
+    W = oracle.quantize_q4_0((rng.standard_normal((N, K)) * 0.02).astype(np.float32))
+    x = act_rows(rng, M, K)
+    x[0] *= 500.0   # a row of large activations (|a| ~ 4000) and a tiny one: the hi/lo split must hold over the range
+    x[3] *= 1e-4
+    b = (rng.standard_normal(N) * 0.02).astype(np.float32)
+    want = oracle.linear(W, x, b)
+    ys = _with_env("MLLMCU_TC_EXACT", "0", lambda: cu.linear(dev(W), dev(x), dev(b)).cpu().numpy())
+    ye = _with_env("MLLMCU_TC_EXACT", "1", lambda: cu.linear(dev(W), dev(x), dev(b)).cpu().numpy())
+    for m in (0, 3, 7, M - 1):  # per row: each row has its own scale
+        lin_check(ys[m], want[m])
+        lin_check(ye[m], want[m])
+    lin_check(ys, want)
+    lin_check(ye, want)
+    assert not np.array_equal(ys, ye) or M == 0  # two different kernels really ran
+
+
+def test_linear_tensor_core_exact_kernel_block_sums(cu):
+    rng = np.random.default_rng(6)
+    M, N, K = 128, 128, 512
+    blocks = rng.integers(0, 256, (N, K // 32, 18), dtype=np.uint8)
+    one = np.float16(1.0).view(np.uint16)
+    blocks[:, :, 0] = one & 0xFF
+    blocks[:, :, 1] = one >> 8
+    q = rng.integers(-127, 128, (M, K)).astype(np.float32)
+    q[:, ::32] = 127.0
+    y = _with_env("MLLMCU_TC_EXACT", "1", lambda: cu.linear(dev(blocks.reshape(N, -1)), dev(q)).cpu().numpy())
+    qs = blocks[:, :, 2:]
+    w = np.concatenate([(qs & 0x0F).astype(np.int64) - 8, (qs >> 4).astype(np.int64) - 8], axis=2).reshape(N, K)
+    assert np.array_equal(y.astype(np.int64), q.astype(np.int64) @ w.T)
+
+
 def test_linear_tensor_core_fp16_out_strided(cu, oracle):
     import torch
     rng = np.random.default_rng(8)
