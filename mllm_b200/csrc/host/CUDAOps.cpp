@@ -671,6 +671,79 @@ public:
     }
 };
 
+// ---------------------------------------------------------------- Parameter
+// CPUParameter (op/CPUParameter.cpp:8-60): a learned tensor loaded under the op's own name (ViT cls_token and
+// position_embeddings, models/vit/modeling_vit.hpp:66-84); no inputs, the output is the weight.
+class CUDAParameter final : public Op {
+public:
+    CUDAParameter(Backend *bn, string name, int b, int h, int s, int d) : Op(bn, name), b_(b), h_(h), s_(s), d_(d) {}
+    ErrorCode reshape(vector<shared_ptr<Tensor>>, vector<shared_ptr<Tensor>> out) override {
+        out[0]->reshape(b_, h_, s_, d_);
+        return MLLM_NO_ERROR;
+    }
+    ErrorCode load(ParamLoader &loader) override {
+        w_ = Tensor(backend_);
+        w_.setName(name());
+        w_.reshape(b_, h_, s_, d_);
+        w_.setDtype(MLLM_TYPE_F32);
+        w_.alloc();
+        if (loader.getDataType(w_.name()) != MLLM_TYPE_COUNT) loader.load(&w_);
+        return MLLM_NO_ERROR;
+    }
+    ErrorCode execute(vector<shared_ptr<Tensor>>, vector<shared_ptr<Tensor>> out) override {
+        auto *b = cb(backend_);
+        MLLMCU_CHECK(mllmcu_memcpy_d2d(out[0]->rawDevPtr(), w_.rawDevPtr(), w_.cntSize(), b->stream()));
+        return MLLM_NO_ERROR;
+    }
+
+private:
+    int b_, h_, s_, d_;
+    Tensor w_;
+};
+
+// ---------------------------------------------------------------------- Cat
+// CPUcatFunction (op/CPUCatFunc.hpp:14-260): concatenate along BATCH / SEQUENCE / HEAD / DIMENSION (Chl values 0 / 1 / 2 / 3,
+// Types.hpp:133-137).  The reference aliases the inputs into the output where it can; the result is the same bytes.  Here
+// every input is placed with one strided copy (cls token + patches, image + text embeddings, rotary halves).
+class CUDACat final : public Op {
+public:
+    CUDACat(Backend *bn, string name, int axis) : Op(bn, name), axis_(axis) {
+        if (axis_ < 0 || axis_ > 3) throw std::runtime_error("[mllm-cuda] cat: axis must be BATCH, SEQUENCE, HEAD or DIMENSION");
+    }
+    ErrorCode reshape(vector<shared_ptr<Tensor>> in, vector<shared_ptr<Tensor>> out) override {
+        int n[4] = {in[0]->batch(), in[0]->sequence(), in[0]->head(), in[0]->dimension()}; // indexed by Chl
+        n[axis_] = 0;
+        for (auto &t : in) {
+            const int v[4] = {t->batch(), t->sequence(), t->head(), t->dimension()};
+            for (int a = 0; a < 4; a++)
+                if (a != axis_ && v[a] != n[a]) throw std::runtime_error("[mllm-cuda] cat: shapes differ off the concatenation axis");
+            n[axis_] += v[axis_];
+        }
+        out[0]->reshape(n[0], n[2], n[1], n[3]);
+        out[0]->setDtype(in[0]->dtype());
+        return MLLM_NO_ERROR;
+    }
+    ErrorCode execute(vector<shared_ptr<Tensor>> in, vector<shared_ptr<Tensor>> out) override {
+        auto *b = cb(backend_);
+        Tensor &y = *out[0];
+        const int esz = y.dtype() == MLLM_TYPE_F16 ? 2 : 4;
+        // element (b, s, h, d) of a BSHD tensor: b * batchStride + s * seqStride + h * D + d
+        const long long ys[4] = {y.batchStride(), y.seqStride(), y.dimension(), 1};
+        long long at = 0;
+        for (auto &t : in) {
+            const int n[4] = {t->batch(), t->sequence(), t->head(), t->dimension()};
+            const long long ss[4] = {t->batchStride(), t->seqStride(), t->dimension(), 1};
+            MLLMCU_CHECK(mllmcu_copy_strided(t->rawDevPtr(), (char *)y.rawDevPtr() + (size_t)(at * ys[axis_]) * esz, esz, n, ss, ys, b->stream()));
+            b->kernel_launches++;
+            at += n[axis_];
+        }
+        return MLLM_NO_ERROR;
+    }
+
+private:
+    int axis_;
+};
+
 // ------------------------------------------------------------ Convolution2D
 // CPUConvolution2D (op/CPUConvolution2D.cpp) VALID padding: input [B, H=height, S=channel, D=width] (NCHW bytes in BSHD), weight
 // name + ".weight" [O][C][kh][kw] F32, optional bias; output [B, H=oh, S=O, D=ow].
@@ -827,6 +900,8 @@ CREATOR(CUDASoftMax, new CUDASoftMax(bn, name, (int)getp(p, "axis", 3), (bool)ge
 CREATOR(CUDADivScalar, new CUDADivScalar(bn, name, getp(p, "data", 1.f)))
 CREATOR(CUDAMatmulFunc, new CUDAMatmulFunc(bn, name, (bool)getp(p, "transpose1", 0)))
 CREATOR(CUDATranspose, new CUDATranspose(bn, name))
+CREATOR(CUDAParameter, new CUDAParameter(bn, name, (int)p.at("batch"), (int)p.at("head"), (int)p.at("seq"), (int)p.at("dim")))
+CREATOR(CUDACat, new CUDACat(bn, name, (int)p.at("axis")))
 CREATOR(CUDAConvolution2D, new CUDAConvolution2D(bn, name, p))
 CREATOR(CUDAMultimodalRoPE, new CUDAMultimodalRoPE(bn, name, p))
 CREATOR(CUDAVisionRoPEFunc, new CUDAVisionRoPEFunc(bn, name))
@@ -850,6 +925,8 @@ void CUDABackend::registerOps() { // CPUBackend::registerOps, CPUBackend.cpp:142
     addCreator(F_DIV, new CUDADivScalarCreator());
     addCreator(F_MM, new CUDAMatmulFuncCreator());
     addCreator(F_TRANPOSE, new CUDATransposeCreator());
+    addCreator(PARAMETER, new CUDAParameterCreator());
+    addCreator(F_CAT, new CUDACatCreator());
     addCreator(CONVOLUTION2D, new CUDAConvolution2DCreator());
     addCreator(MULTIMODALROPE, new CUDAMultimodalRoPECreator());
     addCreator(F_APPLY_VISIOROPE, new CUDAVisionRoPEFuncCreator());

@@ -242,7 +242,8 @@ static int launch_gemv(int M, const uint8_t *W, const int8_t *xq, const float *x
 }
 
 MLLMCU_API int mllmcu_linear_quant_kind(int wtype, int M, int N, int K, const void *W) {
-    return (gemm_tc_supported(wtype, M, N, K) && !((uintptr_t)W & 15)) ? gemm_tc_quant_kind() : 0;
+    if (wtype != 2 && wtype != 8) return 0; // k-quants keep their own Q8_K image
+    return (gemm_tc_supported(wtype, M, N, K) && !((uintptr_t)W & 15)) ? gemm_tc_quant_kind() : 3; // 3: split Q8_0 (GEMV / dp4a / scaled tcgen05)
 }
 
 MLLMCU_API int mllmcu_linear_ex(int wtype, const void *W, const float *x, const float *bias, void *y, int M, int N, int K,
@@ -262,8 +263,10 @@ MLLMCU_API int mllmcu_linear_ex(int wtype, const void *W, const float *x, const 
     if (gemm_tc_supported(wtype, M, N, K) && !((uintptr_t)W & 15)) return launch_gemm_q4_0_tc(W, x, ldx, bias, y, M, N, K, ldy, out_f16, ws, flags & 1, st);
     int8_t *xq = (int8_t *)ws;
     float *xd = (float *)((char *)ws + align_up((size_t)M * K, 256));
-    int rc = launch_quantize_q8_0_split(x, xq, xd, M, K, ldx, st);
-    if (rc) return rc;
+    if (!(flags & 1)) {
+        const int rc = launch_quantize_q8_0_split(x, xq, xd, M, K, ldx, st);
+        if (rc) return rc;
+    }
     if (M <= GEMV_MAX_M) {
         return wtype == 2 ? launch_gemv<2>(M, (const uint8_t *)W, xq, xd, bias, y, N, K, ldy, out_f16, st)
                           : launch_gemv<8>(M, (const uint8_t *)W, xq, xd, bias, y, N, K, ldy, out_f16, st);

@@ -49,8 +49,10 @@ def test_model_with_other_weight_formats(be, oracle, tmp_path_factory, name, wty
     for L in range(1, cfg["layers"] + 1):
         # as in test_model_gpu.py: re-ordered fp32 sums can flip one activation rounding downstream; a flipped Q8_K value moves an
         # output by d_x * d_w * scale (6-bit scale up to 63), hence the wider bar for k-quants (kernels themselves agree to 2e-5)
-        tol = 1.5e-2 if wtype == mf.Q4_K else 5e-3
-        assert np.abs(dg[L] - dc[L]).max() <= tol * max(np.abs(dc[L]).max(), 1e-3), f"layer {L}"
+        # bulk of the elements (99th percentile) within 2e-3 of max; the few downstream of a flipped rounding within 1.5e-2
+        err, ref = np.abs(dg[L] - dc[L]), max(np.abs(dc[L]).max(), 1e-3)
+        assert np.quantile(err, 0.99) <= (4e-3 if wtype == mf.Q4_K else 2e-3) * ref, f"layer {L}"
+        assert err.max() <= 1.5e-2 * ref, f"layer {L}"
         assert cosine(dg[L], dc[L]) >= 0.99999, f"layer {L}"
     assert cosine(lg, lc) >= 0.9999
     for step in range(6):
@@ -131,3 +133,28 @@ def test_transpose_then_mm_is_qk(be):
                    shapes=[(H, 1, S, D), (H, 1, S, D)])
     want = np.einsum("hqd,hkd->hqk", q[0].transpose(1, 0, 2).astype(np.float64), k[0].transpose(1, 0, 2).astype(np.float64))
     assert np.abs(sc.reshape(H, S, S) - want).max() <= 1e-5 * np.abs(want).max()
+
+
+def test_parameter_op_is_the_loaded_tensor(be, tmp_path_factory):
+    """ViT cls_token / position_embeddings (models/vit/modeling_vit.hpp:66-84): Parameter(batch, seq, head, dim, name)."""
+    rng = np.random.default_rng(8)
+    w = rng.standard_normal((1, 5, 1, 64)).astype(np.float32)   # BSHD memory
+    p = str(tmp_path_factory.mktemp("op") / "param.mllm")
+    mf.write_mllm(p, {"embeddings.position_embedding": w}, {"embeddings.position_embedding": mf.F32})
+    y = be.run_op({"type": 1.0, "batch": 1.0, "seq": 5.0, "head": 1.0, "dim": 64.0}, "embeddings.position_embedding", [], p)
+    assert np.array_equal(bits(y), bits(w))
+
+
+@pytest.mark.parametrize("axis", [0, 1, 2, 3])
+def test_cat_op_every_axis(be, axis):
+    """Tensor::cat along BATCH / SEQUENCE / HEAD / DIMENSION (Chl 0/1/2/3): cls token + patches is the SEQUENCE case."""
+    rng = np.random.default_rng(9 + axis)
+    shp = [2, 7, 3, 16]  # BSHD memory order (b, s, h, d) == Chl order
+    parts = []
+    for n in (1, 4, 2):
+        s = list(shp)
+        s[axis] = n
+        parts.append(rng.standard_normal(s).astype(np.float32))
+    logical = [(a.shape[0], a.shape[2], a.shape[1], a.shape[3]) for a in parts]  # (b, h, s, d)
+    y = be.run_op({"type": 90.0, "axis": float(axis)}, "cat", parts, shapes=logical)
+    assert np.array_equal(bits(y), bits(np.concatenate(parts, axis=axis)))

@@ -124,8 +124,8 @@ def _with_env(name, val, fn):
 
 @pytest.mark.parametrize("M,N,K", [(128, 128, 256), (300, 384, 2048), (512, 256, 11008)])
 def test_linear_tensor_core_both_kernels(cu, oracle, M, N, K):
-    """The scaled-operand kernel (default: scales folded into exactly-split fp16 operands, one accumulator over all of K)
-    and the per-block integer-sum kernel (MLLMCU_TC_EXACT=1) against the oracle and against each other."""
+    """The per-block integer-sum kernel (default) and the scaled-operand kernel (MLLMCU_TC_EXACT=0: scales folded into exactly
+    split fp16 operands, activations in tensor memory, chained fp32 accumulation) against the oracle and against each other."""
     rng = np.random.default_rng(M + N + K + 1)
     W = oracle.quantize_q4_0((rng.standard_normal((N, K)) * 0.02).astype(np.float32))
     x = act_rows(rng, M, K)
