@@ -52,6 +52,8 @@ CONFIGS = {
     # small graphs with the same structure, for parity tests the CPU oracle finishes in seconds
     "toy-llama": dict(vocab=512, hidden=256, layers=2, heads=4, kv_heads=4, ffn=512, rope_type=ROPE_LLAMA, rope_theta=10000.0, rms_eps=1e-6, qkv_bias=0),
     "toy-d128": dict(vocab=320, hidden=256, layers=2, heads=2, kv_heads=1, ffn=512, rope_type=ROPE_LLAMA, rope_theta=10000.0, rms_eps=1e-6, qkv_bias=0),
+    # ffn = 128 x odd: Q4_0 rows of 18 * ffn / 32 bytes are 8 mod 16, as in Qwen1.5-1.8B (ffn 5504)
+    "toy-qwen": dict(vocab=320, hidden=256, layers=2, heads=2, kv_heads=2, ffn=384, rope_type=ROPE_HF, rope_theta=1000000.0, rms_eps=1e-6, qkv_bias=1),
     "toy-gqa": dict(vocab=384, hidden=256, layers=3, heads=8, kv_heads=2, ffn=768, rope_type=ROPE_HF, rope_theta=10000.0, rms_eps=1e-5, qkv_bias=1),
 }
 

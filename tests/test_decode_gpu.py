@@ -153,7 +153,7 @@ def make(tmp_path_factory, name, limit, seed):
     return cfg, t, path
 
 
-@pytest.mark.parametrize("name,B,S", [("toy-llama", 1, 8), ("toy-gqa", 2, 6), ("toy-d128", 1, 11), ("toy-d128", 3, 4)])
+@pytest.mark.parametrize("name,B,S", [("toy-llama", 1, 8), ("toy-gqa", 2, 6), ("toy-d128", 1, 11), ("toy-d128", 3, 4), ("toy-qwen", 3, 5), ("toy-qwen", 8, 4)])
 def test_fused_step_matches_eager_ops_and_oracle(be, oracle, tmp_path_factory, name, B, S):
     from oracle import pyoracle as po
     cfg, t, path = make(tmp_path_factory, name, 64, seed=S + B)
@@ -172,8 +172,14 @@ def test_fused_step_matches_eager_ops_and_oracle(be, oracle, tmp_path_factory, n
         # the fused GEMVs are bit-equal to the op-by-op ones; attention and the RMSNorm sum order differ
         assert np.abs(lf - le).max() <= 2e-3 * np.abs(le).max(), step
         assert cosine(lf, le) >= 0.999999, step
-        assert cosine(lf, lc) >= 0.9999, step
-        assert np.array_equal(lf.argmax(1), lc.argmax(1)), step
+        assert cosine(lf, lc) >= 0.9999, (step, cosine(lf, lc), [cosine(lf[i], lc[i]) for i in range(B)])
+        # random-init toy logits are nearly flat: the greedy pick must agree wherever the CPU's own top-2 margin is clear of the
+        # rounding-flip noise (same rule as tests/test_backend_ops_gpu.py); at batch 8 some row always has a near tie
+        top2 = np.sort(lc, axis=1)[:, -2:]
+        clear = (top2[:, 1] - top2[:, 0]) > 2e-2 * np.abs(lc).max()
+        assert np.array_equal(lf.argmax(1)[clear], lc.argmax(1)[clear]), step
+        if B <= 3:
+            assert np.array_equal(lf.argmax(1), lc.argmax(1)), step
     fused.close()
     eager.close()
 

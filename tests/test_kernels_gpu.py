@@ -352,7 +352,8 @@ def _q4(oracle, rng, n, k, scale=0.02):
     return oracle.quantize_q4_0((rng.standard_normal((n, k)) * scale).astype(np.float32))
 
 
-@pytest.mark.parametrize("M,N,K", [(1, 4096, 4096), (1, 64, 256), (2, 1000, 2048), (8, 72, 1024), (3, 4096, 11008), (1, 136, 5504)])
+@pytest.mark.parametrize("M,N,K", [(1, 4096, 4096), (1, 64, 256), (2, 1000, 2048), (8, 72, 1024), (3, 4096, 11008), (1, 136, 5504),
+                                    (3, 136, 5504), (8, 2048, 5504)])  # K = 5504 (Qwen1.5-1.8B ffn): rows of 3096 B go in pairs at every batch
 def test_gemv_fused_plain_bit_equal_to_linear(cu, oracle, M, N, K):
     """Same arithmetic, same order as mllmcu_linear's GEMV: bit-identical; and within tolerance of the oracle."""
     rng = np.random.default_rng(N + K + M)
@@ -399,6 +400,19 @@ def test_gemv_fused_residual_and_silu_mul(cu, oracle):
     xo = oracle.only.rmsnorm(x, w, 1e-6)
     a_o = oracle.silu(oracle.linear(Wg, xo)) * oracle.linear(Wu, xo)
     lin_check(out, oracle.linear(Wd, a_o) + x)
+
+
+@pytest.mark.parametrize("M", [3, 8])
+def test_gemv_fused_residual_batched_odd_row_bytes(cu, oracle, M):
+    """Qwen1.5-1.8B down projection at batch 3 / 8 (demo_qwen_batch shapes): K = 5504, residual epilogue."""
+    rng = np.random.default_rng(40 + M)
+    N, K = 2048, 5504
+    W = _q4(oracle, rng, N, K)
+    x = act_rows(rng, M, K)
+    r = rng.standard_normal((M, N)).astype(np.float32)
+    out = cu.gemv_fused([dev(W)], dev(x), epilogue=1, residual=dev(r)).cpu().numpy()
+    want = oracle.linear(W, x) + r
+    assert np.abs(out - want).max() <= 2e-5 * np.abs(want).max()
 
 
 def test_gemv_fused_rejects_unsupported(cu, oracle):
