@@ -3,8 +3,9 @@
 
 A step = one request: clear the KV cache, prefill 512 synthetic tokens, then 256 greedy decode steps.
   value : tokens/s of the whole request with inputs resident in HBM (device-timed, CUDA events).
-  e2e   : the same request through the host-buffer API (Module::generate-style loop: ids H2D every
-          forward, logits D2H every step, host argmax), wall clock around synchronous calls.
+  e2e   : the same request through the host-buffer API a user calls (LlamaModel.generate: prompt ids H2D,
+          prefill + greedy decode with the pick made on the device, the 256 token ids D2H), wall clock
+          around the synchronous call.
   roofline : the decode GEMV (k_gemv*, the dominant kernel) -- algorithmic weight bytes / launch time,
           measured live with CUDA events on the backend stream over all Linear shapes of a decode step.
   cpu_baseline : the reference's CPU kernels (oracle/_ref) or the port, on a bounded sample.
@@ -217,7 +218,10 @@ def gemv_roofline(cfg, peaks):
     achieved = total_b / total_t / 1e9
     peak = peaks.get("hbm_gbs", 6650.0)
     return {"bound": "hbm", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s", "frac": round(achieved / peak, 4),
-            "traffic": None, "kernel": "k_gemv_tma (decode Linear: fused RMSNorm/Q8_0 prologue + Q4_0 GEMV), launch-weighted over one decode step",
+            # DRAM bytes of one gate|up launch (its largest share of the step) from the ncu --set full capture summarised in
+            # profiles/r01_ncu_gemv_gateup.txt: 50.80 MB read + 3.6 KB written against 50.72 MB algorithmic -- no re-reads
+            "traffic": 50802688, "traffic_of": "one gate|up launch (k_gemv_tma<1,1,2,1>): dram read 50.799 MB + write 0.004 MB vs 50.725 MB algorithmic",
+            "kernel": "k_gemv_tma (decode Linear: fused RMSNorm/Q8_0 prologue + Q4_0 GEMV), launch-weighted over one decode step",
             "peak_source": "measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in peaks else "fallback 6650",
             "per_shape": per}
 
@@ -268,7 +272,7 @@ def gpu_arm(args, rank, world, local_rank):
     torch.cuda.synchronize()
     launches = backend.kernel_launches() - l0
     total_ms = float(np.sum(tp) + np.sum(td))
-    # e2e: host-buffer API (H2D ids every forward, D2H logits every step, host argmax), wall clock
+    # e2e: host-buffer API (prompt ids H2D, device-side greedy loop, token ids D2H), wall clock around the synchronous call
     e2e_ms = []
     for _ in range(max(1, min(args.steps, 2))):
         model.clear_kvcache()
@@ -297,8 +301,8 @@ def gpu_arm(args, rank, world, local_rank):
                         "GBs": round((wbytes + kv_bytes) / (dec_ms * 1e-3) / 1e9, 1),
                         "frac_of_hbm_peak": round((wbytes + kv_bytes) / (dec_ms * 1e-3) / 1e9 / peaks.get("hbm_gbs", 6650.0), 4)},
         "prefill": {"ms": round(float(np.mean(tp)), 3), "int8_TOPs": round(2 * (wbytes / 0.5625) * PREFILL / (float(np.mean(tp)) * 1e-3) / 1e12, 1)},
-        "e2e": {"value": round(job_tokens_per_s(PREFILL + DECODE, world, e2e_mean), 2), "unit": "tok/s", "h2d_bytes_per_step": (PREFILL + DECODE - 1) * 4,
-                "d2h_bytes_per_step": DECODE * cfg["vocab"] * 4, "ms_per_step": round(e2e_mean, 2)},
+        "e2e": {"value": round(job_tokens_per_s(PREFILL + DECODE, world, e2e_mean), 2), "unit": "tok/s", "h2d_bytes_per_step": PREFILL * 4,
+                "d2h_bytes_per_step": DECODE * 4, "ms_per_step": round(e2e_mean, 2)},
         "decode_mode": model.decode_mode(), "gpu_launches": int(launches), "clocks": clocks, "roofline": roof,
     }
     if not args.no_cpu:

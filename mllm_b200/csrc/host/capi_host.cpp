@@ -4,6 +4,7 @@
 // Module::generate mllm/Module.cpp:63-205).  Errors: C++ exceptions are caught, the message
 // is kept for mllm_cuda_last_error(), and a negative code is returned.
 #include "Module.hpp"
+#include <cstdlib>
 
 #include <chrono>
 #include <cstring>
@@ -82,7 +83,18 @@ HAPI int mllm_cuda_llama_forward(void *hv, const float *ids_host, int B, int S, 
 // Greedy generation, the loop of Module::generate (mllm/Module.cpp:63-100,146-205): forward,
 // D2H logits, host argmax (LlmTextGenerator greedy, Generate.cpp:46-53), feed the token back.
 // ids_host [B,S]; out_tokens [B,max_new] int32.
+HAPI int mllm_cuda_llama_request_device(void *hv, const float *ids_host, int B, int S, int n_decode, float *ms_prefill,
+                                        float *ms_decode, int *tokens_out);
+// Module::generate with the greedy LlmTextGenerator (mllm/Module.cpp:63-205, Generate.cpp:46-53): prompt ids go to the device
+// once, every pick is made on the device (first maximum wins, as std::max_element) and feeds the next step without leaving HBM,
+// the max_new token ids come back in one copy.  MLLM_CUDA_HOST_PICK=1 keeps the reference's literal loop (logits to the host
+// every step, host argmax) for comparison.
 HAPI int mllm_cuda_llama_generate(void *hv, const float *ids_host, int B, int S, int max_new, int *out_tokens) {
+    static const bool host_pick = [] { const char *e = getenv("MLLM_CUDA_HOST_PICK"); return e && e[0] == '1'; }();
+    if (!host_pick) {
+        float a = 0.f, b = 0.f;
+        return mllm_cuda_llama_request_device(hv, ids_host, B, S, max_new, &a, &b, out_tokens);
+    }
     GUARD({
         auto *h = (HostModel *)hv;
         CUDABackend *bn = h->model->backend();
