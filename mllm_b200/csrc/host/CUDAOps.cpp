@@ -499,10 +499,17 @@ public:
     ErrorCode execute(vector<shared_ptr<Tensor>> in, vector<shared_ptr<Tensor>> out) override {
         auto *b = cb(backend_);
         Tensor &q = *in[0], &k = *in[1], &v = *in[2];
-        if (k.dtype() != MLLM_TYPE_F16 || v.dtype() != MLLM_TYPE_F16) throw std::runtime_error("[mllm-cuda] flash_attention2: fp16 K/V (KV cache) expected");
+        if (k.dtype() != v.dtype() || (k.dtype() != MLLM_TYPE_F16 && k.dtype() != MLLM_TYPE_F32))
+            throw std::runtime_error("[mllm-cuda] flash_attention2: K/V must both be fp16 (KV cache) or both fp32 (no cache: vision towers)");
         if (k.seqStride() != (long long)k.head() * k.dimension()) throw std::runtime_error("[mllm-cuda] flash_attention2: K/V rows must be dense");
         const size_t wsb = mllmcu_flash_attn_workspace_bytes(q.batch(), q.sequence(), q.head(), q.dimension());
         void *ws = b->workspace(wsb);
+        if (k.dtype() == MLLM_TYPE_F32) { // flash_attention_2_forward's fp32 variant (compute/FlashAttention2.hpp:87-1210): ViT blocks keep no cache
+            MLLMCU_CHECK(mllmcu_flash_attn_f32kv(q.devPtr<float>(), k.devPtr<float>(), v.devPtr<float>(), out[0]->devPtr<float>(), q.batch(), q.sequence(),
+                                                 k.sequence(), q.head(), k.head(), q.dimension(), causal_, k.batchStride(), ws, b->workspaceBytes(), b->stream()));
+            b->kernel_launches += 1;
+            return MLLM_NO_ERROR;
+        }
         MLLMCU_CHECK(mllmcu_flash_attn_f16kv(q.devPtr<float>(), k.rawDevPtr(), v.rawDevPtr(), out[0]->devPtr<float>(), q.batch(), q.sequence(), k.sequence(),
                                              q.head(), k.head(), q.dimension(), causal_, k.batchStride(), ws, b->workspaceBytes(), b->stream()));
         b->kernel_launches += 2;

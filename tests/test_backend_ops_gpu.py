@@ -158,3 +158,68 @@ def test_cat_op_every_axis(be, axis):
     logical = [(a.shape[0], a.shape[2], a.shape[1], a.shape[3]) for a in parts]  # (b, h, s, d)
     y = be.run_op({"type": 90.0, "axis": float(axis)}, "cat", parts, shapes=logical)
     assert np.array_equal(bits(y), bits(np.concatenate(parts, axis=axis)))
+
+
+def test_clip_vit_block_through_backend_ops(be, oracle, tmp_path_factory):
+    """BASELINE configs[2] vision tower, one ViTBlock (models/vit/modeling_vit.hpp:31-62 with CLIP's QuickGELU and biased
+    LayerNorm / Linear): norm1 -> q,k,v Linear (Q4_K weights, as the LLaVA file quantises them) -> non-causal flash attention
+    over fp32 K/V (no cache) -> o Linear -> +x -> norm2 -> up Linear -> QuickGELU -> down Linear -> +tmp, every op created
+    through CUDABackend::opCreate / runOp, against the same composition of the CPU oracle's functions."""
+    from oracle import pyoracle as po
+    rng = np.random.default_rng(21)
+    S, Hd, H, F = 77, 256, 4, 512
+    D = Hd // H
+    x = rng.standard_normal((1, S, 1, Hd)).astype(np.float32)
+    t, dt = {}, {}
+    for n, (rows, cols) in {"q_proj": (Hd, Hd), "k_proj": (Hd, Hd), "v_proj": (Hd, Hd), "out_proj": (Hd, Hd), "fc1": (F, Hd), "fc2": (Hd, F)}.items():
+        t[n + ".weight"] = mf.quantize_q4_K_np((0.05 * rng.standard_normal((rows, cols))).astype(np.float32))
+        t[n + ".bias"] = (0.02 * rng.standard_normal(rows)).astype(np.float32)
+        dt[n + ".weight"], dt[n + ".bias"] = mf.Q4_K, mf.F32
+    for n in ("layer_norm1", "layer_norm2"):
+        t[n + ".weight"] = (1 + 0.02 * rng.standard_normal(Hd)).astype(np.float32)
+        t[n + ".bias"] = (0.02 * rng.standard_normal(Hd)).astype(np.float32)
+        dt[n + ".weight"] = dt[n + ".bias"] = mf.F32
+    path = str(tmp_path_factory.mktemp("vit") / "block.mllm")
+    mf.write_mllm(path, t, dt)
+
+    row = [(1, 1, S, Hd)]  # logical [b, h, s, d] of an activation whose BSHD memory is [S][hidden]
+
+    def lin(name, a, n_in, n_out):
+        return be.run_op({"type": 14.0, "in_features": float(n_in), "out_features": float(n_out), "bias": 1.0}, name, [a], path, shapes=[(1, 1, S, n_in)])
+
+    def ln(name, a):
+        return be.run_op({"type": 26.0, "norm_size": float(Hd), "bias": 1.0, "epsilon": 1e-5}, name, [a], path, shapes=row)
+
+    # ---- GPU: op by op through the backend
+    h1 = ln("layer_norm1", x)
+    q, k, v = (lin(n, h1, Hd, Hd) for n in ("q_proj", "k_proj", "v_proj"))
+    hs = [(1, H, S, D)] * 3  # view(-1, heads, -1, head_dim): same bytes, BSHD memory [S][H][D]
+    a = be.run_op({"type": 110.0, "causal_mask": 0.0}, "fa2", [q, k, v], shapes=hs)
+    o = lin("out_proj", a, Hd, Hd)
+    tmp = be.run_op({"type": 83.0}, "add1", [o, x], shapes=row * 2)
+    h2 = ln("layer_norm2", tmp)
+    u = be.run_op({"type": 25.0}, "act", [lin("fc1", h2, Hd, F)], shapes=[(1, 1, S, F)])
+    y = be.run_op({"type": 83.0}, "add2", [lin("fc2", u, F, Hd), tmp], shapes=row * 2)
+
+    # ---- CPU oracle: the same composition
+    def olin(name, a2):
+        return oracle.linear_kq(t[name + ".weight"], a2, t[name + ".bias"], po.Q4_K)
+
+    x2 = x.reshape(S, Hd)
+    c1 = oracle.only.layernorm(x2, t["layer_norm1.weight"], t["layer_norm1.bias"], 1e-5)
+    cq, ck, cv = (olin(n, c1).reshape(S, H, D) for n in ("q_proj", "k_proj", "v_proj"))
+    sc = np.einsum("qhd,khd->hqk", cq.astype(np.float64), ck.astype(np.float64)) / np.sqrt(D)
+    p = np.exp(sc - sc.max(-1, keepdims=True))
+    p /= p.sum(-1, keepdims=True)
+    ca = np.einsum("hqk,khd->qhd", p, cv.astype(np.float64)).astype(np.float32).reshape(S, Hd)
+    ctmp = olin("out_proj", ca) + x2
+    c2 = oracle.only.layernorm(ctmp, t["layer_norm2.weight"], t["layer_norm2.bias"], 1e-5)
+    cu_ = oracle.only.gelu(oracle.gelu_table(1), olin("fc1", c2).reshape(-1)).reshape(S, F)
+    want = olin("fc2", cu_) + ctmp
+
+    # stage by stage first (each stage fed by the GPU's own previous stage would hide nothing; here both chains run end to end)
+    assert np.abs(h1.reshape(S, Hd) - c1).max() <= 1e-5 * np.abs(c1).max()
+    assert np.abs(q.reshape(S, H, D) - cq).max() <= 2e-5 * np.abs(cq).max()
+    err, ref = np.abs(y.reshape(S, Hd) - want), np.abs(want).max()
+    assert np.quantile(err, 0.99) <= 2e-3 * ref and err.max() <= 1.5e-2 * ref   # a flipped Q8_K rounding downstream, as in the model tests
+    assert cosine(y.reshape(-1), want.reshape(-1)) >= 0.99999
