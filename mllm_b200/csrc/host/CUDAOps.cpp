@@ -751,6 +751,55 @@ private:
     int axis_;
 };
 
+// -------------------------------------------------------------------- Split
+// CPUsplitFunction (op/CPUSplitFunc.hpp:18-175): cut the input into pieces of each_dims along HEAD / SEQUENCE / DIMENSION (Chl 2 / 1 / 3).
+// The merged-qkv layouts D_HD / HD (Chl 313 / 113) are not built.
+class CUDASplit final : public Op {
+public:
+    CUDASplit(Backend *bn, string name, vector<int> each, int axis) : Op(bn, name), each_(std::move(each)), axis_(axis) {
+        if (axis_ < 1 || axis_ > 3) throw std::runtime_error("[mllm-cuda] split: HEAD, SEQUENCE or DIMENSION only");
+    }
+    ErrorCode reshape(vector<shared_ptr<Tensor>> in, vector<shared_ptr<Tensor>> out) override {
+        if (out.size() != each_.size()) throw std::runtime_error("[mllm-cuda] split: one output per piece");
+        const int n[4] = {in[0]->batch(), in[0]->sequence(), in[0]->head(), in[0]->dimension()}; // indexed by Chl
+        int total = 0;
+        for (int e : each_) total += e;
+        if (total != n[axis_]) throw std::runtime_error("[mllm-cuda] split: pieces do not add up to the axis length");
+        for (size_t i = 0; i < out.size(); i++) {
+            int m[4] = {n[0], n[1], n[2], n[3]};
+            m[axis_] = each_[i];
+            out[i]->reshape(m[0], m[2], m[1], m[3]);
+            out[i]->setDtype(in[0]->dtype());
+        }
+        return MLLM_NO_ERROR;
+    }
+    ErrorCode execute(vector<shared_ptr<Tensor>> in, vector<shared_ptr<Tensor>> out) override {
+        auto *b = cb(backend_);
+        Tensor &x = *in[0];
+        const int esz = x.dtype() == MLLM_TYPE_F16 ? 2 : 4;
+        const long long xs[4] = {x.batchStride(), x.seqStride(), x.dimension(), 1};
+        long long at = 0;
+        for (size_t i = 0; i < out.size(); i++) {
+            Tensor &y = *out[i];
+            const int n[4] = {y.batch(), y.sequence(), y.head(), y.dimension()};
+            const long long ys[4] = {y.batchStride(), y.seqStride(), y.dimension(), 1};
+            MLLMCU_CHECK(mllmcu_copy_strided((const char *)x.rawDevPtr() + (size_t)(at * xs[axis_]) * esz, y.rawDevPtr(), esz, n, xs, ys, b->stream()));
+            b->kernel_launches++;
+            at += n[axis_];
+        }
+        return MLLM_NO_ERROR;
+    }
+
+private:
+    vector<int> each_;
+    int axis_;
+};
+static Op *make_split(const OpParam &p, Backend *bn, const string &name) {
+    vector<int> each;
+    for (int i = 0; i < (int)p.at("num_splits"); i++) each.push_back((int)p.at("dim_" + std::to_string(i)));
+    return new CUDASplit(bn, name, each, (int)p.at("split_dim"));
+}
+
 // ------------------------------------------------------------ Convolution2D
 // CPUConvolution2D (op/CPUConvolution2D.cpp) VALID padding: input [B, H=height, S=channel, D=width] (NCHW bytes in BSHD), weight
 // name + ".weight" [O][C][kh][kw] F32, optional bias; output [B, H=oh, S=O, D=ow].
@@ -909,6 +958,7 @@ CREATOR(CUDAMatmulFunc, new CUDAMatmulFunc(bn, name, (bool)getp(p, "transpose1",
 CREATOR(CUDATranspose, new CUDATranspose(bn, name))
 CREATOR(CUDAParameter, new CUDAParameter(bn, name, (int)p.at("batch"), (int)p.at("head"), (int)p.at("seq"), (int)p.at("dim")))
 CREATOR(CUDACat, new CUDACat(bn, name, (int)p.at("axis")))
+CREATOR(CUDASplit, make_split(p, bn, name))
 CREATOR(CUDAConvolution2D, new CUDAConvolution2D(bn, name, p))
 CREATOR(CUDAMultimodalRoPE, new CUDAMultimodalRoPE(bn, name, p))
 CREATOR(CUDAVisionRoPEFunc, new CUDAVisionRoPEFunc(bn, name))
@@ -934,6 +984,7 @@ void CUDABackend::registerOps() { // CPUBackend::registerOps, CPUBackend.cpp:142
     addCreator(F_TRANPOSE, new CUDATransposeCreator());
     addCreator(PARAMETER, new CUDAParameterCreator());
     addCreator(F_CAT, new CUDACatCreator());
+    addCreator(F_SPLIT, new CUDASplitCreator());
     addCreator(CONVOLUTION2D, new CUDAConvolution2DCreator());
     addCreator(MULTIMODALROPE, new CUDAMultimodalRoPECreator());
     addCreator(F_APPLY_VISIOROPE, new CUDAVisionRoPEFuncCreator());

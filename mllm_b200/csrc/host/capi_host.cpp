@@ -142,7 +142,12 @@ HAPI int mllm_cuda_run_op(const char **keys, const float *vals, int n_params, co
     GUARD({
         CUDABackend *bn = backend();
         OpParam p;
-        for (int i = 0; i < n_params; i++) p[keys[i]] = vals[i];
+        int n_out = 1, out_index = 0; // test-harness keys, not op parameters: ops with several outputs (split) return the chosen one
+        for (int i = 0; i < n_params; i++) {
+            if (string(keys[i]) == "__n_out") n_out = (int)vals[i];
+            else if (string(keys[i]) == "__out_index") out_index = (int)vals[i];
+            else p[keys[i]] = vals[i];
+        }
         std::unique_ptr<Op> op(bn->opCreate(p, name));
         ParamLoader loader(path ? path : "");
         op->load(loader);
@@ -154,8 +159,10 @@ HAPI int mllm_cuda_run_op(const char **keys, const float *vals, int n_params, co
             t.copyFromHost(inputs[i]);
             in.push_back(t);
         }
-        vector<Tensor> out = bn->runOp(op.get(), in, {string("out-") + name}, false);
-        Tensor &o = out[0];
+        vector<string> out_names;
+        for (int i = 0; i < n_out; i++) out_names.push_back(string("out-") + name + (n_out > 1 ? "-" + std::to_string(i) : ""));
+        vector<Tensor> out = bn->runOp(op.get(), in, out_names, false);
+        Tensor &o = out.at(out_index);
         out_shape[0] = o.batch(); out_shape[1] = o.head(); out_shape[2] = o.sequence(); out_shape[3] = o.dimension();
         if (o.dtype() != MLLM_TYPE_F32 || !o.contiguous()) throw std::runtime_error("run_op: output must be dense fp32");
         o.copyToHost(out_host);

@@ -41,7 +41,7 @@ enum RoPEType { NONE = 0, PERSIMMONROPE = 1, LLAMAROPE = 2, HFHUBROPE = 4 };
 enum OpType {
     INVALID_VALUE_OP = 0, PARAMETER = 1, ADD = 2, SOFTMAX = 3, SILU = 4, MATMUL = 6, ROPE = 8, RMSNORM = 11, LINEAR = 14,
     EMBEDDING = 17, MUL = 18, VIEW = 19, KVCACHE = 20, OP_GELU = 24, QUICKGLUE = 25, LAYERNORM = 26, CONVOLUTION2D = 29, CONVOLUTION3D = 30,
-    MULTIMODALROPE = 35, F_DIV = 81, F_TTADD = 83, F_TTMUL = 85, F_MM = 87, F_CAT = 90, F_VIEW = 91, F_TRANPOSE = 92, F_CLIP = 94,
+    MULTIMODALROPE = 35, F_DIV = 81, F_TTADD = 83, F_TTMUL = 85, F_MM = 87, F_CAT = 90, F_VIEW = 91, F_TRANPOSE = 92, F_CLIP = 94, F_SPLIT = 100,
     F_APPLY_VISIOROPE = 109, F_FA2 = 110,
 };
 typedef map<string, float> OpParam; // mllm/Types.hpp:21

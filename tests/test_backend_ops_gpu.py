@@ -223,3 +223,20 @@ def test_clip_vit_block_through_backend_ops(be, oracle, tmp_path_factory):
     err, ref = np.abs(y.reshape(S, Hd) - want), np.abs(want).max()
     assert np.quantile(err, 0.99) <= 2e-3 * ref and err.max() <= 1.5e-2 * ref   # a flipped Q8_K rounding downstream, as in the model tests
     assert cosine(y.reshape(-1), want.reshape(-1)) >= 0.99999
+
+
+@pytest.mark.parametrize("axis", [1, 2, 3])
+def test_split_op(be, axis):
+    """Tensor::split(each_dims, SEQUENCE / HEAD / DIMENSION): each piece is the matching slice (CPUsplitFunction)."""
+    rng = np.random.default_rng(30 + axis)
+    x = rng.standard_normal((2, 9, 4, 24)).astype(np.float32)  # BSHD memory order == Chl order (b, s, h, d)
+    n = x.shape[axis]
+    each = [1, n - 3, 2]
+    params = {"type": 100.0, "num_splits": 3.0, "dim_0": float(each[0]), "dim_1": float(each[1]), "dim_2": float(each[2]), "split_dim": float(axis),
+              "head_size": 1.0, "__n_out": 3.0}
+    at = 0
+    for i, e in enumerate(each):
+        y = be.run_op(dict(params, __out_index=float(i)), "split", [x], shapes=[(2, 4, 9, 24)])
+        want = np.take(x, range(at, at + e), axis=axis)
+        assert y.shape == want.shape and np.array_equal(bits(y), bits(want))
+        at += e
