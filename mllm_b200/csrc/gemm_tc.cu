@@ -109,18 +109,33 @@ static __device__ __forceinline__ void tc_wait_ld() { asm volatile("tcgen05.wait
 // a pipeline stage (8 chunks x 128 rows) is ONE contiguous 16 KB range and moves with a single bulk copy.
 //   qt[((mt * K/8 + kc) * 128 + r) * 8 + e]   row = mt*128 + r, k = kc*8 + e;   dt[(mt * nb + b) * 128 + r] = d_x
 // Rows beyond `rows` in the last tile are written as zeros.
-__global__ void k_quantize_q8_0_f16_tiled(const float *__restrict__ x, __half *__restrict__ qt, float *__restrict__ dt, int rows, int rows_pad,
-                                          int nb, int ldx) {
-    const int lane = threadIdx.x & 31;
-    const long long wid = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-    if (wid >= (long long)rows_pad * nb) return;
-    const int row = (int)(wid / nb), b = (int)(wid % nb);
+// Thread = 8 consecutive k of one row (one 16-byte chunk of the image); a warp = 8 rows x the 4 chunks of one Q block, so a row's
+// 128 bytes are read by 4 adjacent lanes and each chunk column is written as 8 adjacent 16-byte stores (full sectors both ways).
+__global__ void __launch_bounds__(256) k_quantize_q8_0_f16_tiled(const float *__restrict__ x, __half *__restrict__ qt, float *__restrict__ dt, int rows,
+                                                                  int rows_pad, int nb, int ldx) {
+    const int lane = threadIdx.x & 31, kc = lane & 3, rl = lane >> 2;
+    const long long wid = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); // (row group of 8, block)
+    const long long ngroups = (long long)(rows_pad >> 3) * nb;
+    if (wid >= ngroups) return;
+    const int b = (int)(wid % nb), row = (int)(wid / nb) * 8 + rl;
     const int mt = row >> 7, r = row & 127;
-    const float v = row < rows ? x[(size_t)row * ldx + (size_t)b * QK + lane] : 0.f;
-    const float amax = warp_max(fabsf(v));
-    const size_t kc = (size_t)b * 4 + (lane >> 3);
-    qt[(((size_t)mt * nb * 4 + kc) * 128 + r) * 8 + (lane & 7)] = __int2half_rn(q8_0_quant(v, amax));
-    if (lane == 0) dt[((size_t)mt * nb + b) * 128 + r] = __half2float(q8_0_scale(amax));
+    float4 v0 = make_float4(0.f, 0.f, 0.f, 0.f), v1 = v0;
+    if (row < rows) {
+        const float *p = x + (size_t)row * ldx + (size_t)b * QK + kc * 8;
+        v0 = *(const float4 *)p;
+        v1 = *(const float4 *)(p + 4);
+    }
+    float amax = fmaxf(fmaxf(fmaxf(fabsf(v0.x), fabsf(v0.y)), fmaxf(fabsf(v0.z), fabsf(v0.w))), fmaxf(fmaxf(fabsf(v1.x), fabsf(v1.y)), fmaxf(fabsf(v1.z), fabsf(v1.w))));
+    amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 1));
+    amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 2));
+    const __half2 h0 = __halves2half2(__int2half_rn(q8_0_quant(v0.x, amax)), __int2half_rn(q8_0_quant(v0.y, amax)));
+    const __half2 h1 = __halves2half2(__int2half_rn(q8_0_quant(v0.z, amax)), __int2half_rn(q8_0_quant(v0.w, amax)));
+    const __half2 h2 = __halves2half2(__int2half_rn(q8_0_quant(v1.x, amax)), __int2half_rn(q8_0_quant(v1.y, amax)));
+    const __half2 h3 = __halves2half2(__int2half_rn(q8_0_quant(v1.z, amax)), __int2half_rn(q8_0_quant(v1.w, amax)));
+    uint4 o;
+    o.x = *(const uint32_t *)&h0; o.y = *(const uint32_t *)&h1; o.z = *(const uint32_t *)&h2; o.w = *(const uint32_t *)&h3;
+    *(uint4 *)(qt + (((size_t)mt * nb * 4 + (size_t)b * 4 + kc) * 128 + r) * 8) = o;
+    if (kc == 0) dt[((size_t)mt * nb + b) * 128 + r] = __half2float(q8_0_scale(amax));
 }
 
 // 4 bytes holding values 0..15 -> two half2 (value - 8), exact: 0x6400 | v is the fp16 1024 + v
@@ -632,7 +647,8 @@ int launch_gemm_q4_0_tc(const void *W, const float *x, int ldx, const float *bia
     const int nb = K / QK;
     const long long warps = (long long)mp * nb;
     if (!skip_quant) {
-        k_quantize_q8_0_f16_tiled<<<(unsigned)((warps + 7) / 8), 256, 0, st>>>(x, qt, dt, M, mp, nb, ldx);
+        const long long groups = (long long)(mp >> 3) * nb; // a warp per 8 rows x 1 block
+        k_quantize_q8_0_f16_tiled<<<(unsigned)((groups + 7) / 8), 256, 0, st>>>(x, qt, dt, M, mp, nb, ldx);
         CU_LAUNCH_CHECK();
     }
     static bool configured = false;

@@ -260,7 +260,8 @@ MLLMCU_API int mllmcu_linear_ex(int wtype, const void *W, const float *x, const 
     if (ws == nullptr || ws_bytes < mllmcu_linear_workspace_bytes(M, K)) return -3;
     cudaStream_t st = (cudaStream_t)stream;
     if (wtype == 12 || wtype == 14) return launch_linear_kq(wtype, W, x, bias, y, M, N, K, ldx, ldy, out_f16, ws, st);
-    if (gemm_tc_supported(wtype, M, N, K) && !((uintptr_t)W & 15)) return launch_gemm_q4_0_tc(W, x, ldx, bias, y, M, N, K, ldy, out_f16, ws, flags & 1, st);
+    if (gemm_tc_supported(wtype, M, N, K) && !((uintptr_t)W & 15) && !((uintptr_t)x & 15) && !(ldx & 3)) // 16-byte loads of the activation rows
+        return launch_gemm_q4_0_tc(W, x, ldx, bias, y, M, N, K, ldy, out_f16, ws, flags & 1, st);
     int8_t *xq = (int8_t *)ws;
     float *xd = (float *)((char *)ws + align_up((size_t)M * K, 256));
     if (!(flags & 1)) {
