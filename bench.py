@@ -302,7 +302,8 @@ def gpu_arm(args, rank, world, local_rank):
                         "frac_of_hbm_peak": round((wbytes + kv_bytes) / (dec_ms * 1e-3) / 1e9 / peaks.get("hbm_gbs", 6650.0), 4)},
         "prefill": {"ms": round(float(np.mean(tp)), 3), "int8_TOPs": round(2 * (wbytes / 0.5625) * PREFILL / (float(np.mean(tp)) * 1e-3) / 1e12, 1)},
         "e2e": {"value": round(job_tokens_per_s(PREFILL + DECODE, world, e2e_mean), 2), "unit": "tok/s", "h2d_bytes_per_step": PREFILL * 4,
-                "d2h_bytes_per_step": DECODE * 4, "ms_per_step": round(e2e_mean, 2)},
+                # token ids of the first pick (fp32 row per step) + the device-side token log the fused steps write (one int32 per position)
+                "d2h_bytes_per_step": DECODE * 4 + (LIMIT + 1) * 4, "ms_per_step": round(e2e_mean, 2)},
         "decode_mode": model.decode_mode(), "gpu_launches": int(launches), "clocks": clocks, "roofline": roof,
     }
     if not args.no_cpu:

@@ -26,6 +26,18 @@ static thread_local std::string g_err;
 struct HostModel {
     std::unique_ptr<LlamaModel> model;
     double last_ms = 0;
+    void *pin = nullptr; // pinned staging for the request's ids (H2D) and token ids (D2H)
+    size_t pin_bytes = 0;
+    void *pinned(size_t bytes) {
+        if (bytes > pin_bytes) {
+            if (pin) mllmcu_host_free(pin);
+            pin = nullptr;
+            pin_bytes = (bytes + 4095) / 4096 * 4096;
+            MLLMCU_CHECK(mllmcu_host_alloc(&pin, pin_bytes));
+        }
+        return pin;
+    }
+    ~HostModel() { if (pin) mllmcu_host_free(pin); }
 };
 
 HAPI const char *mllm_cuda_last_error() { return g_err.c_str(); }
@@ -186,7 +198,9 @@ HAPI int mllm_cuda_llama_request_device(void *hv, const float *ids_host, int B, 
         const int V = h->model->config().vocab;
         Tensor ids(B, 1, S, 1, bn);
         ids.setName("input_ids");
-        ids.copyFromHost(ids_host);
+        float *stage = (float *)h->pinned(sizeof(float) * (size_t)B * S); // the copy engine reads pinned memory directly
+        memcpy(stage, ids_host, sizeof(float) * (size_t)B * S);
+        ids.copyFromHost(stage);
         Tensor toks(1, 1, n_decode > 0 ? n_decode : 1, B, bn); // fp32 ids, row per step
         void *e0, *e1, *e2;
         MLLMCU_CHECK(mllmcu_event_create(&e0));

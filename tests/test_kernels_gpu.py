@@ -430,3 +430,25 @@ def test_fast_division_is_ieee_exhaustive(cu):
     cu.check(cu.lib().mllmcu_selftest_div(0, 0x7F800000, bad.data_ptr(), cu._stream()))
     torch.cuda.synchronize()
     assert int(bad.item()) == 0
+
+
+# ---------------------------------------------------------------- argument errors surface as codes, never as silent fallbacks
+def test_c_abi_rejects_bad_arguments(cu):
+    import torch
+    L = cu.lib()
+    z = torch.zeros(4096, device="cuda")
+    st = cu._stream()
+    p = cu._ptr
+    # Linear: empty batch, K not a multiple of 32, unknown weight dtype, workspace too small
+    assert L.mllmcu_linear(2, p(z), p(z), None, p(z), 0, 64, 256, 256, 64, 0, p(z), z.numel() * 4, st) == -1
+    assert L.mllmcu_linear(2, p(z), p(z), None, p(z), 1, 64, 250, 250, 64, 0, p(z), z.numel() * 4, st) == -1
+    assert L.mllmcu_linear(3, p(z), p(z), None, p(z), 1, 64, 256, 256, 64, 0, p(z), z.numel() * 4, st) == -2
+    assert L.mllmcu_linear(2, p(z), p(z), None, p(z), 1, 64, 256, 256, 64, 0, p(z), 16, st) == -3
+    # attention: causal with more queries than keys, heads not a multiple of kv heads, head dim outside the kernels
+    assert L.mllmcu_flash_attn_f16kv(p(z), p(z), p(z), p(z), 1, 8, 4, 4, 4, 64, 1, 1024, None, 0, st) == -1
+    assert L.mllmcu_flash_attn_f16kv(p(z), p(z), p(z), p(z), 1, 4, 4, 6, 4, 64, 1, 1024, None, 0, st) == -1
+    assert L.mllmcu_flash_attn_f16kv(p(z), p(z), p(z), p(z), 1, 4, 4, 4, 4, 48, 1, 1024, None, 0, st) == -2
+    # fused decode Linear: batch above 8, K not a multiple of 128
+    with pytest.raises(cu.MllmcuError):
+        cu.gemv_fused([torch.zeros((64, 144), dtype=torch.uint8, device="cuda")], torch.zeros((9, 256), device="cuda"))
+    torch.cuda.synchronize()  # nothing was launched, nothing is pending
