@@ -12,10 +12,22 @@ __global__ void __launch_bounds__(256) k_rmsnorm(const float *__restrict__ x, co
     const int r = blockIdx.x;
     const float *xr = x + (size_t)r * dim;
     float *yr = y + (size_t)r * dim;
+    const bool vec = (dim & 3) == 0 && ((((uintptr_t)xr) | ((uintptr_t)yr) | ((uintptr_t)w)) & 15) == 0; // 16-byte loads and stores
     double ss = 0.0;
-    for (int d = threadIdx.x; d < dim; d += blockDim.x) {
-        const float v = xr[d];
-        ss += (double)v * (double)v;
+    if (vec) {
+        const float4 *x4 = (const float4 *)xr;
+        double s0 = 0.0, s1 = 0.0;
+        for (int d = threadIdx.x; d < (dim >> 2); d += blockDim.x) {
+            const float4 v = x4[d];
+            s0 = fma((double)v.x, (double)v.x, s0); s1 = fma((double)v.y, (double)v.y, s1);
+            s0 = fma((double)v.z, (double)v.z, s0); s1 = fma((double)v.w, (double)v.w, s1);
+        }
+        ss = s0 + s1;
+    } else {
+        for (int d = threadIdx.x; d < dim; d += blockDim.x) {
+            const float v = xr[d];
+            ss += (double)v * (double)v;
+        }
     }
     __shared__ double sred[8];
     __shared__ float s_rms;
@@ -30,6 +42,18 @@ __global__ void __launch_bounds__(256) k_rmsnorm(const float *__restrict__ x, co
     }
     __syncthreads();
     const float rms = s_rms;
+    if (vec) {
+        const float4 *x4 = (const float4 *)xr, *w4 = (const float4 *)w;
+        float4 *y4 = (float4 *)yr;
+        for (int d = threadIdx.x; d < (dim >> 2); d += blockDim.x) {
+            const float4 v = x4[d];
+            float4 ww = w4[d];
+            if (add_unit_offset) { ww.x = __fadd_rn(1.0f, ww.x); ww.y = __fadd_rn(1.0f, ww.y); ww.z = __fadd_rn(1.0f, ww.z); ww.w = __fadd_rn(1.0f, ww.w); }
+            y4[d] = make_float4(__fmul_rn(__fmul_rn(v.x, rms), ww.x), __fmul_rn(__fmul_rn(v.y, rms), ww.y), __fmul_rn(__fmul_rn(v.z, rms), ww.z),
+                                __fmul_rn(__fmul_rn(v.w, rms), ww.w));
+        }
+        return;
+    }
     for (int d = threadIdx.x; d < dim; d += blockDim.x) {
         const float t = __fmul_rn(xr[d], rms);
         const float ww = add_unit_offset ? __fadd_rn(1.0f, w[d]) : w[d];
@@ -133,11 +157,43 @@ __global__ void k_rope(int type, const float *__restrict__ x, void *out, int B, 
     }
 }
 
+// LLaMA-type rotation (adjacent pairs) over the whole head: two pairs per thread, 16-byte loads of x and of the table rows.  Same
+// operations per element as k_rope (products rounded separately), so the results are bit-identical.
+__global__ void k_rope_llama4(const float *__restrict__ x, void *out, int B, int S, int H, int D, int pos0, const float *__restrict__ sin_t,
+                              const float *__restrict__ cos_t, int tdim, int out_f16, long long obs, long long oss) {
+    const int q4 = D / 4;
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= (long long)B * S * H * q4) return;
+    const int p = (int)(i % q4);
+    const int h = (int)((i / q4) % H);
+    const int s = (int)((i / ((long long)q4 * H)) % S);
+    const int b = (int)(i / ((long long)q4 * H * S));
+    const float4 v = *(const float4 *)(x + (((size_t)b * S + s) * H + h) * D + 4 * p);
+    const float4 sn = *(const float4 *)(sin_t + (size_t)(s + pos0) * tdim + 4 * p), cs = *(const float4 *)(cos_t + (size_t)(s + pos0) * tdim + 4 * p);
+    const float o0 = __fsub_rn(__fmul_rn(v.x, cs.x), __fmul_rn(v.y, sn.x)), o1 = __fadd_rn(__fmul_rn(v.x, sn.x), __fmul_rn(v.y, cs.x));
+    const float o2 = __fsub_rn(__fmul_rn(v.z, cs.z), __fmul_rn(v.w, sn.z)), o3 = __fadd_rn(__fmul_rn(v.z, sn.z), __fmul_rn(v.w, cs.z));
+    const size_t at = (size_t)b * obs + (size_t)s * oss + (size_t)h * D + 4 * p;
+    if (out_f16) {
+        const __half2 a = __halves2half2(__float2half_rn(o0), __float2half_rn(o1)), c = __halves2half2(__float2half_rn(o2), __float2half_rn(o3));
+        *(uint2 *)((__half *)out + at) = make_uint2(*(const uint32_t *)&a, *(const uint32_t *)&c);
+    } else {
+        *(float4 *)((float *)out + at) = make_float4(o0, o1, o2, o3);
+    }
+}
+
 MLLMCU_API int mllmcu_rope(int rope_type, const float *x, void *out, int B, int S, int H, int D, int rot_dim, int pos0,
                            const float *sin_t, const float *cos_t, int tdim, int out_f16, long long obs, long long oss, void *stream) {
     if ((rope_type != 2 && rope_type != 4) || D % 2 || rot_dim % 2 || rot_dim > D || rot_dim > tdim) return -1;
     const long long total = (long long)B * S * H * (D / 2);
     if (total <= 0) return -1;
+    const size_t esz = out_f16 ? 2 : 4;
+    if (rope_type == 2 && rot_dim == D && D % 4 == 0 && tdim % 4 == 0 && obs % 4 == 0 && oss % 4 == 0 && total >= 4096 &&
+        !((uintptr_t)x & 15) && !((uintptr_t)sin_t & 15) && !((uintptr_t)cos_t & 15) && !((uintptr_t)out & (4 * esz - 1))) {
+        const long long t4 = total / 2;
+        k_rope_llama4<<<(unsigned)((t4 + 255) / 256), 256, 0, (cudaStream_t)stream>>>(x, out, B, S, H, D, pos0, sin_t, cos_t, tdim, out_f16, obs, oss);
+        CU_LAUNCH_CHECK();
+        return 0;
+    }
     k_rope<<<(unsigned)((total + 255) / 256), 256, 0, (cudaStream_t)stream>>>(rope_type, x, out, B, S, H, D, rot_dim, pos0, sin_t, cos_t, tdim, out_f16, obs, oss);
     CU_LAUNCH_CHECK();
     return 0;

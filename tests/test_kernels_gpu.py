@@ -264,6 +264,21 @@ def test_rope_bit_exact(cu, oracle, rtype, f16):
             assert np.array_equal(bits(y[b]), bits(want))
 
 
+@pytest.mark.parametrize("f16", [False, True])
+def test_rope_llama_prefill_shape_bit_exact(cu, oracle, f16):
+    """A prefill-sized LLaMA-type rotation takes the 16-byte kernel (two pairs per thread): same bits as the oracle."""
+    rng = np.random.default_rng(12)
+    B, S, H, D, pos0 = 1, 40, 8, 128, 3
+    s, c = oracle.only.rope_tables(2, 64, D, 10000.0)
+    x = rng.standard_normal((B, S, H, D)).astype(np.float32)
+    y = cu.rope(2, dev(x), pos0, dev(s), dev(c), out_f16=f16).cpu().numpy()
+    want = oracle.only.rope_apply(2, x[0], pos0, s, c, out_fp16=f16)
+    if f16:
+        assert np.array_equal(y[0].view(np.uint16), want)
+    else:
+        assert np.array_equal(bits(y[0]), bits(want))
+
+
 def test_rope_partial_and_cache_slice(cu, oracle):
     import torch
     rng = np.random.default_rng(8)
