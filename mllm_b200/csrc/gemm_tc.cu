@@ -645,7 +645,6 @@ int launch_gemm_q4_0_tc(const void *W, const float *x, int ldx, const float *bia
     }
     float *dt = (float *)((char *)ws + ((size_t)mp * K * 2 + 255) / 256 * 256);
     const int nb = K / QK;
-    const long long warps = (long long)mp * nb;
     if (!skip_quant) {
         const long long groups = (long long)(mp >> 3) * nb; // a warp per 8 rows x 1 block
         k_quantize_q8_0_f16_tiled<<<(unsigned)((groups + 7) / 8), 256, 0, st>>>(x, qt, dt, M, mp, nb, ldx);
