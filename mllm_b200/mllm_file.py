@@ -48,6 +48,8 @@ class Names:
 CONFIGS = {
     "tinyllama-1.1b": dict(vocab=32000, hidden=2048, layers=22, heads=32, kv_heads=4, ffn=5632, rope_type=ROPE_HF, rope_theta=10000.0, rms_eps=1e-5, qkv_bias=0),
     "llama2-7b": dict(vocab=32000, hidden=4096, layers=32, heads=32, kv_heads=32, ffn=11008, rope_type=ROPE_LLAMA, rope_theta=10000.0, rms_eps=1e-6, qkv_bias=0),
+    # the LLM of Qwen2-VL-2B (models/qwen/configuration_qwen.hpp:167-181); text-only positions here (M-RoPE reduces to HF RoPE when t = h = w)
+    "qwen2-vl-2b-llm": dict(vocab=151936, hidden=1536, layers=28, heads=12, kv_heads=2, ffn=8960, rope_type=ROPE_HF, rope_theta=1000000.0, rms_eps=1e-6, qkv_bias=1),
     "qwen1.5-1.8b": dict(vocab=151936, hidden=2048, layers=24, heads=16, kv_heads=16, ffn=5504, rope_type=ROPE_HF, rope_theta=1000000.0, rms_eps=1e-6, qkv_bias=1),
     # small graphs with the same structure, for parity tests the CPU oracle finishes in seconds
     "toy-llama": dict(vocab=512, hidden=256, layers=2, heads=4, kv_heads=4, ffn=512, rope_type=ROPE_LLAMA, rope_theta=10000.0, rms_eps=1e-6, qkv_bias=0),
