@@ -230,7 +230,11 @@ def gpu_arm(args, rank, world, local_rank):
     import torch
     torch.cuda.set_device(local_rank)
     from mllm_b200 import backend, build
-    build.build_all()
+    if rank == 0:
+        build.build_all()  # a no-op when the in-tree libraries are current; never two ranks compiling the same objects
+    if world > 1:
+        import torch.distributed as dist
+        dist.barrier()
     peaks = {}
     try:
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
