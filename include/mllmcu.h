@@ -285,6 +285,8 @@ int mllmcu_flash_attn_f32kv(const float *q, const float *k, const float *v, floa
 /* ---- fp32 -> fp16 RNE rows (KV-cache append of a tensor that is not produced
  * by a Linear/RoPE writing in place). dst row stride ld_dst, src row stride ld_src (elements) */
 int mllmcu_f32_to_f16_rows(const float *src, void *dst, int rows, int cols, long long ld_src, long long ld_dst, void *stream);
+/* the reverse, exact widening: Backend::convert_fp_data (mllm/Backend.hpp:73, CPUBackend.cpp:260-277) for Tensor::fp32() */
+int mllmcu_f16_to_f32_rows(const void *src, float *dst, int rows, int cols, long long ld_src, long long ld_dst, void *stream);
 
 /* ---- greedy sampling: LlmTextGenerator argmax (Generate.cpp:46-53) on device;
  * first maximum wins, as std::max_element does. out: int32 per row. */

@@ -39,6 +39,7 @@ def lib():
         L.mllm_cuda_llama_set_step_kernel.argtypes = [C.c_void_p, C.c_int]
         L.mllm_cuda_llama_request_device.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_float),
                                                      C.POINTER(C.c_float), C.c_void_p]
+        L.mllm_cuda_convert_fp_roundtrip.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
         L.mllm_cuda_run_op.argtypes = [C.POINTER(C.c_char_p), C.c_void_p, C.c_int, C.c_char_p, C.c_char_p, C.POINTER(C.c_void_p),
                                        C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
         _lib = L
@@ -53,6 +54,16 @@ def _check(rc):
 def init_backend(device=0):
     """Module::initBackend `case MLLM_CUDA` -- Backend::global_backends[MLLM_CUDA]."""
     _check(lib().mllm_cuda_init_backend(device))
+
+
+def convert_fp_roundtrip(x):
+    """fp32 [rows, cols] -> (fp16 bits, fp32 again) through Backend::convert_fp_data (Tensor::half() / Tensor::fp32())."""
+    init_backend()
+    x = np.ascontiguousarray(x, dtype=np.float32)
+    h = np.empty(x.shape, dtype=np.uint16)
+    b = np.empty(x.shape, dtype=np.float32)
+    _check(lib().mllm_cuda_convert_fp_roundtrip(_p(x), x.shape[0], x.shape[1], _p(h), _p(b)))
+    return h, b
 
 
 def kernel_launches():

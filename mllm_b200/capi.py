@@ -79,6 +79,7 @@ SYMBOLS = {
     "mllmcu_conv3d_valid": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _vp]),
     "mllmcu_flash_attn_f32kv": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _ll, _vp, _sz, _vp]),
     "mllmcu_f32_to_f16_rows": (_i, [_vp, _vp, _i, _i, _ll, _ll, _vp]),
+    "mllmcu_f16_to_f32_rows": (_i, [_vp, _vp, _i, _i, _ll, _ll, _vp]),
     "mllmcu_argmax": (_i, [_vp, _i, _i, _vp, _vp]),
     "mllmcu_argmax_ids": (_i, [_vp, _i, _i, _vp, _vp]),
     "mllmcu_decode_embed": (_i, [_vp, _vp, _vp, _i, _i, _vp, _vp]),

@@ -294,6 +294,22 @@ MLLMCU_API int mllmcu_f32_to_f16_rows(const float *src, void *dst, int rows, int
     return 0;
 }
 
+// fp16 -> fp32 (Backend::convert_fp_data, Tensor::fp32(): exact widening)
+__global__ void k_f16_to_f32_rows(const __half *__restrict__ src, float *__restrict__ dst, int rows, int cols, long long lds, long long ldd) {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= (long long)rows * cols) return;
+    const int c = (int)(i % cols);
+    const long long r = i / cols;
+    dst[r * ldd + c] = __half2float(src[r * lds + c]);
+}
+MLLMCU_API int mllmcu_f16_to_f32_rows(const void *src, float *dst, int rows, int cols, long long lds, long long ldd, void *stream) {
+    if (rows <= 0 || cols <= 0) return -1;
+    const long long tot = (long long)rows * cols;
+    k_f16_to_f32_rows<<<(unsigned)((tot + 255) / 256), 256, 0, (cudaStream_t)stream>>>((const __half *)src, dst, rows, cols, lds, ldd);
+    CU_LAUNCH_CHECK();
+    return 0;
+}
+
 // ------------------------------------------------------------------- argmax
 // LlmTextGenerator greedy (Generate.cpp:46-53): first maximum wins.
 __global__ void __launch_bounds__(1024) k_argmax(const float *__restrict__ x, int n, int *__restrict__ out, float *__restrict__ out_f) {

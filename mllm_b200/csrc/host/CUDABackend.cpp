@@ -5,6 +5,7 @@
 // mllm/ParamLoader.cpp:88-141,157-286, mllm/backends/cpu/CPUBackend.cpp:314-405 (runOp).
 #include "mllm_cuda.hpp"
 
+#include <chrono>
 #include <cstring>
 #include <fcntl.h>
 #include <sys/mman.h>
@@ -270,6 +271,37 @@ vector<Tensor> CUDABackend::runOp(Op *op, vector<Tensor> inputs, vector<string> 
         }
     }
     return shells;
+}
+
+void *CUDABackend::funcCreate(int type) {
+    throw std::runtime_error("[mllm-cuda] funcCreate(" + std::to_string(type) + "): tensor functions are Ops on this backend (opCreate with the F_* type)");
+}
+
+// .half() / .fp32(): dense tensors of equal shape; fp32 -> fp16 rounds to nearest even like MLLM_FP32_TO_FP16 (F16C), fp16 -> fp32 is exact
+void CUDABackend::convert_fp_data(Tensor *src, Tensor *dest) {
+    if (!src || !dest || src->count() != dest->count() || !src->contiguous() || !dest->contiguous())
+        throw std::runtime_error("[mllm-cuda] convert_fp_data: dense tensors of equal size expected");
+    const long long n = (long long)src->count();
+    const int cols = src->dimension(), rows = (int)(n / cols);
+    if (src->dtype() == MLLM_TYPE_F32 && dest->dtype() == MLLM_TYPE_F16)
+        MLLMCU_CHECK(mllmcu_f32_to_f16_rows(src->devPtr<float>(), dest->rawDevPtr(), rows, cols, cols, cols, stream_));
+    else if (src->dtype() == MLLM_TYPE_F16 && dest->dtype() == MLLM_TYPE_F32)
+        MLLMCU_CHECK(mllmcu_f16_to_f32_rows(src->rawDevPtr(), dest->devPtr<float>(), rows, cols, cols, cols, stream_));
+    else
+        throw std::runtime_error("[mllm-cuda] convert_fp_data: only fp32 <-> fp16"); // CPUBackend.cpp:274-276
+    kernel_launches++;
+    dropQuantTag();
+}
+
+// The outermost Forward is timed on the host; the clock stops only after the stream has drained.
+vector<Tensor> CUDABackend::runForward(const std::function<vector<Tensor>()> &forward, double *ms_out) {
+    const auto t0 = std::chrono::steady_clock::now();
+    vector<Tensor> out = forward();
+    if (ms_out) {
+        sync();
+        *ms_out = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    }
+    return out;
 }
 
 // ------------------------------------------------------------- ParamLoader

@@ -28,9 +28,11 @@ public:
             op_->load(*st_->loader);
             loaded_ = true;
         }
-        return st_->backend->runOp(op_.get(), inputs, {"out-" + name_ + st_->tag}, false); // part 4
+        return st_->backend->runLayer(this, inputs, 1); // part 4 (Backend::runLayer names the outputs and calls runOp)
     }
     Op *op() { return op_.get(); }
+    const string &name() const { return name_; }
+    const string &tag() const { return st_->tag; }
 
 private:
     ModuleState *st_ = nullptr;

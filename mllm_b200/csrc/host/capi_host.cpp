@@ -85,10 +85,11 @@ HAPI int mllm_cuda_llama_forward(void *hv, const float *ids_host, int B, int S, 
         Tensor dump;
         const LlamaConfig &c = h->model->config();
         if (dump_host) dump = Tensor(1, 1, (c.layers + 1) * B * S, c.hidden, bn);
-        Tensor logits = h->model->forward(ids, dump_host ? dump.devPtr<float>() : nullptr);
+        // Module::operator() -> Backend::runForward (mllm/Module.hpp:193-261): the outermost forward is timed, device drained before the clock stops
+        Tensor logits = bn->runForward([&]() { return vector<Tensor>{h->model->forward(ids, dump_host ? dump.devPtr<float>() : nullptr)}; }, &h->last_ms)[0];
         logits.copyToHost(logits_host);
         if (dump_host) dump.copyToHost(dump_host);
-        h->last_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+        (void)t0;
     })
 }
 
@@ -178,6 +179,21 @@ HAPI int mllm_cuda_run_op(const char **keys, const float *vals, int n_params, co
         out_shape[0] = o.batch(); out_shape[1] = o.head(); out_shape[2] = o.sequence(); out_shape[3] = o.dimension();
         if (o.dtype() != MLLM_TYPE_F32 || !o.contiguous()) throw std::runtime_error("run_op: output must be dense fp32");
         o.copyToHost(out_host);
+    })
+}
+
+// Tensor::half() / Tensor::fp32() through Backend::convert_fp_data: x [rows][cols] fp32 -> fp16 bits -> fp32 again (test access)
+HAPI int mllm_cuda_convert_fp_roundtrip(const float *x, int rows, int cols, uint16_t *half_out, float *back_out) {
+    GUARD({
+        CUDABackend *bn = backend();
+        Tensor a(1, 1, rows, cols, bn), h(bn), b(bn);
+        a.copyFromHost(x);
+        h.reshape(1, 1, rows, cols); h.setDtype(MLLM_TYPE_F16); h.alloc();
+        b.reshape(1, 1, rows, cols); b.setDtype(MLLM_TYPE_F32); b.alloc();
+        bn->convert_fp_data(&a, &h);
+        bn->convert_fp_data(&h, &b);
+        h.copyToHost(half_out);
+        b.copyToHost(back_out);
     })
 }
 

@@ -183,6 +183,15 @@ public:
     virtual Op *opCreate(const OpParam &op_param, string name = "", int threadCount = 4) = 0;
     virtual vector<Tensor> runOp(Op *op, vector<Tensor> inputs, vector<string> out_names, bool in_place) = 0;
     virtual void registerOps() = 0;
+    virtual void registerFuncs() {}                              // legacy TensorFunction table (mllm/Backend.hpp:58): nothing to register
+    virtual void *funcCreate(int /*TensorFuncType*/) { return nullptr; }
+    // .half() / .fp32() between tensors of this backend (mllm/Backend.hpp:73)
+    virtual void convert_fp_data(Tensor *src, Tensor *dest) = 0;
+    // Layer::run's hand-off (CPUBackend.cpp:407-417): names the N outputs "out-<op>[-i]" and calls runOp
+    virtual vector<Tensor> runLayer(class Layer *layer, vector<Tensor> inputs, int N) = 0;
+    // Module::operator() hand-off (CPUBackend.cpp:419-460): runs the module's Forward; the outermost call is timed and must not
+    // stop the clock before the device has finished (cf. finishQueue, OpenCLBackend.cpp:1087)
+    virtual vector<Tensor> runForward(const std::function<vector<Tensor>()> &forward, double *ms_out) = 0;
     virtual bool load_from_file(Tensor *tensor, ParamLoader *loader) { return false; }
     BackendType type() const { return type_; }
     static map<BackendType, std::unique_ptr<Backend>> global_backends; // mllm/Backend.hpp:125
@@ -232,6 +241,10 @@ public:
     Op *opCreate(const OpParam &op_param, string name = "", int threadCount = 4) override;
     vector<Tensor> runOp(Op *op, vector<Tensor> inputs, vector<string> out_names, bool in_place) override;
     void registerOps() override;
+    void *funcCreate(int type) override; // throws, like OpenCLBackend::funcCreate (OpenCLBackend.cpp:805): every function is an Op here
+    void convert_fp_data(Tensor *src, Tensor *dest) override;
+    vector<Tensor> runLayer(class Layer *layer, vector<Tensor> inputs, int N) override;
+    vector<Tensor> runForward(const std::function<vector<Tensor>()> &forward, double *ms_out) override;
     bool addCreator(OpType t, Creator *c);
 
     void *stream() const { return stream_; }

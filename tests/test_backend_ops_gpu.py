@@ -240,3 +240,16 @@ def test_split_op(be, axis):
         want = np.take(x, range(at, at + e), axis=axis)
         assert y.shape == want.shape and np.array_equal(bits(y), bits(want))
         at += e
+
+
+def test_convert_fp_data_half_and_back(be):
+    """Backend::convert_fp_data (Tensor::half() / fp32()): fp32 -> fp16 rounds to nearest even like the reference's F16C conversion,
+    fp16 -> fp32 is exact."""
+    rng = np.random.default_rng(44)
+    x = (rng.standard_normal((7, 96)) * np.float32(10.0) ** rng.integers(-6, 5, (7, 96))).astype(np.float32)
+    x[0, :4] = [0.0, -0.0, 65504.0, 1e-8]
+    x[1, 0] = np.float32(1.0 + 2.0 ** -11)  # a tie: rounds to even
+    h, b = be.convert_fp_roundtrip(x)
+    want = x.astype(np.float16)
+    assert np.array_equal(h, want.view(np.uint16))
+    assert np.array_equal(bits(b), bits(want.astype(np.float32)))
