@@ -467,3 +467,34 @@ def test_c_abi_rejects_bad_arguments(cu):
     with pytest.raises(cu.MllmcuError):
         cu.gemv_fused([torch.zeros((64, 144), dtype=torch.uint8, device="cuda")], torch.zeros((9, 256), device="cuda"))
     torch.cuda.synchronize()  # nothing was launched, nothing is pending
+
+
+# ---------------------------------------------------------------- full BASELINE sizes: properties instead of the (slow) oracle
+@pytest.mark.parametrize("N,K", [(11008, 4096), (4096, 11008), (32000, 4096)])
+def test_full_size_decode_and_prefill_linears_agree(cu, N, K):
+    """LLaMA-2-7B Linear shapes: the decode kernel (one row, fused TMA GEMV) and the prefill kernel (the same row nine times,
+    tcgen05) are independent implementations of the same sum; they must agree row for row, and the nine prefill rows must be
+    bit-identical to each other.  Spot rows are also checked against exact integer arithmetic in numpy."""
+    import torch
+    rng = np.random.default_rng(N + K)
+    W = torch.randint(0, 256, (N, K // 32 * 18), dtype=torch.uint8, device="cuda")
+    Wv = W.view(N, K // 32, 18)
+    Wv[:, :, 1] = 0x1C + torch.randint(0, 4, (N, K // 32), dtype=torch.uint8, device="cuda")  # fp16 scales around 2^-8 .. 2^-5
+    x = torch.from_numpy(rng.standard_normal((1, K)).astype(np.float32)).cuda()
+    y1 = cu.gemv_fused([W], x).cpu().numpy()[0]
+    y9 = cu.linear(W, x.repeat(9, 1).contiguous()).cpu().numpy()
+    for m in range(1, 9):
+        assert np.array_equal(bits(y9[m]), bits(y9[0]))
+    scale = np.abs(y9[0]).max()
+    assert np.abs(y1 - y9[0]).max() <= 2e-5 * scale
+    # three rows against float64 arithmetic on the dequantised blocks and the Q8_0 activations the kernels use
+    xq = cu.quantize_q8_0(x).cpu().numpy().reshape(K // 32, 34)
+    dx = xq[:, :2].copy().view(np.float16).astype(np.float64)[:, 0]
+    qx = xq[:, 2:].view(np.int8).astype(np.float64)
+    Wh = W.cpu().numpy().reshape(N, K // 32, 18)
+    for n in (0, N // 2, N - 1):
+        dw = Wh[n, :, :2].copy().view(np.float16).astype(np.float64)[:, 0]
+        qs = Wh[n, :, 2:]
+        qw = np.concatenate([(qs & 0x0F).astype(np.float64) - 8, (qs >> 4).astype(np.float64) - 8], axis=1)
+        want = float(np.sum(dw * dx * np.sum(qw * qx, axis=1)))
+        assert abs(y1[n] - want) <= 2e-5 * scale and abs(y9[0][n] - want) <= 2e-5 * scale
