@@ -150,6 +150,11 @@ struct LlamaModel::DecodePlan {
     vector<L> layers;
     FuseInfo embd, norm, head;
     Tensor x, x2, qkv, ao, g, logits, ids, ctl, tok_log, attn_ws;
+    // k-quant (Q4_K / Q6_K) Linears have no fused TMA GEMV: they run as rmsnorm -> mllmcu_linear (Q8_K quantiser + k-quant GEMV) ->
+    // add / silu*mul launches on these fixed buffers, still inside the one captured graph with the device-resident position
+    bool kquant = false;
+    Tensor kq_xn, kq_t1, kq_t2, kq_ws;
+    size_t kq_ws_bytes = 0;
     // activation replicas: x, x2 and g are stored `reps` times ([reps][B][width]) by their producers and every RMSNorm weight is
     // copied `reps` times ([norm][reps][H]), so the CTAs of the consuming Linear spread their reads over more L2 slices
     int reps = 1;
@@ -203,12 +208,19 @@ bool LlamaModel::decode_plan_usable(int B) {
                  get(b.gate, l.gate) && get(b.up, l.up) && get(b.down, l.down) && get(b.q_rope, l.rope) && get(b.k_cache, l.kc) &&
                  get(b.v_cache, l.vc);
             if (!ok) break;
-            for (const FuseInfo *f : {&l.q, &l.k, &l.v, &l.o, &l.gate, &l.up, &l.down}) ok = ok && f->wtype == MLLM_TYPE_Q4_0;
+            for (const FuseInfo *f : {&l.q, &l.k, &l.v, &l.o, &l.gate, &l.up, &l.down}) {
+                ok = ok && (f->wtype == MLLM_TYPE_Q4_0 || f->wtype == MLLM_TYPE_Q4_K || f->wtype == MLLM_TYPE_Q6_K);
+                if (f->wtype != MLLM_TYPE_Q4_0) p->kquant = true;
+            }
             ok = ok && !l.n1.unit_offset && !l.n2.unit_offset && l.kc.cache_batch == B && l.vc.cache_batch == B && l.kc.cache_dim == D &&
                  l.kc.cache_heads == cfg_.kv_heads && l.rope.rot_dim % 2 == 0;
             l.advance[0] = b.q_rope.op(); l.advance[1] = b.k_rope.op(); l.advance[2] = b.k_cache.op(); l.advance[3] = b.v_cache.op();
         }
-        ok = ok && p->head.wtype == MLLM_TYPE_Q4_0 && p->embd.wtype == MLLM_TYPE_Q4_0 && !p->norm.unit_offset;
+        ok = ok && (p->head.wtype == MLLM_TYPE_Q4_0 || p->head.wtype == MLLM_TYPE_Q4_K || p->head.wtype == MLLM_TYPE_Q6_K) &&
+             p->embd.wtype == MLLM_TYPE_Q4_0 && !p->norm.unit_offset;
+        if (p->head.wtype != MLLM_TYPE_Q4_0) p->kquant = true;
+        static const bool no_kq_plan = env_on("MLLM_CUDA_NO_KQUANT_PLAN");
+        if (p->kquant && (no_kq_plan || cfg_.hidden % 256 || cfg_.ffn % 256)) ok = false;
         if (!ok) return false; // caches not allocated yet (no prefill so far) or a dtype outside the fused kernels
         CUDABackend *bn = st_.backend;
         const int QKV = (cfg_.heads + 2 * cfg_.kv_heads) * D;
@@ -230,6 +242,15 @@ bool LlamaModel::decode_plan_usable(int B) {
         }
         p->ids = Tensor(B, 1, 1, 1, bn); p->ctl = Tensor(1, 1, 1, 4, bn);
         p->tok_log = Tensor(1, 1, cfg_.cache_limit + 1, B, bn);
+        if (p->kquant) {
+            p->reps = 1;
+            const int W = cfg_.ffn > cfg_.hidden ? cfg_.ffn : cfg_.hidden;
+            p->kq_xn = Tensor(1, 1, B, cfg_.hidden, bn);
+            p->kq_t1 = Tensor(1, 1, B, W, bn);
+            p->kq_t2 = Tensor(1, 1, B, W, bn);
+            p->kq_ws_bytes = mllmcu_linear_workspace_bytes(B, W);
+            p->kq_ws = Tensor(1, 1, 1, (int)((p->kq_ws_bytes + 3) / 4), bn);
+        }
         p->attn_ws_bytes = mllmcu_decode_attn_workspace_bytes(B, cfg_.heads, D);
         p->attn_ws = Tensor(1, 1, 1, (int)((p->attn_ws_bytes + 3) / 4), bn);
         MLLMCU_CHECK(mllmcu_memset(p->attn_ws.rawDevPtr(), 0, p->attn_ws.cntSize(), bn->stream()));
@@ -239,7 +260,7 @@ bool LlamaModel::decode_plan_usable(int B) {
         p->launches = 3 + (p->layers[0].rope.rot_dim == D ? 5 : 6) * cfg_.layers;
         // the persistent whole-step kernel is opt-in: on B200 its grid barriers + in-order per-warp rings currently lose
         // to the PDL-chained persistent GEMVs (2.2 vs 1.7 ms/token on the 7B, profiles/r01_step_kernel_phases.txt)
-        if ((env_on("MLLM_CUDA_STEP_KERNEL") || want_step_kernel_) && B <= 4) build_step_kernel(*p);
+        if ((env_on("MLLM_CUDA_STEP_KERNEL") || want_step_kernel_) && B <= 4 && !p->kquant) build_step_kernel(*p);
         if (p->step) p->launches = 3;
         plan_ = std::move(p);
     }
@@ -368,6 +389,33 @@ bool LlamaModel::issue_step(DecodePlan &p, bool pick, bool pdl_on) {
     // replicated RMSNorm weight (2 * layer, 2 * layer + 1, or 2 * layers for the final norm)
     auto gemv = [&](std::initializer_list<const FuseInfo *> ws, const float *in, int K, int in_reps, const FuseInfo *norm, int norm_idx, int epi,
                     const float *res, int ldr, float *out, int ldy, int out_reps, bool late_trigger = false) -> bool {
+        if (p.kquant) { // op-level kernels on the plan's fixed buffers (graph-capturable: no host-side position, no allocation)
+            launch_no++;
+            const float *src = in;
+            if (norm) {
+                MLLMCU_CHECK(mllmcu_rmsnorm(in, p.norm_rep.devPtr<float>() + (size_t)norm_idx * R * H, p.kq_xn.devPtr<float>(), B, K, norm->eps, 0, st));
+                src = p.kq_xn.devPtr<float>();
+            }
+            auto lin = [&](const FuseInfo *f, float *y, int ld) {
+                MLLMCU_CHECK(mllmcu_linear(f->wtype, f->weight, src, f->bias, y, B, f->out, K, K, ld, 0, p.kq_ws.rawDevPtr(), p.kq_ws_bytes, st));
+            };
+            if (epi == 0) {
+                int col = 0;
+                for (const FuseInfo *f : ws) { lin(f, out + col, ldy); col += f->out; }
+            } else if (epi == 1) {
+                const FuseInfo *f = *ws.begin();
+                lin(f, p.kq_t1.devPtr<float>(), f->out);
+                if (ldr != f->out || ldy != f->out) throw std::runtime_error("[mllm-cuda] decode plan: residual rows must be dense");
+                MLLMCU_CHECK(mllmcu_add(p.kq_t1.devPtr<float>(), res, out, (size_t)B * f->out, st));
+            } else {
+                const FuseInfo *fg = *ws.begin(), *fu = *(ws.begin() + 1);
+                lin(fg, p.kq_t1.devPtr<float>(), fg->out);
+                lin(fu, p.kq_t2.devPtr<float>(), fu->out);
+                if (ldy != fg->out) throw std::runtime_error("[mllm-cuda] decode plan: gate rows must be dense");
+                MLLMCU_CHECK(mllmcu_silu_mul(p.kq_t1.devPtr<float>(), p.kq_t2.devPtr<float>(), out, (size_t)B * fg->out, st));
+            }
+            return true;
+        }
         mllmcu_gemv_desc d = {};
         d.wtype = MLLM_TYPE_Q4_0;
         for (const FuseInfo *f : ws) { d.W[d.nW] = f->weight; d.N[d.nW] = f->out; d.bias[d.nW] = f->bias; d.nW++; }
@@ -405,7 +453,7 @@ bool LlamaModel::issue_step(DecodePlan &p, bool pick, bool pdl_on) {
         if (l.rope.rot_dim == D && !no_rope_fusion) { // full rotary: RoPE and the KV append ride inside the attention kernel
             MLLMCU_CHECK(mllmcu_decode_attn_rope(l.rope.rope_type, qkv, QKV, l.kc.cache, l.vc.cache, ao, Hq * D, ctl, B, Hq, Hkv, D, l.rope.sin_t,
                                                  l.rope.cos_t, l.rope.rot_dim, l.kc.cache_bstride, l.kc.cache_limit, p.attn_ws.rawDevPtr(),
-                                                 p.attn_ws_bytes, pdl ? 2 : 0, st));
+                                                 p.attn_ws_bytes, (pdl && !p.kquant) ? 2 : 0, st));
         } else {
             MLLMCU_CHECK(mllmcu_decode_rope_kv(l.rope.rope_type, qkv, QKV, B, Hq, Hkv, D, l.rope.rot_dim, l.rope.sin_t, l.rope.cos_t, l.rope.rot_dim,
                                                ctl, l.kc.cache, l.vc.cache, l.kc.cache_bstride, l.kc.cache_limit, pdl, st));

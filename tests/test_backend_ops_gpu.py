@@ -63,6 +63,8 @@ def test_model_with_other_weight_formats(be, oracle, tmp_path_factory, name, wty
         assert np.array_equal(lg.argmax(1)[clear], lc.argmax(1)[clear])
         nxt = lc.argmax(1).astype(np.float32)[:, None]
         lc, lg = cpu.forward(nxt), gpu.forward(nxt)
+        # single-token steps replay the captured decode graph for every weight format (k-quants: op-level kernels on fixed buffers)
+        assert gpu.last_step_fused()
         assert cosine(lg, lc) >= (0.9995 if wtype == mf.Q4_K else 0.9999)
     gpu.close()
 
