@@ -190,7 +190,7 @@ static bool env_on(const char *k) {
 
 bool LlamaModel::decode_plan_usable(int B) {
     static const bool eager = env_on("MLLM_CUDA_EAGER_DECODE");
-    if (eager || force_eager_ || B < 1 || B > 8) return false;
+    if (eager || force_eager_ || B < 1 || B > 64) return false; // 1-8: fused TMA GEMVs; 9-64: op-level kernels inside the captured graph
     if (plan_ && plan_->unsupported) return false;
     const int H = cfg_.hidden, D = cfg_.head_dim();
     if (H % 128 || cfg_.ffn % 128 || (D != 32 && D != 64 && D != 128)) return false;
@@ -221,6 +221,9 @@ bool LlamaModel::decode_plan_usable(int B) {
         if (p->head.wtype != MLLM_TYPE_Q4_0) p->kquant = true;
         static const bool no_kq_plan = env_on("MLLM_CUDA_NO_KQUANT_PLAN");
         if (p->kquant && (no_kq_plan || cfg_.hidden % 256 || cfg_.ffn % 256)) ok = false;
+        // the fused GEMV holds at most 8 activation rows: 9-32 rows run it in chunks of 8 (later chunks read the layer's weights from L2),
+        // larger batches take the op-level kernels (tcgen05 / dp4a Linear)
+        if (B > 32) p->kquant = true;
         if (!ok) return false; // caches not allocated yet (no prefill so far) or a dtype outside the fused kernels
         CUDABackend *bn = st_.backend;
         const int QKV = (cfg_.heads + 2 * cfg_.kv_heads) * D;
@@ -229,6 +232,7 @@ bool LlamaModel::decode_plan_usable(int B) {
             p->reps = (e && e[0]) ? atoi(e) : 1; // measured on B200: copies do not shorten the prologue loads (profiles/r01_gemv_timeline.txt)
             if (p->reps < 1) p->reps = 1;
             if (p->reps > 16) p->reps = 16;
+            if (B > 8) p->reps = 1; // chunked launches address rows by pointer offsets: one copy of every activation
         }
         const int R = p->reps;
         p->x = Tensor(R, 1, B, H, bn); p->x2 = Tensor(R, 1, B, H, bn);
@@ -397,6 +401,22 @@ bool LlamaModel::issue_step(DecodePlan &p, bool pick, bool pdl_on) {
                 src = p.kq_xn.devPtr<float>();
             }
             auto lin = [&](const FuseInfo *f, float *y, int ld) {
+                if (f->wtype == MLLM_TYPE_Q4_0 && B <= 32) {
+                    // 9-32 rows of Q4_0: the decode GEMV in chunks of 8 rows (later chunks read the weights from L2) fills the machine, the
+                    // 128-row tcgen05 tile does not (N / 128 CTAs: 16 for a 2048-wide Linear)
+                    bool done = true;
+                    for (int m0 = 0; m0 < B; m0 += 8) {
+                        const void *Wp[1] = {f->weight};
+                        const int Ns[1] = {f->out};
+                        const float *bs[1] = {f->bias};
+                        const int rows = B - m0 < 8 ? B - m0 : 8;
+                        const int rc = mllmcu_gemv_fused(MLLM_TYPE_Q4_0, Wp, Ns, bs, 1, src + (size_t)m0 * K, K, rows, K, nullptr, 0.f, 0, nullptr, 0,
+                                                         y + (size_t)m0 * ld, ld, 0, 0, st);
+                        if (rc == -2) { done = false; break; }
+                        MLLMCU_CHECK(rc);
+                    }
+                    if (done) return;
+                }
                 MLLMCU_CHECK(mllmcu_linear(f->wtype, f->weight, src, f->bias, y, B, f->out, K, K, ld, 0, p.kq_ws.rawDevPtr(), p.kq_ws_bytes, st));
             };
             if (epi == 0) {
@@ -413,6 +433,23 @@ bool LlamaModel::issue_step(DecodePlan &p, bool pick, bool pdl_on) {
                 lin(fu, p.kq_t2.devPtr<float>(), fu->out);
                 if (ldy != fg->out) throw std::runtime_error("[mllm-cuda] decode plan: gate rows must be dense");
                 MLLMCU_CHECK(mllmcu_silu_mul(p.kq_t1.devPtr<float>(), p.kq_t2.devPtr<float>(), out, (size_t)B * fg->out, st));
+            }
+            return true;
+        }
+        if (B > 8) { // chunks of 8 rows through the same fused kernel
+            launch_no++;
+            for (int m0 = 0; m0 < B; m0 += 8) {
+                mllmcu_gemv_desc c = {};
+                c.wtype = MLLM_TYPE_Q4_0;
+                for (const FuseInfo *f : ws) { c.W[c.nW] = f->weight; c.N[c.nW] = f->out; c.bias[c.nW] = f->bias; c.nW++; }
+                c.x = in + (size_t)m0 * K; c.ldx = K; c.M = B - m0 < 8 ? B - m0 : 8; c.K = K;
+                if (norm) { c.norm_w = p.norm_rep.devPtr<float>() + (size_t)norm_idx * H; c.eps = norm->eps; c.norm_reps = 1; c.norm_rep_stride = H; }
+                c.epilogue = epi; c.residual = res ? res + (size_t)m0 * ldr : nullptr; c.ldr = ldr; c.y = out + (size_t)m0 * ldy; c.ldy = ldy;
+                c.pdl = (pdl && late_trigger && m0 == 0) ? 2 : pdl;
+                c.x_reps = 1; c.y_reps = 1;
+                const int rc = mllmcu_gemv_fused_ex(&c, st);
+                if (rc == -2) return false;
+                MLLMCU_CHECK(rc);
             }
             return true;
         }

@@ -153,7 +153,7 @@ def make(tmp_path_factory, name, limit, seed):
     return cfg, t, path
 
 
-@pytest.mark.parametrize("name,B,S", [("toy-llama", 1, 8), ("toy-gqa", 2, 6), ("toy-d128", 1, 11), ("toy-d128", 3, 4), ("toy-qwen", 3, 5), ("toy-qwen", 8, 4)])
+@pytest.mark.parametrize("name,B,S", [("toy-llama", 1, 8), ("toy-gqa", 2, 6), ("toy-d128", 1, 11), ("toy-d128", 3, 4), ("toy-qwen", 3, 5), ("toy-qwen", 8, 4), ("toy-qwen", 12, 3)])
 def test_fused_step_matches_eager_ops_and_oracle(be, oracle, tmp_path_factory, name, B, S):
     from oracle import pyoracle as po
     cfg, t, path = make(tmp_path_factory, name, 64, seed=S + B)
