@@ -10,10 +10,7 @@ namespace mllm {
 // CPUBackend::runLayer (CPUBackend.cpp:407-417): "out-<op name>" (or "-i" suffixed for N outputs), then runOp.  The module tag keeps the
 // activation names of two loaded models apart.
 vector<Tensor> CUDABackend::runLayer(Layer *layer, vector<Tensor> inputs, int N) {
-    vector<string> out_names;
-    const int count = N > 1 ? N : 1;
-    for (int i = 0; i < count; i++) out_names.push_back("out-" + layer->name() + (N > 1 ? "-" + std::to_string(i) : "") + layer->tag());
-    return runOp(layer->op(), inputs, out_names, false);
+    return runOp(layer->op(), inputs, layer->out_names(N), false);
 }
 
 

@@ -33,6 +33,15 @@ public:
     Op *op() { return op_.get(); }
     const string &name() const { return name_; }
     const string &tag() const { return st_->tag; }
+    // "out-<op>[-i]<tag>", built once per layer (runLayer is on the host's critical path for short prompts on small models)
+    const vector<string> &out_names(int N) {
+        const int count = N > 1 ? N : 1;
+        if ((int)out_names_.size() != count) {
+            out_names_.clear();
+            for (int i = 0; i < count; i++) out_names_.push_back("out-" + name_ + (N > 1 ? "-" + std::to_string(i) : "") + st_->tag);
+        }
+        return out_names_;
+    }
 
 private:
     ModuleState *st_ = nullptr;
@@ -40,6 +49,7 @@ private:
     OpParam param_;
     std::unique_ptr<Op> op_;
     bool loaded_ = false;
+    vector<string> out_names_;
 };
 
 // Tensor::runFunc-style functional ops (mllm/Tensor.cpp:361-422): ops created per call site, cached by name.
