@@ -21,6 +21,13 @@ static_assert(sizeof(block_q8_0) == 34, "q8_0 block");
     } while (0)
 #define CU_LAUNCH_CHECK() CU_TRY(cudaGetLastError())
 
+// RoPE rotation of the pair (a, b) by (sin, cos): the reference writes `a*cos - b*sin` and `a*sin + b*cos` in scalar C++
+// (op/CPURoPE.cpp:241-242, CPUMultimodalRoPE.cpp:171-172, CPUVisionRoPEFunc.hpp:44-45); compiled for an FMA target gcc contracts
+// the FIRST product of each into the add -- fma(a, cos, -(b*sin)), fma(a, sin, b*cos) -- which is what its users get and what the
+// compiled reference Op classes return (tests/test_oracle_refops.py pins it).  Written out so nvcc cannot choose differently.
+static __device__ __forceinline__ float rope_lo(float a, float b, float sn, float cs) { return __fmaf_rn(a, cs, -__fmul_rn(b, sn)); }
+static __device__ __forceinline__ float rope_hi(float a, float b, float sn, float cs) { return __fmaf_rn(a, sn, __fmul_rn(b, cs)); }
+
 static __device__ __forceinline__ float warp_max(float v) {
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));

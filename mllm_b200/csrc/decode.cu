@@ -78,8 +78,8 @@ __global__ void k_decode_rope_kv(int type, float *__restrict__ qkv, int ld, int 
         else { d0 = p; d1 = p + hr; }
         const float a = xi[d0], bb = xi[d1];
         const float sn = sin_t[(size_t)pos * tdim + d0], cs = cos_t[(size_t)pos * tdim + d0];
-        v0 = __fsub_rn(__fmul_rn(a, cs), __fmul_rn(bb, sn));
-        v1 = __fadd_rn(__fmul_rn(a, sn), __fmul_rn(bb, cs));
+        v0 = rope_lo(a, bb, sn, cs);
+        v1 = rope_hi(a, bb, sn, cs);
     } else {
         d0 = rot + 2 * (p - hr); d1 = d0 + 1;
         v0 = xi[d0]; v1 = xi[d1];
@@ -166,8 +166,8 @@ static __device__ __forceinline__ void rope16(float (&x)[16], int type, int sub,
 #pragma unroll
         for (int i = 0; i < 16; i += 2) {
             const float a = x[i], bb = x[i + 1];
-            x[i] = __fsub_rn(__fmul_rn(a, cs[i]), __fmul_rn(bb, sn[i]));
-            x[i + 1] = __fadd_rn(__fmul_rn(a, sn[i]), __fmul_rn(bb, cs[i]));
+            x[i] = rope_lo(a, bb, sn[i], cs[i]);
+            x[i + 1] = rope_hi(a, bb, sn[i], cs[i]);
         }
     } else { // pairs (d, d + D/2): the partner lives LPK/2 lanes away
         const bool upper = sub >= LPK / 2;
@@ -175,7 +175,7 @@ static __device__ __forceinline__ void rope16(float (&x)[16], int type, int sub,
         for (int i = 0; i < 16; i++) {
             const float other = __shfl_xor_sync(0xffffffffu, x[i], LPK / 2);
             // lower half: a*cos - b*sin (a = own, b = partner); upper half: a*sin + b*cos (a = partner, b = own)
-            x[i] = upper ? __fadd_rn(__fmul_rn(other, sn[i]), __fmul_rn(x[i], cs[i])) : __fsub_rn(__fmul_rn(x[i], cs[i]), __fmul_rn(other, sn[i]));
+            x[i] = upper ? rope_hi(other, x[i], sn[i], cs[i]) : rope_lo(x[i], other, sn[i], cs[i]);
         }
     }
 }

@@ -244,8 +244,8 @@ static __device__ void step_rope_kv(const StepParams &P, int layer) {
             else { d0 = p; d1 = p + hr; }
             const float a = __ldcg(xi + d0), bb = __ldcg(xi + d1);
             const float sn = P.sin_t[(size_t)pos * P.tdim + d0], cs = P.cos_t[(size_t)pos * P.tdim + d0];
-            v0 = __fsub_rn(__fmul_rn(a, cs), __fmul_rn(bb, sn));
-            v1 = __fadd_rn(__fmul_rn(a, sn), __fmul_rn(bb, cs));
+            v0 = rope_lo(a, bb, sn, cs);
+            v1 = rope_hi(a, bb, sn, cs);
         } else {
             d0 = P.rot + 2 * (p - hr); d1 = d0 + 1;
             v0 = __ldcg(xi + d0); v1 = __ldcg(xi + d1);

@@ -69,7 +69,7 @@ MLLMCU_API int mllmcu_rmsnorm(const float *x, const float *w, float *y, int rows
 }
 
 // ---------------------------------------------------------------- LayerNorm
-// CPULayerNorm::execute (op/CPULayerNorm.cpp:49-89): two-pass mean / variance.
+// CPULayerNorm::execute (op/CPULayerNorm.cpp:49-89): two-pass mean / sum of squared deviations.
 __global__ void __launch_bounds__(256) k_layernorm(const float *__restrict__ x, const float *__restrict__ w, const float *__restrict__ b,
                                                    float *__restrict__ y, int dim, float eps) {
     const int r = blockIdx.x;
@@ -98,14 +98,17 @@ __global__ void __launch_bounds__(256) k_layernorm(const float *__restrict__ x, 
     if (threadIdx.x == 0) {
         float t = 0.f;
         for (int i = 0; i < (int)(blockDim.x >> 5); i++) t += sred[i];
-        s_val = 1.0f / sqrtf(t / dim + eps);
+        s_val = __fsqrt_rn(__fadd_rn(__fdiv_rn(t, (float)dim), eps));
     }
     __syncthreads();
-    const float rstd = s_val;
+    const float rms = s_val;
+    // the reference's element formula, in its order: w * (x - mean) / rms + b -- a multiply, a DIVISION, an add (:77-81).
+    // Only the two sums differ from it (tree order here, serial there): results within a few ulp, tested against the compiled op.
     for (int d = threadIdx.x; d < dim; d += blockDim.x) {
-        float v = (xr[d] - mean) * rstd;
-        if (w) v = v * w[d];
-        if (b) v = v + b[d];
+        float v = __fsub_rn(xr[d], mean);
+        if (w) v = __fmul_rn(w[d], v);
+        v = __fdiv_rn(v, rms);
+        if (b) v = __fadd_rn(v, b[d]);
         yr[d] = v;
     }
 }
@@ -142,8 +145,8 @@ __global__ void k_rope(int type, const float *__restrict__ x, void *out, int B, 
         const float a = xi[d0], bb = xi[d1];
         const float sn = sin_t[(size_t)(s + pos0) * tdim + d0], cs = cos_t[(size_t)(s + pos0) * tdim + d0];
         // a*cos - b*sin, a*sin + b*cos; products rounded separately (host build uses no FMA here: tolerance noted in tests)
-        v0 = __fsub_rn(__fmul_rn(a, cs), __fmul_rn(bb, sn));
-        v1 = __fadd_rn(__fmul_rn(a, sn), __fmul_rn(bb, cs));
+        v0 = rope_lo(a, bb, sn, cs);
+        v1 = rope_hi(a, bb, sn, cs);
     } else { // beyond the rotated part: copy through
         d0 = rot + 2 * (p - hr); d1 = d0 + 1;
         v0 = xi[d0]; v1 = xi[d1];
@@ -170,8 +173,8 @@ __global__ void k_rope_llama4(const float *__restrict__ x, void *out, int B, int
     const int b = (int)(i / ((long long)q4 * H * S));
     const float4 v = *(const float4 *)(x + (((size_t)b * S + s) * H + h) * D + 4 * p);
     const float4 sn = *(const float4 *)(sin_t + (size_t)(s + pos0) * tdim + 4 * p), cs = *(const float4 *)(cos_t + (size_t)(s + pos0) * tdim + 4 * p);
-    const float o0 = __fsub_rn(__fmul_rn(v.x, cs.x), __fmul_rn(v.y, sn.x)), o1 = __fadd_rn(__fmul_rn(v.x, sn.x), __fmul_rn(v.y, cs.x));
-    const float o2 = __fsub_rn(__fmul_rn(v.z, cs.z), __fmul_rn(v.w, sn.z)), o3 = __fadd_rn(__fmul_rn(v.z, sn.z), __fmul_rn(v.w, cs.z));
+    const float o0 = rope_lo(v.x, v.y, sn.x, cs.x), o1 = rope_hi(v.x, v.y, sn.x, cs.x);
+    const float o2 = rope_lo(v.z, v.w, sn.z, cs.z), o3 = rope_hi(v.z, v.w, sn.z, cs.z);
     const size_t at = (size_t)b * obs + (size_t)s * oss + (size_t)h * D + 4 * p;
     if (out_f16) {
         const __half2 a = __halves2half2(__float2half_rn(o0), __float2half_rn(o1)), c = __halves2half2(__float2half_rn(o2), __float2half_rn(o3));

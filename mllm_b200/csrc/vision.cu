@@ -126,8 +126,8 @@ __global__ void k_rope_vision(const float *__restrict__ x, const float *__restri
     if (table) { sn = a0[(size_t)s * half + d]; cs = a1[(size_t)s * half + d]; }
     else { const float a = a0[(size_t)s * half + d]; sn = sinf(a); cs = cosf(a); }
     const float v0 = x[base], v1 = x[base + half];
-    const float o0 = __fsub_rn(__fmul_rn(v0, cs), __fmul_rn(v1, sn));
-    const float o1 = __fadd_rn(__fmul_rn(v0, sn), __fmul_rn(v1, cs));
+    const float o0 = rope_lo(v0, v1, sn, cs);
+    const float o1 = rope_hi(v0, v1, sn, cs);
     if (out_f16) { ((__half *)out)[base] = __float2half_rn(o0); ((__half *)out)[base + half] = __float2half_rn(o1); }
     else { ((float *)out)[base] = o0; ((float *)out)[base + half] = o1; }
 }

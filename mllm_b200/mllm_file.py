@@ -46,7 +46,8 @@ class Names:
 
 # shapes from the reference's config classes
 CONFIGS = {
-    "tinyllama-1.1b": dict(vocab=32000, hidden=2048, layers=22, heads=32, kv_heads=4, ffn=5632, rope_type=ROPE_HF, rope_theta=10000.0, rms_eps=1e-5, qkv_bias=0),
+    # rms_eps: the reference's TinyLLaMABlock hard-codes RMSNorm(hidden_dim, 1e-6, ...) (models/tinyllama/modeling_tinyllama.hpp:31-32)
+    "tinyllama-1.1b": dict(vocab=32000, hidden=2048, layers=22, heads=32, kv_heads=4, ffn=5632, rope_type=ROPE_HF, rope_theta=10000.0, rms_eps=1e-6, qkv_bias=0),
     "llama2-7b": dict(vocab=32000, hidden=4096, layers=32, heads=32, kv_heads=32, ffn=11008, rope_type=ROPE_LLAMA, rope_theta=10000.0, rms_eps=1e-6, qkv_bias=0),
     # the LLM of Qwen2-VL-2B (models/qwen/configuration_qwen.hpp:167-181); text-only positions here (M-RoPE reduces to HF RoPE when t = h = w)
     "qwen2-vl-2b-llm": dict(vocab=151936, hidden=1536, layers=28, heads=12, kv_heads=2, ffn=8960, rope_type=ROPE_HF, rope_theta=1000000.0, rms_eps=1e-6, qkv_bias=1),

@@ -373,3 +373,156 @@ class ModelRunner:
             self.lib.mr_destroy(self.h)
         except Exception:
             pass
+
+
+# ---------------------------------------------------------------- the reference's whole CPU backend (oracle/cpuref.mk)
+_cpuref = None
+F32, F16 = 0, 1
+BSHD, BHSD, BCTHW = 0, 1, 3
+
+
+class _TDesc(C.Structure):
+    _fields_ = [("data", C.c_void_p), ("shape", C.c_int * 5), ("ndim", C.c_int), ("dtype", C.c_int), ("ctype", C.c_int)]
+
+
+def build_cpuref():
+    """g++ over the reference's CPU-backend sources where they lie (no cmake) + ref_ops_shim.cpp; needs /root/reference."""
+    subprocess.run(["make", "-s", "-j", str(os.cpu_count() or 4), "-f", os.path.join(HERE, "cpuref.mk")], check=True, cwd=HERE)
+
+
+def cpuref():
+    """oracle/_ref/libmllm_cpu_ref.so (the reference's Op classes and model graphs on MLLM_CPU), or None when not built."""
+    global _cpuref
+    if _cpuref is None:
+        so = os.path.join(HERE, "_ref", "libmllm_cpu_ref.so")
+        if not os.path.exists(so):
+            return None
+        L = C.CDLL(so)
+        L.cpuref_set_threads.argtypes = [C.c_int]
+        L.cpuref_op_create.restype = C.c_void_p
+        L.cpuref_op_create.argtypes = [C.POINTER(C.c_char_p), C.POINTER(C.c_float), C.c_int, C.c_char_p, C.c_int]
+        L.cpuref_op_load.argtypes = [C.c_void_p, C.c_char_p]
+        L.cpuref_op_run.argtypes = [C.c_void_p, C.POINTER(_TDesc), C.c_int, C.c_int]
+        L.cpuref_op_out_info.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)]
+        L.cpuref_op_out_read.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
+        L.cpuref_op_clear_cache.argtypes = [C.c_void_p]
+        L.cpuref_op_destroy.argtypes = [C.c_void_p]
+        L.cpuref_model_create.restype = C.c_void_p
+        L.cpuref_model_create.argtypes = [C.c_char_p, C.c_int, C.c_int, C.c_void_p, C.c_float, C.c_float, C.c_int]
+        L.cpuref_model_load.argtypes = [C.c_void_p, C.c_char_p]
+        L.cpuref_model_vocab.argtypes = [C.c_void_p]
+        L.cpuref_model_forward.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int]
+        L.cpuref_model_clear.argtypes = [C.c_void_p]
+        L.cpuref_model_generate.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
+        L.cpuref_model_destroy.argtypes = [C.c_void_p]
+        _cpuref = L
+    return _cpuref
+
+
+class RefOp:
+    """One of the reference's own CPU Op classes (CPUBackend::opCreate), driven as test/cpu/CPUTest.hpp drives them.
+    params: the OpParam map (must hold "type" = OpType, OpDefined.hpp:10-134); weights: dict suffix -> (array, dtype) written to
+    a temporary .mllm and loaded through the reference's ParamLoader under the names `name + suffix`."""
+
+    def __init__(self, params, name="op", weights=None, threads=4):
+        self.L = cpuref()
+        if self.L is None:
+            raise RuntimeError("oracle/_ref/libmllm_cpu_ref.so not built")
+        keys = (C.c_char_p * len(params))(*[k.encode() for k in params])
+        vals = (C.c_float * len(params))(*[float(v) for v in params.values()])
+        self.h = C.c_void_p(self.L.cpuref_op_create(keys, vals, len(params), name.encode(), threads))
+        if not self.h:
+            raise RuntimeError(f"reference CPUBackend has no creator for {params}")
+        if weights is not None:
+            import tempfile
+            from mllm_b200 import mllm_file as mf  # the container writer only (file format), no device code
+            with tempfile.TemporaryDirectory() as d:
+                p = os.path.join(d, "w.mllm")
+                mf.write_mllm(p, {name + s: np.ascontiguousarray(a) for s, (a, _) in weights.items()}, {name + s: dt for s, (_, dt) in weights.items()})
+                self.L.cpuref_op_load(self.h, p.encode())
+        else:
+            self.L.cpuref_op_load(self.h, b"")
+
+    def run(self, inputs, n_out=1):
+        """inputs: list of (array, shape, dtype, ctype); shape = (batch, head, sequence, dimension) -- the array's MEMORY order is the
+        ctype's (BSHD: [b][s][h][d]) -- or 5 numbers (batch, channel, time, height, width) for BCTHW.  Returns fp32 arrays shaped
+        [batch, sequence, head, dimension] (or [b, c, t, h, w])."""
+        descs = (_TDesc * len(inputs))()
+        keep = []
+        for i, (a, shape, dtype, ctype) in enumerate(inputs):
+            a = np.ascontiguousarray(a)
+            keep.append(a)
+            descs[i].data = a.ctypes.data
+            for j, s in enumerate(shape):
+                descs[i].shape[j] = int(s)
+            descs[i].ndim, descs[i].dtype, descs[i].ctype = len(shape), dtype, ctype
+        rc = self.L.cpuref_op_run(self.h, descs, len(inputs), n_out)
+        if rc != 0:
+            raise RuntimeError(f"reference op failed at stage {rc}")
+        outs = []
+        for i in range(n_out):
+            shp = (C.c_int * 5)()
+            dt, ct = C.c_int(), C.c_int()
+            nd = self.L.cpuref_op_out_info(self.h, i, shp, C.byref(dt), C.byref(ct))
+            b, x1, x2, x3, x4 = list(shp)
+            out = np.empty((b, x2, x1, x3) if nd == 4 else (b, x1, x2, x3, x4), dtype=np.float32)
+            self.L.cpuref_op_out_read(self.h, i, _p(out))
+            outs.append(out)
+        return outs
+
+    def clear_cache(self):
+        self.L.cpuref_op_clear_cache(self.h)
+
+    def close(self):
+        if self.h:
+            self.L.cpuref_op_destroy(self.h)
+            self.h = None
+
+
+class RefGraph:
+    """The reference's own model graph (LLaMAModel / TinyLLaMAModel / QWenForCausalLM) on MLLM_CPU over a .mllm file.
+    family: "llama2-7b", "tinyllama-1.1b", "qwen1.5-1.8b", or "llama-generic" with cfg dims (toy models)."""
+
+    def __init__(self, cfg, path, family=None, threads=None):
+        self.L = cpuref()
+        if self.L is None:
+            raise RuntimeError("oracle/_ref/libmllm_cpu_ref.so not built")
+        if family is None:
+            if cfg["name"] in ("llama2-7b", "tinyllama-1.1b", "qwen1.5-1.8b"):
+                family = cfg["name"]
+            else:  # toy shapes: LLaMAModel (no bias, eps 1e-6 hard-coded in LLaMABlock) or QWenForCausalLM (qkv bias, config eps)
+                family = "qwen-generic" if (cfg["qkv_bias"] or abs(cfg["rms_eps"] - 1e-6) > 1e-12) else "llama-generic"
+        dims = np.array([cfg["vocab"], cfg["hidden"], cfg["heads"], cfg["kv_heads"], cfg["ffn"], cfg["layers"], cfg.get("pos_max", cfg["cache_limit"])], dtype=np.int32)
+        self.vocab = cfg["vocab"]
+        self.h = C.c_void_p(self.L.cpuref_model_create(family.encode(), cfg["cache_limit"], cfg["rope_type"], _p(dims), cfg["rope_theta"], cfg["rms_eps"],
+                                                       threads or (os.cpu_count() or 1)))
+        if not self.h:
+            raise RuntimeError(f"unknown model family {family}")
+        self.L.cpuref_model_load(self.h, path.encode())
+
+    def forward(self, ids):
+        """ids [B, S] -> last-position logits [B, vocab] (the graph's own output rows; TinyLLaMAModel returns all S rows)."""
+        ids = np.ascontiguousarray(ids, dtype=np.float32)
+        B, S = ids.shape
+        out = np.empty((B * S, self.vocab), dtype=np.float32)
+        so = self.L.cpuref_model_forward(self.h, _p(ids), B, S, _p(out), B * S)
+        if so <= 0:
+            raise RuntimeError("reference forward failed")
+        return out[:B * so].reshape(B, so, self.vocab)[:, -1, :].copy()
+
+    def generate(self, ids, max_new, end_token=-1):
+        """The reference's Module::generate (greedy) on a [B, S] batch -> uint32 [B, max_new] (rows that hit end_token are shorter: n)."""
+        ids = np.ascontiguousarray(ids, dtype=np.float32)
+        B, S = ids.shape
+        out = np.zeros((B, max_new), dtype=np.uint32)
+        n = np.zeros(B, dtype=np.int32)
+        self.L.cpuref_model_generate(self.h, _p(ids), B, S, max_new, end_token, _p(out), _p(n))
+        return out, n
+
+    def reset(self):
+        self.L.cpuref_model_clear(self.h)
+
+    def close(self):
+        if self.h:
+            self.L.cpuref_model_destroy(self.h)
+            self.h = None
