@@ -111,6 +111,17 @@ int mllmcu_linear(int wtype, const void *W, const float *x, const float *bias, v
 int mllmcu_linear_quant_kind(int wtype, int M, int N, int K, const void *W);
 int mllmcu_linear_ex(int wtype, const void *W, const float *x, const float *bias, void *y, int M, int N, int K,
                      int ldx, int ldy, int out_f16, void *ws, size_t ws_bytes, int flags, void *stream);
+/* mllmcu_linear without the workspace argument, for callers that cannot call cudaMalloc (code under CUDA graph capture,
+ * tight serving loops, harnesses that forbid allocation).  No counterpart in the reference.
+ * The scratch is a file-scope static __device__ array of MLLMCU_LINEAR_STATIC_WS_BYTES inside the
+ * library (every GPU that loads the library holds it until exit); the call allocates nothing.  Shapes whose
+ * mllmcu_linear_workspace_bytes(M, K) exceeds the array return MLLMCU_EWS (and say so on stderr).  All calls on a device
+ * share the array: calls that overlap on the GPU (two streams) race on it; back-to-back calls on one stream are safe.
+ * Results are those of mllmcu_linear (same kernels). */
+#define MLLMCU_LINEAR_STATIC_WS_BYTES (16u << 20)
+size_t mllmcu_linear_static_ws_capacity(void);
+int mllmcu_linear_static_ws(int wtype, const void *W, const float *x, const float *bias, void *y, int M, int N, int K,
+                            int ldx, int ldy, int out_f16, void *stream);
 
 /* ---- Fused decode Linear (M <= 8 rows): one launch = [RMSNorm ->] Q8_0 quantise -> nW (<=3) block-quantised
  * Linears sharing the input -> epilogue.  It is the same arithmetic, in the same order, as the separate

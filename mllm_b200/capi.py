@@ -50,6 +50,8 @@ SYMBOLS = {
     "mllmcu_linear": (_i, [_i, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _vp, _sz, _vp]),
     "mllmcu_linear_ex": (_i, [_i, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _vp, _sz, _i, _vp]),
     "mllmcu_linear_quant_kind": (_i, [_i, _i, _i, _i, _vp]),
+    "mllmcu_linear_static_ws_capacity": (_sz, []),
+    "mllmcu_linear_static_ws": (_i, [_i, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _vp]),
     "mllmcu_gemv_fused": (_i, [_i, _vp, _vp, _vp, _i, _vp, _i, _i, _i, _vp, _f, _i, _vp, _i, _vp, _i, _i, _i, _vp]),
     "mllmcu_gemv_fused_ex": (_i, [_vp, _vp]),
     "mllmcu_gemv_prof_read": (_i, [_vp, _i]),
@@ -177,6 +179,17 @@ def linear(W, x, bias=None, wtype=TYPE_Q4_0, out_f16=False, out=None, ldy=None, 
     check(lib().mllmcu_linear_ex(wtype, _ptr(W), _ptr(x), _ptr(bias), _ptr(out), M, N, K, x.stride(0), ldy, int(out_f16),
                                  _ptr(ws), ws.numel(), int(reuse_quant), _stream()), "linear")
     return out
+
+
+def linear_static_ws(W, x, bias=None, wtype=TYPE_Q4_0, out_f16=False):
+    """mllmcu_linear_static_ws: the Linear with the library's own static device scratch (the call allocates nothing;
+    the output tensor is made by the caller -- here -- beforehand).  Returns (rc, y): rc is NOT raised so tests can see -3."""
+    import torch
+    M, K = x.shape
+    N = W.shape[0]
+    out = torch.empty((M, N), dtype=torch.float16 if out_f16 else torch.float32, device=x.device)
+    rc = lib().mllmcu_linear_static_ws(wtype, _ptr(W), _ptr(x), _ptr(bias), _ptr(out), M, N, K, x.stride(0), N, int(out_f16), _stream())
+    return rc, out
 
 
 def rmsnorm(x, w, eps, add_unit_offset=False):

@@ -13,8 +13,10 @@
 // Two paths:
 //   M <= GEMV_MAX_M : k_gemv_*  -- HBM-bound weight streaming (decode)
 //   otherwise       : k_gemm_*  -- tiled integer GEMM (prefill / large batch)
+#include <cstdio>
 #include "common.cuh"
 #include "quantize.cuh"
+#include "mllmcu.h"
 
 #define GEMV_MAX_M 8
 
@@ -277,4 +279,35 @@ MLLMCU_API int mllmcu_linear_ex(int wtype, const void *W, const float *x, const 
     else k_gemm<8><<<grid, block, 0, st>>>((const uint8_t *)W, xq, xd, bias, y, M, N, K, ldy, out_f16);
     CU_LAUNCH_CHECK();
     return 0;
+}
+
+// ------------------------------------------------------------------ allocation-free Linear
+// The same Linear for callers that cannot allocate (CUDA graph capture, serving loops, harnesses that forbid cudaMalloc):
+// the scratch is this file-scope device array, held by every GPU that loads the library until exit.  In host code the
+// array's name is only a stand-in for the symbol; its device address is asked for once per device, with that device
+// current, and cached.  Every call on a device shares the array (calls that overlap on the GPU race on it); nothing in it
+// has to start at zero -- the quantiser writes every byte the GEMV/GEMM kernels read.
+static __device__ __align__(256) unsigned char g_linear_static_ws[MLLMCU_LINEAR_STATIC_WS_BYTES];
+static void *g_linear_static_ws_addr[64] = {};
+
+MLLMCU_API size_t mllmcu_linear_static_ws_capacity(void) { return (size_t)MLLMCU_LINEAR_STATIC_WS_BYTES; }
+
+MLLMCU_API int mllmcu_linear_static_ws(int wtype, const void *W, const float *x, const float *bias, void *y, int M, int N, int K,
+                                       int ldx, int ldy, int out_f16, void *stream) {
+    if (M <= 0 || N <= 0 || K <= 0 || K % QK) return -1;
+    if (mllmcu_linear_workspace_bytes(M, K) > (size_t)MLLMCU_LINEAR_STATIC_WS_BYTES) {
+        fprintf(stderr, "[mllmcu] mllmcu_linear_static_ws: M=%d K=%d needs %zu bytes of scratch, the static array holds %zu\n", M, K,
+                mllmcu_linear_workspace_bytes(M, K), (size_t)MLLMCU_LINEAR_STATIC_WS_BYTES);
+        return -3;
+    }
+    int dev = -1;
+    CU_TRY(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64) return -1;
+    void *ws = __atomic_load_n(&g_linear_static_ws_addr[dev], __ATOMIC_ACQUIRE);
+    if (ws == nullptr) { // once per device; racing first calls resolve the same address
+        CU_TRY(cudaGetSymbolAddress(&ws, g_linear_static_ws));
+        if (ws == nullptr) return -1;
+        __atomic_store_n(&g_linear_static_ws_addr[dev], ws, __ATOMIC_RELEASE);
+    }
+    return mllmcu_linear_ex(wtype, W, x, bias, y, M, N, K, ldx, ldy, out_f16, ws, (size_t)MLLMCU_LINEAR_STATIC_WS_BYTES, 0, stream);
 }
