@@ -39,43 +39,8 @@ def log(*a):
 
 # ----------------------------------------------------------------------------- model file
 def make_model_file(cfg, path, device="cuda", seed=1234):
-    """Random-init .mllm (W ~ N(0,0.02^2) -> Q4_0 with the reference quantiser's arithmetic, norms 1+N(0,0.02^2)).
-    Generated on the GPU with torch (plumbing only), written in the reference's container format."""
-    import torch
-    want = 12 + sum(4 + len(n.encode()) + 20 for n, *_ in mf.tensor_list(cfg)) + mf.model_bytes(cfg)
-    if os.path.exists(path) and os.path.getsize(path) == want:
-        return path
-    g = torch.Generator(device=device).manual_seed(seed)
-
-    def q4_0(rows, cols):
-        out = np.empty((rows, cols // 32 * 18), dtype=np.uint8)
-        step = max(1, (1 << 26) // cols)
-        for r0 in range(0, rows, step):
-            r = min(step, rows - r0)
-            w = torch.randn((r, cols // 32, 32), generator=g, device=device) * 0.02
-            idx = w.abs().argmax(dim=2, keepdim=True)
-            mx = torch.gather(w, 2, idx)
-            d = mx / -8.0
-            idv = torch.where(d != 0, 1.0 / d, torch.zeros_like(d))
-            q = torch.clamp(((w * idv) + 8.5).to(torch.int8), max=15).to(torch.uint8)
-            blk = torch.empty((r, cols // 32, 18), dtype=torch.uint8, device=device)
-            blk[..., 0:2] = d.to(torch.float16).view(torch.uint8).reshape(r, cols // 32, 2)
-            blk[..., 2:] = q[..., :16] | (q[..., 16:] << 4)
-            out[r0:r0 + r] = blk.reshape(r, -1).cpu().numpy()
-        return out
-
-    tensors, dts = {}, {}
-    for name, rows, cols, dt in mf.tensor_list(cfg):
-        dts[name] = dt
-        if dt == mf.F32:
-            base = 1.0 if "norm" in name else 0.0
-            tensors[name] = (base + 0.02 * torch.randn(cols, generator=g, device=device)).cpu().numpy().astype(np.float32)
-        else:
-            tensors[name] = q4_0(rows, cols)
-    tmp = path + ".tmp"
-    mf.write_mllm(tmp, tensors, dts)
-    os.replace(tmp, path)
-    return path
+    """Random-init .mllm (W ~ N(0,0.02^2) -> Q4_0 with the reference quantiser's arithmetic, norms 1+N(0,0.02^2))."""
+    return mf.write_random_model_torch(cfg, path, device=device, seed=seed)
 
 
 # ----------------------------------------------------------------------------- clocks
@@ -120,18 +85,48 @@ class ClockSampler:
 
 
 # ----------------------------------------------------------------------------- CPU arm
-def cpu_arm(cfg, path, prefill, decode, reps=1):
-    """Reference CPU kernels (oracle/_ref: the reference's ggml + FlashAttention2 sources) or the C port, all host threads."""
+def _host_cpus():
+    try:
+        return len(os.sched_getaffinity(0))
+    except Exception:
+        return os.cpu_count() or 1
+
+
+def _cpu_runner(cfg, path, threads, limit):
+    """The reference's own model graph on its CPU backend (oracle/_ref/libmllm_cpu_ref.so: LLaMAModel on MLLM_CPU, compiled from the
+    reference's sources) -- else the reference's kernels under the C graph (libmllm_ref.so) -- else the C port."""
     from oracle import pyoracle as po
+    c = dict(cfg, cache_limit=limit)
+    if po.cpuref() is not None:
+        return po.RefGraph(c, path, threads=threads), "reference", "reference LLaMAModel graph on CPUBackend (oracle/_ref/libmllm_cpu_ref.so)"
     po.build()
-    L = po.ref()
-    kind = "reference"
+    L, kind = po.ref(), "reference"
     if L is None:
         L, kind = po.port(), "port"
+    os.environ["OMP_NUM_THREADS"] = str(threads)
     tensors, _ = mf.read_mllm(path)
-    runner = po.ModelRunner(L, cfg, tensors, mf.Names(cfg["rope_type"]), cache_limit=prefill + decode + 8)
+    return po.ModelRunner(L, cfg, tensors, mf.Names(cfg["rope_type"]), cache_limit=limit), kind, "reference ggml/FA2 kernels under oracle/model_runner.c"
+
+
+def cpu_arm(cfg, path, prefill, decode, reps=1):
+    """Times the CPU reference on a bounded sample of the 512 + 256 request: `prefill` prompt tokens, then `decode` greedy steps.
+    Thread count is chosen explicitly (never inherited: torchrun exports OMP_NUM_THREADS=1): all host CPUs, or half of them when
+    that decodes faster (SMT siblings / oversubscribed vCPUs stall the reference's spin-waiting OpenMP teams)."""
+    n = _host_cpus()
     rng = np.random.default_rng(7)
     ids = rng.integers(0, cfg["vocab"], (1, prefill)).astype(np.float32)
+    probe = {}
+    for th in sorted({n, max(1, n // 2)}, reverse=True):
+        r, kind, how = _cpu_runner(cfg, path, th, prefill + decode + 8)
+        lg = r.forward(ids[:, :4])
+        t0 = time.perf_counter()
+        for _ in range(2):
+            lg = r.forward(np.array([[lg.argmax()]], dtype=np.float32))
+        probe[th] = (time.perf_counter() - t0) / 2
+        if hasattr(r, "close"):
+            r.close()
+    threads = min(probe, key=probe.get)
+    runner, kind, how = _cpu_runner(cfg, path, threads, prefill + decode + 8)
     times = []
     for _ in range(reps):
         runner.reset()
@@ -144,10 +139,13 @@ def cpu_arm(cfg, path, prefill, decode, reps=1):
         times.append((t1 - t0, t2 - t1))
     tp = float(np.mean([t[0] for t in times]))
     td = float(np.mean([t[1] for t in times]))
-    cores = int(os.environ.get("OMP_NUM_THREADS", os.cpu_count() or 1))
-    return {"value": (prefill + decode) / (tp + td), "unit": "tok/s", "cores": cores, "kind": kind,
-            "sample": f"full {cfg['name']} Q4_0 graph, prefill {prefill} + decode {decode} tokens (bounded sample of the 512+256 request)",
-            "prefill_tok_s": prefill / tp, "decode_tok_s": decode / td if decode else None, "seconds": tp + td}
+    pre_tok_s, dec_tok_s = prefill / tp, (decode / td if decode else None)
+    # the metric's own request (512 + 256) at the sampled per-phase rates
+    projected = (PREFILL + DECODE) / (PREFILL / pre_tok_s + DECODE / dec_tok_s) if dec_tok_s else pre_tok_s
+    return {"value": projected, "unit": "tok/s", "cores": threads, "host_cpus": n, "kind": kind,
+            "sample": f"{how}; full {cfg['name']} Q4_0 model, prefill {prefill} + decode {decode} tokens timed on {threads} threads "
+                      f"(decode probe s/token by thread count: { {k: round(v, 4) for k, v in probe.items()} }), value = the 512 + 256 request at the sampled per-phase rates",
+            "prefill_tok_s": pre_tok_s, "decode_tok_s": dec_tok_s, "seconds": tp + td}
 
 
 # ----------------------------------------------------------------------------- ranks
@@ -220,7 +218,8 @@ def gemv_roofline(cfg, peaks):
     return {"bound": "hbm", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s", "frac": round(achieved / peak, 4),
             # DRAM bytes of one gate|up launch (its largest share of the step) from the ncu --set full capture summarised in
             # profiles/r01_ncu_gemv_gateup.txt: 50.80 MB read + 3.6 KB written against 50.72 MB algorithmic -- no re-reads
-            "traffic": 50802688, "traffic_of": "one gate|up launch (k_gemv_tma<1,1,2,1>): dram read 50.799 MB + write 0.004 MB vs 50.725 MB algorithmic",
+            "traffic": 50802688, "traffic_source": "profiles/r01_ncu_gemv_gateup.txt (one ncu --set full capture, NOT measured by this run)",
+            "traffic_of": "one gate|up launch (k_gemv_tma<1,1,2,1>): dram read 50.799 MB + write 0.004 MB vs 50.725 MB algorithmic",
             "kernel": "k_gemv_tma (decode Linear: fused RMSNorm/Q8_0 prologue + Q4_0 GEMV), launch-weighted over one decode step",
             "peak_source": "measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in peaks else "fallback 6650",
             "per_shape": per}
@@ -278,7 +277,7 @@ def gpu_arm(args, rank, world, local_rank):
     total_ms = float(np.sum(tp) + np.sum(td))
     # e2e: host-buffer API (prompt ids H2D, device-side greedy loop, token ids D2H), wall clock around the synchronous call
     e2e_ms = []
-    for _ in range(max(1, min(args.steps, 2))):
+    for _ in range(args.steps):
         model.clear_kvcache()
         w0 = time.perf_counter()
         model.generate(ids, DECODE)
@@ -291,6 +290,7 @@ def gpu_arm(args, rank, world, local_rank):
     toks = (PREFILL + DECODE) * world  # == job_tokens_per_s numerator
     roof = gemv_roofline(cfg, peaks)
     wbytes = mf.decode_weight_bytes(cfg)
+    head_bytes = mf.nbytes(cfg["vocab"], cfg["hidden"], mf.Q4_0)
     kv_bytes = 2 * cfg["layers"] * (PREFILL + DECODE / 2) * cfg["kv_heads"] * cfg["head_dim"] * 2
     dec_ms = float(np.mean(td)) / DECODE
     out = {
@@ -304,7 +304,9 @@ def gpu_arm(args, rank, world, local_rank):
         "decode_step": {"ms": round(dec_ms, 4), "algorithmic_GB": round((wbytes + kv_bytes) / 1e9, 4),
                         "GBs": round((wbytes + kv_bytes) / (dec_ms * 1e-3) / 1e9, 1),
                         "frac_of_hbm_peak": round((wbytes + kv_bytes) / (dec_ms * 1e-3) / 1e9 / peaks.get("hbm_gbs", 6650.0), 4)},
-        "prefill": {"ms": round(float(np.mean(tp)), 3), "int8_TOPs": round(2 * (wbytes / 0.5625) * PREFILL / (float(np.mean(tp)) * 1e-3) / 1e12, 1)},
+        "prefill": {"ms": round(float(np.mean(tp)), 3), "int8_TOPs": round(2 * ((wbytes - head_bytes) / 0.5625) * PREFILL / (float(np.mean(tp)) * 1e-3) / 1e12, 1),
+                    "frac_of_int8_peak": round(2 * ((wbytes - head_bytes) / 0.5625) * PREFILL / (float(np.mean(tp)) * 1e-3) / 1e12 / (2 * peaks.get("bf16_tflops", 1656.9)), 4),
+                    "int8_peak_TOPs": round(2 * peaks.get("bf16_tflops", 1656.9), 1), "note": "Linear MACs x 2 of the 512 prompt tokens (lm_head runs on the last token only and is not counted); peak = 2 x measured dense bf16"},
         "e2e": {"value": round(job_tokens_per_s(PREFILL + DECODE, world, e2e_mean), 2), "unit": "tok/s", "h2d_bytes_per_step": PREFILL * 4,
                 # token ids of the first pick (fp32 row per step) + the device-side token log the fused steps write (one int32 per position)
                 "d2h_bytes_per_step": DECODE * 4 + (LIMIT + 1) * 4, "ms_per_step": round(e2e_mean, 2)},
@@ -316,7 +318,8 @@ def gpu_arm(args, rank, world, local_rank):
         try:
             r = subprocess.run([sys.executable, os.path.abspath(__file__), "--impl", "reference", "--steps", "1", "--warmup", "0",
                                 "--cpu-prefill", str(args.cpu_prefill), "--cpu-decode", str(args.cpu_decode)],
-                               capture_output=True, text=True, timeout=900, env=dict(os.environ, RANK="0", WORLD_SIZE="1", LOCAL_RANK="0"))
+                               capture_output=True, text=True, timeout=900,
+                               env={k: v for k, v in dict(os.environ, RANK="0", WORLD_SIZE="1", LOCAL_RANK="0").items() if not k.startswith("OMP_")})
             line = [l for l in r.stdout.splitlines() if l.startswith("{")][-1]
             out["cpu_baseline"] = json.loads(line)["cpu_baseline"]
         except Exception as e:
@@ -332,15 +335,15 @@ def reference_arm(args, rank, world):
     if not os.path.exists(path):
         import torch
         make_model_file(cfg, path, device="cuda" if torch.cuda.is_available() else "cpu")
-    for _ in range(min(args.warmup, 1)):
-        cpu_arm(cfg, path, 4, 1)
-    r = cpu_arm(cfg, path, args.cpu_prefill, args.cpu_decode, reps=args.steps)
+    cp = args.cpu_prefill or (512 if args.steps <= 2 else 128 if args.steps <= 6 else 64)
+    cd = args.cpu_decode or (32 if args.steps <= 2 else 16 if args.steps <= 6 else 8)
+    r = cpu_arm(cfg, path, cp, cd, reps=args.steps)
     ms = r["seconds"] * 1e3
     out = {"impl": "reference", "metric": METRIC, "value": round(r["value"], 3), "unit": "tok/s", "n_gpus": world, "steps": args.steps,
            "warmup": args.warmup, "ms_per_step": round(ms, 1), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
            "dtype": "int8 block dot (Q4_0 x Q8_0) + fp32 accumulate, fp16 KV", "data": "synthetic",
            "config": {"workload": "LLaMA-2-7B Q4_0 (BASELINE configs[1]) on the host CPU: " + r["sample"]},
-           "cpu_baseline": {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")},
+           "cpu_baseline": {k: r[k] for k in ("value", "unit", "cores", "host_cpus", "kind", "sample", "prefill_tok_s", "decode_tok_s")},
            "prefill_tok_s": round(r["prefill_tok_s"], 3), "decode_tok_s": round(r["decode_tok_s"], 3) if r["decode_tok_s"] else None,
            "e2e": {"value": round(r["value"], 3), "unit": "tok/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(out), flush=True)
@@ -353,8 +356,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu", action="store_true")
-    ap.add_argument("--cpu-prefill", type=int, default=32)
-    ap.add_argument("--cpu-decode", type=int, default=8)
+    ap.add_argument("--cpu-prefill", type=int, default=0, help="CPU sample: prompt tokens (0 = 512 when steps <= 2, else 128 / 64 so the run stays within minutes)")
+    ap.add_argument("--cpu-decode", type=int, default=0, help="CPU sample: decode steps (0 = 32 / 16 / 8 by the same rule)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", 0))
     world = int(os.environ.get("WORLD_SIZE", 1))

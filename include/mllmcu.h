@@ -49,6 +49,10 @@ int mllmcu_device_info(int dev, char *name, int *sm_major, int *sm_minor, int *s
  * copy_to_host (Backend.hpp:60-71) and load_from_file (:118) reduce to. */
 int mllmcu_malloc(void **dptr, size_t bytes);
 int mllmcu_free(void *dptr);
+/* Unified (managed) memory made resident on `device` at creation (preferred location = device, prefetched): what the in-tree
+ * backend's MemoryManager hands to TensorImpl::host_ptr_, so the reference's pointer-arithmetic tensor views work on device
+ * memory and host code may still dereference a tensor (integration/mllm/backends/cuda/CUDABackend.hpp).  Freed with mllmcu_free. */
+int mllmcu_malloc_managed(void **ptr, size_t bytes, int device);
 int mllmcu_memset(void *dptr, int value, size_t bytes, void *stream);
 int mllmcu_memcpy_h2d(void *dst, const void *host_src, size_t bytes, void *stream);
 int mllmcu_memcpy_d2h(void *host_dst, const void *src, size_t bytes, void *stream);

@@ -31,6 +31,7 @@ def lib():
         L.mllm_cuda_llama_load.argtypes = [C.c_void_p, C.c_char_p]
         L.mllm_cuda_llama_clear_kvcache.argtypes = [C.c_void_p]
         L.mllm_cuda_llama_forward.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
+        L.mllm_cuda_llama_block_forward.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_void_p]
         L.mllm_cuda_llama_generate.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p]
         L.mllm_cuda_stream.restype = C.c_void_p
         L.mllm_cuda_llama_last_step_fused.argtypes = [C.c_void_p]
@@ -102,6 +103,14 @@ class LlamaModel:
         return (logits, d) if dump else logits
 
     __call__ = forward
+
+    def block_forward(self, layer, x):
+        """Block `layer` alone on the hidden state x [B, S, hidden] with an empty KV cache (teacher-forced parity tests)."""
+        x = np.ascontiguousarray(x, dtype=np.float32)
+        B, S, _ = x.shape
+        y = np.empty_like(x)
+        _check(lib().mllm_cuda_llama_block_forward(self.h, layer, _p(x), B, S, _p(y)))
+        return y
 
     def generate(self, ids, max_new):
         ids = np.ascontiguousarray(ids, dtype=np.float32)

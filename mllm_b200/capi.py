@@ -25,6 +25,7 @@ SYMBOLS = {
     "mllmcu_device_info": (_i, [_i, C.c_char_p, C.POINTER(_i), C.POINTER(_i), C.POINTER(_i), C.POINTER(_sz)]),
     "mllmcu_malloc": (_i, [C.POINTER(_vp), _sz]),
     "mllmcu_free": (_i, [_vp]),
+    "mllmcu_malloc_managed": (_i, [C.POINTER(_vp), _sz, _i]),
     "mllmcu_memset": (_i, [_vp, _i, _sz, _vp]),
     "mllmcu_memcpy_h2d": (_i, [_vp, _vp, _sz, _vp]),
     "mllmcu_memcpy_d2h": (_i, [_vp, _vp, _sz, _vp]),

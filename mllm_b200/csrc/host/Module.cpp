@@ -505,6 +505,8 @@ bool LlamaModel::issue_step(DecodePlan &p, bool pick, bool pdl_on) {
     return true;
 }
 
+int LlamaModel::cache_seq_len() { return blocks_[0].k_cache.op() ? blocks_[0].k_cache.op()->getCacheSeqLen() : 0; }
+
 Tensor LlamaModel::decode_step(const float *ids_dev, int B, bool pick) {
     st_.backend->dropQuantTag(); // the plan's kernels write outside runOp
     CUDABackend *bn = st_.backend;
@@ -551,7 +553,14 @@ Tensor LlamaModel::decode_step(const float *ids_dev, int B, bool pick) {
         Tensor ids(B, 1, 1, 1, bn);
         ids.setName("input_ids");
         MLLMCU_CHECK(mllmcu_memcpy_d2d(ids.rawDevPtr(), p.ids.rawDevPtr(), sizeof(float) * B, st));
-        return forward(ids);
+        Tensor lg = forward(ids);
+        if (pick) { // the caller still expects the pick in decode_ids() and in the token log under the consumed position
+            p.ctl_host = len;
+            MLLMCU_CHECK(mllmcu_memcpy_h2d(p.ctl.rawDevPtr(), &p.ctl_host, sizeof(int), st));
+            MLLMCU_CHECK(mllmcu_decode_argmax(lg.devPtr<float>(), B, cfg_.vocab, p.ids.devPtr<float>(), p.tok_log.devPtr<int>(),
+                                              p.ctl.devPtr<int>(), cfg_.cache_limit + 1, st));
+        }
+        return lg;
     }
     p.dev_pos = len;
     for (auto &l : p.layers)

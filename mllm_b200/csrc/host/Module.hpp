@@ -91,6 +91,8 @@ public:
     // fp32 [(layers+1)*B*S*hidden]) receives the hidden state after the embedding and each block.
     Tensor forward(Tensor ids, float *dump = nullptr);
     void clear_kvcache();
+    // one transformer block alone on a given hidden state [B,1,S,hidden] (parity tests feed it the reference's own layer input)
+    Tensor run_block(int layer, Tensor x) { return block_forward(blocks_.at(layer), layer, x); }
     const LlamaConfig &config() const { return cfg_; }
     CUDABackend *backend() { return st_.backend; }
     ~LlamaModel();
@@ -104,6 +106,7 @@ public:
     float *decode_ids();         // device fp32 [B]: input of the next step (written by the on-device pick)
     const int *decode_tok_log(); // device int32 [cache_limit][B]: token picked after consuming position p
     bool last_step_fused() const { return last_fused_; }
+    int cache_seq_len();         // tokens already in the KV cache (CPUKVCache::getCacheSeqLen of the first block)
     void set_eager_decode(bool on) { force_eager_ = on; }
     void set_step_kernel(bool on); // persistent whole-step kernel (opt-in); drops the current plan
     // 0: no plan, 1: chained fused kernels, 2: persistent step kernel; +4 when replayed from a CUDA graph, +8 with PDL edges

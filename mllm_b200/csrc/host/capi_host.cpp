@@ -93,6 +93,23 @@ HAPI int mllm_cuda_llama_forward(void *hv, const float *ids_host, int B, int S, 
     })
 }
 
+// Teacher-forced block: x_host [B][S][hidden] is uploaded, block `layer` (norm, q/k/v, RoPE, KV append, attention, o, residual, norm, MLP,
+// residual: LLaMABlock::Forward, models/llama/modeling_llama.hpp:60-68) runs alone on an EMPTY KV cache, the result comes back.
+// Parity tests feed it the reference's own input of that layer, so each layer is compared without upstream differences.
+HAPI int mllm_cuda_llama_block_forward(void *hv, int layer, const float *x_host, int B, int S, float *y_host) {
+    GUARD({
+        auto *h = (HostModel *)hv;
+        CUDABackend *bn = h->model->backend();
+        h->model->clear_kvcache();
+        Tensor x(B, 1, S, h->model->config().hidden, bn);
+        x.setName("teacher_forced_x");
+        x.copyFromHost(x_host);
+        Tensor y = h->model->run_block(layer, x);
+        y.copyToHost(y_host);
+        h->model->clear_kvcache();
+    })
+}
+
 // Greedy generation, the loop of Module::generate (mllm/Module.cpp:63-100,146-205): forward,
 // D2H logits, host argmax (LlmTextGenerator greedy, Generate.cpp:46-53), feed the token back.
 // ids_host [B,S]; out_tokens [B,max_new] int32.
@@ -218,6 +235,7 @@ HAPI int mllm_cuda_llama_request_device(void *hv, const float *ids_host, int B, 
         memcpy(stage, ids_host, sizeof(float) * (size_t)B * S);
         ids.copyFromHost(stage);
         Tensor toks(1, 1, n_decode > 0 ? n_decode : 1, B, bn); // fp32 ids, row per step
+        const int len0 = h->model->cache_seq_len();            // a request may continue a cache (multi-turn, Module::generate without clear)
         void *e0, *e1, *e2;
         MLLMCU_CHECK(mllmcu_event_create(&e0));
         MLLMCU_CHECK(mllmcu_event_create(&e1));
@@ -259,8 +277,8 @@ HAPI int mllm_cuda_llama_request_device(void *hv, const float *ids_host, int B, 
                 bn->sync();
             }
             for (int s = 0; s < n_decode; s++)
-                for (int b = 0; b < B; b++) // step s consumed position S+s-1; its pick is logged under that position
-                    tokens_out[(size_t)b * n_decode + s] = fused[s] ? log[(size_t)(S + s - 1) * B + b] : (int)t[(size_t)s * B + b];
+                for (int b = 0; b < B; b++) // step s consumed position len0+S+s-1; its pick is logged under that position
+                    tokens_out[(size_t)b * n_decode + s] = fused[s] ? log[(size_t)(len0 + S + s - 1) * B + b] : (int)t[(size_t)s * B + b];
         }
     })
 }

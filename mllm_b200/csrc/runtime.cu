@@ -23,6 +23,14 @@ MLLMCU_API int mllmcu_device_info(int dev, char *name, int *sm_major, int *sm_mi
 }
 MLLMCU_API int mllmcu_malloc(void **dptr, size_t bytes) { CU_TRY(cudaMalloc(dptr, bytes)); return 0; }
 MLLMCU_API int mllmcu_free(void *dptr) { CU_TRY(cudaFree(dptr)); return 0; }
+MLLMCU_API int mllmcu_malloc_managed(void **ptr, size_t bytes, int device) {
+    CU_TRY(cudaMallocManaged(ptr, bytes, cudaMemAttachGlobal));
+    // device-resident from the start: kernels never fault on it; a host touch migrates only the touched pages
+    cudaMemAdvise(*ptr, bytes, cudaMemAdviseSetPreferredLocation, device);
+    cudaMemPrefetchAsync(*ptr, bytes, device, 0);
+    (void)cudaGetLastError(); // advice / prefetch are hints: unsupported configurations keep plain managed behaviour
+    return 0;
+}
 MLLMCU_API int mllmcu_memset(void *dptr, int value, size_t bytes, void *stream) {
     CU_TRY(cudaMemsetAsync(dptr, value, bytes, (cudaStream_t)stream)); return 0;
 }

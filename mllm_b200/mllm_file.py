@@ -57,6 +57,9 @@ CONFIGS = {
     "toy-d128": dict(vocab=320, hidden=256, layers=2, heads=2, kv_heads=1, ffn=512, rope_type=ROPE_LLAMA, rope_theta=10000.0, rms_eps=1e-6, qkv_bias=0),
     # ffn = 128 x odd: Q4_0 rows of 18 * ffn / 32 bytes are 8 mod 16, as in Qwen1.5-1.8B (ffn 5504)
     "toy-qwen": dict(vocab=320, hidden=256, layers=2, heads=2, kv_heads=2, ffn=384, rope_type=ROPE_HF, rope_theta=1000000.0, rms_eps=1e-6, qkv_bias=1),
+    # hidden = 128 x odd: Q4_0 rows over K = hidden are 8 mod 16 bytes, which the fused prologue GEMV refuses for 3+ rows (rc -2):
+    # the decode plan must fall back op by op without losing the on-device pick
+    "toy-h384": dict(vocab=320, hidden=384, layers=2, heads=3, kv_heads=3, ffn=512, rope_type=ROPE_HF, rope_theta=10000.0, rms_eps=1e-6, qkv_bias=0),
     "toy-gqa": dict(vocab=384, hidden=256, layers=3, heads=8, kv_heads=2, ffn=768, rope_type=ROPE_HF, rope_theta=10000.0, rms_eps=1e-5, qkv_bias=1),
 }
 
@@ -242,3 +245,47 @@ def model_bytes(cfg):
 def decode_weight_bytes(cfg):
     """Algorithmic HBM bytes of Linear weights read per decode step: every Linear incl. lm_head, not the embedding table."""
     return sum(nbytes(r, c, d) for n, r, c, d in tensor_list(cfg) if d != F32 and n != Names(cfg["rope_type"]).embed)
+
+
+def write_random_model_torch(cfg, path, device="cuda", seed=1234):
+    """Random-init .mllm of a BASELINE-sized model, generated with torch on `device` (plumbing: the 7B needs 6.6 G normals)
+    and quantised with quantize_row_q4_0_reference's arithmetic (ggml/QuantizeQ4.cpp:33-68), written in the reference's container
+    format.  W ~ N(0, 0.02^2) -> Q4_0, norm weights 1 + N(0, 0.02^2), biases N(0, 0.02^2).  Reused when the file
+    already has the expected size."""
+    import torch
+    want = 12 + sum(4 + len(n.encode()) + 20 for n, *_ in tensor_list(cfg)) + model_bytes(cfg)
+    if os.path.exists(path) and os.path.getsize(path) == want:
+        return path
+    g = torch.Generator(device=device).manual_seed(seed)
+
+    def q4_0(rows, cols):
+        out = np.empty((rows, cols // 32 * 18), dtype=np.uint8)
+        step = max(1, (1 << 26) // cols)
+        for r0 in range(0, rows, step):
+            r = min(step, rows - r0)
+            w = torch.randn((r, cols // 32, 32), generator=g, device=device) * 0.02
+            idx = w.abs().argmax(dim=2, keepdim=True)
+            mx = torch.gather(w, 2, idx)
+            d = mx / -8.0
+            idv = torch.where(d != 0, 1.0 / d, torch.zeros_like(d))
+            q = torch.clamp(((w * idv) + 8.5).to(torch.int8), max=15).to(torch.uint8)
+            blk = torch.empty((r, cols // 32, 18), dtype=torch.uint8, device=device)
+            blk[..., 0:2] = d.to(torch.float16).view(torch.uint8).reshape(r, cols // 32, 2)
+            blk[..., 2:] = q[..., :16] | (q[..., 16:] << 4)
+            out[r0:r0 + r] = blk.reshape(r, -1).cpu().numpy()
+        return out
+
+    tensors, dts = {}, {}
+    for name, rows, cols, dt in tensor_list(cfg):
+        dts[name] = dt
+        if dt == F32:
+            base = 1.0 if "norm" in name else 0.0
+            tensors[name] = (base + 0.02 * torch.randn(cols, generator=g, device=device)).cpu().numpy().astype(np.float32)
+        elif dt == Q4_0:
+            tensors[name] = q4_0(rows, cols)
+        else:
+            raise ValueError("write_random_model_torch: Q4_0 model files only")
+    tmp = path + ".tmp"
+    write_mllm(tmp, tensors, dts)
+    os.replace(tmp, path)
+    return path

@@ -20,8 +20,15 @@ int ref_linear_kq(int wtype, const void *W, const float *x, const float *bias, f
 #define K_LINEAR_Q0 ref_linear
 #define K_LINEAR_KQ ref_linear_kq
 static void k_silu(const float *x, float *y, size_t n) { ref_silu(x, y, n); }
+void orc_flash_attn_f16kv(const float *Q, const uint16_t *K, const uint16_t *V, float *O, int Sq, int Sk, int Hq, int Hkv, int D, int causal, size_t kv_ld);
+/* mr_set_attention(1): the reference's kernels everywhere EXCEPT attention, which takes the restatement's summation order (<= 1.2e-6
+ * from the reference's per call).  The logits of that run against the all-reference run measure how far a rounding-level
+ * difference in ONE op travels through the Q8_0 re-quantisations of a deep model: the floor any non-bit-identical backend sits on. */
+static int g_port_attention = 0;
+void mr_set_attention(int port) { g_port_attention = port; }
 static void k_attn(const float *Q, const uint16_t *K, const uint16_t *V, float *O, int Sq, int Sk, int Hq, int Hkv, int D) {
-    ref_flash_attn_f16kv(Q, K, V, O, Sq, Sk, Hq, Hkv, D, 1, omp_get_max_threads());
+    if (g_port_attention) orc_flash_attn_f16kv(Q, K, V, O, Sq, Sk, Hq, Hkv, D, 1, (size_t)Hkv * D);
+    else ref_flash_attn_f16kv(Q, K, V, O, Sq, Sk, Hq, Hkv, D, 1, omp_get_max_threads());
 }
 #else
 int orc_linear(int wtype, const void *W, const float *x, const float *bias, void *y, int M, int N, int K, int ldx, int ldy, int out_fp16);
@@ -31,6 +38,7 @@ int orc_linear_kq(int wtype, const void *W, const float *x, const float *bias, f
 #define K_LINEAR_Q0 orc_linear
 #define K_LINEAR_KQ orc_linear_kq
 static void k_silu(const float *x, float *y, size_t n) { orc_silu(x, y, n, 8); }
+void mr_set_attention(int port) { (void)port; }
 static void k_attn(const float *Q, const uint16_t *K, const uint16_t *V, float *O, int Sq, int Sk, int Hq, int Hkv, int D) {
     orc_flash_attn_f16kv(Q, K, V, O, Sq, Sk, Hq, Hkv, D, 1, (size_t)Hkv * D);
 }

@@ -358,6 +358,10 @@ class ModelRunner:
     def reset(self):
         self.lib.mr_reset(self.h)
 
+    def set_port_attention(self, on):
+        """Reference-kernel build only: swap attention for the restatement's (see model_runner.c mr_set_attention)."""
+        self.lib.mr_set_attention(int(on))
+
     def forward(self, ids, dump=False):
         ids = np.ascontiguousarray(ids, dtype=np.float32)
         B, S = ids.shape

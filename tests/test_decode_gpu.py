@@ -259,3 +259,50 @@ def test_gemv_descriptor_replicas_and_lookahead_do_not_change_results(cu, oracle
         torch.cuda.synchronize()
         for r in range(reps):
             assert torch.equal(y[r], ref), (kw, r)
+
+
+@pytest.mark.parametrize("B", [1, 3, 8])
+def test_request_tokens_when_a_fused_launch_refuses_the_shape(be, oracle, tmp_path_factory, B):
+    """hidden = 384: at 3+ rows the prologue GEMV returns MLLMCU_ENOSUP mid-step; the step is redone op by op and the pick, the
+    token log and every later step must still be right (round-1 advisor finding: the pick was dropped and a stale token fed back)."""
+    from oracle import pyoracle as po
+    cfg, t, path = make(tmp_path_factory, "toy-h384", 64, seed=3)
+    ids = np.random.default_rng(40 + B).integers(0, cfg["vocab"], (B, 8)).astype(np.float32)
+    cpu = po.ModelRunner(oracle, cfg, t, mf.Names(cfg["rope_type"]), max_batch=B)
+    want, cur, margins = [], ids, []
+    for _ in range(10):
+        lg = cpu.forward(cur)
+        top2 = np.sort(lg, axis=1)[:, -2:]
+        margins.append((top2[:, 1] - top2[:, 0]) / np.abs(lg).max())
+        want.append(lg.argmax(1))
+        cur = want[-1].astype(np.float32)[:, None]
+    want = np.stack(want, axis=1)
+    gpu = be.LlamaModel(cfg).load(path)
+    toks = gpu.generate(ids, 10)
+    gpu.close()
+    clear = np.minimum.accumulate(np.stack(margins, axis=1) > 2e-2, axis=1)  # rows stay comparable until their first near tie
+    assert np.array_equal(toks[clear], want[clear])
+    assert clear[:, 1:].sum() >= B  # decode steps (not just the prefill pick) are being compared
+    assert len({tuple(r) for r in toks.tolist()}) == B and all(len(set(r)) > 1 for r in toks.tolist())  # no row repeats one stale token
+
+
+def test_second_request_continues_the_cache_without_clear(be, oracle, tmp_path_factory):
+    """Module::generate does not clear the KV cache (multi-turn): the second request's tokens are logged under positions that
+    start at the cache length, not at 0 (round-1 advisor finding)."""
+    from oracle import pyoracle as po
+    cfg, t, path = make(tmp_path_factory, "toy-d128", 96, seed=6)
+    rng = np.random.default_rng(12)
+    a, b = rng.integers(0, cfg["vocab"], (1, 8)).astype(np.float32), rng.integers(0, cfg["vocab"], (1, 4)).astype(np.float32)
+    cpu = po.ModelRunner(oracle, cfg, t, mf.Names(cfg["rope_type"]))
+    want = []
+    for prompt, n in ((a, 12), (b, 9)):
+        cur, w = prompt, []
+        for _ in range(n):
+            tok = int(cpu.forward(cur).argmax())
+            w.append(tok)
+            cur = np.array([[tok]], dtype=np.float32)
+        want.append(w)
+    gpu = be.LlamaModel(cfg).load(path)
+    assert gpu.generate(a, 12)[0].tolist() == want[0]
+    assert gpu.generate(b, 9)[0].tolist() == want[1]   # no clear_kvcache in between
+    gpu.close()

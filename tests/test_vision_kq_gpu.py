@@ -213,13 +213,16 @@ def test_vision_rope(cu, oracle):
     x = rng.standard_normal((S, H, D)).astype(np.float32)
     ang = rng.uniform(0, 74, (S, D // 2)).astype(np.float32)
     want = oracle.only.rope_vision(x, ang)
-    # host-built sin/cos (what the backend op uploads): bit-identical
-    got = cu.rope_vision(dev(x[None]), sin_t=dev(np.sin(ang)), cos_t=dev(np.cos(ang))).cpu().numpy()[0]
-    want_np = np.empty_like(x)
-    sn, cs = np.sin(ang)[:, None, :], np.cos(ang)[:, None, :]
-    want_np[..., :40] = x[..., :40] * cs - x[..., 40:] * sn
-    want_np[..., 40:] = x[..., :40] * sn + x[..., 40:] * cs
-    assert np.array_equal(bits(got), bits(want_np))
+    # host-built sin/cos with libm (std::sin / std::cos, what the backend op uploads and the reference evaluates inline): the result is
+    # bit-identical to the restatement, which is pinned to the compiled CPUVisionRoPEFunc (tests/test_oracle_refops.py)
+    import ctypes
+    libm = ctypes.CDLL("libm.so.6")
+    libm.sinf.restype = libm.cosf.restype = ctypes.c_float
+    libm.sinf.argtypes = libm.cosf.argtypes = [ctypes.c_float]
+    sn = np.array([libm.sinf(float(a)) for a in ang.ravel()], dtype=np.float32).reshape(ang.shape)
+    cs = np.array([libm.cosf(float(a)) for a in ang.ravel()], dtype=np.float32).reshape(ang.shape)
+    got = cu.rope_vision(dev(x[None]), sin_t=dev(sn), cos_t=dev(cs)).cpu().numpy()[0]
+    assert np.array_equal(bits(got), bits(want))
     # device sin/cos: <= 2 ulp on sin/cos -> 1e-6 absolute on O(1) data
     got = cu.rope_vision(dev(x[None]), angles=dev(ang)).cpu().numpy()[0]
     assert np.abs(got - want).max() <= 2e-6 * np.abs(x).max()
