@@ -1,0 +1,404 @@
+// mllm/backends/cuda/CUDAOps.cpp -- the CUDA ops of the in-tree backend, written against the reference's real Op / Tensor /
+// AbstructLoader interfaces.  Each op keeps the reshape / setUp / load / execute semantics of the CPU op it replaces (cited) and
+// reaches the device only through the C ABI of include/mllmcu.h.  Tensors are BSHD; a tensor may be a child view of a KV cache
+// (allocFromTemplate), so every kernel call passes the view's base pointer and its batch / sequence strides.
+#include "CUDABackend.hpp"
+
+#include "Module.hpp"
+#include "ParamLoader.hpp"
+#include "Tensor.hpp"
+#include "backends/cpu/op/CPUKVCache.hpp"
+#include "backends/cpu/op/CPUViewFunc.hpp"
+#include "mllmcu.h"
+
+#include <cmath>
+#include <cstring>
+#include <stdexcept>
+
+namespace mllm {
+
+static CUDABackend *cb(Backend *b) { return static_cast<CUDABackend *>(b); }
+static float getp(const OpParam &p, const char *k, float dflt) {
+    auto it = p.find(k);
+    return it == p.end() ? dflt : it->second;
+}
+
+// element strides of a BSHD tensor or child view (Tensor::offset, Tensor.hpp:264-311)
+struct View {
+    long long bs, ss; // elements between consecutive batches / sequence positions; (head, dimension) are contiguous
+};
+static View strides(Tensor &t) {
+    if (t.ctype() != BSHD) throw std::runtime_error("[mllm-cuda] " + t.name() + ": only BSHD tensors");
+    const auto m = t.shapeMaster();
+    if (m.size() == 4 && t.shapeOffset().size() == 4) return {(long long)m[2] * m[1] * m[3], (long long)m[1] * m[3]};
+    return {(long long)t.sequence() * t.head() * t.dimension(), (long long)t.head() * t.dimension()};
+}
+static bool dense(Tensor &t) {
+    const View v = strides(t);
+    return v.ss == (long long)t.head() * t.dimension() && (t.batch() == 1 || v.bs == (long long)t.sequence() * v.ss);
+}
+static void *base(Tensor &t) { // address of element (0,0,0,0) of the view
+    const size_t esz = t.dtype() == MLLM_TYPE_F16 ? 2 : 4;
+    return (char *)t.rawHostPtr() + (size_t)t.offset(0, 0, 0, 0) * esz;
+}
+static float *fbase(Tensor &t) {
+    if (t.dtype() != MLLM_TYPE_F32) throw std::runtime_error("[mllm-cuda] " + t.name() + ": fp32 tensor expected");
+    return (float *)base(t);
+}
+static void load_param(Tensor &t, Backend *bn, const string &name, int rows, int cols, AbstructLoader &loader, DataType dflt) {
+    t.setBackend(bn);
+    t.setName(name);
+    t.reshape(1, 1, rows, cols);
+    const DataType dt = loader.getDataType(name);
+    t.setDtype(dt != MLLM_TYPE_COUNT ? dt : dflt);
+    t.alloc();
+    if (dt != MLLM_TYPE_COUNT) loader.load(&t);
+}
+
+// ------------------------------------------------------------------ Linear (op/CPULinear.cpp:22-233, compute/Matmul.cpp:77-279)
+class CUDALinear final : public CUDAOpBase {
+public:
+    CUDALinear(Backend *bn, string name, int in_features, int out_features, bool bias) :
+        CUDAOpBase(bn, name), in_(in_features), out_(out_features), bias_(bias) {}
+    ErrorCode reshape(vector<shared_ptr<Tensor>> in, vector<shared_ptr<Tensor>> out) override {
+        if (in[0]->count() == 0 && in[0]->sequence() != 0) { out[0]->reshape(0, 0, 0, 0); return MLLM_NO_ERROR; }
+        if (in[0]->head() != 1 || in[0]->dimension() != in_) throw std::runtime_error("[mllm-cuda] Linear " + name() + ": input must be [B,1,S," + std::to_string(in_) + "]");
+        out[0]->reshape(in[0]->batch(), in[0]->head(), in[0]->sequence(), out_);
+        return MLLM_NO_ERROR;
+    }
+    ErrorCode load(AbstructLoader &loader) override { // CPULinear.cpp:47-95
+        DataType dt = loader.getDataType(name() + ".weight");
+        const DataType eff = dt != MLLM_TYPE_COUNT ? dt : Op::noLoadWeightsDtype();
+        if (eff != MLLM_TYPE_Q4_0 && eff != MLLM_TYPE_Q8_0 && eff != MLLM_TYPE_Q4_K && eff != MLLM_TYPE_Q6_K)
+            throw std::runtime_error("[mllm-cuda] Linear " + name() + ": weight dtype " + std::to_string((int)eff) + " has no CUDA kernel");
+        load_param(weight_, backend_, name() + ".weight", out_, in_, loader, eff);
+        if (bias_) load_param(biasT_, backend_, name() + ".bias", 1, out_, loader, MLLM_TYPE_F32);
+        return Op::load(loader);
+    }
+    ErrorCode execute(vector<shared_ptr<Tensor>> in, vector<shared_ptr<Tensor>> out) override {
+        auto *b = cb(backend_);
+        Tensor &x = *in[0], &y = *out[0];
+        if (x.count() == 0) return MLLM_NO_ERROR;
+        const int f16 = y.dtype() == MLLM_TYPE_F16;
+        const float *bias = bias_ ? biasT_.hostPtr<float>() : nullptr;
+        const View xs = strides(x), ys = strides(y);
+        const bool one = dense(x) && (y.batch() == 1 || ys.bs == (long long)y.sequence() * ys.ss);
+        const int nbatch = one ? 1 : x.batch();
+        const int M = one ? x.batch() * x.sequence() : x.sequence();
+        void *ws = b->workspace(mllmcu_linear_workspace_bytes(M, in_));
+        const int kind = nbatch == 1 ? mllmcu_linear_quant_kind((int)weight_.dtype(), M, out_, in_, weight_.rawHostPtr()) : 0;
+        for (int i = 0; i < nbatch; i++) {
+            const float *xp = fbase(x) + (size_t)i * xs.bs;
+            char *yp = (char *)base(y) + (size_t)i * ys.bs * (f16 ? 2 : 4);
+            const int reuse = b->quantTagMatches(xp, M, in_, (int)xs.ss, kind) ? 1 : 0;
+            MLLMCU_CHECK(mllmcu_linear_ex((int)weight_.dtype(), weight_.rawHostPtr(), xp, bias, yp, M, out_, in_, (int)xs.ss, (int)ys.ss, f16, ws,
+                                          b->workspaceBytes(), reuse, b->stream()));
+            if (kind) b->setQuantTag(xp, M, in_, (int)xs.ss, kind);
+            else b->dropQuantTag();
+            b->kernel_launches += 2 - reuse;
+        }
+        return MLLM_NO_ERROR;
+    }
+    ErrorCode free(vector<shared_ptr<Tensor>>, vector<shared_ptr<Tensor>>) override { weight_.free(); if (bias_) biasT_.free(); return MLLM_NO_ERROR; }
+    bool fuseInfo(CUDAFuseInfo &f) override {
+        if (!weight_.allocted()) return false;
+        f.weight = weight_.rawHostPtr(); f.wtype = (int)weight_.dtype(); f.in = in_; f.out = out_;
+        f.bias = bias_ ? biasT_.hostPtr<float>() : nullptr;
+        return true;
+    }
+
+private:
+    int in_, out_;
+    bool bias_;
+    Tensor weight_, biasT_;
+};
+
+// ----------------------------------------------------------------- RMSNorm (op/CPURMSNorm.cpp:31-135)
+class CUDARMSNorm final : public CUDAOpBase {
+public:
+    CUDARMSNorm(Backend *bn, string name, int norm_size, float eps, bool add_unit_offset) :
+        CUDAOpBase(bn, name), n_(norm_size), eps_(eps), unit_(add_unit_offset) {}
+    ErrorCode reshape(vector<shared_ptr<Tensor>> in, vector<shared_ptr<Tensor>> out) override {
+        out[0]->reshape(in[0]->batch(), in[0]->head(), in[0]->sequence(), in[0]->dimension());
+        return MLLM_NO_ERROR;
+    }
+    ErrorCode load(AbstructLoader &loader) override {
+        const DataType dt = loader.getDataType(name() + ".weight");
+        if (dt != MLLM_TYPE_COUNT && dt != MLLM_TYPE_F32) throw std::runtime_error("[mllm-cuda] RMSNorm " + name() + ": only F32 weights (the quantizer keeps *norm* F32)");
+        load_param(weight_, backend_, name() + ".weight", 1, n_, loader, MLLM_TYPE_F32);
+        return Op::load(loader);
+    }
+    ErrorCode execute(vector<shared_ptr<Tensor>> in, vector<shared_ptr<Tensor>> out) override {
+        auto *b = cb(backend_);
+        if (!dense(*in[0]) || !dense(*out[0])) throw std::runtime_error("[mllm-cuda] RMSNorm " + name() + ": dense tensors expected");
+        const int rows = in[0]->batch() * in[0]->sequence() * in[0]->head();
+        MLLMCU_CHECK(mllmcu_rmsnorm(fbase(*in[0]), weight_.hostPtr<float>(), fbase(*out[0]), rows, in[0]->dimension(), eps_, unit_, b->stream()));
+        b->kernel_launches++;
+        return MLLM_NO_ERROR;
+    }
+    bool fuseInfo(CUDAFuseInfo &f) override {
+        if (!weight_.allocted()) return false;
+        f.norm_w = weight_.hostPtr<float>(); f.eps = eps_; f.unit_offset = unit_; f.in = n_;
+        return true;
+    }
+
+private:
+    int n_;
+    float eps_;
+    bool unit_;
+    Tensor weight_;
+};
+
+// -------------------------------------------------------------------- RoPE (op/CPURoPE.cpp:22-128,200-515)
+// Tables are built on the host as the reference builds them (theta in double -> float, t = s * theta in float, libm sin / cos)
+// and uploaded once per (pose type, width, theta, positions); the rotation kernel uses the compiled reference's FMA form.
+struct RopeTables { Tensor sin_t, cos_t; };
+static map<string, shared_ptr<RopeTables>> g_rope_tables;
+
+class CUDARoPE final : public CUDAOpBase {
+public:
+    CUDARoPE(Backend *bn, string name, const OpParam &p) : CUDAOpBase(bn, name) {
+        pose_type_ = (int)getp(p, "pose_type", LLAMAROPE);
+        rope_theta_ = getp(p, "rope_theta", 10000.f);
+        partial_ = getp(p, "partial_rotary_factor", 1.0f);
+        pos_max_ = (int)getp(p, "max_position_embeddings", 16384);
+        if (pose_type_ != LLAMAROPE && pose_type_ != HFHUBROPE) throw std::runtime_error("[mllm-cuda] RoPE " + name + ": pose_type " + std::to_string(pose_type_) + " has no CUDA kernel");
+        if ((int)getp(p, "rope_type", 0) != 0) throw std::runtime_error("[mllm-cuda] RoPE " + name + ": rope scaling has no CUDA kernel yet");
+    }
+    ErrorCode reshape(vector<shared_ptr<Tensor>> in, vector<shared_ptr<Tensor>> out) override {
+        out[0]->reshape(in[0]->batch(), in[0]->head(), in[0]->sequence(), in[0]->dimension());
+        ishape_ = (int)(in[0]->dimension() * partial_);
+        if (!tab_ || tab_dim_ != ishape_) {
+            char key[160];
+            snprintf(key, sizeof key, "%p-%d-%d-%.9g-%d", (void *)backend_, pose_type_, ishape_, rope_theta_, pos_max_);
+            auto it = g_rope_tables.find(key);
+            if (it == g_rope_tables.end()) it = g_rope_tables.emplace(key, build()).first;
+            tab_ = it->second;
+            tab_dim_ = ishape_;
+        }
+        return MLLM_NO_ERROR;
+    }
+    ErrorCode execute(vector<shared_ptr<Tensor>> in, vector<shared_ptr<Tensor>> out) override {
+        auto *b = cb(backend_);
+        Tensor &x = *in[0], &y = *out[0];
+        if (h_cnt_ + x.sequence() > pos_max_) throw std::runtime_error("[mllm-cuda] RoPE " + name() + ": position exceeds max_position_embeddings");
+        if (!dense(x)) throw std::runtime_error("[mllm-cuda] RoPE " + name() + ": dense input expected");
+        const View ys = strides(y);
+        MLLMCU_CHECK(mllmcu_rope(pose_type_, fbase(x), base(y), x.batch(), x.sequence(), x.head(), x.dimension(), ishape_, h_cnt_,
+                                 tab_->sin_t.hostPtr<float>(), tab_->cos_t.hostPtr<float>(), ishape_, y.dtype() == MLLM_TYPE_F16, ys.bs, ys.ss, b->stream()));
+        b->kernel_launches++;
+        h_cnt_ += x.sequence(); // CPURoPE.cpp:517-530
+        return MLLM_NO_ERROR;
+    }
+    void clearCache() override { h_cnt_ = 0; }
+    bool fuseInfo(CUDAFuseInfo &f) override {
+        if (!tab_) return false;
+        f.sin_t = tab_->sin_t.hostPtr<float>(); f.cos_t = tab_->cos_t.hostPtr<float>();
+        f.rope_type = pose_type_; f.rot_dim = ishape_; f.pos_max = pos_max_;
+        return true;
+    }
+    void advance(int tokens) override { h_cnt_ += tokens; }
+    int position() const { return h_cnt_; }
+
+private:
+    shared_ptr<RopeTables> build() {
+        const int dim = ishape_;
+        vector<float> theta(dim / 2), s((size_t)pos_max_ * dim), c((size_t)pos_max_ * dim);
+        for (int i = 0; i < dim / 2; i++) theta[i] = (float)(1.0 / pow((double)rope_theta_, 2.0 * i / dim));
+        for (int p = 0; p < pos_max_; p++)
+            for (int i = 0; i < dim / 2; i++) {
+                const float ang = p * theta[i];
+                const float sv = sinf(ang), cv = cosf(ang);
+                const int d0 = pose_type_ == LLAMAROPE ? 2 * i : i;
+                const int d1 = pose_type_ == LLAMAROPE ? 2 * i + 1 : i + dim / 2;
+                s[(size_t)p * dim + d0] = sv; c[(size_t)p * dim + d0] = cv;
+                s[(size_t)p * dim + d1] = sv; c[(size_t)p * dim + d1] = cv;
+            }
+        auto t = std::make_shared<RopeTables>();
+        auto up = [&](Tensor &dst, const vector<float> &src) {
+            dst.setBackend(backend_);
+            dst.reshape(1, 1, pos_max_, dim);
+            dst.setDtype(MLLM_TYPE_F32);
+            dst.alloc();
+            MLLMCU_CHECK(mllmcu_memcpy_h2d(dst.rawHostPtr(), src.data(), src.size() * sizeof(float), cb(backend_)->stream()));
+            cb(backend_)->sync();
+        };
+        up(t->sin_t, s);
+        up(t->cos_t, c);
+        return t;
+    }
+    int pose_type_, pos_max_, ishape_ = 0, h_cnt_ = 0, tab_dim_ = -1;
+    float rope_theta_, partial_;
+    shared_ptr<RopeTables> tab_;
+};
+
+// --------------------------------------------------------------- Embedding (op/CPUEmbedding.cpp:30-143)
+class CUDAEmbedding final : public CUDAOpBase {
+public:
+    CUDAEmbedding(Backend *bn, string name, int hidden, int vocab) : CUDAOpBase(bn, name), hidden_(hidden), vocab_(vocab) {}
+    ErrorCode reshape(vector<shared_ptr<Tensor>> in, vector<shared_ptr<Tensor>> out) override {
+        out[0]->reshape(in[0]->batch(), 1, in[0]->sequence(), hidden_);
+        return MLLM_NO_ERROR;
+    }
+    ErrorCode load(AbstructLoader &loader) override {
+        const DataType dt = loader.getDataType(name() + ".weight");
+        const DataType eff = dt != MLLM_TYPE_COUNT ? dt : MLLM_TYPE_Q4_0;
+        if (eff != MLLM_TYPE_Q4_0) throw std::runtime_error("[mllm-cuda] Embedding " + name() + ": only Q4_0 tables (the quantizer forces embed_tokens to Q4_0)");
+        load_param(weight_, backend_, name() + ".weight", vocab_, hidden_, loader, eff);
+        return Op::load(loader);
+    }
+    ErrorCode execute(vector<shared_ptr<Tensor>> in, vector<shared_ptr<Tensor>> out) override {
+        auto *b = cb(backend_);
+        MLLMCU_CHECK(mllmcu_embedding_q4_0(weight_.rawHostPtr(), fbase(*in[0]), fbase(*out[0]), in[0]->batch() * in[0]->sequence(), hidden_, b->stream()));
+        b->kernel_launches++;
+        return MLLM_NO_ERROR;
+    }
+    bool fuseInfo(CUDAFuseInfo &f) override {
+        if (!weight_.allocted()) return false;
+        f.weight = weight_.rawHostPtr(); f.wtype = (int)weight_.dtype(); f.in = vocab_; f.out = hidden_;
+        return true;
+    }
+
+private:
+    int hidden_, vocab_;
+    Tensor weight_;
+};
+
+// ------------------------------------------------------ SiLU, x + y, x * y (op/CPUSiLU.cpp, op/CPUBinaryFunc.hpp)
+class CUDAElementwise final : public CUDAOpBase {
+public:
+    enum Kind { SILU_K, ADD_K, MUL_K };
+    CUDAElementwise(Backend *bn, string name, Kind k) : CUDAOpBase(bn, name), kind_(k) {}
+    ErrorCode reshape(vector<shared_ptr<Tensor>> in, vector<shared_ptr<Tensor>> out) override {
+        out[0]->reshape(in[0]->batch(), in[0]->head(), in[0]->sequence(), in[0]->dimension());
+        return MLLM_NO_ERROR;
+    }
+    ErrorCode execute(vector<shared_ptr<Tensor>> in, vector<shared_ptr<Tensor>> out) override {
+        auto *b = cb(backend_);
+        for (auto &t : in)
+            if (!dense(*t) || t->count() != in[0]->count()) throw std::runtime_error("[mllm-cuda] " + name() + ": same-shape dense operands only (no broadcast)");
+        const size_t n = (size_t)in[0]->count();
+        b->dropQuantTag();
+        if (kind_ == SILU_K) MLLMCU_CHECK(mllmcu_silu(fbase(*in[0]), fbase(*out[0]), n, b->stream()));
+        else if (kind_ == ADD_K) MLLMCU_CHECK(mllmcu_add(fbase(*in[0]), fbase(*in[1]), fbase(*out[0]), n, b->stream()));
+        else MLLMCU_CHECK(mllmcu_mul(fbase(*in[0]), fbase(*in[1]), fbase(*out[0]), n, b->stream()));
+        b->kernel_launches++;
+        return MLLM_NO_ERROR;
+    }
+
+private:
+    Kind kind_;
+};
+
+// ----------------------------------------------------- F_CLIP (op/CPUClipFunc.hpp:34-140): sequence / batch slices as device copies
+class CUDAClip final : public CUDAOpBase {
+public:
+    CUDAClip(Backend *bn, string name, const OpParam &p) : CUDAOpBase(bn, name) {
+        auto rd = [&](const char *k, vector<int> &v) {
+            const int n = (int)getp(p, (string(k) + "_size").c_str(), 0);
+            for (int i = 0; i < n; i++) v.push_back((int)p.at(string(k) + "_" + std::to_string(i)));
+        };
+        rd("b", b_); rd("h", h_); rd("s", s_); rd("d", d_);
+        if (!h_.empty() || !d_.empty() || !b_.empty()) throw std::runtime_error("[mllm-cuda] clip " + name + ": only sequence slices have a CUDA path");
+    }
+    ErrorCode reshape(vector<shared_ptr<Tensor>> in, vector<shared_ptr<Tensor>> out) override {
+        int S = in[0]->sequence();
+        if (s_.size() == 2) S = s_[1] - s_[0];
+        else if (s_.size() == 1) S = 1;
+        out[0]->reshape(in[0]->batch(), in[0]->head(), S, in[0]->dimension());
+        out[0]->setDtype(in[0]->dtype());
+        return MLLM_NO_ERROR;
+    }
+    ErrorCode execute(vector<shared_ptr<Tensor>> in, vector<shared_ptr<Tensor>> out) override {
+        auto *b = cb(backend_);
+        Tensor &x = *in[0], &y = *out[0];
+        int s0 = s_.empty() ? 0 : s_[0];
+        if (s0 < 0) s0 += x.sequence();
+        const View xs = strides(x), ys = strides(y);
+        const size_t row = (size_t)x.head() * x.dimension() * 4;
+        for (int i = 0; i < x.batch(); i++)
+            for (int s = 0; s < y.sequence(); s++)
+                MLLMCU_CHECK(mllmcu_memcpy_d2d((char *)base(y) + ((size_t)i * ys.bs + (size_t)s * ys.ss) * 4,
+                                               (char *)base(x) + ((size_t)i * xs.bs + (size_t)(s0 + s) * xs.ss) * 4, row, b->stream()));
+        return MLLM_NO_ERROR;
+    }
+
+private:
+    vector<int> b_, h_, s_, d_;
+};
+
+// ----------------------------------- F_FA2 (op/CPUFlashAttention2Func.hpp:49-125 -> compute/FlashAttention2.hpp:2236-2284)
+class CUDAFlashAttention2 final : public CUDAOpBase {
+public:
+    CUDAFlashAttention2(Backend *bn, string name, bool causal) : CUDAOpBase(bn, name), causal_(causal) {}
+    ErrorCode reshape(vector<shared_ptr<Tensor>> in, vector<shared_ptr<Tensor>> out) override {
+        out[0]->reshape(in[0]->batch(), in[0]->head(), in[0]->sequence(), in[0]->dimension());
+        return MLLM_NO_ERROR;
+    }
+    ErrorCode execute(vector<shared_ptr<Tensor>> in, vector<shared_ptr<Tensor>> out) override {
+        auto *b = cb(backend_);
+        Tensor &q = *in[0], &k = *in[1], &v = *in[2], &o = *out[0];
+        const int B = q.batch(), Sq = q.sequence(), Sk = k.sequence(), Hq = q.head(), Hkv = k.head(), D = q.dimension();
+        if (!dense(q) || !dense(o)) throw std::runtime_error("[mllm-cuda] flash attention: dense q / o expected");
+        const View ks = strides(k), vs = strides(v);
+        if (ks.ss != (long long)Hkv * D || vs.ss != ks.ss || vs.bs != ks.bs) throw std::runtime_error("[mllm-cuda] flash attention: k / v must share one [B][limit][Hkv][D] layout");
+        const size_t wsb = mllmcu_flash_attn_workspace_bytes(B, Sq, Hq, D);
+        void *ws = b->workspace(wsb);
+        b->dropQuantTag();
+        if (k.dtype() == MLLM_TYPE_F16)
+            MLLMCU_CHECK(mllmcu_flash_attn_f16kv(fbase(q), base(k), base(v), fbase(o), B, Sq, Sk, Hq, Hkv, D, causal_, ks.bs, ws, b->workspaceBytes(), b->stream()));
+        else
+            MLLMCU_CHECK(mllmcu_flash_attn_f32kv(fbase(q), fbase(k), fbase(v), fbase(o), B, Sq, Sk, Hq, Hkv, D, causal_, ks.bs, ws, b->workspaceBytes(), b->stream()));
+        b->kernel_launches += 2;
+        return MLLM_NO_ERROR;
+    }
+
+private:
+    bool causal_;
+};
+
+// ------------------------------------------------------------------ creators
+#define CREATOR(NAME, EXPR)                                                                                   \
+    class NAME final : public CUDABackend::Creator {                                                          \
+    public:                                                                                                   \
+        Op *create(OpParam p, Backend *bn, string name, int threadCount) const override { return EXPR; }     \
+    }
+CREATOR(LinearCreator, new CUDALinear(bn, name, (int)p["in_features"], (int)p["out_features"], (bool)p["bias"]));
+CREATOR(RMSNormCreator, new CUDARMSNorm(bn, name, (int)p["norm_size"], p["epsilon"], p.count("add_unit_offset") ? (bool)p["add_unit_offset"] : false));
+CREATOR(RoPECreator, new CUDARoPE(bn, name, p));
+CREATOR(EmbeddingCreator, new CUDAEmbedding(bn, name, (int)p["hidden_size"], (int)p["vocab_size"]));
+CREATOR(SiLUCreator, new CUDAElementwise(bn, name, CUDAElementwise::SILU_K));
+CREATOR(AddCreator, new CUDAElementwise(bn, name, CUDAElementwise::ADD_K));
+CREATOR(MulCreator, new CUDAElementwise(bn, name, CUDAElementwise::MUL_K));
+CREATOR(ClipCreator, new CUDAClip(bn, name, p));
+CREATOR(FA2Creator, new CUDAFlashAttention2(bn, name, p.count("causal_mask") ? p["causal_mask"] != 0.f : true));
+// metadata-only ops: the reference's own classes, constructed on this backend (they do no arithmetic and, under flash attention,
+// touch no tensor data after construction: CPUViewFunc.hpp:31-50, CPUKVCache.cpp:137-151,253-275)
+CREATOR(ViewCreator, new CPUviewFunction(bn, name, threadCount, (int)p.at("b"), (int)p.at("h"), (int)p.at("s"), (int)p.at("d")));
+class KVCacheCreator final : public CUDABackend::Creator {
+public:
+    Op *create(OpParam p, Backend *bn, string name, int threadCount) const override {
+        const int n_rep = (int)p["n_rep"];
+        const bool fa2 = (bool)p["fa2"];
+        if (!fa2 && n_rep > 1) throw std::runtime_error("[mllm-cuda] KVCache " + name + ": eager GQA head replication copies on the host; use attn_implementation flash_attention_2");
+        auto *ret = new CPUKVCache(bn, name, (int)p["hidden"], (int)p["head"], n_rep, fa2, (int)p["cache_max"], threadCount);
+        ret->setForXnn((bool)p["for_xnn"]);
+        return ret;
+    }
+};
+
+void CUDABackend::registerOps() {
+    addCreator(LINEAR, new LinearCreator());
+    addCreator(RMSNORM, new RMSNormCreator());
+    addCreator(ROPE, new RoPECreator());
+    addCreator(EMBEDDING, new EmbeddingCreator());
+    addCreator(SILU, new SiLUCreator());
+    addCreator(F_TTADD, new AddCreator());
+    addCreator(F_TTMUL, new MulCreator());
+    addCreator(F_CLIP, new ClipCreator());
+    addCreator(F_FA2, new FA2Creator());
+    addCreator(F_VIEW, new ViewCreator());
+    addCreator(KVCACHE, new KVCacheCreator());
+}
+
+} // namespace mllm
