@@ -6,6 +6,7 @@
 //
 //   run_llama_cuda --device 0|4 --model llama2-7b|tinyllama-1.1b|qwen1.5-1.8b --file m.mllm --prompt 128 --decode 32 [--limit 512]
 // prints one JSON line: tokens, prefill / decode tok/s from Module::profiling's inference_times_.
+#include <algorithm>
 #include <chrono>
 #include <cstdio>
 #include <cstring>
@@ -39,8 +40,12 @@ static int run(Model &model, BackendType device, const std::string &file, int vo
     for (auto &v : ids) v = rng() % vocab;
     std::vector<std::vector<unsigned>> out(B);
     Tensor in = make_input(ids, B, S);
+    int fused_steps = 0;
     for (int step = 0; step < n_decode; step++) {
         auto result = model({in});
+#ifdef USE_CUDA
+        if (device == MLLM_CUDA) fused_steps += static_cast<CUDABackend *>(Backend::global_backends[MLLM_CUDA].get())->last_forward_fused;
+#endif
         Tensor lg = result[0];
         if (lg.backend()->type() != MLLM_CPU) lg.cpu(); // as the OpenCL demos do before reading a result on the host
         std::vector<unsigned> next(B);
@@ -59,8 +64,11 @@ static int run(Model &model, BackendType device, const std::string &file, int vo
     }
     double pre_ms = model.inference_times_.empty() ? 0.0 : model.inference_times_[0], dec_ms = 0.0;
     for (size_t i = 1; i < model.inference_times_.size(); i++) dec_ms += model.inference_times_[i];
-    printf("{\"device\": %d, \"B\": %d, \"prompt\": %d, \"decode\": %d, \"prefill_ms\": %.3f, \"decode_ms_per_step\": %.4f, \"tokens\": [", (int)device, B, S, n_decode,
-           pre_ms, n_decode > 1 ? dec_ms / (n_decode - 1) : 0.0);
+    std::vector<double> tail(model.inference_times_.begin() + std::min<size_t>(model.inference_times_.size(), 4), model.inference_times_.end());
+    std::sort(tail.begin(), tail.end());
+    const double dec_median = tail.empty() ? 0.0 : tail[tail.size() / 2];
+    printf("{\"device\": %d, \"B\": %d, \"prompt\": %d, \"decode\": %d, \"prefill_ms\": %.3f, \"decode_ms_per_step\": %.4f, \"decode_ms_median\": %.4f, \"fused_steps\": %d, \"tokens\": [", (int)device, B,
+           S, n_decode, pre_ms, n_decode > 1 ? dec_ms / (n_decode - 1) : 0.0, dec_median, fused_steps);
     for (int b = 0; b < B; b++) {
         printf("%s[", b ? ", " : "");
         for (size_t i = 0; i < out[b].size(); i++) printf("%s%u", i ? ", " : "", out[b][i]);

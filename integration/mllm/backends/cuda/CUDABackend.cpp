@@ -34,19 +34,21 @@ static size_t size_class(size_t bytes) { // 256 B granules up to 64 KiB, then 1/
 void CUDAMemoryManager::alloc(void **ptr, size_t size, size_t /*alignment: blocks are 256 B aligned or better*/) {
     if (size == 0) size = 1;
     const size_t cls = size_class(size);
-    auto it = free_list_.find(cls);
-    if (it != free_list_.end()) {
+    const int kind = device_only ? 1 : 0;
+    auto it = free_list_[kind].find(cls);
+    if (it != free_list_[kind].end()) {
         *ptr = it->second;
-        free_list_.erase(it);
-        live_[*ptr] = cls;
+        free_list_[kind].erase(it);
+        live_[*ptr] = {cls, kind};
         pool_hits++;
         return;
     }
     void *p = nullptr;
-    MLLMCU_CHECK(mllmcu_malloc_managed(&p, cls, device_));
+    if (kind) MLLMCU_CHECK(mllmcu_malloc(&p, cls));
+    else MLLMCU_CHECK(mllmcu_malloc_managed(&p, cls, device_));
     bytes_allocated += cls;
     pool_misses++;
-    live_[p] = cls;
+    live_[p] = {cls, kind};
     *ptr = p;
 }
 
@@ -54,12 +56,13 @@ void CUDAMemoryManager::free(void *ptr) {
     if (!ptr) return;
     auto it = live_.find(ptr);
     if (it == live_.end()) return; // not ours (e.g. an mmap view handed to setHostPtr)
-    free_list_.emplace(it->second, ptr);
+    free_list_[it->second.second].emplace(it->second.first, ptr);
     live_.erase(it);
 }
 
 CUDAMemoryManager::~CUDAMemoryManager() {
-    for (auto &kv : free_list_) mllmcu_free(kv.second);
+    for (auto &fl : free_list_)
+        for (auto &kv : fl) mllmcu_free(kv.second);
     for (auto &kv : live_) mllmcu_free(kv.first);
 }
 
@@ -122,10 +125,12 @@ Op *CUDABackend::opCreate(const OpParam &op_param, string name, int threadCount)
         if (pit != probed_.end()) {
             Op *op = pit->second;
             probed_.erase(pit);
+            op->type() = optype;
             return op;
         }
     }
     Op *op = it->second->create(op_param, this, name, threadCount);
+    op->type() = optype; // tensor functions reach here through Tensor::runFunc, which does not set it; the decode-step recogniser reads it
     if (probing) probed_[name] = op;
     return op;
 }
@@ -300,7 +305,7 @@ std::vector<Tensor> CUDABackend::runForward(Module *module, std::vector<Tensor> 
     }
     std::vector<Tensor> output;
     last_forward_fused = 0;
-    if (!(outer && try_decode_plan(module, inputs, output))) output = module->Forward(inputs, args);
+    if (!(outer && try_decode_plan(module, inputs, args, output))) output = module->Forward(inputs, args);
     if (outer) {
         sync(); // the clock must not stop before the device has finished (cf. finishQueue, OpenCLBackend.cpp:1087)
         module->inference_times_.push_back((mllm_time_us() - time_start) / 1000.0F);

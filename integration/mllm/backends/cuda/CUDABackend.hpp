@@ -40,11 +40,14 @@ public:
     void alloc(void **ptr, size_t size, size_t alignment) override;
     void free(void *ptr) override;
     size_t bytes_allocated = 0, pool_hits = 0, pool_misses = 0;
+    // Weights and the decode plan's buffers are never dereferenced by host code: while this is set, blocks come from plain device
+    // memory (cudaMalloc: large pages, no unified-memory bookkeeping on the streaming path) instead of unified memory.
+    bool device_only = false;
 
 private:
     int device_;
-    std::multimap<size_t, void *> free_list_;       // size class -> free blocks (stream-ordered reuse: one stream per backend)
-    std::unordered_map<void *, size_t> live_;       // block -> its size class
+    std::multimap<size_t, void *> free_list_[2];    // [unified | device-only] size class -> free blocks (stream-ordered reuse: one stream per backend)
+    std::unordered_map<void *, std::pair<size_t, int>> live_; // block -> (size class, kind)
 };
 
 // What the decode-step fuser reads from an op it folds into a fused launch (pointers stay owned by the op).
@@ -92,6 +95,7 @@ public:
 
     bool addCreator(OpType t, Creator *c);
     void *stream() const { return stream_; }
+    CUDAMemoryManager *memory() const { return static_cast<CUDAMemoryManager *>(mem_manager_.get()); }
     void sync();
     void *workspace(size_t bytes); // scratch shared by ops (activation quantisation, split-K partials); grows monotonically
     size_t workspaceBytes() const { return ws_bytes_; }
@@ -127,7 +131,7 @@ private:
     std::vector<Op *> rec_ops_;
     bool recording_ = false;
     std::shared_ptr<DecodePlan> plan_; // shared_ptr: the type is complete only in CUDADecodePlan.cpp
-    bool try_decode_plan(Module *module, std::vector<Tensor> &inputs, std::vector<Tensor> &out);
+    bool try_decode_plan(Module *module, std::vector<Tensor> &inputs, std::vector<std::any> &args, std::vector<Tensor> &out);
 };
 
 [[noreturn]] void cuda_fail(int rc, const char *what, const char *file, int line);

@@ -1,10 +1,272 @@
 // mllm/backends/cuda/CUDADecodePlan.cpp -- the fused single-token step behind an UNCHANGED model header.
-// (first cut: recogniser not wired yet -- every forward runs op by op through runOp)
+//
+// The reference executes a decode token as ~25 runOp calls per transformer block (Layer::run -> Backend::runOp,
+// Layer.hpp:116-222); on a B200 that is ~770 launches and ~6 ms of host dispatch per token for the 7B.  The CUDA backend
+// therefore RECORDS the op sequence of the first single-token forward it sees (runOp appends every executed op), recognises the
+// LLaMA-family decoder pattern
+//     EMBEDDING, N x [RMSNORM, LINEAR q, LINEAR k, LINEAR v, ROPE q, ROPE k, KVCACHE k, KVCACHE v, F_FA2, LINEAR o, F_TTADD,
+//                     RMSNORM, LINEAR gate, SILU, LINEAR up, F_TTMUL, LINEAR down, F_TTADD], RMSNORM, LINEAR lm_head
+// (F_VIEW is metadata and ignored; this is LLaMAModel, TinyLLaMAModel and QWenForCausalLM as their headers issue them), reads
+// each op's device state through CUDAOpBase::fuseInfo, and from then on answers single-token forwards with the fused launches of
+// the decode step -- five per block, captured once in a CUDA graph with the position held in device memory -- without calling
+// Module::Forward.  The ops stay the owners of state: after every replay the RoPE counters and KV-cache lengths are advanced, so
+// op-by-op forwards (the next prefill, a chunk) and fused steps interleave freely.  Anything that does not match the pattern or
+// the fused kernels' shapes simply keeps running op by op.
 #include "CUDABackend.hpp"
+
 #include "Module.hpp"
 #include "Tensor.hpp"
+#include "backends/cpu/op/CPUKVCache.hpp"
+#include "mllmcu.h"
+
+#include <cstdlib>
+#include <iostream>
 
 namespace mllm {
-struct CUDABackend::DecodePlan {};
-bool CUDABackend::try_decode_plan(Module *, std::vector<Tensor> &, std::vector<Tensor> &) { return false; }
+
+struct CUDABackend::DecodePlan {
+    struct L {
+        CUDAFuseInfo n1, n2, q, k, v, o, gate, up, down, rope;
+        CUDAOpBase *q_rope = nullptr, *k_rope = nullptr;
+        CPUKVCache *kc = nullptr, *vc = nullptr;
+        void *kptr = nullptr, *vptr = nullptr; // cache addresses the captured graph holds
+    };
+    Module *module = nullptr;
+    int B = 0, H = 0, Hq = 0, Hkv = 0, D = 0, F = 0, V = 0, limit = 0;
+    long long kv_bstride = 0;
+    std::vector<L> layers;
+    CUDAFuseInfo embd, norm, head;
+    Tensor x, x2, qkv, ao, g, logits, ids, ctl, attn_ws;
+    size_t attn_ws_bytes = 0;
+    int dev_pos = -2, ctl_host = 0;
+    bool warmed = false, use_graph = true, use_pdl = true, unsupported = false;
+    void *graph = nullptr;
+    float *stage_ids = nullptr; // pinned
+    ~DecodePlan() {
+        if (graph) mllmcu_graph_destroy(graph);
+        if (stage_ids) mllmcu_host_free(stage_ids);
+    }
+};
+
+static bool env_on(const char *k) {
+    const char *e = getenv(k);
+    return e && e[0] && e[0] != '0';
+}
+
+struct DecodePlanBuilder {
+    // builds a plan from the recorded ops, or returns nullptr when the sequence is not the pattern above
+    static std::shared_ptr<CUDABackend::DecodePlan> build(CUDABackend *bn, Module *module, const std::vector<Op *> &rec, int B) {
+        std::vector<Op *> ops;
+        for (Op *o : rec)
+            if (o->type() != F_VIEW) ops.push_back(o);
+        static const OpType block[18] = {RMSNORM, LINEAR, LINEAR, LINEAR, ROPE, ROPE, KVCACHE, KVCACHE, F_FA2, LINEAR, F_TTADD,
+                                         RMSNORM, LINEAR, SILU, LINEAR, F_TTMUL, LINEAR, F_TTADD};
+        if (ops.size() < 3 + 18 || (ops.size() - 3) % 18 != 0) return nullptr;
+        const int nl = (int)(ops.size() - 3) / 18;
+        if (ops[0]->type() != EMBEDDING || ops[ops.size() - 2]->type() != RMSNORM || ops[ops.size() - 1]->type() != LINEAR) return nullptr;
+        for (int l = 0; l < nl; l++)
+            for (int j = 0; j < 18; j++)
+                if (ops[1 + l * 18 + j]->type() != block[j]) return nullptr;
+        auto p = std::make_shared<CUDABackend::DecodePlan>();
+        auto fi = [](Op *o, CUDAFuseInfo &f) {
+            auto *c = dynamic_cast<CUDAOpBase *>(o);
+            return c && c->fuseInfo(f);
+        };
+        if (!fi(ops[0], p->embd) || !fi(ops[ops.size() - 2], p->norm) || !fi(ops[ops.size() - 1], p->head)) return nullptr;
+        p->layers.resize(nl);
+        for (int l = 0; l < nl; l++) {
+            Op **o = &ops[1 + l * 18];
+            auto &L = p->layers[l];
+            if (!(fi(o[0], L.n1) && fi(o[1], L.q) && fi(o[2], L.k) && fi(o[3], L.v) && fi(o[4], L.rope) && fi(o[9], L.o) && fi(o[11], L.n2) &&
+                  fi(o[12], L.gate) && fi(o[14], L.up) && fi(o[16], L.down)))
+                return nullptr;
+            L.q_rope = dynamic_cast<CUDAOpBase *>(o[4]);
+            L.k_rope = dynamic_cast<CUDAOpBase *>(o[5]);
+            L.kc = dynamic_cast<CPUKVCache *>(o[6]);
+            L.vc = dynamic_cast<CPUKVCache *>(o[7]);
+            if (!L.q_rope || !L.k_rope || !L.kc || !L.vc) return nullptr;
+            L.kptr = L.kc->cache_->rawHostPtr();
+            L.vptr = L.vc->cache_->rawHostPtr();
+            for (const CUDAFuseInfo *f : {&L.q, &L.k, &L.v, &L.o, &L.gate, &L.up, &L.down})
+                if (f->wtype != MLLM_TYPE_Q4_0) return nullptr;
+            if (L.n1.unit_offset || L.n2.unit_offset) return nullptr;
+        }
+        const auto &L0 = p->layers[0];
+        Tensor &kc = *L0.kc->cache_;
+        if (kc.dtype() != MLLM_TYPE_F16 || kc.ctype() != BSHD || kc.batch() != B) return nullptr;
+        p->module = module;
+        p->B = B;
+        p->H = L0.q.in;
+        p->D = kc.dimension();
+        p->Hkv = kc.head();
+        p->Hq = L0.q.out / p->D;
+        p->F = L0.gate.out;
+        p->V = p->head.out;
+        p->limit = kc.sequence();
+        p->kv_bstride = (long long)kc.sequence() * kc.head() * kc.dimension();
+        if (p->embd.wtype != MLLM_TYPE_Q4_0 || p->head.wtype != MLLM_TYPE_Q4_0 || p->norm.unit_offset) return nullptr;
+        if (p->H % 128 || p->F % 128 || (p->D != 32 && p->D != 64 && p->D != 128) || L0.rope.rot_dim != p->D || B < 1 || B > 8) return nullptr;
+        for (auto &L : p->layers) {
+            Tensor &a = *L.kc->cache_, &b = *L.vc->cache_;
+            if (a.batch() != B || b.batch() != B || a.sequence() != p->limit || b.sequence() != p->limit || a.head() != p->Hkv || a.dimension() != p->D ||
+                L.rope.rot_dim != p->D || L.rope.sin_t != L0.rope.sin_t)
+                return nullptr;
+        }
+        auto mk = [&](Tensor &t, int rows, int cols) {
+            t.setBackend(bn);
+            t.reshape(1, 1, rows, cols);
+            t.setDtype(MLLM_TYPE_F32);
+            bn->memory()->device_only = true; // plan buffers never leave the device
+            t.alloc();
+            bn->memory()->device_only = false;
+        };
+        const int QKV = (p->Hq + 2 * p->Hkv) * p->D;
+        mk(p->x, B, p->H); mk(p->x2, B, p->H); mk(p->qkv, B, QKV); mk(p->ao, B, p->Hq * p->D); mk(p->g, B, p->F); mk(p->logits, B, p->V);
+        mk(p->ids, 1, B); mk(p->ctl, 1, 4);
+        p->attn_ws_bytes = mllmcu_decode_attn_workspace_bytes(B, p->Hq, p->D);
+        mk(p->attn_ws, 1, (int)((p->attn_ws_bytes + 3) / 4));
+        MLLMCU_CHECK(mllmcu_memset(p->attn_ws.rawHostPtr(), 0, p->attn_ws.cntSize(), bn->stream()));
+        MLLMCU_CHECK(mllmcu_memset(p->ctl.rawHostPtr(), 0, 16, bn->stream()));
+        void *hp = nullptr;
+        MLLMCU_CHECK(mllmcu_host_alloc(&hp, sizeof(float) * 8));
+        p->stage_ids = (float *)hp;
+        p->use_graph = !env_on("MLLM_CUDA_NO_GRAPH");
+        p->use_pdl = !env_on("MLLM_CUDA_NO_PDL");
+        return p;
+    }
+
+    // the kernel sequence of one token (five launches per block); false when a fused kernel refuses the shape
+    static bool issue(CUDABackend *bn, CUDABackend::DecodePlan &p, bool pdl_on) {
+        void *st = bn->stream();
+        const int B = p.B, H = p.H, D = p.D, Hq = p.Hq, Hkv = p.Hkv, F = p.F, QKV = (Hq + 2 * Hkv) * D, pdl = pdl_on ? 1 : 0;
+        int *ctl = (int *)p.ctl.rawHostPtr();
+        float *x = p.x.hostPtr<float>(), *x2 = p.x2.hostPtr<float>(), *qkv = p.qkv.hostPtr<float>(), *ao = p.ao.hostPtr<float>(), *g = p.g.hostPtr<float>();
+        auto gemv = [&](std::initializer_list<const CUDAFuseInfo *> ws, const float *in, int K, const CUDAFuseInfo *norm, int epi, const float *res,
+                        float *out, int ldy, bool late_trigger = false) -> bool {
+            mllmcu_gemv_desc d = {};
+            d.wtype = MLLM_TYPE_Q4_0;
+            for (const CUDAFuseInfo *f : ws) { d.W[d.nW] = f->weight; d.N[d.nW] = f->out; d.bias[d.nW] = f->bias; d.nW++; }
+            d.x = in; d.ldx = K; d.M = B; d.K = K;
+            if (norm) { d.norm_w = norm->norm_w; d.eps = norm->eps; d.norm_reps = 1; d.norm_rep_stride = K; }
+            d.epilogue = epi; d.residual = res; d.ldr = ldy; d.y = out; d.ldy = ldy; d.pdl = (pdl && late_trigger) ? 2 : pdl;
+            d.x_reps = 1; d.y_reps = 1;
+            const int rc = mllmcu_gemv_fused_ex(&d, st);
+            if (rc == -2) return false;
+            MLLMCU_CHECK(rc);
+            return true;
+        };
+        MLLMCU_CHECK(mllmcu_decode_embed(p.embd.weight, p.ids.hostPtr<float>(), x, B, H, ctl, st));
+        for (size_t li = 0; li < p.layers.size(); li++) {
+            auto &l = p.layers[li];
+            // layer 0's projection releases its dependents only after its own wait: every later kernel then starts with the embedding
+            // kernel (which bumps ctl[0]) complete and may read the position and its K/V rows ahead of its own wait
+            if (!gemv({&l.q, &l.k, &l.v}, x, H, &l.n1, 0, nullptr, qkv, QKV, li == 0)) return false;
+            MLLMCU_CHECK(mllmcu_decode_attn_rope(l.rope.rope_type, qkv, QKV, l.kptr, l.vptr, ao, Hq * D, ctl, B, Hq,
+                                                 Hkv, D, l.rope.sin_t, l.rope.cos_t, l.rope.rot_dim, p.kv_bstride, p.limit, p.attn_ws.rawHostPtr(),
+                                                 p.attn_ws_bytes, pdl ? 2 : 0, st));
+            if (!gemv({&l.o}, ao, Hq * D, nullptr, 1, x, x2, H)) return false;
+            if (!gemv({&l.gate, &l.up}, x2, H, &l.n2, 2, nullptr, g, F)) return false;
+            if (!gemv({&l.down}, g, F, nullptr, 1, x2, x, H)) return false;
+        }
+        return gemv({&p.head}, x, H, &p.norm, 0, nullptr, p.logits.hostPtr<float>(), p.V);
+    }
+};
+
+// Called by runForward for every outermost forward.  Returns true when `out` holds the logits of a fused step.
+bool CUDABackend::try_decode_plan(Module *module, std::vector<Tensor> &inputs, std::vector<std::any> &args, std::vector<Tensor> &out) {
+    if (!fused_decode || inputs.size() != 1) return false;
+    Tensor &in = inputs[0];
+    const int B = in.batch();
+    if (in.sequence() != 1 || in.head() != 1 || in.dimension() != 1 || in.dtype() != MLLM_TYPE_F32 || B < 1 || B > 8) return false;
+    if (plan_ && (plan_->module != module || plan_->B != B)) { sync(); plan_.reset(); }
+    if (plan_ && plan_->unsupported) return false;
+    if (!plan_) {
+        // record this forward: it runs op by op (and is the result of this call); the plan, if the sequence matches, serves the next ones
+        recording_ = true;
+        rec_ops_.clear();
+        std::vector<Tensor> res;
+        try { res = module->Forward(inputs, args); } catch (...) { recording_ = false; throw; }
+        recording_ = false;
+        plan_ = DecodePlanBuilder::build(this, module, rec_ops_, B);
+        if (!plan_) { plan_ = std::make_shared<DecodePlan>(); plan_->module = module; plan_->B = B; plan_->unsupported = true; }
+        rec_ops_.clear();
+        out = res;
+        return true;
+    }
+    DecodePlan &p = *plan_;
+    // per-step state: every RoPE counter and cache length must agree, and there must be room
+    const int len = p.layers[0].kc->getCacheSeqLen();
+    for (auto &l : p.layers) {
+        if (l.kc->getCacheSeqLen() != len || l.vc->getCacheSeqLen() != len) return false;
+        if (l.kc->cache_->rawHostPtr() != l.kptr || l.vc->cache_->rawHostPtr() != l.vptr) { // the cache was re-made (batch change): record again
+            sync();
+            plan_.reset();
+            return false;
+        }
+    }
+    if (len + 1 > p.limit) { // CPUKVCache.cpp:121-126
+        std::cerr << "\n[ERROR]: Current tokens exceed cache limit: " << len + 1 << ">" << p.limit << ";"
+                  << "\n         Please set args `--limits` >" << p.limit << std::endl;
+        throw std::runtime_error("[mllm-cuda] KV cache limit exceeded");
+    }
+    if (len + 1 > p.layers[0].rope.pos_max) throw std::runtime_error("[mllm-cuda] RoPE: position exceeds max_position_embeddings");
+    dropQuantTag();
+    // token ids: the demos build the input on the CPU backend (host memory); a CUDA-backend tensor is copied device to device
+    if (in.backend()->type() == MLLM_CPU) {
+        for (int b = 0; b < B; b++) p.stage_ids[b] = in.dataAt<float>(b, 0, 0, 0);
+        MLLMCU_CHECK(mllmcu_memcpy_h2d(p.ids.rawHostPtr(), p.stage_ids, sizeof(float) * B, stream_));
+    } else {
+        MLLMCU_CHECK(mllmcu_memcpy_d2d(p.ids.rawHostPtr(), in.ptrAt<float>(0, 0, 0, 0), sizeof(float) * B, stream_));
+    }
+    if (p.dev_pos != len - 1) { // the embedding kernel pre-increments ctl[0]
+        p.ctl_host = len - 1;
+        MLLMCU_CHECK(mllmcu_memcpy_h2d(p.ctl.rawHostPtr(), &p.ctl_host, sizeof(int), stream_));
+        p.dev_pos = len - 1;
+    }
+    bool ran = false;
+    if (p.use_graph && !p.graph && p.warmed) { // second fused step: every kernel attribute is configured, capture the sequence
+        for (int attempt = 0; attempt < 2 && !p.graph; attempt++) {
+            MLLMCU_CHECK(mllmcu_graph_begin_capture(stream_));
+            bool ok = false;
+            try { ok = DecodePlanBuilder::issue(this, p, p.use_pdl); } catch (...) { mllmcu_graph_abort_capture(stream_); throw; }
+            void *ge = nullptr;
+            if (!ok) { mllmcu_graph_abort_capture(stream_); break; }
+            if (mllmcu_graph_end_capture(stream_, &ge) == 0) p.graph = ge;
+            else if (p.use_pdl) p.use_pdl = false;
+            else { p.use_graph = false; break; }
+        }
+    }
+    if (p.graph) {
+        MLLMCU_CHECK(mllmcu_graph_launch(p.graph, stream_));
+        ran = true;
+    } else {
+        ran = DecodePlanBuilder::issue(this, p, p.use_pdl);
+        p.warmed = true;
+    }
+    if (!ran) { // a kernel refused the shape mid-step (nothing stateful ran before it): this model stays op by op
+        p.unsupported = true;
+        p.dev_pos = -2;
+        return false;
+    }
+    p.dev_pos = len;
+    // the ops own the state: advance RoPE positions and cache lengths by one token
+    static Tensor one_token(1, 1, 1, 1, Backend::global_backends[MLLM_CPU].get(), false);
+    auto one = std::shared_ptr<Tensor>(&one_token, [](Tensor *) {});
+    for (auto &l : p.layers) {
+        l.q_rope->advance(1);
+        l.k_rope->advance(1);
+        l.kc->execute({one}, {}); // n_rep == 1: only cache_seq_len_ += inputs[0]->sequence() (CPUKVCache.cpp:148-151)
+        l.vc->execute({one}, {});
+    }
+    kernel_launches += 2 + 5 * (long long)p.layers.size();
+    last_forward_fused = 1;
+    // hand out a fresh tensor (callers may migrate it with .cpu(), which would take the plan's buffer with it)
+    Tensor lg(B, 1, 1, p.V, this, true);
+    lg.setName("out-lm_head-fused");
+    lg.setModule(module);
+    MLLMCU_CHECK(mllmcu_memcpy_d2d(lg.rawHostPtr(), p.logits.rawHostPtr(), sizeof(float) * (size_t)B * p.V, stream_));
+    out = {lg};
+    return true;
+}
+
 } // namespace mllm

@@ -51,7 +51,9 @@ static void load_param(Tensor &t, Backend *bn, const string &name, int rows, int
     t.reshape(1, 1, rows, cols);
     const DataType dt = loader.getDataType(name);
     t.setDtype(dt != MLLM_TYPE_COUNT ? dt : dflt);
+    cb(bn)->memory()->device_only = true; // parameters are read by kernels only
     t.alloc();
+    cb(bn)->memory()->device_only = false;
     if (dt != MLLM_TYPE_COUNT) loader.load(&t);
 }
 
@@ -219,7 +221,9 @@ private:
             dst.setBackend(backend_);
             dst.reshape(1, 1, pos_max_, dim);
             dst.setDtype(MLLM_TYPE_F32);
+            cb(backend_)->memory()->device_only = true;
             dst.alloc();
+            cb(backend_)->memory()->device_only = false;
             MLLMCU_CHECK(mllmcu_memcpy_h2d(dst.rawHostPtr(), src.data(), src.size() * sizeof(float), cb(backend_)->stream()));
             cb(backend_)->sync();
         };

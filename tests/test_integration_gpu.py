@@ -42,6 +42,11 @@ def test_unchanged_llama_graph_same_tokens_on_cpu_and_cuda_backends(have_bin, tm
     gpu = run(4, "llama-generic", path, 16, 48, batch=B, limit=128, dims=dims)
     assert cpu["tokens"] == gpu["tokens"]
     assert all(len(set(r)) > 4 for r in gpu["tokens"])
+    # the first single-token forward is recorded op by op, every later one is answered by the fused, graph-replayed step ...
+    assert gpu["fused_steps"] == 48 - 2
+    # ... and the op-by-op path (what any graph the recogniser does not know gets) gives the same tokens
+    eager = run(4, "llama-generic", path, 16, 48, batch=B, limit=128, dims=dims, env={"MLLM_CUDA_EAGER_DECODE": "1"})
+    assert eager["fused_steps"] == 0 and eager["tokens"] == cpu["tokens"]
 
 
 def test_tinyllama_graph_on_cuda_backend(have_bin):
@@ -54,4 +59,28 @@ def test_tinyllama_graph_on_cuda_backend(have_bin):
     cpu = run(0, "tinyllama-1.1b", path, 32, 8, limit=512)
     gpu = run(4, "tinyllama-1.1b", path, 32, 8, limit=512)
     assert cpu["tokens"][0][:4] == gpu["tokens"][0][:4]
+    assert gpu["fused_steps"] == 6
     assert gpu["decode_ms_per_step"] < cpu["decode_ms_per_step"]
+
+
+def test_llama2_7b_demo_rate_through_the_unchanged_header(have_bin):
+    """BASELINE configs[1]: LLaMAModel from models/llama/modeling_llama.hpp on MLLM_CUDA.  The literal demo loop (logits to the host
+    every step, host argmax, token back) must run the fused step and land within 10 % + 0.1 ms of the device-resident request's
+    decode time per token (what bench.py's e2e measures)."""
+    import torch  # noqa: F401
+    from mllm_b200 import backend
+    cfg = mf.config("llama2-7b", cache_limit=1024)
+    path = "/tmp/mllm_test_llama2-7b_q4_0.mllm"
+    mf.write_random_model_torch(cfg, path, device="cuda", seed=1234)
+    gpu = run(4, "llama2-7b", path, 512, 64, limit=1024)
+    assert gpu["fused_steps"] == 62
+    m = backend.LlamaModel(cfg).load(path)
+    ids = np.random.default_rng(1).integers(0, cfg["vocab"], (1, 512)).astype(np.float32)
+    m.request_device(ids, 64)
+    m.clear_kvcache()
+    _, dec_ms, _ = m.request_device(ids, 64)
+    m.close()
+    per_tok = dec_ms / 63
+    print("7B decode ms/token: demo loop mean", gpu["decode_ms_per_step"], "median after the recorded / captured steps", gpu["decode_ms_median"],
+          "device-resident request", per_tok, "prefill ms", gpu["prefill_ms"])
+    assert gpu["decode_ms_median"] <= 1.10 * per_tok + 0.1
