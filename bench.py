@@ -166,7 +166,7 @@ def job_tokens_per_s(tokens_per_replica, world, ms):
 
 
 # ----------------------------------------------------------------------------- GPU arm
-def gemv_roofline(cfg, peaks):
+def gemv_roofline(cfg, peaks, M=1):
     """The dominant kernel of the request is the decode Linear, k_gemv_tma (fused activation quantise + Q4_0 GEMV).
     Every Linear launch of one decode step (qkv, o, gate|up, down per block + lm_head) is timed live: the launches are
     captured in a CUDA graph (device time, not ctypes dispatch), weights rotate over buffers larger than L2 (cold HBM
@@ -184,9 +184,9 @@ def gemv_roofline(cfg, peaks):
         wbytes = sum(Ns) * (K // 32) * 18
         nbuf = max(2, int(200e6 // wbytes) + 1)
         bufs = [[torch.randint(0, 255, (n, K // 32 * 18), dtype=torch.uint8, device="cuda") for n in Ns] for _ in range(nbuf)]
-        x = torch.randn((1, K), device="cuda")
+        x = torch.randn((M, K), device="cuda")
         nw = torch.ones(K, device="cuda") if norm else None
-        res = torch.randn((1, Ns[0]), device="cuda") if epi == 1 else None
+        res = torch.randn((M, Ns[0]), device="cuda") if epi == 1 else None
 
         def call(ws):
             capi.gemv_fused(ws, x, norm_w=nw, epilogue=epi, residual=res, pdl=True)
@@ -220,7 +220,8 @@ def gemv_roofline(cfg, peaks):
             # profiles/r01_ncu_gemv_gateup.txt: 50.80 MB read + 3.6 KB written against 50.72 MB algorithmic -- no re-reads
             "traffic": 50802688, "traffic_source": "profiles/r01_ncu_gemv_gateup.txt (one ncu --set full capture, NOT measured by this run)",
             "traffic_of": "one gate|up launch (k_gemv_tma<1,1,2,1>): dram read 50.799 MB + write 0.004 MB vs 50.725 MB algorithmic",
-            "kernel": "k_gemv_tma (decode Linear: fused RMSNorm/Q8_0 prologue + Q4_0 GEMV), launch-weighted over one decode step",
+            "kernel": ("k_gemv_tma (decode Linear: fused RMSNorm/Q8_0 prologue + Q4_0 GEMV)" if M < 3 else
+                       f"k_gemv_mma (batched decode Linear, {M} rows: mma.sync.m16n8k32.u8.s8 over TMA-staged Q4_0 tiles) + k_act_quant_mma") + ", launch-weighted over one decode step",
             "peak_source": "measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in peaks else "fallback 6650",
             "per_shape": per}
 
@@ -327,6 +328,105 @@ def gpu_arm(args, rank, world, local_rank):
     print(json.dumps(out), flush=True)
 
 
+def gpu_arm_c5(args, rank, world, local_rank):
+    """BASELINE configs[4]: Qwen1.5-1.8B Q4_0 batched greedy decode, the demo_qwen_batch shape (examples/demo_qwen_batch.cpp:61-68:
+    Module::generate over a batch of prompts, 200 new tokens) with B requests of 32 prompt tokens PER GPU; requests are sharded
+    data-parallel, one replica per GPU, no collective (weak scaling).  A step = one batch request (prefill + 200 greedy steps);
+    value = decode tokens/s of the whole job (B x 200 x N / slowest rank's decode time), device-timed."""
+    import torch
+    torch.cuda.set_device(local_rank)
+    from mllm_b200 import backend, build
+    if rank == 0:
+        build.build_all()
+    if world > 1:
+        import torch.distributed as dist
+        dist.barrier()
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    B, S, ND = args.batch, 32, 200
+    cfg = mf.config("qwen1.5-1.8b", cache_limit=S + ND + 8)
+    path = os.environ.get("MLLM_BENCH_MODEL_C5", "/tmp/mllm_bench_qwen1.5-1.8b_q4_0.mllm")
+    if rank == 0:
+        make_model_file(cfg, path, device=f"cuda:{local_rank}")
+    if world > 1:
+        import torch.distributed as dist
+        dist.barrier()
+    model = backend.LlamaModel(cfg, device=local_rank).load(path)
+    ids = np.random.default_rng(1234 + rank).integers(0, cfg["vocab"], (B, S)).astype(np.float32)  # every rank serves its own requests
+
+    def request():
+        model.clear_kvcache()
+        return model.request_device(ids, ND)
+
+    for _ in range(args.warmup):
+        request()
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    if world > 1:
+        import torch.distributed as dist
+        dist.barrier()
+    torch.cuda.synchronize()
+    l0 = backend.kernel_launches()
+    tp, td = [], []
+    for _ in range(args.steps):
+        a, b, _ = request()
+        tp.append(a)
+        td.append(b)
+    torch.cuda.synchronize()
+    launches = backend.kernel_launches() - l0
+    e2e_ms = []
+    for _ in range(args.steps):
+        model.clear_kvcache()
+        w0 = time.perf_counter()
+        model.generate(ids, ND)
+        e2e_ms.append((time.perf_counter() - w0) * 1e3)
+    clocks = sampler.stop()
+    dec_ms, pre_ms, e2e_mean = max_over_ranks([float(np.sum(td)), float(np.sum(tp)), float(np.mean(e2e_ms))], world, "cuda")
+    if rank != 0:
+        return
+    step_ms = dec_ms / args.steps / (ND - 1)
+    wbytes = mf.decode_weight_bytes(cfg)
+    kv = 2 * cfg["layers"] * (S + ND / 2) * cfg["kv_heads"] * cfg["head_dim"] * 2 * B
+    peak = peaks.get("hbm_gbs", 6650.0)
+    roof = gemv_roofline(cfg, peaks, M=B)
+    roof["traffic"] = None
+    roof.pop("traffic_source", None)
+    roof.pop("traffic_of", None)
+    out = {
+        "metric": f"qwen1.5_1.8b_q4_0_batch{B}_decode_tok_s", "value": round(B * (ND - 1) * world / (dec_ms / args.steps) * 1e3, 1), "unit": "tok/s",
+        "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": round((dec_ms + pre_ms) / args.steps, 3), "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "int8 block dot (Q4_0 x Q8_0) + fp32 accumulate, fp16 KV", "data": "synthetic",
+        "config": {"workload": f"Qwen1.5-1.8B Q4_0 (BASELINE configs[4], demo_qwen_batch shape): {B} requests per GPU, prompt {S} + {ND} greedy tokens, "
+                               "random-init .mllm through ParamLoader; requests sharded data-parallel, one replica per GPU",
+                   "l2": "weights 0.86 GB per decode step >> 126 MB L2 (inputs larger than L2)", "parallelism": f"dp{world} replicas, no collective"},
+        "decode_step": {"ms": round(step_ms, 4), "algorithmic_GB": round((wbytes + kv) / 1e9, 4), "GBs": round((wbytes + kv) / (step_ms * 1e-3) / 1e9, 1),
+                        "frac_of_hbm_peak": round((wbytes + kv) / (step_ms * 1e-3) / 1e9 / peak, 4)},
+        "prefill": {"ms": round(pre_ms / args.steps, 3), "tokens": B * S},
+        "e2e": {"value": round(B * ND * world / e2e_mean * 1e3, 1), "unit": "tok/s (prefill + decode wall clock, all generated tokens)", "h2d_bytes_per_step": B * S * 4,
+                "d2h_bytes_per_step": B * ND * 4 + (S + ND + 9) * B * 4, "ms_per_step": round(e2e_mean, 2)},
+        "decode_mode": model.decode_mode(), "gpu_launches": int(launches), "clocks": clocks, "roofline": roof,
+    }
+    if not args.no_cpu:
+        try:  # the reference graph (QWenForCausalLM on MLLM_CPU) on a bounded sample: 3 requests (the demo's batch), 32 + 8 tokens
+            from oracle import pyoracle as po
+            n = _host_cpus()
+            th = max(1, n // 2)
+            g = po.RefGraph(dict(cfg, cache_limit=64), path, threads=th)
+            cid = ids[:3]
+            t0 = time.perf_counter()
+            g.generate(cid, 8)
+            dt = time.perf_counter() - t0
+            g.close()
+            out["cpu_baseline"] = {"value": round(3 * 8 / dt, 2), "unit": "tok/s", "cores": th, "host_cpus": n, "kind": "reference",
+                                   "sample": "reference QWenForCausalLM graph on CPUBackend (oracle/_ref/libmllm_cpu_ref.so), Module::generate on 3 requests x (32 prompt + 8 new tokens), wall clock incl. prefill"}
+        except Exception as e:
+            out["cpu_baseline"] = {"error": repr(e)[:300]}
+    print(json.dumps(out), flush=True)
+
+
 def reference_arm(args, rank, world):
     if rank != 0:
         return
@@ -356,6 +456,9 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--config", default=os.environ.get("MLLM_BENCH_CONFIG", "c2"), choices=["c2", "c5"],
+                    help="c2: LLaMA-2-7B single request (the headline metric, default); c5: Qwen1.5-1.8B batched decode, data-parallel")
+    ap.add_argument("--batch", type=int, default=int(os.environ.get("MLLM_BENCH_BATCH", "64")), help="c5: requests per GPU")
     ap.add_argument("--cpu-prefill", type=int, default=0, help="CPU sample: prompt tokens (0 = 512 when steps <= 2, else 128 / 64 so the run stays within minutes)")
     ap.add_argument("--cpu-decode", type=int, default=0, help="CPU sample: decode steps (0 = 32 / 16 / 8 by the same rule)")
     args = ap.parse_args()
@@ -369,7 +472,10 @@ def main():
         import torch.distributed as dist
         torch.cuda.set_device(local_rank)
         dist.init_process_group("nccl")
-    gpu_arm(args, rank, world, local_rank)
+    if args.config == "c5":
+        gpu_arm_c5(args, rank, world, local_rank)
+    else:
+        gpu_arm(args, rank, world, local_rank)
     if world > 1:
         import torch.distributed as dist
         dist.barrier()

@@ -176,6 +176,10 @@ typedef struct mllmcu_gemv_desc {
     size_t pf_bytes[8];
 } mllmcu_gemv_desc;
 int mllmcu_gemv_fused_ex(const mllmcu_gemv_desc *d, void *stream);
+/* Largest M mllmcu_gemv_fused / _ex accepts: 64 (3..64 rows run on the tensor cores, gemv_mma.cu: one mma.sync.m16n8k32.u8.s8 per
+ * 16 weight rows x 8 batch rows x Q block, exact integer block sums -- the demo_qwen_batch shape, examples/demo_qwen_batch.cpp:61-68),
+ * or 8 when MLLMCU_GEMV_MMA=0 keeps the CUDA-core kernel. */
+int mllmcu_gemv_fused_max_rows(void);
 
 /* development aid (MLLMCU_GEMV_PROF=1): 64 %globaltimer slots {entry, dependency wait passed, prologue done, exit, 4 spare, then per warp w: [8+2w] activation
  * loads landed, [9+2w] quantisation done} of CTA 0 for the

@@ -165,14 +165,19 @@ public:
         partial_ = getp(p, "partial_rotary_factor", 1.0f);
         pos_max_ = (int)getp(p, "max_position_embeddings", 16384);
         if (pose_type_ != LLAMAROPE && pose_type_ != HFHUBROPE) throw std::runtime_error("[mllm-cuda] RoPE " + name + ": pose_type " + std::to_string(pose_type_) + " has no CUDA kernel");
-        if ((int)getp(p, "rope_type", 0) != 0) throw std::runtime_error("[mllm-cuda] RoPE " + name + ": rope scaling has no CUDA kernel yet");
+        theta_type_ = (int)getp(p, "rope_type", 0); // RoPEThetaType: 0 DEFAULT, 1 LLAMA3 (Types.hpp:180-183)
+        if (theta_type_ != 0 && theta_type_ != 1) throw std::runtime_error("[mllm-cuda] RoPE " + name + ": rope_type " + std::to_string(theta_type_) + " has no CUDA path");
+        if (theta_type_ == 1) {
+            l3_factor_ = p.at("factor"); l3_low_ = p.at("low_freq_factor"); l3_high_ = p.at("high_freq_factor");
+            l3_old_ctx_ = p.at("original_max_position_embeddings");
+        }
     }
     ErrorCode reshape(vector<shared_ptr<Tensor>> in, vector<shared_ptr<Tensor>> out) override {
         out[0]->reshape(in[0]->batch(), in[0]->head(), in[0]->sequence(), in[0]->dimension());
         ishape_ = (int)(in[0]->dimension() * partial_);
         if (!tab_ || tab_dim_ != ishape_) {
-            char key[160];
-            snprintf(key, sizeof key, "%p-%d-%d-%.9g-%d", (void *)backend_, pose_type_, ishape_, rope_theta_, pos_max_);
+            char key[256];
+            snprintf(key, sizeof key, "%p-%d-%d-%.9g-%d-%d-%g-%g-%g-%g", (void *)backend_, pose_type_, ishape_, rope_theta_, pos_max_, theta_type_, l3_factor_, l3_low_, l3_high_, l3_old_ctx_);
             auto it = g_rope_tables.find(key);
             if (it == g_rope_tables.end()) it = g_rope_tables.emplace(key, build()).first;
             tab_ = it->second;
@@ -207,6 +212,18 @@ private:
         const int dim = ishape_;
         vector<float> theta(dim / 2), s((size_t)pos_max_ * dim), c((size_t)pos_max_ * dim);
         for (int i = 0; i < dim / 2; i++) theta[i] = (float)(1.0 / pow((double)rope_theta_, 2.0 * i / dim));
+        if (theta_type_ == 1) { // _compute_llama3_theta (op/CPURoPE.cpp:34-72), statement for statement in float
+            const float low_freq_wavelen = l3_old_ctx_ / l3_low_, high_freq_wavelen = l3_old_ctx_ / l3_high_;
+            for (int i = 0; i < dim / 2; i++) {
+                const float wavelen = 2 * M_PI / theta[i];
+                if (wavelen > low_freq_wavelen) {
+                    theta[i] /= l3_factor_;
+                } else if (wavelen >= high_freq_wavelen && wavelen <= low_freq_wavelen) {
+                    const float smooth_factor = (l3_old_ctx_ / wavelen - l3_low_) / (l3_high_ - l3_low_);
+                    theta[i] = (1 - smooth_factor) * (theta[i] / l3_factor_) + smooth_factor * theta[i];
+                }
+            }
+        }
         for (int p = 0; p < pos_max_; p++)
             for (int i = 0; i < dim / 2; i++) {
                 const float ang = p * theta[i];
@@ -233,6 +250,8 @@ private:
     }
     int pose_type_, pos_max_, ishape_ = 0, h_cnt_ = 0, tab_dim_ = -1;
     float rope_theta_, partial_;
+    int theta_type_ = 0;
+    float l3_factor_ = 8.f, l3_low_ = 1.f, l3_high_ = 4.f, l3_old_ctx_ = 8192.f;
     shared_ptr<RopeTables> tab_;
 };
 

@@ -55,6 +55,7 @@ SYMBOLS = {
     "mllmcu_linear_static_ws": (_i, [_i, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _vp]),
     "mllmcu_gemv_fused": (_i, [_i, _vp, _vp, _vp, _i, _vp, _i, _i, _i, _vp, _f, _i, _vp, _i, _vp, _i, _i, _i, _vp]),
     "mllmcu_gemv_fused_ex": (_i, [_vp, _vp]),
+    "mllmcu_gemv_fused_max_rows": (_i, []),
     "mllmcu_gemv_prof_read": (_i, [_vp, _i]),
     "mllmcu_decode_attn_prof_read": (_i, [_vp, _i]),
     "mllmcu_selftest_div": (_i, [C.c_uint32, C.c_uint32, _vp, _vp]),

@@ -220,7 +220,7 @@ bool LlamaModel::decode_plan_usable(int B) {
         if (p->kquant && (no_kq_plan || cfg_.hidden % 256 || cfg_.ffn % 256)) ok = false;
         // the fused GEMV holds at most 8 activation rows: 9-32 rows run it in chunks of 8 (later chunks read the layer's weights from L2),
         // larger batches take the op-level kernels (tcgen05 / dp4a Linear)
-        if (B > 32) p->kquant = true;
+        if (B > 32 && mllmcu_gemv_fused_max_rows() < B) p->kquant = true;
         if (!ok) return false; // caches not allocated yet (no prefill so far) or a dtype outside the fused kernels
         CUDABackend *bn = st_.backend;
         const int QKV = (cfg_.heads + 2 * cfg_.kv_heads) * D;
@@ -433,6 +433,20 @@ bool LlamaModel::issue_step(DecodePlan &p, bool pick, bool pdl_on) {
             }
             return true;
         }
+        if (B > 8 && B <= mllmcu_gemv_fused_max_rows()) { // up to 64 rows in ONE launch on the tensor cores (gemv_mma.cu)
+            mllmcu_gemv_desc c = {};
+            c.wtype = MLLM_TYPE_Q4_0;
+            for (const FuseInfo *f : ws) { c.W[c.nW] = f->weight; c.N[c.nW] = f->out; c.bias[c.nW] = f->bias; c.nW++; }
+            c.x = in; c.ldx = K; c.M = B; c.K = K;
+            if (norm) { c.norm_w = p.norm_rep.devPtr<float>() + (size_t)norm_idx * H; c.eps = norm->eps; c.norm_reps = 1; c.norm_rep_stride = H; }
+            c.epilogue = epi; c.residual = res; c.ldr = ldr; c.y = out; c.ldy = ldy;
+            c.pdl = (pdl && late_trigger) ? 2 : pdl;
+            c.x_reps = 1; c.y_reps = 1;
+            const int rc = mllmcu_gemv_fused_ex(&c, st);
+            if (rc == 0) { launch_no++; return true; }
+            if (rc != -2) MLLMCU_CHECK(rc);
+        }
+        if (B > 32) return false;
         if (B > 8) { // chunks of 8 rows through the same fused kernel
             launch_no++;
             for (int m0 = 0; m0 < B; m0 += 8) {

@@ -243,8 +243,17 @@ static int launch_gemv(int M, const uint8_t *W, const int8_t *xq, const float *x
     return 0;
 }
 
+int launch_gemv_mma(const mllmcu_gemv_desc &D, void *stream); // gemv_mma.cu
+bool gemv_mma_supported(int wtype, int M, int K, const int *Ns, int nW, const void *const *W);
+static bool linear_mma_enabled() {
+    static int on = -1;
+    if (on < 0) { const char *e = getenv("MLLMCU_GEMV_MMA"); on = (e && e[0] == '0') ? 0 : 1; }
+    return on == 1;
+}
+
 MLLMCU_API int mllmcu_linear_quant_kind(int wtype, int M, int N, int K, const void *W) {
     if (wtype != 2 && wtype != 8) return 0; // k-quants keep their own Q8_K image
+    if (wtype == 2 && M >= 3 && M <= 64 && linear_mma_enabled() && gemv_mma_supported(wtype, M, K, &N, 1, &W)) return 0; // own image, not in ws
     return (gemm_tc_supported(wtype, M, N, K) && !((uintptr_t)W & 15)) ? gemm_tc_quant_kind() : 3; // 3: split Q8_0 (GEMV / dp4a / scaled tcgen05)
 }
 
@@ -262,6 +271,14 @@ MLLMCU_API int mllmcu_linear_ex(int wtype, const void *W, const float *x, const 
     if (ws == nullptr || ws_bytes < mllmcu_linear_workspace_bytes(M, K)) return -3;
     cudaStream_t st = (cudaStream_t)stream;
     if (wtype == 12 || wtype == 14) return launch_linear_kq(wtype, W, x, bias, y, M, N, K, ldx, ldy, out_f16, ws, st);
+    // 3..64 rows of Q4_0 (batched decode, short prompts): the tensor-core GEMV (gemv_mma.cu), which keeps its own activation image
+    if (wtype == 2 && M >= 3 && M <= 64 && linear_mma_enabled()) {
+        mllmcu_gemv_desc d = {};
+        d.wtype = 2; d.nW = 1; d.W[0] = W; d.N[0] = N; d.bias[0] = bias; d.x = x; d.ldx = ldx; d.M = M; d.K = K;
+        d.y = y; d.ldy = ldy; d.out_f16 = out_f16; d.x_reps = 1; d.y_reps = 1;
+        const int rc = launch_gemv_mma(d, stream);
+        if (rc != -2) return rc;
+    }
     if (gemm_tc_supported(wtype, M, N, K) && !((uintptr_t)W & 15) && !((uintptr_t)x & 15) && !(ldx & 3)) // 16-byte loads of the activation rows
         return launch_gemm_q4_0_tc(W, x, ldx, bias, y, M, N, K, ldy, out_f16, ws, flags & 1, st);
     int8_t *xq = (int8_t *)ws;

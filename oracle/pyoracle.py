@@ -498,6 +498,13 @@ class RefGraph:
                 family = "qwen-generic" if (cfg["qkv_bias"] or abs(cfg["rms_eps"] - 1e-6) > 1e-12) else "llama-generic"
         dims = np.array([cfg["vocab"], cfg["hidden"], cfg["heads"], cfg["kv_heads"], cfg["ffn"], cfg["layers"], cfg.get("pos_max", cfg["cache_limit"])], dtype=np.int32)
         self.vocab = cfg["vocab"]
+        # CPURoPE keeps its sin/cos tables in process-global statics and rebuilds them only when the rotated width grows or the pose
+        # type changes (op/CPURoPE.cpp:13-18,207-224: one model per process).  A graph made after other RoPE users of this process
+        # would silently rotate with THEIR tables: flip the pose type with a throw-away op so this model builds its own.
+        other = 2 if cfg["rope_type"] == 4 else 4
+        dummy = RefOp({"type": 8, "pose_type": other, "rope_theta": 10000.0, "max_position_embeddings": 4}, "dummy", None)
+        dummy.run([(np.zeros((1, 1, 1, 8), dtype=np.float32), (1, 1, 1, 8), F32, BSHD)])
+        dummy.close()
         self.h = C.c_void_p(self.L.cpuref_model_create(family.encode(), cfg["cache_limit"], cfg["rope_type"], _p(dims), cfg["rope_theta"], cfg["rms_eps"],
                                                        threads or (os.cpu_count() or 1)))
         if not self.h:

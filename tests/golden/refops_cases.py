@@ -44,6 +44,11 @@ def cases(P):
     xr = rng.standard_normal((1, 4, 2, 64)).astype(np.float32)
     c["rope_hf_partial"] = dict(params={"type": OP["ROPE"], "pose_type": 4, "rope_theta": 10000.0, "max_position_embeddings": 32, "partial_rotary_factor": 0.5},
                                 weights=None, inputs=[(xr, (1, 2, 4, 64), F32, BSHD)])
+    xr = rng.standard_normal((1, 6, 2, 128)).astype(np.float32)
+    # LLaMA-3 frequency scaling (RoPEThetaType LLAMA3 = 1, op/CPURoPE.cpp:34-72); small original context so all three branches occur
+    c["rope_hf_llama3"] = dict(params={"type": OP["ROPE"], "pose_type": 4, "rope_theta": 500000.0, "max_position_embeddings": 64, "rope_type": 1, "factor": 8.0,
+                                       "low_freq_factor": 1.0, "high_freq_factor": 4.0, "original_max_position_embeddings": 64.0},
+                               weights=None, inputs=[(xr, (1, 2, 6, 128), F32, BSHD)], calls=2)
     S, H, D = 11, 2, 128
     pos = np.stack([np.arange(S) + 3, 2 * np.arange(S), 3 * np.arange(S) + 1]).astype(np.float32)
     params = {"type": OP["MULTIMODALROPE"], "rope_theta": 1000000.0, "max_position_embeddings": 1024}
@@ -117,6 +122,8 @@ def run_port(P, name, case):
         return [P.only.rmsnorm(x.reshape(-1, x.shape[-1]), w[".weight"][0], pr["epsilon"], bool(pr.get("add_unit_offset", 0))).reshape(x.shape)]
     if name.startswith("layernorm"):
         return [P.only.layernorm(x.reshape(-1, x.shape[-1]), w[".weight"][0], w[".bias"][0] if ".bias" in w else None, pr["epsilon"]).reshape(x.shape)]
+    if name == "rope_hf_llama3":
+        return None  # the scaled-theta table has no C restatement: the CUDA op is checked against this golden directly (GPU tests)
     if name.startswith("rope_"):
         B, S, H, D = x.shape
         rot = int(D * pr.get("partial_rotary_factor", 1.0))

@@ -463,9 +463,11 @@ def test_c_abi_rejects_bad_arguments(cu):
     assert L.mllmcu_flash_attn_f16kv(p(z), p(z), p(z), p(z), 1, 8, 4, 4, 4, 64, 1, 1024, None, 0, st) == -1
     assert L.mllmcu_flash_attn_f16kv(p(z), p(z), p(z), p(z), 1, 4, 4, 6, 4, 64, 1, 1024, None, 0, st) == -1
     assert L.mllmcu_flash_attn_f16kv(p(z), p(z), p(z), p(z), 1, 4, 4, 4, 4, 48, 1, 1024, None, 0, st) == -2
-    # fused decode Linear: batch above 8, K not a multiple of 128
+    # fused decode Linear: batch above 64 (above 8 when N % 16 != 0), K not a multiple of 128
     with pytest.raises(cu.MllmcuError):
-        cu.gemv_fused([torch.zeros((64, 144), dtype=torch.uint8, device="cuda")], torch.zeros((9, 256), device="cuda"))
+        cu.gemv_fused([torch.zeros((64, 144), dtype=torch.uint8, device="cuda")], torch.zeros((65, 256), device="cuda"))
+    with pytest.raises(cu.MllmcuError):
+        cu.gemv_fused([torch.zeros((72, 144), dtype=torch.uint8, device="cuda")], torch.zeros((9, 256), device="cuda"))  # 9 rows need N % 16 == 0
     torch.cuda.synchronize()  # nothing was launched, nothing is pending
 
 
@@ -498,3 +500,50 @@ def test_full_size_decode_and_prefill_linears_agree(cu, N, K):
         qw = np.concatenate([(qs & 0x0F).astype(np.float64) - 8, (qs >> 4).astype(np.float64) - 8], axis=1)
         want = float(np.sum(dw * dx * np.sum(qw * qx, axis=1)))
         assert abs(y1[n] - want) <= 2e-5 * scale and abs(y9[0][n] - want) <= 2e-5 * scale
+
+
+# ---------------------------------------------------------------- batched decode Linear on the tensor cores (gemv_mma.cu)
+@pytest.mark.parametrize("M,Ns,K,epi", [(3, [2048], 2048, 0), (8, [2048, 2048, 2048], 2048, 0), (8, [5504, 5504], 2048, 2), (8, [2048], 5504, 1),
+                                        (16, [4096], 4096, 1), (24, [512, 256, 256], 1024, 0), (33, [1024, 1024], 512, 2), (64, [2048], 5504, 1),
+                                        (64, [11008, 11008], 4096, 2), (5, [32000], 4096, 0)])
+def test_gemv_mma_against_oracle(cu, oracle, M, Ns, K, epi):
+    """3..64 activation rows through mllmcu_gemv_fused: RMSNorm prologue (epilogues 0 / 2), bias, residual, silu(gate) * up; every
+    output within the Linear tolerance of the oracle (the integer block sums inside are exact: test below)."""
+    assert cu.lib().mllmcu_gemv_fused_max_rows() == 64
+    rng = np.random.default_rng(M * 7 + K + len(Ns))
+    Ws = [_q4(oracle, rng, n, K) for n in Ns]
+    x = act_rows(rng, M, K)
+    w = (1 + 0.02 * rng.standard_normal(K)).astype(np.float32) if epi != 1 else None
+    bs = [(rng.standard_normal(n) * 0.02).astype(np.float32) for n in Ns] if epi == 0 else None
+    res = rng.standard_normal((M, Ns[0])).astype(np.float32) if epi == 1 else None
+    y = cu.gemv_fused([dev(v) for v in Ws], dev(x), norm_w=dev(w) if w is not None else None, eps=1e-6,
+                      biases=[dev(b) for b in bs] if bs else None, epilogue=epi, residual=dev(res) if res is not None else None).cpu().numpy()
+    xo = oracle.only.rmsnorm(x, w, 1e-6) if w is not None else x
+    if epi == 0:
+        want = np.concatenate([oracle.linear(Wi, xo, bi) for Wi, bi in zip(Ws, bs)], axis=1)
+    elif epi == 1:
+        want = oracle.linear(Ws[0], xo) + res
+    else:
+        want = oracle.silu(oracle.linear(Ws[0], xo)) * oracle.linear(Ws[1], xo)
+    lin_check(y, want)
+    # the same rows through mllmcu_linear (op-by-op path) take the same kernel: bit-identical for a single matrix
+    if epi == 0 and len(Ns) == 1:
+        xn = cu.rmsnorm(dev(x), dev(w), 1e-6)
+        assert np.array_equal(bits(cu.linear(dev(Ws[0]), xn, dev(bs[0])).cpu().numpy()), bits(y))
+
+
+def test_gemv_mma_exact_for_integer_data(cu):
+    """Activations and weights chosen so every product is an integer and every scale a power of two: the fp32 result must be EXACT,
+    which it is only if each mma.sync block sum is the exact integer Sum((nibble - 8) * q8)."""
+    import torch
+    rng = np.random.default_rng(3)
+    M, N, K = 16, 64, 1024
+    q = rng.integers(0, 16, (N, K // 32, 32)).astype(np.uint8)
+    blk = np.empty((N, K // 32, 18), dtype=np.uint8)
+    blk[..., 0:2] = np.array([1.0], dtype=np.float16).view(np.uint8)           # d_w = 1
+    blk[..., 2:] = q[..., :16] | (q[..., 16:] << 4)
+    xi = rng.integers(-127, 128, (M, K)).astype(np.float32)
+    xi[:, ::32] = 127.0                                                         # amax = 127 in every block: d_x = 1, q8 = x
+    y = cu.gemv_fused([dev(blk.reshape(N, -1))], dev(xi)).cpu().numpy()
+    want = xi.astype(np.int64) @ (q.reshape(N, K).astype(np.int64) - 8).T
+    assert np.array_equal(y.astype(np.int64), want) and np.abs(want).max() < 2 ** 24

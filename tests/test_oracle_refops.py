@@ -41,7 +41,7 @@ def all_cases(oracle):
 
 
 CASE_NAMES = ["rmsnorm", "rmsnorm_unit_offset", "rmsnorm_headwise", "layernorm", "layernorm_nobias", "rope_llama", "rope_hf", "rope_hf_theta1e6_d128",
-              "rope_hf_partial", "mrope", "vision_rope", "embedding_q4_0", "embedding_f32", "conv2d_patch", "conv3d_patch", "softmax",
+              "rope_hf_partial", "rope_hf_llama3", "mrope", "vision_rope", "embedding_q4_0", "embedding_f32", "conv2d_patch", "conv3d_patch", "softmax",
               "linear_q4_0_bias", "linear_f32"]
 
 
