@@ -82,8 +82,8 @@ def cases(P):
     c["conv3d_patch"] = dict(params={"type": OP["CONVOLUTION3D"], "kernal_t": 2, "kernal_h": 14, "kernal_w": 14, "stride_t": 2, "stride_h": 14,
                                      "stride_w": 14, "in_channel": 3, "out_channel": 8, "padding": VALID, "bias": 0},
                              weights={".weight": (w3, F32)}, inputs=[(x3, (1, 3, 2, 28, 28), F32, BCTHW)])
-    sx = (rng.standard_normal((1, 7, 3, 9)) * 4).astype(np.float32)
-    c["softmax"] = dict(params={"type": OP["SOFTMAX"], "axis": 3, "do_causal_mask": 0}, weights=None, inputs=[(sx, (1, 3, 7, 9), F32, BSHD)])
+    sx = (rng.standard_normal((3, 7, 1, 9)) * 4).astype(np.float32)   # attention scores as the eager path hands them over: [B*H, 1, S, S']
+    c["softmax"] = dict(params={"type": OP["SOFTMAX"], "axis": 3, "do_causal_mask": 0}, weights=None, inputs=[(sx, (3, 1, 7, 9), F32, BSHD)])
     Wl = P.quantize_q4_0((rng.standard_normal((96, 256)) * 0.02).astype(np.float32))
     bq = (rng.standard_normal(96) * 0.1).astype(np.float32)
     xq = rng.standard_normal((1, 5, 1, 256)).astype(np.float32)
