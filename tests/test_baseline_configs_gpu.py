@@ -17,8 +17,8 @@ tokens leave the reference's after 6 / 6 / 1 steps -- so "identical tokens over 
 against itself on these weights.  Asserted here:
   * the CPU runner over the reference's kernels IS the reference graph, bit for bit, at full size (logits and every token);
   * the CUDA logits are as close to the reference as the floor run is (1 - cos within 2.5x of the floor's);
-  * CUDA greedy tokens equal the reference's until the first step whose reference top-2 margin is inside that noise, and that first
-    difference does not come earlier than half the floor run's;
+  * CUDA greedy tokens equal the reference's until the first step whose reference top-2 margin is inside that noise (WHICH step that
+    is moves with every change of summation order, for the floor run as for the CUDA path: 39 steps with one GEMV kernel, 2 with another);
   * every transformer block, fed the reference's own input of that block, reproduces the reference's output of that block
     (cosine >= 0.9999, 99.9 % of elements within 1e-2 of the block's max): no block is wrong, the differences are the flips.
 Exact token identity over the full horizon IS asserted where it is a meaningful property: tests/test_model_gpu.py,
@@ -67,7 +67,6 @@ def check(r):
         if k == n:
             continue
         assert r["margin_at_first_mismatch"][b] <= r["gpu_relerr_prefill"], (b, k, r["margin_at_first_mismatch"][b])
-        assert k >= r["floor_tokens_equal"][b] // 2, (b, k, r["floor_tokens_equal"])
     for t in r["teacher_forced"]:
         assert t["cos"] >= 0.9999, t
         assert t["p999"] <= 1e-2 and t["max"] <= 3e-2, t
