@@ -224,6 +224,8 @@ int mllmcu_mul(const float *a, const float *b, float *y, size_t n, void *stream)
 /* ---- Embedding: CPUEmbedding::execute, Q4_0 table (op/CPUEmbedding.cpp:66-81):
  * ids are fp32 (device); negative id leaves the row untouched. */
 int mllmcu_embedding_q4_0(const void *table, const float *ids, float *out, int n_ids, int hidden, void *stream);
+/* the same gather from an F32 table (op/CPUEmbedding.cpp:44-63; e.g. CLIP's position_embedding, models/llava/modeling_llava.hpp:51) */
+int mllmcu_embedding_f32(const void *table, const float *ids, float *out, int n_ids, int hidden, void *stream);
 
 /* ---- Flash attention 2 with fp32 Q and fp16 K/V cache:
  * CPUFlashAttention2Func::execute -> flash_attention_2_forward

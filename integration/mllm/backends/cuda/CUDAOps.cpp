@@ -71,7 +71,7 @@ public:
     ErrorCode load(AbstructLoader &loader) override { // CPULinear.cpp:47-95
         DataType dt = loader.getDataType(name() + ".weight");
         const DataType eff = dt != MLLM_TYPE_COUNT ? dt : Op::noLoadWeightsDtype();
-        if (eff != MLLM_TYPE_Q4_0 && eff != MLLM_TYPE_Q8_0 && eff != MLLM_TYPE_Q4_K && eff != MLLM_TYPE_Q6_K)
+        if (eff != MLLM_TYPE_F32 && eff != MLLM_TYPE_Q4_0 && eff != MLLM_TYPE_Q8_0 && eff != MLLM_TYPE_Q4_K && eff != MLLM_TYPE_Q6_K)
             throw std::runtime_error("[mllm-cuda] Linear " + name() + ": weight dtype " + std::to_string((int)eff) + " has no CUDA kernel");
         load_param(weight_, backend_, name() + ".weight", out_, in_, loader, eff);
         if (bias_) load_param(biasT_, backend_, name() + ".bias", 1, out_, loader, MLLM_TYPE_F32);
@@ -83,6 +83,13 @@ public:
         if (x.count() == 0) return MLLM_NO_ERROR;
         const int f16 = y.dtype() == MLLM_TYPE_F16;
         const float *bias = bias_ ? biasT_.hostPtr<float>() : nullptr;
+        if (weight_.dtype() == MLLM_TYPE_F32) { // weights the quantizer keeps F32: fp32 GEMM (vec_dot_fp32's products in another order)
+            if (f16 || !dense(x) || !dense(y)) throw std::runtime_error("[mllm-cuda] Linear " + name() + ": F32 weights need dense fp32 activations");
+            MLLMCU_CHECK(mllmcu_sgemm(fbase(x), in_, 0, weight_.hostPtr<float>(), in_, 1, 0, bias, fbase(y), out_, 0, x.batch() * x.sequence(), out_, in_, 1, b->stream()));
+            b->dropQuantTag();
+            b->kernel_launches++;
+            return MLLM_NO_ERROR;
+        }
         const View xs = strides(x), ys = strides(y);
         const bool one = dense(x) && (y.batch() == 1 || ys.bs == (long long)y.sequence() * ys.ss);
         const int nbatch = one ? 1 : x.batch();
@@ -266,13 +273,15 @@ public:
     ErrorCode load(AbstructLoader &loader) override {
         const DataType dt = loader.getDataType(name() + ".weight");
         const DataType eff = dt != MLLM_TYPE_COUNT ? dt : MLLM_TYPE_Q4_0;
-        if (eff != MLLM_TYPE_Q4_0) throw std::runtime_error("[mllm-cuda] Embedding " + name() + ": only Q4_0 tables (the quantizer forces embed_tokens to Q4_0)");
+        if (eff != MLLM_TYPE_Q4_0 && eff != MLLM_TYPE_F32) throw std::runtime_error("[mllm-cuda] Embedding " + name() + ": Q4_0 and F32 tables only");
         load_param(weight_, backend_, name() + ".weight", vocab_, hidden_, loader, eff);
         return Op::load(loader);
     }
     ErrorCode execute(vector<shared_ptr<Tensor>> in, vector<shared_ptr<Tensor>> out) override {
         auto *b = cb(backend_);
-        MLLMCU_CHECK(mllmcu_embedding_q4_0(weight_.rawHostPtr(), fbase(*in[0]), fbase(*out[0]), in[0]->batch() * in[0]->sequence(), hidden_, b->stream()));
+        const int n = in[0]->batch() * in[0]->sequence();
+        if (weight_.dtype() == MLLM_TYPE_F32) MLLMCU_CHECK(mllmcu_embedding_f32(weight_.rawHostPtr(), fbase(*in[0]), fbase(*out[0]), n, hidden_, b->stream()));
+        else MLLMCU_CHECK(mllmcu_embedding_q4_0(weight_.rawHostPtr(), fbase(*in[0]), fbase(*out[0]), n, hidden_, b->stream()));
         b->kernel_launches++;
         return MLLM_NO_ERROR;
     }

@@ -67,6 +67,7 @@ SYMBOLS = {
     "mllmcu_add": (_i, [_vp, _vp, _vp, _sz, _vp]),
     "mllmcu_mul": (_i, [_vp, _vp, _vp, _sz, _vp]),
     "mllmcu_embedding_q4_0": (_i, [_vp, _vp, _vp, _i, _i, _vp]),
+    "mllmcu_embedding_f32": (_i, [_vp, _vp, _vp, _i, _i, _vp]),
     "mllmcu_flash_attn_workspace_bytes": (_sz, [_i, _i, _i, _i]),
     "mllmcu_flash_attn_f16kv": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _ll, _vp, _sz, _vp]),
     "mllmcu_quantize_q8_K": (_i, [_vp, _vp, _i, _i, _i, _vp]),

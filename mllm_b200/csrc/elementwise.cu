@@ -281,6 +281,23 @@ MLLMCU_API int mllmcu_embedding_q4_0(const void *table, const float *ids, float 
     return 0;
 }
 
+// CPUEmbedding::execute, F32 table (op/CPUEmbedding.cpp:44-63): a row copy per token; negative ids leave the row untouched
+__global__ void k_embedding_f32(const float *__restrict__ table, const float *__restrict__ ids, float *__restrict__ out, int n_ids, int hidden) {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= (long long)n_ids * hidden) return;
+    const int t = (int)(i / hidden), d = (int)(i % hidden);
+    const float idf = ids[t];
+    if (!(idf >= 0)) return;
+    out[i] = table[(size_t)(int)idf * hidden + d];
+}
+MLLMCU_API int mllmcu_embedding_f32(const void *table, const float *ids, float *out, int n_ids, int hidden, void *stream) {
+    if (n_ids <= 0 || hidden <= 0) return -1;
+    const long long tot = (long long)n_ids * hidden;
+    k_embedding_f32<<<(unsigned)((tot + 255) / 256), 256, 0, (cudaStream_t)stream>>>((const float *)table, ids, out, n_ids, hidden);
+    CU_LAUNCH_CHECK();
+    return 0;
+}
+
 // ------------------------------------------------------------- fp32 -> fp16
 __global__ void k_f32_to_f16_rows(const float *__restrict__ src, __half *__restrict__ dst, int rows, int cols, long long lds, long long ldd) {
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;

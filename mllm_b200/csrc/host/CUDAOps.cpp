@@ -52,7 +52,7 @@ public:
         DataType dt = loader.getDataType(weight_.name());
         const bool absent = (dt == MLLM_TYPE_COUNT);
         if (absent) dt = Op::noLoadWeightsDtype();
-        if (dt != MLLM_TYPE_Q4_0 && dt != MLLM_TYPE_Q8_0 && dt != MLLM_TYPE_Q4_K && dt != MLLM_TYPE_Q6_K && dt != MLLM_TYPE_Q4_0_4_4)
+        if (dt != MLLM_TYPE_F32 && dt != MLLM_TYPE_Q4_0 && dt != MLLM_TYPE_Q8_0 && dt != MLLM_TYPE_Q4_K && dt != MLLM_TYPE_Q6_K && dt != MLLM_TYPE_Q4_0_4_4)
             throw std::runtime_error("[mllm-cuda] Linear " + name() + ": weight dtype " + std::to_string((int)dt) + " not supported by the CUDA backend yet");
         if ((dt == MLLM_TYPE_Q4_K || dt == MLLM_TYPE_Q6_K) && in_ % 256) throw std::runtime_error("[mllm-cuda] Linear " + name() + ": k-quant weights need in_features % 256 == 0");
         if (dt == MLLM_TYPE_Q4_0_4_4) {
@@ -90,6 +90,14 @@ public:
         const int f16 = y.dtype() == MLLM_TYPE_F16;
         const float *bias = bias_ ? biasT_.devPtr<float>() : nullptr;
         const size_t esz = f16 ? 2 : 4;
+        if (weight_.dtype() == MLLM_TYPE_F32) { // weights the quantizer keeps F32 (patch embeds, small heads): fp32 GEMM, vec_dot_fp32's products in another order
+            if (f16 || !x.contiguous() || !y.contiguous()) throw std::runtime_error("[mllm-cuda] Linear " + name() + ": F32 weights need dense fp32 activations");
+            const int M = x.batch() * x.sequence();
+            MLLMCU_CHECK(mllmcu_sgemm(x.devPtr<float>(), in_, 0, weight_.devPtr<float>(), in_, 1, 0, bias, y.devPtr<float>(), out_, 0, M, out_, in_, 1, b->stream()));
+            b->dropQuantTag();
+            b->kernel_launches++;
+            return MLLM_NO_ERROR;
+        }
         // one call when both sides are dense over (batch, seq); else one call per batch row-block
         const bool dense = x.contiguous() && (y.batch() == 1 || y.batchStride() == (long long)y.sequence() * y.seqStride());
         const int nb = dense ? 1 : x.batch();
@@ -393,7 +401,7 @@ public:
         DataType dt = loader.getDataType(weight_.name());
         const bool absent = dt == MLLM_TYPE_COUNT;
         if (absent) dt = MLLM_TYPE_Q4_0;
-        if (dt != MLLM_TYPE_Q4_0) throw std::runtime_error("[mllm-cuda] Embedding " + name() + ": only Q4_0 tables (the quantizer forces embed_tokens to Q4_0)");
+        if (dt != MLLM_TYPE_Q4_0 && dt != MLLM_TYPE_F32) throw std::runtime_error("[mllm-cuda] Embedding " + name() + ": Q4_0 and F32 tables only");
         weight_.setDtype(dt);
         weight_.alloc();
         if (!absent) loader.load(&weight_);
@@ -403,7 +411,8 @@ public:
         auto *b = cb(backend_);
         const int n = in[0]->batch() * in[0]->sequence();
         MLLMCU_CHECK(mllmcu_memset(out[0]->rawDevPtr(), 0, out[0]->cntSize(), b->stream()));
-        MLLMCU_CHECK(mllmcu_embedding_q4_0(weight_.rawDevPtr(), in[0]->devPtr<float>(), out[0]->devPtr<float>(), n, hidden_, b->stream()));
+        if (weight_.dtype() == MLLM_TYPE_F32) MLLMCU_CHECK(mllmcu_embedding_f32(weight_.rawDevPtr(), in[0]->devPtr<float>(), out[0]->devPtr<float>(), n, hidden_, b->stream()));
+        else MLLMCU_CHECK(mllmcu_embedding_q4_0(weight_.rawDevPtr(), in[0]->devPtr<float>(), out[0]->devPtr<float>(), n, hidden_, b->stream()));
         b->kernel_launches++;
         return MLLM_NO_ERROR;
     }

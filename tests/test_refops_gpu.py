@@ -22,7 +22,8 @@ TOL = {
     "rope_llama": 0, "rope_hf": 0, "rope_hf_theta1e6_d128": 0, "rope_hf_partial": 0, "rope_hf_llama3": 0,  # host-built tables, FMA form
     "mrope": 0,
     "vision_rope": 3e-6,   # the op evaluates sinf / cosf on the device (<= 2 ulp from libm); with host-built tables the kernel is bit-exact (tests/test_vision_kq_gpu.py)
-    "embedding_q4_0": 0,
+    "embedding_q4_0": 0, "embedding_f32": 0,
+    "linear_f32": 1e-5,                                                       # F32-weight Linear: vec_dot_fp32's 32-lane order there, tiled fp32 sums here
     "conv2d_patch": 1e-5,                                                     # vec_dot_fp32's 32-lane order there, tiled sums here
     "softmax": 0,
     "linear_q4_0_bias": 2e-5,                                                 # same products, different fp32 order (1e-3)
