@@ -283,6 +283,21 @@ int mllmcu_rope_vision(const float *x, const float *angles_or_sin, const float *
  * n, ss, ds are HOST arrays of 4. */
 int mllmcu_copy_strided(const void *src, void *dst, int elem_bytes, const int *n, const long long *ss, const long long *ds, void *stream);
 
+/* ---- the index functions that splice image embeddings into the text prefill (models/llava/modeling_llava.hpp:128-131,
+ * models/qwen2_vl/modeling_qwen2_vl.hpp:386-389).  Tensor::where (CPUwhereFunction, op/CPUWhereFunc.hpp:32-95): positions with
+ * x == value of a dense BSHD tensor of `total` elements, compacted in the reference's visit order (b, s, h, d = memory order) as
+ * linear indices into lin_idx (capacity total), *count on the device; mllmcu_where_unravel turns them into the coordinate of one
+ * axis (0 b, 1 s, 2 h, 3 d; n = sizes in that order) as floats, which is what the reference returns. */
+int mllmcu_where_eq(const float *x, long long total, float value, int *lin_idx, int *count, void *stream);
+int mllmcu_where_unravel(const int *lin_idx, int count, const int *n, int axis, float *out, void *stream);
+/* Tensor::index_put (CPUIndexPutFunction, op/CPUIndexPutFunc.hpp:73-131), indices read on the device: rows -- dst row (int)idx[r]
+ * <- src row r (accumulate == false); splice -- out [S-1+R][dim] = dest[0:p] ++ src[0:R] ++ dest[p+1:S], p = (int)idx[0]
+ * (accumulate == true with one replaced position, the LLaVA image splice). */
+int mllmcu_index_put_rows(float *dst, long long dst_ld, const float *src, long long src_ld, const float *idx, int n_rows, int dim, void *stream);
+int mllmcu_index_splice(const float *dest, const float *src, const float *idx, float *out, int S, int R, int dim, void *stream);
+/* Tensor::range (CPURangeFunction, op/CPURangeFunc.hpp:33-41): out[i] = start + i */
+int mllmcu_range(float *out, int start, int n, void *stream);
+
 /* ---- fp32 GEMM C[b][m][n] = sum_k A[b][m*lda + k] * B[b][n*ldbn + k*ldbk] + bias[n]  (batch strides in elements):
  * the fp32 mat_mul of the eager attention spelling (CPUMatmul::execute, op/CPUMatmul.cpp:63-83: Q.K^T with ldbn = row
  * stride of K, ldbk = 1; P.V with ldbn = 1, ldbk = row stride of V) and Linears whose weights stay F32. */

@@ -81,6 +81,7 @@ public:
     Op *opCreate(const OpParam &op_param, string name = "", int threadCount = 4) override;
     TensorFunction *funcCreate(TensorFuncType type) override;
     void registerOps() override;
+    void registerVisionOps(); // CUDAVisionOps.cpp
     void registerFuncs() override {}
     std::vector<Tensor> runLayer(Layer *layer, std::vector<Tensor> inputs, int N) override;
     std::vector<Tensor> runOp(Op *op, std::vector<Tensor> input, std::vector<std::string> out_names, bool in_place) override;

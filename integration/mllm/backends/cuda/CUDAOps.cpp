@@ -9,6 +9,7 @@
 #include "Tensor.hpp"
 #include "backends/cpu/op/CPUKVCache.hpp"
 #include "backends/cpu/op/CPUViewFunc.hpp"
+#include "CUDAOpHelpers.hpp"
 #include "mllmcu.h"
 
 #include <cmath>
@@ -16,46 +17,6 @@
 #include <stdexcept>
 
 namespace mllm {
-
-static CUDABackend *cb(Backend *b) { return static_cast<CUDABackend *>(b); }
-static float getp(const OpParam &p, const char *k, float dflt) {
-    auto it = p.find(k);
-    return it == p.end() ? dflt : it->second;
-}
-
-// element strides of a BSHD tensor or child view (Tensor::offset, Tensor.hpp:264-311)
-struct View {
-    long long bs, ss; // elements between consecutive batches / sequence positions; (head, dimension) are contiguous
-};
-static View strides(Tensor &t) {
-    if (t.ctype() != BSHD) throw std::runtime_error("[mllm-cuda] " + t.name() + ": only BSHD tensors");
-    const auto m = t.shapeMaster();
-    if (m.size() == 4 && t.shapeOffset().size() == 4) return {(long long)m[2] * m[1] * m[3], (long long)m[1] * m[3]};
-    return {(long long)t.sequence() * t.head() * t.dimension(), (long long)t.head() * t.dimension()};
-}
-static bool dense(Tensor &t) {
-    const View v = strides(t);
-    return v.ss == (long long)t.head() * t.dimension() && (t.batch() == 1 || v.bs == (long long)t.sequence() * v.ss);
-}
-static void *base(Tensor &t) { // address of element (0,0,0,0) of the view
-    const size_t esz = t.dtype() == MLLM_TYPE_F16 ? 2 : 4;
-    return (char *)t.rawHostPtr() + (size_t)t.offset(0, 0, 0, 0) * esz;
-}
-static float *fbase(Tensor &t) {
-    if (t.dtype() != MLLM_TYPE_F32) throw std::runtime_error("[mllm-cuda] " + t.name() + ": fp32 tensor expected");
-    return (float *)base(t);
-}
-static void load_param(Tensor &t, Backend *bn, const string &name, int rows, int cols, AbstructLoader &loader, DataType dflt) {
-    t.setBackend(bn);
-    t.setName(name);
-    t.reshape(1, 1, rows, cols);
-    const DataType dt = loader.getDataType(name);
-    t.setDtype(dt != MLLM_TYPE_COUNT ? dt : dflt);
-    cb(bn)->memory()->device_only = true; // parameters are read by kernels only
-    t.alloc();
-    cb(bn)->memory()->device_only = false;
-    if (dt != MLLM_TYPE_COUNT) loader.load(&t);
-}
 
 // ------------------------------------------------------------------ Linear (op/CPULinear.cpp:22-233, compute/Matmul.cpp:77-279)
 class CUDALinear final : public CUDAOpBase {
@@ -346,12 +307,13 @@ public:
         Tensor &x = *in[0], &y = *out[0];
         int s0 = s_.empty() ? 0 : s_[0];
         if (s0 < 0) s0 += x.sequence();
+        if (s0 < 0 || s0 + y.sequence() > x.sequence()) throw std::runtime_error("[mllm-cuda] clip " + name() + ": sequence range outside the tensor");
         const View xs = strides(x), ys = strides(y);
-        const size_t row = (size_t)x.head() * x.dimension() * 4;
-        for (int i = 0; i < x.batch(); i++)
-            for (int s = 0; s < y.sequence(); s++)
-                MLLMCU_CHECK(mllmcu_memcpy_d2d((char *)base(y) + ((size_t)i * ys.bs + (size_t)s * ys.ss) * 4,
-                                               (char *)base(x) + ((size_t)i * xs.bs + (size_t)(s0 + s) * xs.ss) * 4, row, b->stream()));
+        const int esz = x.dtype() == MLLM_TYPE_F16 ? 2 : 4;
+        const int n[4] = {x.batch(), y.sequence(), 1, x.head() * x.dimension()};
+        const long long ss[4] = {xs.bs, xs.ss, 0, 1}, ds[4] = {ys.bs, ys.ss, 0, 1};
+        MLLMCU_CHECK(mllmcu_copy_strided((const char *)base(x) + (size_t)s0 * xs.ss * esz, base(y), esz, n, ss, ds, b->stream()));
+        b->kernel_launches++;
         return MLLM_NO_ERROR;
     }
 
@@ -431,6 +393,7 @@ void CUDABackend::registerOps() {
     addCreator(F_FA2, new FA2Creator());
     addCreator(F_VIEW, new ViewCreator());
     addCreator(KVCACHE, new KVCacheCreator());
+    registerVisionOps(); // CUDAVisionOps.cpp: the ops the ViT towers and the image splice add
 }
 
 } // namespace mllm

@@ -80,6 +80,11 @@ SYMBOLS = {
     "mllmcu_rope_vision": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _vp]),
     "mllmcu_copy_strided": (_i, [_vp, _vp, _i, _vp, _vp, _vp, _vp]),
     "mllmcu_sgemm": (_i, [_vp, _ll, _ll, _vp, _ll, _ll, _ll, _vp, _vp, _ll, _ll, _i, _i, _i, _i, _vp]),
+    "mllmcu_where_eq": (_i, [_vp, _ll, _f, _vp, _vp, _vp]),
+    "mllmcu_where_unravel": (_i, [_vp, _i, _vp, _i, _vp, _vp]),
+    "mllmcu_index_put_rows": (_i, [_vp, _ll, _vp, _ll, _vp, _i, _i, _vp]),
+    "mllmcu_index_splice": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _vp]),
+    "mllmcu_range": (_i, [_vp, _i, _i, _vp]),
     "mllmcu_conv2d_valid": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _vp]),
     "mllmcu_conv3d_valid": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _i, _vp]),
     "mllmcu_flash_attn_f32kv": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _ll, _vp, _sz, _vp]),
