@@ -53,7 +53,8 @@ public:
         if (dt == MLLM_TYPE_F32) {
             float *f = (float *)buf.data();
             const bool norm_w = (n.find("norm") != string::npos || n.find("ln_") != string::npos) && n.find(".weight") != string::npos;
-            const float a = n.find("patch_embed") != string::npos ? 0.05f : n.find(".bias") != string::npos ? 0.02f : n.find("embedding") != string::npos ? 0.5f : 0.5f;
+            const bool lin_w = getDataType(n) != MLLM_TYPE_F32 || (linear_ == MLLM_TYPE_F32 && n.find(".weight") != string::npos && !norm_w && n.find("embedding") == string::npos && n.find("patch_embed") == string::npos);
+            const float a = lin_w ? 0.05f : n.find("patch_embed") != string::npos ? 0.05f : n.find(".bias") != string::npos ? 0.02f : 0.5f;
             for (size_t i = 0; i < bytes / 4; i++) f[i] = norm_w ? 1.0f + 0.1f * u(rng_) : a * u(rng_);
         } else if (dt == MLLM_TYPE_Q4_0) {
             for (size_t b = 0; b < bytes / 18; b++) {
@@ -180,6 +181,7 @@ int main(int argc, char **argv) {
     cp.add<int>("limit", 'l', "KV cache size", false, 1024);
     cp.add<int>("thread", 't', "CPU backend threads", false, 4);
     cp.add<int>("seed", 's', "input seed", false, 7);
+    cp.add<string>("linear", 0, "--write: dtype of the Linear weights: default (llava q4_k, qwen2vl q4_0) | f32 | q4_0 | q4_k", false, "default");
     cp.add<string>("dump", 0, "write every step's last-position logits (fp32) here", false, "");
     cp.parse_check(argc, argv);
     const string which = cp.get<string>("model");
@@ -195,6 +197,10 @@ int main(int argc, char **argv) {
             i = j + 1;
         }
     }
+    auto linear_type = [&](DataType dflt) {
+        const string l = cp.get<string>("linear");
+        return l == "f32" ? MLLM_TYPE_F32 : l == "q4_0" ? MLLM_TYPE_Q4_0 : l == "q4_k" ? MLLM_TYPE_Q4_K : dflt;
+    };
     const int n_text = cp.get<int>("text"), n_decode = cp.get<int>("decode"), limit = cp.get<int>("limit");
     std::mt19937 rng((unsigned)cp.get<int>("seed"));
     std::uniform_real_distribution<float> upix(-1.f, 1.f);
@@ -210,7 +216,7 @@ int main(int argc, char **argv) {
         LLaVAModel model(vocab, dims[1], dims[2], dims[3], dims[4], cfg.RoPE_type, cfg.rope_theta, cfg.max_position_embeddings, limit, cfg.names_config, dims[5], dims[6],
                          dims[7], patch, img, dims[8], cfg.attn_implementation, cfg.vit_names_config);
         if (!cp.get<string>("write").empty()) {
-            auto loader = std::make_shared<RandomInitLoader>(MLLM_TYPE_Q4_K, 1234u);
+            auto loader = std::make_shared<RandomInitLoader>(linear_type(MLLM_TYPE_Q4_K), 1234u);
             load_with(model, loader);
             loader->save(cp.get<string>("write"));
             printf("{\"written\": \"%s\", \"tensors\": %zu}\n", cp.get<string>("write").c_str(), loader->count());
@@ -252,7 +258,7 @@ int main(int argc, char **argv) {
         cfg.cache_limit = limit;
         Qwen2VLModel model(cfg);
         if (!cp.get<string>("write").empty()) {
-            auto loader = std::make_shared<RandomInitLoader>(MLLM_TYPE_Q4_0, 4321u);
+            auto loader = std::make_shared<RandomInitLoader>(linear_type(MLLM_TYPE_Q4_0), 4321u);
             load_with(model, loader);
             loader->save(cp.get<string>("write"));
             printf("{\"written\": \"%s\", \"tensors\": %zu}\n", cp.get<string>("write").c_str(), loader->count());

@@ -5,6 +5,9 @@
 #include "Layer.hpp"
 #include "Module.hpp"
 #include "ParamLoader.hpp"
+#ifdef MLLM_DEBUG_DUMP
+#include "CUDADebugDump.hpp"
+#endif
 #include "Tensor.hpp"
 #include "Timing.hpp"
 #include "mllmcu.h"
@@ -274,6 +277,9 @@ std::vector<Tensor> CUDABackend::runOp(Op *op, std::vector<Tensor> inputs, std::
     }
     if (recording_) rec_ops_.push_back(op);
     op->execute(input_tensors, out_tensors);
+#ifdef MLLM_DEBUG_DUMP
+    if (getenv("MLLM_DUMP_OPS")) { sync(); mllm_debug_dump(out_tensors); }
+#endif
     vector<Tensor> results;
     for (const auto &out_tensor : out_tensors) results.push_back(*out_tensor);
     return results;

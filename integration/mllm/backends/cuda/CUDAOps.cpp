@@ -45,10 +45,27 @@ public:
         const int f16 = y.dtype() == MLLM_TYPE_F16;
         const float *bias = bias_ ? biasT_.hostPtr<float>() : nullptr;
         if (weight_.dtype() == MLLM_TYPE_F32) { // weights the quantizer keeps F32: fp32 GEMM (vec_dot_fp32's products in another order)
-            if (f16 || !dense(x) || !dense(y)) throw std::runtime_error("[mllm-cuda] Linear " + name() + ": F32 weights need dense fp32 activations");
-            MLLMCU_CHECK(mllmcu_sgemm(fbase(x), in_, 0, weight_.hostPtr<float>(), in_, 1, 0, bias, fbase(y), out_, 0, x.batch() * x.sequence(), out_, in_, 1, b->stream()));
-            b->dropQuantTag();
+            if (!dense(x)) throw std::runtime_error("[mllm-cuda] Linear " + name() + ": F32 weights need a dense fp32 input");
+            const int M = x.batch() * x.sequence();
+            const bool direct = !f16 && dense(y);
+            float *dst = direct ? fbase(y) : (float *)b->workspace((size_t)M * out_ * 4);
+            MLLMCU_CHECK(mllmcu_sgemm(fbase(x), in_, 0, weight_.hostPtr<float>(), in_, 1, 0, bias, dst, out_, 0, M, out_, in_, 1, b->stream()));
             b->kernel_launches++;
+            if (!direct) { // the output is a slice of a KV cache (fp16 and / or strided): rows go there through the converting / strided copy
+                const View ys = strides(y);
+                for (int i = 0; i < y.batch(); i++) {
+                    const float *src = dst + (size_t)i * y.sequence() * out_;
+                    char *yp = (char *)base(y) + (size_t)i * ys.bs * (f16 ? 2 : 4);
+                    if (f16) MLLMCU_CHECK(mllmcu_f32_to_f16_rows(src, yp, y.sequence(), out_, out_, ys.ss, b->stream()));
+                    else {
+                        const int n[4] = {1, y.sequence(), 1, out_};
+                        const long long ss[4] = {0, out_, 0, 1}, ds[4] = {0, ys.ss, 0, 1};
+                        MLLMCU_CHECK(mllmcu_copy_strided(src, yp, 4, n, ss, ds, b->stream()));
+                    }
+                    b->kernel_launches++;
+                }
+            }
+            b->dropQuantTag();
             return MLLM_NO_ERROR;
         }
         const View xs = strides(x), ys = strides(y);
