@@ -324,6 +324,22 @@ int mllmcu_f32_to_f16_rows(const float *src, void *dst, int rows, int cols, long
 /* the reverse, exact widening: Backend::convert_fp_data (mllm/Backend.hpp:73, CPUBackend.cpp:260-277) for Tensor::fp32() */
 int mllmcu_f16_to_f32_rows(const void *src, float *dst, int rows, int cols, long long ld_src, long long ld_dst, void *stream);
 
+/* ---- optional tensor-parallel Linear (north_star): the exchange step of the row-parallel o_proj / down_proj for the
+ * decode shape, as one kernel over peer memory (p2p.cu).  No counterpart in the reference (single process, CPUBackend threads).
+ * Every rank cudaMalloc's one region and publishes it through CUDA IPC (get_handle -> 64 bytes to the peers -> open); a call
+ * names a "site": buf_offset = where the producing GEMV of EVERY rank wrote its partial [n] floats inside its region, flag_offset
+ * = `world` 32-bit words inside the region reserved for this site.  out[i] = residual[i] + sum_r partial_r[i], ranks added in
+ * order 0..world-1 on every rank (bit-identical results everywhere).  *epoch_ctr (device) must hold the same, never repeated,
+ * value on all ranks for one step: mllmcu_p2p_bump once per step.  peer_bases: HOST array of `world` device pointers (own region
+ * at [rank]).  world <= 8, n % 4 == 0, one CTA (a decode-sized reduction; prefill goes through NCCL).  A peer that never arrives
+ * traps the kernel after 10 s instead of hanging the device. */
+int mllmcu_ipc_get_handle(void *dev_ptr, void *handle64);
+int mllmcu_ipc_open(const void *handle64, void **dev_ptr);
+int mllmcu_ipc_close(void *dev_ptr);
+int mllmcu_p2p_bump(unsigned *epoch_ctr, void *stream);
+int mllmcu_p2p_allreduce(int world, int rank, const void *const *peer_bases, size_t buf_offset, size_t flag_offset, const unsigned *epoch_ctr,
+                         const float *residual, float *out, int n, void *stream);
+
 /* ---- greedy sampling: LlmTextGenerator argmax (Generate.cpp:46-53) on device;
  * first maximum wins, as std::max_element does. out: int32 per row. */
 int mllmcu_argmax(const float *logits, int rows, int n, int *out, void *stream);

@@ -9,6 +9,7 @@
 //   run_vlm_cuda --model llava|qwen2vl --dims ... --device 0|4 --file FILE --text 8 --decode 8 [--dump logits.bin]
 // prints one JSON line (tokens, vision + prefill ms, decode ms/step); --dump writes the fp32 logits of every step.
 #include <algorithm>
+#include <cmath>
 #include <cstdio>
 #include <cstring>
 #include <fstream>
@@ -58,14 +59,14 @@ public:
             for (size_t i = 0; i < bytes / 4; i++) f[i] = norm_w ? 1.0f + 0.1f * u(rng_) : a * u(rng_);
         } else if (dt == MLLM_TYPE_Q4_0) {
             for (size_t b = 0; b < bytes / 18; b++) {
-                const mllm_fp16_t d = MLLM_FP32_TO_FP16(0.004f + 0.004f * std::fabs(u(rng_)));
+                const mllm_fp16_t d = MLLM_FP32_TO_FP16(0.003f + 0.003f * std::fabs(u(rng_))) /* weight std ~0.02 */;
                 memcpy(&buf[b * 18], &d, 2);
                 for (int i = 0; i < 16; i++) buf[b * 18 + 2 + i] = (uint8_t)((1 + rng_() % 15) | ((1 + rng_() % 15) << 4)); // nibbles 1..15: (q - 8) is centred on zero
             }
         } else if (dt == MLLM_TYPE_Q4_K) { // block_q4_K: d, dmin (fp16), 12 bytes of 6-bit scales / mins, 128 bytes of nibbles
             for (size_t b = 0; b < bytes / 144; b++) {
                 // weight = d * scale6 * nibble - dmin * min6 with uniform 6-bit scales / mins and nibbles: dmin = 7.5 d centres it on zero
-                const float dv = 0.0002f + 0.0002f * std::fabs(u(rng_));
+                const float dv = 0.00005f + 0.00005f * std::fabs(u(rng_)); // weight std ~0.02 (W ~ N(0, 0.02^2))
                 const mllm_fp16_t d = MLLM_FP32_TO_FP16(dv), dm = MLLM_FP32_TO_FP16(7.5f * dv);
                 memcpy(&buf[b * 144], &d, 2);
                 memcpy(&buf[b * 144 + 2], &dm, 2);
@@ -182,6 +183,7 @@ int main(int argc, char **argv) {
     cp.add<int>("thread", 't', "CPU backend threads", false, 4);
     cp.add<int>("seed", 's', "input seed", false, 7);
     cp.add<string>("linear", 0, "--write: dtype of the Linear weights: default (llava q4_k, qwen2vl q4_0) | f32 | q4_0 | q4_k", false, "default");
+    cp.add<int>("perturb", 0, "move every pixel to the next representable float (1 ulp): the noise-floor experiment", false, 0);
     cp.add<string>("dump", 0, "write every step's last-position logits (fp32) here", false, "");
     cp.parse_check(argc, argv);
     const string which = cp.get<string>("model");
@@ -236,7 +238,7 @@ int main(int argc, char **argv) {
         Tensor image = host_tensor("input_imgs", 1, img, 3, img); // [B, head = H, seq = C, dim = W]
         for (int c = 0; c < 3; c++)
             for (int h = 0; h < img; h++)
-                for (int w = 0; w < img; w++) image.setDataAt<float>(0, h, c, w, upix(rng));
+                for (int w = 0; w < img; w++) { const float v = upix(rng); image.setDataAt<float>(0, h, c, w, cp.get<int>("perturb") ? std::nextafterf(v, 2.f) : v); }
         const int prompt_tokens = S - 1 + (img / patch) * (img / patch);
         for (int step = 0; step < n_decode; step++) {
             auto result = model({ids, image});
@@ -286,7 +288,7 @@ int main(int argc, char **argv) {
         patches.setDtype(MLLM_TYPE_F32);
         patches.alloc();
         patches.setTtype(INPUT_TENSOR);
-        for (size_t i = 0; i < (size_t)n_patch * 3 * 2 * 14 * 14; i++) patches.hostPtr<float>()[i] = upix(rng);
+        for (size_t i = 0; i < (size_t)n_patch * 3 * 2 * 14 * 14; i++) { const float v = upix(rng); patches.hostPtr<float>()[i] = cp.get<int>("perturb") ? std::nextafterf(v, 2.f) : v; }
         Tensor grid = host_tensor("image_grid_thw", 1, 1, 1, 3);
         grid.setDataAt<float>(0, 0, 0, 0, 1.f);
         grid.setDataAt<float>(0, 0, 0, 1, (float)gh);

@@ -80,6 +80,11 @@ SYMBOLS = {
     "mllmcu_rope_vision": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _vp]),
     "mllmcu_copy_strided": (_i, [_vp, _vp, _i, _vp, _vp, _vp, _vp]),
     "mllmcu_sgemm": (_i, [_vp, _ll, _ll, _vp, _ll, _ll, _ll, _vp, _vp, _ll, _ll, _i, _i, _i, _i, _vp]),
+    "mllmcu_ipc_get_handle": (_i, [_vp, _vp]),
+    "mllmcu_ipc_open": (_i, [_vp, _vp]),
+    "mllmcu_ipc_close": (_i, [_vp]),
+    "mllmcu_p2p_bump": (_i, [_vp, _vp]),
+    "mllmcu_p2p_allreduce": (_i, [_i, _i, _vp, _sz, _sz, _vp, _vp, _vp, _i, _vp]),
     "mllmcu_where_eq": (_i, [_vp, _ll, _f, _vp, _vp, _vp]),
     "mllmcu_where_unravel": (_i, [_vp, _i, _vp, _i, _vp, _vp]),
     "mllmcu_index_put_rows": (_i, [_vp, _ll, _vp, _ll, _vp, _i, _i, _vp]),
