@@ -427,6 +427,88 @@ def gpu_arm_c5(args, rank, world, local_rank):
     print(json.dumps(out), flush=True)
 
 
+def gpu_arm_tp(args, rank, world, local_rank):
+    """The optional tensor-parallel path (north_star): ONE LLaMA-2-7B Q4_0 request (BASELINE configs[1]: prefill 512 + 256
+    greedy tokens) with every Linear sharded over the N ranks (mllm_b200/tp.py: column-parallel q/k/v/gate/up, row-parallel o/down,
+    NCCL all-reduce in prefill, the peer-memory exchange kernel of csrc/p2p.cu per decode token; MLLM_TP_NCCL=1: NCCL there too).
+    Strong scaling: the work is fixed, value = the request's tokens / slowest rank's device time."""
+    import torch
+    torch.cuda.set_device(local_rank)
+    from mllm_b200 import build, tp
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+    if rank == 0:
+        build.build_all()
+    if dist:
+        dist.barrier()
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    S, ND = 512, 256
+    cfg = mf.config("llama2-7b", cache_limit=1024)
+    path = os.environ.get("MLLM_BENCH_MODEL", "/tmp/mllm_bench_llama2-7b_q4_0.mllm")
+    if rank == 0:
+        make_model_file(cfg, path, device=f"cuda:{local_rank}")
+    if dist:
+        dist.barrier()
+    model = tp.TPLlama(cfg, path, rank, world, dist)
+    ids = np.random.default_rng(1234).integers(0, cfg["vocab"], (1, S)).astype(np.float32)
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
+
+    def request():
+        model.clear()
+        ev[0].record()
+        first = model.prefill(ids).argmax(dim=1)
+        ev[1].record()
+        toks, _ = model.decode(first.cpu().numpy(), ND - 1)
+        ev[2].record()
+        torch.cuda.synchronize()
+        return ev[0].elapsed_time(ev[1]), ev[1].elapsed_time(ev[2]), [int(first[0])] + [int(t[0]) for t in toks]
+
+    for _ in range(max(args.warmup, 1)):
+        request()
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    if dist:
+        dist.barrier()
+    tp_ms, td_ms, e2e = [], [], []
+    for _ in range(args.steps):
+        w0 = time.perf_counter()
+        a, b, toks = request()
+        e2e.append((time.perf_counter() - w0) * 1e3)
+        tp_ms.append(a)
+        td_ms.append(b)
+    clocks = sampler.stop()
+    pre, dec, wall = max_over_ranks([float(np.mean(tp_ms)), float(np.mean(td_ms)), float(np.mean(e2e))], world, "cuda")
+    launches = model.launches_per_step * (ND - 1) * args.steps
+    exchange = "none" if world == 1 else ("p2p-kernel" if model.use_p2p else "nccl")
+    model.close()
+    if rank != 0:
+        return
+    step_ms = dec / (ND - 1)
+    wbytes = mf.decode_weight_bytes(cfg)
+    lm = cfg["vocab"] * cfg["hidden"] // 32 * 18  # the lm_head stream is replicated on every rank
+    per_rank = (wbytes - lm) / world + lm
+    peak = peaks.get("hbm_gbs", 6650.0)
+    out = {
+        "metric": "llama2_7b_q4_0_prefill512_decode256_tok_s", "value": round((S + ND) / (pre + dec) * 1e3, 1), "unit": "tok/s", "n_gpus": world,
+        "steps": args.steps, "warmup": max(args.warmup, 1), "ms_per_step": round(pre + dec, 3), "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+        "dtype": "int8 block dot (Q4_0 x Q8_0) + fp32 accumulate, fp16 KV", "data": "synthetic",
+        "config": {"workload": "LLaMA-2-7B Q4_0 (BASELINE configs[1]): one request, prefill 512 + greedy decode 256, random-init .mllm; every Linear sharded over the ranks",
+                   "l2": "weights 3.7 GB / N per decode step >> 126 MB L2 (inputs larger than L2)", "parallelism": f"tp{world}", "exchange": exchange},
+        "decode_step": {"ms": round(step_ms, 4), "GB_per_rank": round(per_rank / 1e9, 4), "GBs_per_rank": round(per_rank / (step_ms * 1e-3) / 1e9, 1),
+                        "frac_of_hbm_peak": round(per_rank / (step_ms * 1e-3) / 1e9 / peak, 4), "exchanges_per_token": 0 if world == 1 else 2 * cfg["layers"],
+                        "exchange_bytes": cfg["hidden"] * 4},
+        "prefill": {"ms": round(pre, 3), "tok_s": round(S / pre * 1e3, 1)},
+        "e2e": {"value": round((S + ND) / wall * 1e3, 1), "unit": "tok/s", "h2d_bytes_per_step": S * 4, "d2h_bytes_per_step": ND * 4 + 8, "ms_per_step": round(wall, 2)},
+        "gpu_launches": int(launches), "clocks": clocks, "tokens_head": toks[:8],
+    }
+    print(json.dumps(out), flush=True)
+
+
 def reference_arm(args, rank, world):
     if rank != 0:
         return
@@ -456,8 +538,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu", action="store_true")
-    ap.add_argument("--config", default=os.environ.get("MLLM_BENCH_CONFIG", "c2"), choices=["c2", "c5"],
-                    help="c2: LLaMA-2-7B single request (the headline metric, default); c5: Qwen1.5-1.8B batched decode, data-parallel")
+    ap.add_argument("--config", default=os.environ.get("MLLM_BENCH_CONFIG", "c2"), choices=["c2", "c5", "tp"],
+                    help="c2: LLaMA-2-7B single request (the headline metric, default); c5: Qwen1.5-1.8B batched decode, data-parallel; tp: the 7B request with tensor-parallel Linears over the ranks")
     ap.add_argument("--batch", type=int, default=int(os.environ.get("MLLM_BENCH_BATCH", "64")), help="c5: requests per GPU")
     ap.add_argument("--cpu-prefill", type=int, default=0, help="CPU sample: prompt tokens (0 = 512 when steps <= 2, else 128 / 64 so the run stays within minutes)")
     ap.add_argument("--cpu-decode", type=int, default=0, help="CPU sample: decode steps (0 = 32 / 16 / 8 by the same rule)")
@@ -472,7 +554,9 @@ def main():
         import torch.distributed as dist
         torch.cuda.set_device(local_rank)
         dist.init_process_group("nccl")
-    if args.config == "c5":
+    if args.config == "tp":
+        gpu_arm_tp(args, rank, world, local_rank)
+    elif args.config == "c5":
         gpu_arm_c5(args, rank, world, local_rank)
     else:
         gpu_arm(args, rank, world, local_rank)

@@ -347,6 +347,15 @@ int mllmcu_argmax(const float *logits, int rows, int n, int *out, void *stream);
  * tokenizers/Tokenizer.hpp:78-101) so the next step's input never leaves the device */
 int mllmcu_argmax_ids(const float *logits, int rows, int n, float *ids_out, void *stream);
 
+/* ---- top-k / top-p sampling on the device: _LlmTextGenerateTopkSamplingMethod::generate (Generate.cpp:45-91, mode 0, p_or_k = k in
+ * 2..1024) and _LlmTextGenerateToppSamplingMethod::generate (Generate.cpp:93-143, mode 1, p_or_k = p; x must hold probabilities,
+ * at most 1024 candidates).  x [rows][n] (row stride ldx); candidates in descending order, softmax with temperature in the
+ * reference's float / double mix, renormalised, and the draw of std::discrete_distribution with the caller's u[row] in [0, 1)
+ * in place of the reference's unseeded generator.  ws: rows * n floats of scratch; ids_out[row] = the sampled id as fp32; optional
+ * cand_p / cand_idx [rows][cand_cap] and n_cand [rows] return the candidate distribution (what the parity tests compare). */
+int mllmcu_sample(int mode, const float *x, int rows, int n, long long ldx, float p_or_k, float temperature, const float *u, float *ws, float *ids_out,
+                  float *cand_p, int *cand_idx, int *n_cand, int cand_cap, void *stream);
+
 /* ---- single-token decode step, graph-replayable: per-step scalars live in device memory.
  * ctl[0] = position of the token being consumed (== KV length before its append).
  * mllmcu_decode_embed: CPUEmbedding Q4_0 gather (op/CPUEmbedding.cpp:66-81) and ctl[0] += 1 (ctl may be NULL). */

@@ -85,6 +85,7 @@ SYMBOLS = {
     "mllmcu_ipc_close": (_i, [_vp]),
     "mllmcu_p2p_bump": (_i, [_vp, _vp]),
     "mllmcu_p2p_allreduce": (_i, [_i, _i, _vp, _sz, _sz, _vp, _vp, _vp, _i, _vp]),
+    "mllmcu_sample": (_i, [_i, _vp, _i, _i, _ll, _f, _f, _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp]),
     "mllmcu_where_eq": (_i, [_vp, _ll, _f, _vp, _vp, _vp]),
     "mllmcu_where_unravel": (_i, [_vp, _i, _vp, _i, _vp, _vp]),
     "mllmcu_index_put_rows": (_i, [_vp, _ll, _vp, _ll, _vp, _i, _i, _vp]),
@@ -513,6 +514,21 @@ def decode_attn_rope(rope_type, qkv, kcache, vcache, ctl, Hq, D, sin_t, cos_t, p
                                         _ptr(sin_t), _ptr(cos_t), sin_t.shape[1], kcache.stride(0), kcache.shape[1], _ptr(ws), ws.numel(), int(pdl),
                                         _stream()), "decode_attn_rope")
     return o
+
+
+def sample(x, u, k=None, p=None, temperature=1.0, cand_cap=64):
+    """Top-k (k given; x = logits) or top-p (p given; x = probabilities) sampling of each row with the uniform numbers u [rows].
+    Returns (ids fp32 [rows], candidate probabilities [rows, cand_cap], candidate ids int32 [rows, cand_cap], candidate counts int32 [rows])."""
+    import torch
+    rows, n = x.shape
+    ws = torch.empty((rows, n), dtype=torch.float32, device=x.device)
+    ids = torch.empty((rows,), dtype=torch.float32, device=x.device)
+    cp = torch.zeros((rows, cand_cap), dtype=torch.float32, device=x.device)
+    ci = torch.full((rows, cand_cap), -1, dtype=torch.int32, device=x.device)
+    nc = torch.zeros((rows,), dtype=torch.int32, device=x.device)
+    check(lib().mllmcu_sample(0 if k is not None else 1, _ptr(x), rows, n, x.stride(0), float(k if k is not None else p), float(temperature), _ptr(u), _ptr(ws), _ptr(ids),
+                              _ptr(cp), _ptr(ci), _ptr(nc), cand_cap, _stream()), "sample")
+    return ids, cp, ci, nc
 
 
 def decode_argmax(logits, ctl=None, tok_log=None):

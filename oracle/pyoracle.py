@@ -537,3 +537,67 @@ class RefGraph:
         if self.h:
             self.L.cpuref_model_destroy(self.h)
             self.h = None
+
+
+# ---------------------------------------------------------------------------------------------------------------- samplers
+# Restatement of _LlmTextGenerateTopkSamplingMethod::generate (Generate.cpp:45-91) and _LlmTextGenerateToppSamplingMethod::generate
+# (Generate.cpp:93-143) up to the random draw: the candidate ids and the probabilities handed to std::discrete_distribution, in the
+# reference's float / double mix.  Pinned statistically against the reference itself (cpuref_sample_hist draws from the compiled
+# classes; tests/test_sampling.py).  TEST INFRASTRUCTURE ONLY.
+def _softmax_candidates(vals, temperature):
+    vals = np.asarray(vals, dtype=np.float32)
+    mx = np.float64(vals.max())
+    e = np.exp((vals.astype(np.float64) - mx) / np.float64(np.float32(temperature))).astype(np.float32)  # softmax[i] = exp(double) -> float
+    sum_exp = np.float64(0.0)
+    for v in e:
+        sum_exp += np.float64(v)
+    p = (e.astype(np.float64) / sum_exp).astype(np.float32)                                               # value /= sum_exp (float /= double)
+    s2 = np.float64(0.0)
+    for v in p:
+        s2 += np.float64(v)
+    return (p / np.float32(s2)).astype(np.float32)                                                        # value /= _sum (float)
+
+
+def sample_topk_candidates(logits, k, temperature):
+    """-> (ids [k] in descending order of logit, lowest id first among equals; probabilities [k])."""
+    x = np.asarray(logits, dtype=np.float32)
+    order = np.lexsort((np.arange(x.size), -x.astype(np.float64)))[:k]
+    return order.astype(np.int64), _softmax_candidates(x[order], temperature)
+
+
+def sample_topp_candidates(probs, p, temperature):
+    x = np.asarray(probs, dtype=np.float32)
+    order = np.lexsort((np.arange(x.size), -x.astype(np.float64)))
+    cum, n = np.float32(0.0), 0
+    while cum < np.float32(p):
+        cum = np.float32(cum + x[order[n]])
+        n += 1
+    ids = order[:n].astype(np.int64)
+    if n == 1:
+        return ids, np.ones(1, dtype=np.float32)
+    return ids, _softmax_candidates(x[ids], temperature)
+
+
+def sample_draw(probs, u):
+    """std::discrete_distribution: weights / their double sum, running sums, first bucket whose running sum exceeds u."""
+    w = np.asarray(probs, dtype=np.float32).astype(np.float64)
+    tot = np.float64(0.0)
+    for v in w:
+        tot += v
+    run = np.float64(0.0)
+    for i, v in enumerate(w):
+        run += v / tot
+        if u < run:
+            return i
+    return len(w) - 1
+
+
+def ref_sample_hist(mode, x, p_or_k, temperature, draws):
+    """Counts of `draws` calls of the REFERENCE's sampler on row x (mode 0 top-k on logits, 1 top-p on probabilities)."""
+    L = cpuref()
+    x = np.ascontiguousarray(x, dtype=np.float32)
+    counts = np.zeros(x.size, dtype=np.uint32)
+    L.cpuref_sample_hist.argtypes = [C.c_int, C.c_void_p, C.c_int, C.c_float, C.c_float, C.c_int, C.c_void_p]
+    rc = L.cpuref_sample_hist(mode, x.ctypes.data, x.size, C.c_float(p_or_k), C.c_float(temperature), draws, counts.ctypes.data)
+    assert rc == 0
+    return counts

@@ -17,6 +17,7 @@
 #include <omp.h>
 
 #include "Backend.hpp"
+#include "Generate.hpp"
 #include "Layer.hpp"
 #include "Module.hpp"
 #include "Op.hpp"
@@ -259,3 +260,25 @@ API int cpuref_model_generate(void *h, const float *ids, int B, int S, int max_n
 API void cpuref_model_clear(void *h) { ((RefModel *)h)->m->clear_kvcache(); }
 
 API void cpuref_model_destroy(void *h) { delete (RefModel *)h; }
+
+// ------------------------------------------------------------------ (iii) the reference's samplers, drawn many times
+// _LlmTextGenerateTopkSamplingMethod / _LlmTextGenerateToppSamplingMethod (Generate.cpp:45-143) seed a fresh std::mt19937 from
+// std::random_device on every call, so a single draw cannot be reproduced; their DISTRIBUTION can: counts[id] = how often id came out
+// of `draws` calls on the same row (mode 0: top-k on logits, mode 1: top-p on probabilities).
+API int cpuref_sample_hist(int mode, const float *x, int n, float p_or_k, float temperature, int draws, unsigned *counts) {
+    Tensor t(1, 1, 1, n, cpu_backend(), true);
+    memcpy(t.hostPtr<float>(), x, (size_t)n * 4);
+    memset(counts, 0, (size_t)n * 4);
+    try {
+        if (mode == 0) {
+            _LlmTextGenerateTopkSamplingMethod m((int)p_or_k, temperature);
+            for (int i = 0; i < draws; i++) counts[m.generate(t)]++;
+        } else {
+            _LlmTextGenerateToppSamplingMethod m(p_or_k, temperature);
+            for (int i = 0; i < draws; i++) counts[m.generate(t)]++;
+        }
+    } catch (const std::exception &) {
+        return -1;
+    }
+    return 0;
+}
