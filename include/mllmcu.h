@@ -352,7 +352,8 @@ int mllmcu_argmax_ids(const float *logits, int rows, int n, float *ids_out, void
  * at most 1024 candidates).  x [rows][n] (row stride ldx); candidates in descending order, softmax with temperature in the
  * reference's float / double mix, renormalised, and the draw of std::discrete_distribution with the caller's u[row] in [0, 1)
  * in place of the reference's unseeded generator.  ws: rows * n floats of scratch; ids_out[row] = the sampled id as fp32; optional
- * cand_p / cand_idx [rows][cand_cap] and n_cand [rows] return the candidate distribution (what the parity tests compare). */
+ * cand_p / cand_idx [rows][cand_cap] and n_cand [rows] return the candidate distribution (what the parity tests compare); n_cand < 0:
+ * top-p hit the 1024-candidate limit before its running sum reached p (the draw is from those 1024). */
 int mllmcu_sample(int mode, const float *x, int rows, int n, long long ldx, float p_or_k, float temperature, const float *u, float *ws, float *ids_out,
                   float *cand_p, int *cand_idx, int *n_cand, int cand_cap, void *stream);
 

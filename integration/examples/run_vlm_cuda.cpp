@@ -161,9 +161,11 @@ struct StepLog {
 static void print_json(const char *model, int device, int prompt_tokens, const StepLog &log, const Module &m) {
     double dec = 0;
     for (size_t i = 1; i < m.inference_times_.size(); i++) dec += m.inference_times_[i];
-    printf("{\"model\": \"%s\", \"device\": %d, \"prompt_tokens\": %d, \"decode\": %zu, \"prefill_ms\": %.3f, \"decode_ms_per_step\": %.4f, \"tokens\": [", model, device,
-           prompt_tokens, log.tokens.size(), m.inference_times_.empty() ? 0.0 : m.inference_times_[0],
-           m.inference_times_.size() > 1 ? dec / (m.inference_times_.size() - 1) : 0.0);
+    std::vector<double> tail(m.inference_times_.begin() + std::min<size_t>(m.inference_times_.size(), 1), m.inference_times_.end());
+    std::sort(tail.begin(), tail.end());
+    printf("{\"model\": \"%s\", \"device\": %d, \"prompt_tokens\": %d, \"decode\": %zu, \"prefill_ms\": %.3f, \"decode_ms_per_step\": %.4f, \"decode_ms_median\": %.4f, "
+           "\"decode_ms_max\": %.3f, \"tokens\": [", model, device, prompt_tokens, log.tokens.size(), m.inference_times_.empty() ? 0.0 : m.inference_times_[0],
+           m.inference_times_.size() > 1 ? dec / (m.inference_times_.size() - 1) : 0.0, tail.empty() ? 0.0 : tail[tail.size() / 2], tail.empty() ? 0.0 : tail.back());
     for (size_t i = 0; i < log.tokens.size(); i++) printf("%s%u", i ? ", " : "", log.tokens[i]);
     printf("]}\n");
 }

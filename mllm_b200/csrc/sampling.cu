@@ -103,7 +103,8 @@ __global__ void __launch_bounds__(1024) k_sample(const float *__restrict__ x, in
             c_val[0] = 1.f;
         }
         ids_out[row] = (float)c_idx[pick];
-        if (n_cand_out) n_cand_out[row] = cnt;
+        // top-p that ran into the candidate limit before reaching p: reported as -count (the sample is from the truncated set)
+        if (n_cand_out) n_cand_out[row] = (mode == 1 && cum < p_or_k && cnt < n) ? -cnt : cnt;
         s_n = cnt;
     }
     __syncthreads();

@@ -193,7 +193,7 @@ class TPLlama:
         self.plan = shard_plan(cfg, world)[rank]
         tensors, _ = mf.read_mllm(path)
         sh = shard_tensors(tensors, cfg, rank, world)
-        self.w = {k: torch.from_numpy(np.ascontiguousarray(v)).to(self.dev) for k, v in sh.items()}
+        self.w = {k: torch.from_numpy(np.array(v, copy=True)).to(self.dev) for k, v in sh.items()}
         n = mf.Names(cfg["rope_type"])
         self.n = n
         D, H = cfg["head_dim"], cfg["hidden"]
@@ -240,8 +240,8 @@ class TPLlama:
         for L in range(cfg["layers"]):
             h = capi.rmsnorm(x, self._lw(L, "attn_norm"), eps)
             q = capi.linear(self._lw(L, "wq"), h, self._bias(L, "bq"))
-            k = capi.linear(self._lw(L, "wk"), h, self._bias(L, "bk"), reuse_quant=True)
-            v = capi.linear(self._lw(L, "wv"), h, self._bias(L, "bv"), reuse_quant=True)
+            k = capi.linear(self._lw(L, "wk"), h, self._bias(L, "bk"))
+            v = capi.linear(self._lw(L, "wv"), h, self._bias(L, "bv"))
             q = capi.rope(rt, q.view(B, S, Hq, D), p0, self.sin, self.cos)
             kc, vc = self.kc[L], self.vc[L]
             capi.rope(rt, k.view(B, S, Hkv, D), p0, self.sin, self.cos, out_f16=True, out=kc[:, p0:], out_bstride=kc.stride(0), out_sstride=kc.stride(1))
@@ -252,7 +252,7 @@ class TPLlama:
             x = capi.add(x, o)
             h = capi.rmsnorm(x, self._lw(L, "ffn_norm"), eps)
             g = capi.linear(self._lw(L, "w_gate"), h)
-            u = capi.linear(self._lw(L, "w_up"), h, reuse_quant=True)
+            u = capi.linear(self._lw(L, "w_up"), h)
             d = self._reduce(capi.linear(self._lw(L, "w_down"), capi.silu_mul(g, u)))
             x = capi.add(x, d)
         last = x.view(B, S, H)[:, S - 1].contiguous()

@@ -49,7 +49,7 @@ def test_device_sampler_against_restatement(cu, n, mode, arg, T):
     X[1, 17] = X[1, 900]  # a tie: lowest id first
     u = np.array([0.03, 0.5, 0.97], dtype=np.float32)
     ids, cp, ci, nc = cu.sample(torch.from_numpy(X).cuda(), torch.from_numpy(u).cuda(), k=arg if mode == 0 else None, p=arg if mode == 1 else None,
-                                temperature=T, cand_cap=256)
+                                temperature=T, cand_cap=1024)
     ids, cp, ci, nc = ids.cpu().numpy(), cp.cpu().numpy(), ci.cpu().numpy(), nc.cpu().numpy()
     for r in range(rows):
         wi, wp = po.sample_topk_candidates(X[r], arg, T) if mode == 0 else po.sample_topp_candidates(X[r], arg, T)
