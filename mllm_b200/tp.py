@@ -70,7 +70,8 @@ def shard_tensors(tensors, cfg, rank, world):
     D, H, F = cfg["head_dim"], cfg["hidden"], cfg["ffn"]
     p = shard_plan(cfg, world)[rank]
     (q0, q1), (k0, k1), (f0, f1) = p["q"], p["kv"], p["ffn"]
-    out = {n.embed: tensors[n.embed], n.norm: tensors[n.norm], n.lm_head: tensors[n.lm_head]}
+    V = cfg["vocab"]
+    out = {n.embed: np.asarray(tensors[n.embed]).reshape(V, -1), n.norm: tensors[n.norm], n.lm_head: np.asarray(tensors[n.lm_head]).reshape(V, -1)}
     for L in range(cfg["layers"]):
         out[n.layer(L, "attn_norm")] = tensors[n.layer(L, "attn_norm")]
         out[n.layer(L, "ffn_norm")] = tensors[n.layer(L, "ffn_norm")]

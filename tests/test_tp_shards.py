@@ -51,7 +51,7 @@ def test_shards_reassemble_to_the_parameters():
         full = np.asarray(t[n.layer(0, role)]).reshape(H, K // 32, 18)
         got = np.concatenate([s[n.layer(0, role)].reshape(H, -1, 18) for s in sh], axis=1)
         assert np.array_equal(got, full)
-    assert sh[0][n.embed] is t[n.embed] and np.array_equal(sh[1][n.norm], t[n.norm])
+    assert np.array_equal(sh[0][n.embed].reshape(-1), np.asarray(t[n.embed]).reshape(-1)) and sh[0][n.embed].shape[0] == cfg["vocab"] and np.array_equal(sh[1][n.norm], t[n.norm])
 
 
 @pytest.mark.parametrize("rt", [2, 4])
