@@ -332,13 +332,14 @@ int mllmcu_f16_to_f32_rows(const void *src, float *dst, int rows, int cols, long
  * order 0..world-1 on every rank (bit-identical results everywhere).  *epoch_ctr (device) must hold the same, never repeated,
  * value on all ranks for one step: mllmcu_p2p_bump once per step.  peer_bases: HOST array of `world` device pointers (own region
  * at [rank]).  world <= 8, n % 4 == 0, one CTA (a decode-sized reduction; prefill goes through NCCL).  A peer that never arrives
- * traps the kernel after 10 s instead of hanging the device. */
+ * traps the kernel after 10 s instead of hanging the device.  pdl != 0: launched with programmatic dependent launch (the kernel waits
+ * for its producer itself and releases its dependents at once, so the next GEMV streams weights during the exchange). */
 int mllmcu_ipc_get_handle(void *dev_ptr, void *handle64);
 int mllmcu_ipc_open(const void *handle64, void **dev_ptr);
 int mllmcu_ipc_close(void *dev_ptr);
 int mllmcu_p2p_bump(unsigned *epoch_ctr, void *stream);
 int mllmcu_p2p_allreduce(int world, int rank, const void *const *peer_bases, size_t buf_offset, size_t flag_offset, const unsigned *epoch_ctr,
-                         const float *residual, float *out, int n, void *stream);
+                         const float *residual, float *out, int n, int pdl, void *stream);
 
 /* ---- greedy sampling: LlmTextGenerator argmax (Generate.cpp:46-53) on device;
  * first maximum wins, as std::max_element does. out: int32 per row. */

@@ -84,7 +84,7 @@ SYMBOLS = {
     "mllmcu_ipc_open": (_i, [_vp, _vp]),
     "mllmcu_ipc_close": (_i, [_vp]),
     "mllmcu_p2p_bump": (_i, [_vp, _vp]),
-    "mllmcu_p2p_allreduce": (_i, [_i, _i, _vp, _sz, _sz, _vp, _vp, _vp, _i, _vp]),
+    "mllmcu_p2p_allreduce": (_i, [_i, _i, _vp, _sz, _sz, _vp, _vp, _vp, _i, _i, _vp]),
     "mllmcu_sample": (_i, [_i, _vp, _i, _i, _ll, _f, _f, _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp]),
     "mllmcu_where_eq": (_i, [_vp, _ll, _f, _vp, _vp, _vp]),
     "mllmcu_where_unravel": (_i, [_vp, _i, _vp, _i, _vp, _vp]),

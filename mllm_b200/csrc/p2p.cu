@@ -55,6 +55,10 @@ static __device__ __forceinline__ float4 ld_peer4(const float *p) { // never thr
 // one CTA; n % 4 == 0.  peers.buf[r] / peers.flags[r] already point at this SITE's buffer / flag words of rank r.
 __global__ void __launch_bounds__(1024) k_p2p_allreduce(P2PPeers peers, int world, int rank, const unsigned *epoch_ctr, const float *__restrict__ residual,
                                                         float *__restrict__ out, int n) {
+    // programmatic dependent launch: the producing GEMV must be complete before its partial is announced; the NEXT kernel (a GEMV that
+    // first streams its own weights) may start right away and meets this kernel's result at its own dependency wait
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     const unsigned epoch = *epoch_ctr;
     const int tid = threadIdx.x;
     if (tid < world) {
@@ -84,14 +88,22 @@ __global__ void __launch_bounds__(1024) k_p2p_allreduce(P2PPeers peers, int worl
 }
 
 MLLMCU_API int mllmcu_p2p_allreduce(int world, int rank, const void *const *peer_bases, size_t buf_offset, size_t flag_offset, const unsigned *epoch_ctr,
-                                    const float *residual, float *out, int n, void *stream) {
+                                    const float *residual, float *out, int n, int pdl, void *stream) {
     if (world < 1 || world > 8 || rank < 0 || rank >= world || n <= 0 || n % 4 || buf_offset % 16 || flag_offset % 4) return -1;
     P2PPeers p;
     for (int r = 0; r < world; r++) {
         p.buf[r] = (const float *)((const char *)peer_bases[r] + buf_offset);
         p.flags[r] = (unsigned *)((char *)peer_bases[r] + flag_offset);
     }
-    k_p2p_allreduce<<<1, 1024, 0, (cudaStream_t)stream>>>(p, world, rank, epoch_ctr, residual, out, n);
-    CU_LAUNCH_CHECK();
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(1);
+    cfg.blockDim = dim3(1024);
+    cfg.stream = (cudaStream_t)stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl ? 1 : 0;
+    CU_TRY(cudaLaunchKernelEx(&cfg, k_p2p_allreduce, p, world, rank, epoch_ctr, residual, out, n));
     return 0;
 }

@@ -167,9 +167,9 @@ class PeerRegion:
     def bump(self):
         capi.check(capi.lib().mllmcu_p2p_bump(self.epoch.data_ptr(), capi._stream()), "p2p_bump")
 
-    def allreduce(self, site, residual, out, n):
+    def allreduce(self, site, residual, out, n, pdl=False):
         capi.check(capi.lib().mllmcu_p2p_allreduce(self.world, self.rank, self.bases, self.buf_offset(site), self.flag_offset(site), self.epoch.data_ptr(),
-                                                   capi._ptr(residual), capi._ptr(out), n, capi._stream()), "p2p_allreduce")
+                                                   capi._ptr(residual), capi._ptr(out), n, int(pdl), capi._stream()), "p2p_allreduce")
 
     def close(self):
         lib = capi.lib()
@@ -212,6 +212,7 @@ class TPLlama:
         self.peer = PeerRegion(dist, rank, world, 2 * cfg["layers"], batch * H) if self.use_p2p else None
         self.graph = None
         self.launches_per_step = 0
+        self.pdl = os.environ.get("MLLM_CUDA_NO_PDL", "0") in ("", "0")
 
     # ---- parameters of layer L
     def _lw(self, L, role):
@@ -274,13 +275,16 @@ class TPLlama:
         n_launch += 1
         for L in range(cfg["layers"]):
             bq = [self._bias(L, "bq"), self._bias(L, "bk"), self._bias(L, "bv")] if cfg["qkv_bias"] else None
-            qkv = capi.gemv_fused([self._lw(L, "wq"), self._lw(L, "wk"), self._lw(L, "wv")], x, norm_w=self._lw(L, "attn_norm"), eps=eps, biases=bq)
-            a = capi.decode_attn_rope(rt, qkv, self.kc[L], self.vc[L], self.ctl, Hq, D, self.sin, self.cos)
+            # programmatic dependent launch as in the 1-GPU plan (csrc/host/Module.cpp issue_step): layer 0's projection releases its
+            # dependents only after its own wait (2), so everything behind it may read the position ahead of its own wait
+            qkv = capi.gemv_fused([self._lw(L, "wq"), self._lw(L, "wk"), self._lw(L, "wv")], x, norm_w=self._lw(L, "attn_norm"), eps=eps, biases=bq,
+                                  pdl=(2 if L == 0 else 1) if self.pdl else 0)
+            a = capi.decode_attn_rope(rt, qkv, self.kc[L], self.vc[L], self.ctl, Hq, D, self.sin, self.cos, pdl=2 if self.pdl else 0)
             x = self._row_parallel(2 * L, [self._lw(L, "wo")], a, x, epilogue=0)
             x = self._row_parallel(2 * L + 1, [self._lw(L, "w_down")],
-                                   capi.gemv_fused([self._lw(L, "w_gate"), self._lw(L, "w_up")], x, norm_w=self._lw(L, "ffn_norm"), eps=eps, epilogue=2), x, epilogue=0)
+                                   capi.gemv_fused([self._lw(L, "w_gate"), self._lw(L, "w_up")], x, norm_w=self._lw(L, "ffn_norm"), eps=eps, epilogue=2, pdl=self.pdl), x, epilogue=0)
             n_launch += 4 + (2 if self.world > 1 else 0) + (2 if (self.world > 1 and not self.peer) else 0)
-        logits = capi.gemv_fused([self.w[self.n.lm_head]], x, norm_w=self.w[self.n.norm], eps=eps)
+        logits = capi.gemv_fused([self.w[self.n.lm_head]], x, norm_w=self.w[self.n.norm], eps=eps, pdl=self.pdl)
         nxt = capi.decode_argmax(logits)
         self.launches_per_step = n_launch + 2
         return logits, nxt
@@ -290,14 +294,14 @@ class TPLlama:
         kernel with the residual add; NCCL -> partial, all_reduce, add."""
         torch = self.torch
         if self.world == 1:
-            return capi.gemv_fused(Ws, a, epilogue=1, residual=residual)
+            return capi.gemv_fused(Ws, a, epilogue=1, residual=residual, pdl=self.pdl)
         if self.peer:
             y = self.peer.buf(site, self.B, self.H)
-            capi.gemv_fused_ex(Ws, a, y)
+            capi.gemv_fused_ex(Ws, a, y, pdl=self.pdl)
             out = torch.empty_like(residual)
-            self.peer.allreduce(site, residual, out, self.B * self.H)
+            self.peer.allreduce(site, residual, out, self.B * self.H, pdl=self.pdl)
             return out
-        part = capi.gemv_fused(Ws, a)
+        part = capi.gemv_fused(Ws, a, pdl=self.pdl)
         self.dist.all_reduce(part)
         return capi.add(residual, part)
 
