@@ -484,7 +484,7 @@ def gpu_arm_tp(args, rank, world, local_rank):
     clocks = sampler.stop()
     pre, dec, wall = max_over_ranks([float(np.mean(tp_ms)), float(np.mean(td_ms)), float(np.mean(e2e))], world, "cuda")
     launches = model.launches_per_step * (ND - 1) * args.steps
-    exchange = "none" if world == 1 else ("p2p-kernel" if model.use_p2p else "nccl")
+    exchange = "none" if world == 1 else (("p2p-fused-in-gemv" if model.fused_exchange else "p2p-kernel") if model.use_p2p else "nccl")
     model.close()
     if rank != 0:
         return

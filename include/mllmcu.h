@@ -174,6 +174,18 @@ typedef struct mllmcu_gemv_desc {
     int n_pf;
     const void *pf_ptr[8];
     size_t pf_bytes[8];
+    /* tensor-parallel row-parallel Linear (o_proj / down_proj of one rank): xchg_world > 1 makes the launch
+     * "partial GEMV -> all-reduce over peer memory -> + residual" in ONE kernel: the partial goes to this rank's shared region
+     * (y is ignored; epilogue 0, no norm, M <= 2), and the last CTA to finish announces it, waits for the peers and writes
+     * xchg_out[M][N] = xchg_residual + sum over ranks (mllmcu_p2p_allreduce's arithmetic and arguments; xchg_ticket: a device
+     * word, zero before the first launch, that the kernel leaves zero). */
+    int xchg_world, xchg_rank;
+    const void *xchg_peer_bases[8];
+    size_t xchg_buf_offset, xchg_flag_offset;
+    const unsigned *xchg_epoch;
+    unsigned *xchg_ticket;
+    const float *xchg_residual;
+    float *xchg_out;
 } mllmcu_gemv_desc;
 int mllmcu_gemv_fused_ex(const mllmcu_gemv_desc *d, void *stream);
 /* Largest M mllmcu_gemv_fused / _ex accepts: 64 (3..64 rows run on the tensor cores, gemv_mma.cu: one mma.sync.m16n8k32.u8.s8 per

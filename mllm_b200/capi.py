@@ -418,10 +418,12 @@ class GemvDesc(C.Structure):
                 ("residual", C.c_void_p), ("ldr", C.c_int), ("y", C.c_void_p), ("ldy", C.c_int), ("out_f16", C.c_int), ("pdl", C.c_int),
                 ("x_reps", C.c_int), ("norm_reps", C.c_int), ("y_reps", C.c_int), ("x_rep_stride", C.c_longlong),
                 ("norm_rep_stride", C.c_longlong), ("y_rep_stride", C.c_longlong), ("n_pf", C.c_int), ("pf_ptr", C.c_void_p * 8),
-                ("pf_bytes", C.c_size_t * 8)]
+                ("pf_bytes", C.c_size_t * 8), ("xchg_world", C.c_int), ("xchg_rank", C.c_int), ("xchg_peer_bases", C.c_void_p * 8),
+                ("xchg_buf_offset", C.c_size_t), ("xchg_flag_offset", C.c_size_t), ("xchg_epoch", C.c_void_p), ("xchg_ticket", C.c_void_p),
+                ("xchg_residual", C.c_void_p), ("xchg_out", C.c_void_p)]
 
 
-def gemv_fused_ex(Ws, x, y, norm_w=None, eps=1e-6, epilogue=0, residual=None, pdl=False, x_reps=1, norm_reps=1, y_reps=1, lookahead=()):
+def gemv_fused_ex(Ws, x, y, norm_w=None, eps=1e-6, epilogue=0, residual=None, pdl=False, x_reps=1, norm_reps=1, y_reps=1, lookahead=(), xchg=None):
     """Descriptor form of gemv_fused.  x: cuda fp32 [x_reps, M, K]; norm_w: [norm_reps, K]; y: preallocated [y_reps, M, N];
     residual: [M, N] (copy 0); lookahead: (device pointer, bytes) pairs for the L2 look-ahead."""
     d = GemvDesc()
@@ -441,6 +443,14 @@ def gemv_fused_ex(Ws, x, y, norm_w=None, eps=1e-6, epilogue=0, residual=None, pd
     d.n_pf = len(lookahead)
     for i, (ptr, nbytes) in enumerate(lookahead):
         d.pf_ptr[i], d.pf_bytes[i] = ptr, nbytes
+    if xchg is not None:  # dict(world, rank, bases (c_void_p * world), buf_offset, flag_offset, epoch, ticket, residual, out): see mllmcu_gemv_desc.xchg_*
+        d.xchg_world, d.xchg_rank = xchg["world"], xchg["rank"]
+        for r in range(xchg["world"]):
+            d.xchg_peer_bases[r] = xchg["bases"][r]
+        d.xchg_buf_offset, d.xchg_flag_offset = xchg["buf_offset"], xchg["flag_offset"]
+        d.xchg_epoch, d.xchg_ticket = xchg["epoch"].data_ptr(), xchg["ticket"].data_ptr()
+        d.xchg_residual = xchg["residual"].data_ptr() if xchg.get("residual") is not None else None
+        d.xchg_out = xchg["out"].data_ptr()
     check(lib().mllmcu_gemv_fused_ex(C.byref(d), _stream()), "gemv_fused_ex")
     return y
 

@@ -12,8 +12,12 @@
 // reading this one (stream order) -- so no double buffering is needed as long as a step has two or more sites.  Epochs come from a
 // device counter bumped once per step (graph-replayable: nothing per-step is a kernel argument).
 // Prefill-sized reductions (hundreds of rows) are bandwidth-bound and go through NCCL (mllm_b200/tp.py).
+// The same exchange also runs as the TAIL of the producing GEMV (gemv_tma.cu, mllmcu_gemv_desc.xchg_*): the last CTA of the Linear to
+// finish does steps 1-3, so "row-parallel Linear + all-reduce + residual" is one launch; this standalone kernel serves producers that
+// are not that GEMV (batches on the tensor-core kernel, tests).
 #include "common.cuh"
 #include "mllmcu.h"
+#include "p2p.cuh"
 
 MLLMCU_API int mllmcu_ipc_get_handle(void *dev_ptr, void *handle64) {
     static_assert(sizeof(cudaIpcMemHandle_t) == 64, "ipc handle size");
@@ -38,20 +42,6 @@ MLLMCU_API int mllmcu_p2p_bump(unsigned *epoch_ctr, void *stream) {
     return 0;
 }
 
-struct P2PPeers { const float *buf[8]; unsigned *flags[8]; };
-
-static __device__ __forceinline__ void st_release_sys(unsigned *p, unsigned v) { asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory"); }
-static __device__ __forceinline__ unsigned ld_acquire_sys(const unsigned *p) {
-    unsigned v;
-    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-    return v;
-}
-static __device__ __forceinline__ float4 ld_peer4(const float *p) { // never through L1: the line may hold the previous step's partial
-    float4 v;
-    asm volatile("ld.relaxed.sys.global.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
-    return v;
-}
-
 // one CTA; n % 4 == 0.  peers.buf[r] / peers.flags[r] already point at this SITE's buffer / flag words of rank r.
 __global__ void __launch_bounds__(1024) k_p2p_allreduce(P2PPeers peers, int world, int rank, const unsigned *epoch_ctr, const float *__restrict__ residual,
                                                         float *__restrict__ out, int n) {
@@ -59,32 +49,7 @@ __global__ void __launch_bounds__(1024) k_p2p_allreduce(P2PPeers peers, int worl
     // first streams its own weights) may start right away and meets this kernel's result at its own dependency wait
     asm volatile("griddepcontrol.wait;" ::: "memory");
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
-    const unsigned epoch = *epoch_ctr;
-    const int tid = threadIdx.x;
-    if (tid < world) {
-        __threadfence_system(); // the producer's stores (earlier kernel, this stream) before the flag
-        st_release_sys(peers.flags[tid] + rank, epoch);
-        const unsigned *mine = peers.flags[rank] + tid;
-        unsigned long long t0 = 0;
-        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
-        while (ld_acquire_sys(mine) != epoch) {
-            unsigned long long t1;
-            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
-            if (t1 - t0 > 10000000000ull) __trap(); // 10 s: a peer died or the ranks disagree on the step -- fail, do not hang the box
-        }
-    }
-    __syncthreads();
-    for (int i = tid * 4; i < n; i += blockDim.x * 4) {
-        float4 acc = residual ? *(const float4 *)(residual + i) : make_float4(0.f, 0.f, 0.f, 0.f);
-        float4 v[8];
-#pragma unroll
-        for (int r = 0; r < 8; r++)
-            if (r < world) v[r] = ld_peer4(peers.buf[r] + i);
-#pragma unroll
-        for (int r = 0; r < 8; r++)
-            if (r < world) { acc.x += v[r].x; acc.y += v[r].y; acc.z += v[r].z; acc.w += v[r].w; }
-        *(float4 *)(out + i) = acc;
-    }
+    p2p_exchange_cta(peers, world, rank, *epoch_ctr, residual, out, n);
 }
 
 MLLMCU_API int mllmcu_p2p_allreduce(int world, int rank, const void *const *peer_bases, size_t buf_offset, size_t flag_offset, const unsigned *epoch_ctr,

@@ -153,6 +153,7 @@ class PeerRegion:
             self.bases[r] = q.value
             self.opened.append(q.value)
         self.epoch = torch.zeros(4, dtype=torch.int32, device="cuda")
+        self.ticket = torch.zeros(4, dtype=torch.int32, device="cuda")  # the fused GEMV tail's "last CTA" counter (self-resetting)
         dist.barrier()
 
     def flag_offset(self, site):
@@ -213,6 +214,7 @@ class TPLlama:
         self.graph = None
         self.launches_per_step = 0
         self.pdl = os.environ.get("MLLM_CUDA_NO_PDL", "0") in ("", "0")
+        self.fused_exchange = os.environ.get("MLLM_TP_FUSED", "1") != "0"
 
     # ---- parameters of layer L
     def _lw(self, L, role):
@@ -283,7 +285,7 @@ class TPLlama:
             x = self._row_parallel(2 * L, [self._lw(L, "wo")], a, x, epilogue=0)
             x = self._row_parallel(2 * L + 1, [self._lw(L, "w_down")],
                                    capi.gemv_fused([self._lw(L, "w_gate"), self._lw(L, "w_up")], x, norm_w=self._lw(L, "ffn_norm"), eps=eps, epilogue=2, pdl=self.pdl), x, epilogue=0)
-            n_launch += 4 + (2 if self.world > 1 else 0) + (2 if (self.world > 1 and not self.peer) else 0)
+            n_launch += 4 + ((0 if (self.fused_exchange and self.B <= 2) else 2) if self.peer else (4 if self.world > 1 else 0))
         logits = capi.gemv_fused([self.w[self.n.lm_head]], x, norm_w=self.w[self.n.norm], eps=eps, pdl=self.pdl)
         nxt = capi.decode_argmax(logits)
         self.launches_per_step = n_launch + 2
@@ -297,8 +299,13 @@ class TPLlama:
             return capi.gemv_fused(Ws, a, epilogue=1, residual=residual, pdl=self.pdl)
         if self.peer:
             y = self.peer.buf(site, self.B, self.H)
-            capi.gemv_fused_ex(Ws, a, y, pdl=self.pdl)
             out = torch.empty_like(residual)
+            if self.fused_exchange and self.B <= 2:  # Linear + exchange + residual in ONE launch: the GEMV's last CTA does the exchange
+                capi.gemv_fused_ex(Ws, a, y, pdl=self.pdl, xchg=dict(world=self.world, rank=self.rank, bases=self.peer.bases, buf_offset=self.peer.buf_offset(site),
+                                                                       flag_offset=self.peer.flag_offset(site), epoch=self.peer.epoch, ticket=self.peer.ticket,
+                                                                       residual=residual, out=out))
+                return out
+            capi.gemv_fused_ex(Ws, a, y, pdl=self.pdl)
             self.peer.allreduce(site, residual, out, self.B * self.H, pdl=self.pdl)
             return out
         part = capi.gemv_fused(Ws, a, pdl=self.pdl)

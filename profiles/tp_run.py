@@ -75,7 +75,7 @@ def main():
         dist.all_gather_object(allt, tokens)
         assert all(x == allt[0] for x in allt), "ranks disagree on the tokens"
     if rank == 0:
-        print(json.dumps({"model": a.model, "tp": world, "exchange": "none" if world == 1 else ("p2p-kernel" if m.use_p2p else "nccl"), "prompt": a.prompt, "decode": a.decode,
+        print(json.dumps({"model": a.model, "tp": world, "exchange": "none" if world == 1 else (("p2p-fused-in-gemv" if m.fused_exchange else "p2p-kernel") if m.use_p2p else "nccl"), "prompt": a.prompt, "decode": a.decode,
                           "prefill_ms": round(float(t[0]), 3), "decode_ms_per_token": round(float(t[1]) / a.decode, 4), "launches_per_step": m.launches_per_step,
                           "graph": not a.no_graph, "tokens": tokens[:32]}), flush=True)
     m.close()

@@ -40,14 +40,14 @@ def test_world_1_equals_the_product_model(model, tmp_path):
     assert one["launches_per_step"] == 3 + 4 * cfg["layers"]
 
 
-@pytest.mark.parametrize("exchange", ["p2p-kernel", "nccl"])
+@pytest.mark.parametrize("exchange", ["p2p-fused-in-gemv", "p2p-kernel", "nccl"])
 def test_two_ranks_match_one(exchange, tmp_path):
     import torch
     if torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs (gpurun --gpus 2)")
     args = ["--model", "toy-gqa", "--prompt", 16, "--decode", 24, "--limit", 128]
     one = launch(1, args + ["--save", tmp_path / "one.npz"])
-    two = launch(2, args + ["--save", tmp_path / "two.npz"], env={"MLLM_TP_NCCL": "1" if exchange == "nccl" else "0"})
+    two = launch(2, args + ["--save", tmp_path / "two.npz"], env={"MLLM_TP_NCCL": "1" if exchange == "nccl" else "0", "MLLM_TP_FUSED": "1" if exchange == "p2p-fused-in-gemv" else "0"})
     assert two["tp"] == 2 and two["exchange"] == exchange
     a, b = np.load(tmp_path / "one.npz"), np.load(tmp_path / "two.npz")
     for key in ("logits0",):  # the prefill logits: before any token feedback
