@@ -12,7 +12,9 @@ all-gather/all-reduce over NVLink").  One process per GPU (torch.di
 The all-reduce is where the time goes: a decode step has 2 per layer, each 16 KiB for the 7B.
   prefill (hundreds of rows, MBs): torch.distributed.all_reduce -> NCCL over NVLink / NVSwitch, bandwidth-bound;
   decode (one row): one kernel per rank over CUDA-IPC peer memory (csrc/p2p.cu: flag exchange + direct peer loads + the residual add
-  fused in), launch-to-result a few microseconds where NCCL's latency is 10-20; MLLM_TP_NCCL=1 keeps NCCL there for comparison.
+  fused in), launched with programmatic dependent launch so it sits resident behind the producing GEMV and the next GEMV starts
+  streaming its weights during the exchange; MLLM_TP_NCCL=1 keeps NCCL there for comparison (B200 x 2, LLaMA-2-7B: 1.44 ms/token
+  against 1.97 with NCCL and 1.45 on one GPU).
 The whole decode step (embedding, 7 launches per layer, head, pick) is captured in a CUDA graph per rank and replayed in lockstep.
 
 The reference has no counterpart (one process, CPUBackend threads); the arithmetic per rank is the reference's Linear / RMSNorm / RoPE
@@ -214,7 +216,11 @@ class TPLlama:
         self.graph = None
         self.launches_per_step = 0
         self.pdl = os.environ.get("MLLM_CUDA_NO_PDL", "0") in ("", "0")
-        self.fused_exchange = os.environ.get("MLLM_TP_FUSED", "1") != "0"
+        # MLLM_TP_FUSED=1: the exchange as the producing GEMV's tail (one launch instead of two).  Measured slower on B200 at TP 2 (1.69
+        # against 1.44 ms/token): the next GEMV, released at the producer's START, is already streaming its weights when the tail
+        # exchanges, and the flag round trip queues behind that traffic; as a separate kernel the exchange overlaps the next GEMV's
+        # launch ramp instead.  Kept selectable for that comparison; default off.
+        self.fused_exchange = os.environ.get("MLLM_TP_FUSED", "0") == "1"
 
     # ---- parameters of layer L
     def _lw(self, L, role):
