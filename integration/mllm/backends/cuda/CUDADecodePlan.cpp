@@ -19,6 +19,7 @@
 #include "backends/cpu/op/CPUKVCache.hpp"
 #include "mllmcu.h"
 
+#include <algorithm>
 #include <cstdlib>
 #include <iostream>
 
@@ -37,7 +38,10 @@ struct CUDABackend::DecodePlan {
     std::vector<L> layers;
     CUDAFuseInfo embd, norm, head;
     Tensor x, x2, qkv, ao, g, logits, ids, ctl, attn_ws;
-    size_t attn_ws_bytes = 0;
+    Tensor t1, t2, gu, lin_ws; // k-quant models: normalised row, Linear output, up projection, the Linears' Q8_K workspace
+    size_t attn_ws_bytes = 0, lin_ws_bytes = 0;
+    bool kquant = false;       // Linears are Q4_K / Q6_K: op-level kernels on fixed buffers inside the captured graph
+    int launches = 0;
     int dev_pos = -2, ctl_host = 0;
     bool warmed = false, use_graph = true, use_pdl = true, unsupported = false;
     void *graph = nullptr;
@@ -59,6 +63,8 @@ struct DecodePlanBuilder {
         std::vector<Op *> ops;
         for (Op *o : rec)
             if (o->type() != F_VIEW) ops.push_back(o);
+        // LLaVAModel::Forward ends with clip({}, {}, {-1}, {}) (modeling_llava.hpp:135): on a one-token forward that is the identity
+        if (!ops.empty() && ops.back()->type() == F_CLIP) ops.pop_back();
         static const OpType block[18] = {RMSNORM, LINEAR, LINEAR, LINEAR, ROPE, ROPE, KVCACHE, KVCACHE, F_FA2, LINEAR, F_TTADD,
                                          RMSNORM, LINEAR, SILU, LINEAR, F_TTMUL, LINEAR, F_TTADD};
         if (ops.size() < 3 + 18 || (ops.size() - 3) % 18 != 0) return nullptr;
@@ -87,8 +93,10 @@ struct DecodePlanBuilder {
             if (!L.q_rope || !L.k_rope || !L.kc || !L.vc) return nullptr;
             L.kptr = L.kc->cache_->rawHostPtr();
             L.vptr = L.vc->cache_->rawHostPtr();
-            for (const CUDAFuseInfo *f : {&L.q, &L.k, &L.v, &L.o, &L.gate, &L.up, &L.down})
-                if (f->wtype != MLLM_TYPE_Q4_0) return nullptr;
+            for (const CUDAFuseInfo *f : {&L.q, &L.k, &L.v, &L.o, &L.gate, &L.up, &L.down}) {
+                if (f->wtype == MLLM_TYPE_Q4_K || f->wtype == MLLM_TYPE_Q6_K) p->kquant = true;
+                else if (f->wtype != MLLM_TYPE_Q4_0) return nullptr;
+            }
             if (L.n1.unit_offset || L.n2.unit_offset) return nullptr;
         }
         const auto &L0 = p->layers[0];
@@ -104,7 +112,10 @@ struct DecodePlanBuilder {
         p->V = p->head.out;
         p->limit = kc.sequence();
         p->kv_bstride = (long long)kc.sequence() * kc.head() * kc.dimension();
-        if (p->embd.wtype != MLLM_TYPE_Q4_0 || p->head.wtype != MLLM_TYPE_Q4_0 || p->norm.unit_offset) return nullptr;
+        if (p->head.wtype == MLLM_TYPE_Q4_K || p->head.wtype == MLLM_TYPE_Q6_K) p->kquant = true;
+        else if (p->head.wtype != MLLM_TYPE_Q4_0) return nullptr;
+        if (p->embd.wtype != MLLM_TYPE_Q4_0 || p->norm.unit_offset) return nullptr;
+        if (p->kquant && (p->H % 256 || p->F % 256 || (p->Hq * p->D) % 256)) return nullptr; // Q8_K super-blocks
         if (p->H % 128 || p->F % 128 || (p->D != 32 && p->D != 64 && p->D != 128) || L0.rope.rot_dim != p->D || B < 1 || B > 8) return nullptr;
         for (auto &L : p->layers) {
             Tensor &a = *L.kc->cache_, &b = *L.vc->cache_;
@@ -123,6 +134,12 @@ struct DecodePlanBuilder {
         const int QKV = (p->Hq + 2 * p->Hkv) * p->D;
         mk(p->x, B, p->H); mk(p->x2, B, p->H); mk(p->qkv, B, QKV); mk(p->ao, B, p->Hq * p->D); mk(p->g, B, p->F); mk(p->logits, B, p->V);
         mk(p->ids, 1, B); mk(p->ctl, 1, 4);
+        if (p->kquant) {
+            const int widest = std::max(std::max(p->H, p->F), QKV);
+            mk(p->t1, B, widest); mk(p->t2, B, std::max(p->H, p->V)); mk(p->gu, B, p->F);
+            p->lin_ws_bytes = mllmcu_linear_workspace_bytes(B, widest);
+            mk(p->lin_ws, 1, (int)((p->lin_ws_bytes + 3) / 4));
+        }
         p->attn_ws_bytes = mllmcu_decode_attn_workspace_bytes(B, p->Hq, p->D);
         mk(p->attn_ws, 1, (int)((p->attn_ws_bytes + 3) / 4));
         MLLMCU_CHECK(mllmcu_memset(p->attn_ws.rawHostPtr(), 0, p->attn_ws.cntSize(), bn->stream()));
@@ -135,6 +152,7 @@ struct DecodePlanBuilder {
         return p;
     }
 
+    static bool issue_kquant(CUDABackend *bn, CUDABackend::DecodePlan &p);
     // the kernel sequence of one token (five launches per block); false when a fused kernel refuses the shape
     static bool issue(CUDABackend *bn, CUDABackend::DecodePlan &p, bool pdl_on) {
         void *st = bn->stream();
@@ -156,6 +174,8 @@ struct DecodePlanBuilder {
             return true;
         };
         MLLMCU_CHECK(mllmcu_decode_embed(p.embd.weight, p.ids.hostPtr<float>(), x, B, H, ctl, st));
+        if (p.kquant) return issue_kquant(bn, p);
+        p.launches = 2 + 5 * (int)p.layers.size();
         for (size_t li = 0; li < p.layers.size(); li++) {
             auto &l = p.layers[li];
             // layer 0's projection releases its dependents only after its own wait: every later kernel then starts with the embedding
@@ -172,9 +192,50 @@ struct DecodePlanBuilder {
     }
 };
 
+// k-quant models (the LLaVA body is Q4_K): the same step from the op-level kernels -- RMSNorm, Linear (Q8_K activations, integer
+// super-block sums), the fused RoPE + append + attention kernel, add, SiLU * mul -- on the plan's fixed buffers, so the sequence is still
+// captured once and replayed without host dispatch (no fused k-quant GEMV yet).
+bool DecodePlanBuilder::issue_kquant(CUDABackend *bn, CUDABackend::DecodePlan &p) {
+    void *st = bn->stream();
+    const int B = p.B, H = p.H, D = p.D, Hq = p.Hq, Hkv = p.Hkv, F = p.F, QKV = (Hq + 2 * Hkv) * D;
+    int *ctl = (int *)p.ctl.rawHostPtr();
+    float *x = p.x.hostPtr<float>(), *x2 = p.x2.hostPtr<float>(), *qkv = p.qkv.hostPtr<float>(), *ao = p.ao.hostPtr<float>(), *g = p.g.hostPtr<float>();
+    float *t1 = p.t1.hostPtr<float>(), *t2 = p.t2.hostPtr<float>(), *gu = p.gu.hostPtr<float>();
+    void *ws = p.lin_ws.rawHostPtr();
+    int n = 1;
+    auto lin = [&](const CUDAFuseInfo &f, const float *in, int K, float *out, int ldy, int reuse) {
+        MLLMCU_CHECK(mllmcu_linear_ex(f.wtype, f.weight, in, f.bias, out, B, f.out, K, K, ldy, 0, ws, p.lin_ws_bytes, reuse, st));
+        n += 2 - reuse;
+    };
+    for (auto &l : p.layers) {
+        MLLMCU_CHECK(mllmcu_rmsnorm(x, l.n1.norm_w, t1, B, H, l.n1.eps, 0, st));
+        lin(l.q, t1, H, qkv, QKV, 0);
+        lin(l.k, t1, H, qkv + (size_t)Hq * D, QKV, 0); // the k-quant Linear re-quantises per call (its Q8_K image is not shared yet)
+        lin(l.v, t1, H, qkv + (size_t)(Hq + Hkv) * D, QKV, 0);
+        MLLMCU_CHECK(mllmcu_decode_attn_rope(l.rope.rope_type, qkv, QKV, l.kptr, l.vptr, ao, Hq * D, ctl, B, Hq, Hkv, D, l.rope.sin_t, l.rope.cos_t,
+                                             l.rope.rot_dim, p.kv_bstride, p.limit, p.attn_ws.rawHostPtr(), p.attn_ws_bytes, 0, st));
+        lin(l.o, ao, Hq * D, t2, H, 0);
+        MLLMCU_CHECK(mllmcu_add(x, t2, x2, (size_t)B * H, st));
+        MLLMCU_CHECK(mllmcu_rmsnorm(x2, l.n2.norm_w, t1, B, H, l.n2.eps, 0, st));
+        lin(l.gate, t1, H, g, F, 0);
+        lin(l.up, t1, H, gu, F, 0);
+        MLLMCU_CHECK(mllmcu_silu_mul(g, gu, g, (size_t)B * F, st));
+        lin(l.down, g, F, t2, H, 0);
+        MLLMCU_CHECK(mllmcu_add(x2, t2, x, (size_t)B * H, st));
+        n += 6;
+    }
+    MLLMCU_CHECK(mllmcu_rmsnorm(x, p.norm.norm_w, t1, B, H, p.norm.eps, 0, st));
+    lin(p.head, t1, H, p.logits.hostPtr<float>(), p.V, 0);
+    p.launches = n + 1;
+    return true;
+}
+
 // Called by runForward for every outermost forward.  Returns true when `out` holds the logits of a fused step.
 bool CUDABackend::try_decode_plan(Module *module, std::vector<Tensor> &inputs, std::vector<std::any> &args, std::vector<Tensor> &out) {
-    if (!fused_decode || inputs.size() != 1) return false;
+    if (!fused_decode || inputs.empty()) return false;
+    for (size_t i = 1; i < inputs.size(); i++) // LLaVAModel's decode call: {ids, image emptied by chatPostProcessing} (demo_llava.cpp:57-61)
+        if (inputs[i].count() != 0) return false;
+    if (inputs.size() > 2) return false; // graphs with position-id inputs (Qwen2-VL) stay op by op
     Tensor &in = inputs[0];
     const int B = in.batch();
     if (in.sequence() != 1 || in.head() != 1 || in.dimension() != 1 || in.dtype() != MLLM_TYPE_F32 || B < 1 || B > 8) return false;
@@ -258,7 +319,7 @@ bool CUDABackend::try_decode_plan(Module *module, std::vector<Tensor> &inputs, s
         l.kc->execute({one}, {}); // n_rep == 1: only cache_seq_len_ += inputs[0]->sequence() (CPUKVCache.cpp:148-151)
         l.vc->execute({one}, {});
     }
-    kernel_launches += 2 + 5 * (long long)p.layers.size();
+    kernel_launches += p.launches;
     last_forward_fused = 1;
     // hand out a fresh tensor (callers may migrate it with .cpu(), which would take the plan's buffer with it)
     Tensor lg(B, 1, 1, p.V, this, true);
