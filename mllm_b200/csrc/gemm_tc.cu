@@ -16,7 +16,7 @@
 //   warp 0      : TMEM alloc, single-thread MMA issue, tcgen05.commit -> mbarriers
 //   warps 1-4   : loaders -- Q4_0 rows -> exact fp16 (q-8) into the canonical no-swizzle K-major core-matrix
 //                 layout (generic-proxy stores + fence.proxy.async), fp16 activation rows, d_w / d_x rings
-//   warps 5-20  : epilogue -- tcgen05.ld (32 lanes x 32 columns per warp), scale, accumulate in registers,
+//   warps 5-20  : epilogue -- tcgen05.ld (32 lanes x TC_EPI_COLS = 32 columns per warp), scale, accumulate in registers,
 //                 finally bias and store
 // Pipelines: 4 smem stages of 2 Q blocks, 4 TMEM buffers; all hand-offs through mbarriers.
 #include "common.cuh"
@@ -29,8 +29,14 @@
 #define TC_NS 4   // shared-memory stages
 #define TC_ND 4   // TMEM accumulator buffers (one Q block each)
 #define TC_SR 16  // scale ring depth in Q blocks (> TC_NS*TC_KB + TC_ND: loaders never lap the epilogue)
-#define TC_EPI_WARPS 16 // 4 TMEM lane quarters x 4 column quarters of 32
-#define TC_THREADS ((5 + TC_EPI_WARPS) * 32) // 21 warps; registers are granted per 4 warps, so the budget is 80 per thread
+#ifndef TC_EPI_WARPS
+#define TC_EPI_WARPS 16 // 4 TMEM lane quarters x 4 column quarters of 32.  8 (x 64 columns) executes 30 % fewer instructions per Q block
+                        // (the barrier wait, address arithmetic and loop cost ~56 of the 88 per warp whatever the width) and is SLOWER
+                        // (98.9 against 86 us per 512 x 4096 x 4096, prefill 39.0 against 33.7 ms): the epilogue is bound by the latency
+                        // of tcgen05.ld / LDS chains, which 16 warps hide better (profiles/r02_gemm_tc_epilogue_widths.txt)
+#endif
+#define TC_EPI_COLS (TC_BN / (TC_EPI_WARPS / 4)) // accumulator columns per epilogue warp
+#define TC_THREADS ((5 + TC_EPI_WARPS) * 32)
 #define TC_STAGE_BYTES (2 * TC_KB * 4 * TC_BM * 16) // A + B: KB blocks x 4 16-byte K chunks x 128 rows
 #define TC_OPER_BYTES (TC_KB * 4 * TC_BM * 16)
 
@@ -283,20 +289,22 @@ k_gemm_q4_0_tc(const uint8_t *__restrict__ W, const __half *__restrict__ qt, con
             }
         }
     } else {
-        // ---------------- epilogue: TMEM lane quarter = warp % 4, 32 of the 128 columns per warp
+        // ---------------- epilogue: TMEM lane quarter = warp % 4, TC_EPI_COLS of the 128 columns per warp
+        constexpr int NC = TC_EPI_COLS, NV = NC / 32;
         const int q = warp & 3, cq = (warp - 5) >> 2;
         const int r = 32 * q + lane, m = m0 + r;
-        float2 acc[16]; // columns 2j, 2j+1 of this warp's 32
+        float2 acc[NC / 2]; // columns 2j, 2j+1 of this warp's NC
 #pragma unroll
-        for (int j = 0; j < 16; j++) acc[j] = make_float2(0.f, 0.f);
+        for (int j = 0; j < NC / 2; j++) acc[j] = make_float2(0.f, 0.f);
         for (int b = 0; b < nb; b++) {
             const int buf = b % TC_ND;
             tc_mbar_wait(DFULL(buf), (uint32_t)((b / TC_ND) & 1));
             tc_fence_after();
-            uint32_t v[32];
-            tc_ld32(tmem_base + ((uint32_t)(32 * q) << 16) + (uint32_t)(buf * TC_BN + cq * 32), v);
+            uint32_t v[NV][32];
+#pragma unroll
+            for (int h = 0; h < NV; h++) tc_ld32(tmem_base + ((uint32_t)(32 * q) << 16) + (uint32_t)(buf * TC_BN + cq * NC + h * 32), v[h]);
             const float sx = dxS[(b % TC_SR) * 128 + r];
-            const float4 *dwp = (const float4 *)(dwS + (b % TC_SR) * 128 + cq * 32);
+            const float4 *dwp = (const float4 *)(dwS + (b % TC_SR) * 128 + cq * NC);
             tc_wait_ld();
             tc_fence_before();
             __syncwarp();
@@ -304,25 +312,28 @@ k_gemm_q4_0_tc(const uint8_t *__restrict__ W, const __half *__restrict__ qt, con
             const float2 sx2 = make_float2(sx, sx);
             // packed fp32x2: one FMUL2 (d_w * d_x, rounded as the reference's product) + one FFMA2 per element pair
 #pragma unroll
-            for (int j4 = 0; j4 < 8; j4++) {
-                const float4 wv = dwp[j4];
-                acc[2 * j4] = __ffma2_rn(__fmul2_rn(make_float2(wv.x, wv.y), sx2), make_float2(__uint_as_float(v[4 * j4]), __uint_as_float(v[4 * j4 + 1])), acc[2 * j4]);
-                acc[2 * j4 + 1] = __ffma2_rn(__fmul2_rn(make_float2(wv.z, wv.w), sx2), make_float2(__uint_as_float(v[4 * j4 + 2]), __uint_as_float(v[4 * j4 + 3])), acc[2 * j4 + 1]);
-            }
+            for (int h = 0; h < NV; h++)
+#pragma unroll
+                for (int j4 = 0; j4 < 8; j4++) {
+                    const float4 wv = dwp[h * 8 + j4];
+                    float2 &a0 = acc[h * 16 + 2 * j4], &a1 = acc[h * 16 + 2 * j4 + 1];
+                    a0 = __ffma2_rn(__fmul2_rn(make_float2(wv.x, wv.y), sx2), make_float2(__uint_as_float(v[h][4 * j4]), __uint_as_float(v[h][4 * j4 + 1])), a0);
+                    a1 = __ffma2_rn(__fmul2_rn(make_float2(wv.z, wv.w), sx2), make_float2(__uint_as_float(v[h][4 * j4 + 2]), __uint_as_float(v[h][4 * j4 + 3])), a1);
+                }
         }
         if (m < M) {
-            const int nc = n0 + cq * 32;
+            const int nc = n0 + cq * NC;
             if (out_f16) {
                 __half *yp = (__half *)y + (size_t)m * ldy + nc;
 #pragma unroll
-                for (int j = 0; j < 16; j++) {
+                for (int j = 0; j < NC / 2; j++) {
                     yp[2 * j] = __float2half_rn(bias ? acc[j].x + bias[nc + 2 * j] : acc[j].x);
                     yp[2 * j + 1] = __float2half_rn(bias ? acc[j].y + bias[nc + 2 * j + 1] : acc[j].y);
                 }
             } else {
                 float *yp = (float *)y + (size_t)m * ldy + nc;
 #pragma unroll
-                for (int j = 0; j < 16; j++) {
+                for (int j = 0; j < NC / 2; j++) {
                     yp[2 * j] = bias ? acc[j].x + bias[nc + 2 * j] : acc[j].x;
                     yp[2 * j + 1] = bias ? acc[j].y + bias[nc + 2 * j + 1] : acc[j].y;
                 }
