@@ -12,6 +12,7 @@
 #include "CUDAOpHelpers.hpp"
 #include "mllmcu.h"
 
+#include <algorithm>
 #include <cmath>
 #include <cstring>
 #include <stdexcept>
@@ -280,19 +281,34 @@ public:
     enum Kind { SILU_K, ADD_K, MUL_K };
     CUDAElementwise(Backend *bn, string name, Kind k) : CUDAOpBase(bn, name), kind_(k) {}
     ErrorCode reshape(vector<shared_ptr<Tensor>> in, vector<shared_ptr<Tensor>> out) override {
-        out[0]->reshape(in[0]->batch(), in[0]->head(), in[0]->sequence(), in[0]->dimension());
+        int B = in[0]->batch();
+        if (in.size() > 1) B = std::max(B, in[1]->batch()); // a batch-1 operand is repeated over the other's batches (CPUBinaryFunc.hpp:220-245)
+        out[0]->reshape(B, in[0]->head(), in[0]->sequence(), in[0]->dimension());
         return MLLM_NO_ERROR;
     }
     ErrorCode execute(vector<shared_ptr<Tensor>> in, vector<shared_ptr<Tensor>> out) override {
         auto *b = cb(backend_);
         for (auto &t : in)
-            if (!dense(*t) || t->count() != in[0]->count()) throw std::runtime_error("[mllm-cuda] " + name() + ": same-shape dense operands only (no broadcast)");
-        const size_t n = (size_t)in[0]->count();
+            if (!dense(*t)) throw std::runtime_error("[mllm-cuda] " + name() + ": dense operands expected");
         b->dropQuantTag();
-        if (kind_ == SILU_K) MLLMCU_CHECK(mllmcu_silu(fbase(*in[0]), fbase(*out[0]), n, b->stream()));
-        else if (kind_ == ADD_K) MLLMCU_CHECK(mllmcu_add(fbase(*in[0]), fbase(*in[1]), fbase(*out[0]), n, b->stream()));
-        else MLLMCU_CHECK(mllmcu_mul(fbase(*in[0]), fbase(*in[1]), fbase(*out[0]), n, b->stream()));
-        b->kernel_launches++;
+        if (kind_ == SILU_K) {
+            MLLMCU_CHECK(mllmcu_silu(fbase(*in[0]), fbase(*out[0]), (size_t)in[0]->count(), b->stream()));
+            b->kernel_launches++;
+            return MLLM_NO_ERROR;
+        }
+        Tensor &x = *in[0], &y = *in[1], &o = *out[0];
+        const size_t per = (size_t)x.head() * x.sequence() * x.dimension();
+        if ((size_t)y.head() * y.sequence() * y.dimension() != per || (x.batch() != y.batch() && x.batch() != 1 && y.batch() != 1))
+            throw std::runtime_error("[mllm-cuda] " + name() + ": operands must agree off the batch axis (head broadcast has no CUDA path)");
+        auto run = [&](const float *a, const float *c, float *d, size_t n) {
+            if (kind_ == ADD_K) MLLMCU_CHECK(mllmcu_add(a, c, d, n, b->stream()));
+            else MLLMCU_CHECK(mllmcu_mul(a, c, d, n, b->stream()));
+            b->kernel_launches++;
+        };
+        if (x.batch() == y.batch()) run(fbase(x), fbase(y), fbase(o), per * x.batch());
+        else
+            for (int n = 0; n < o.batch(); n++) // min(n, batch - 1) of the reference: the single batch of the smaller operand
+                run(fbase(x) + (x.batch() == 1 ? 0 : n * per), fbase(y) + (y.batch() == 1 ? 0 : n * per), fbase(o) + n * per, per);
         return MLLM_NO_ERROR;
     }
 

@@ -1,7 +1,7 @@
 // mllm/backends/cuda/CUDAVisionOps.cpp -- the ops the vision towers and the image splice add to the LLaMA-family set of CUDAOps.cpp, so
 // that models/llava/modeling_llava.hpp and models/qwen2_vl/modeling_qwen2_vl.hpp run UNCHANGED on this backend:
 //   LayerNorm, GELU, QuickGELU, Parameter, Convolution2D, Convolution3D, VisionRoPE, MultimodalRoPE and the tensor functions
-//   transpose, flatten, cat, split, range, where, index_put, apply_rotary_pos_emb_vision.
+//   transpose, flatten, cat, split, range, where, index_put, zero_like, apply_rotary_pos_emb_vision.
 // Every tensor of this backend is dense BSHD (Tensor::transpose is never in place off the CPU backend, Tensor.cpp:523-527), so the
 // reference's metadata transposes become one strided copy and flatten / view stay metadata.  Each op cites the CPU op whose
 // reshape / load / execute semantics it keeps; the device is reached only through the C ABI (include/mllmcu.h).
@@ -406,6 +406,26 @@ private:
     int start_, end_;
 };
 
+// ------------------------------------------------------------------ zero_like (F_LIKE, op/CPULikeFunc.hpp:26-36): the reference memsets the
+// output with (int)like_value as the BYTE value, so only 0 gives what the name promises; the same bytes are written here.
+class CUDALike final : public CUDAOpBase {
+public:
+    CUDALike(Backend *bn, string name, float v) : CUDAOpBase(bn, name), v_(v) {}
+    ErrorCode reshape(vector<shared_ptr<Tensor>> in, vector<shared_ptr<Tensor>> out) override {
+        same_shape(in, out);
+        out[0]->setDtype(in[0]->dtype());
+        return MLLM_NO_ERROR;
+    }
+    ErrorCode execute(vector<shared_ptr<Tensor>>, vector<shared_ptr<Tensor>> out) override {
+        auto *b = cb(backend_);
+        MLLMCU_CHECK(mllmcu_memset(out[0]->rawHostPtr(), (int)v_, out[0]->cntSize(), b->stream()));
+        return MLLM_NO_ERROR;
+    }
+
+private:
+    float v_;
+};
+
 // ------------------------------------------------------------------ where (op/CPUWhereFunc.hpp:27-95): positions with x == value in the
 // reference's visit order, compacted on the device; the host reads ONE integer (the count) because the output's shape depends on
 // the data -- the reference allocates its output inside execute for the same reason.
@@ -667,6 +687,7 @@ static Op *make_split(const OpParam &p, Backend *bn, const string &name) {
 }
 CREATOR(SplitCreator, make_split(p, bn, name));
 CREATOR(RangeCreator, new CUDARange(bn, name, (int)p.at("start"), (int)p.at("end")));
+CREATOR(LikeCreator, new CUDALike(bn, name, p.at("like_value")));
 CREATOR(WhereCreator, new CUDAWhere(bn, name, p.at("value"), (int)p.at("axis")));
 CREATOR(IndexPutCreator, new CUDAIndexPut(bn, name, (bool)p.at("accumulate")));
 CREATOR(VisionRoPECreator, new CUDAVisionRoPE(bn, name, (int)p.at("dim"), (int)p.at("spatial_merge_size")));
@@ -686,6 +707,7 @@ void CUDABackend::registerVisionOps() {
     addCreator(F_SPLIT, new SplitCreator());
     addCreator(F_RANGE, new RangeCreator());
     addCreator(F_WHERE, new WhereCreator());
+    addCreator(F_LIKE, new LikeCreator());
     addCreator(F_INDEX_PUT, new IndexPutCreator());
     addCreator(VISIONROPE, new VisionRoPECreator());
     addCreator(F_APPLY_VISIOROPE, new ApplyVisionRoPECreator());

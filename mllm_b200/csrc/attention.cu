@@ -138,9 +138,9 @@ __global__ void k_attn_merge(const float *__restrict__ ws, float *__restrict__ o
 }
 
 static int pick_nsplit(int B, int Sq, int Hq, int Sk) {
-    // enough warps to cover 148 SMs x 16 warps; a split should keep >= 32 keys
+    // enough warps to cover every SM x 16 warps; a split should keep >= 32 keys
     const long long rows = (long long)B * Sq * Hq;
-    long long want = (148LL * 16 + rows - 1) / rows;
+    long long want = ((long long)cu_sm_count() * 16 + rows - 1) / rows;
     long long maxs = (Sk + 31) / 32;
     if (want > maxs) want = maxs;
     if (want < 1) want = 1;
@@ -151,7 +151,7 @@ static int pick_nsplit(int B, int Sq, int Hq, int Sk) {
 MLLMCU_API size_t mllmcu_flash_attn_workspace_bytes(int B, int Sq, int Hq, int D) {
     // worst case nsplit = 64 only happens when rows are few; bound rows*nsplit
     const long long rows = (long long)B * Sq * Hq;
-    long long ns = (148LL * 16 + rows - 1) / rows;
+    long long ns = ((long long)cu_sm_count() * 16 + rows - 1) / rows;
     if (ns > 64) ns = 64;
     if (ns < 1) ns = 1;
     return (size_t)rows * ns * (D + 2) * sizeof(float) + 256;

@@ -21,6 +21,20 @@ static_assert(sizeof(block_q8_0) == 34, "q8_0 block");
     } while (0)
 #define CU_LAUNCH_CHECK() CU_TRY(cudaGetLastError())
 
+// Multiprocessor count of the current device (grid sizing: persistent kernels launch one CTA per SM, split-K heuristics aim at
+// a multiple of it); queried once per device, 148 on a B200.
+static inline int cu_sm_count() {
+    static int cached[64] = {};
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
+    if (cached[dev] == 0) {
+        int n = 0;
+        if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+        cached[dev] = n;
+    }
+    return cached[dev];
+}
+
 // RoPE rotation of the pair (a, b) by (sin, cos): the reference writes `a*cos - b*sin` and `a*sin + b*cos` in scalar C++
 // (op/CPURoPE.cpp:241-242, CPUMultimodalRoPE.cpp:171-172, CPUVisionRoPEFunc.hpp:44-45); compiled for an FMA target gcc contracts
 // the FIRST product of each into the add -- fma(a, cos, -(b*sin)), fma(a, sin, b*cos) -- which is what its users get and what the

@@ -528,7 +528,7 @@ MLLMCU_API int mllmcu_decode_attn_nsplit(int B, int Hq) {
     // ~2 CTAs of 4 warps per SM (swept on B200: 1x 1.70, 2x 1.66, 4x 1.82 ms per 7B decode step)
     static int mult = 0;
     if (mult == 0) { const char *e = getenv("MLLMCU_ATTN_SPLIT_MULT"); mult = (e && e[0]) ? atoi(e) : 2; if (mult < 1) mult = 1; }
-    int n = (mult * 148) / (B * Hq);
+    int n = (mult * cu_sm_count()) / (B * Hq);
     if (n < 1) n = 1;
     if (n > 32) n = 32;
     if (attn_use_cluster() && n > 8) n = 8; // the splits of one head form a thread-block cluster (portable maximum 8)
