@@ -145,6 +145,12 @@ static Tensor host_tensor(const string &name, int b, int h, int s, int d) {
 }
 
 struct StepLog {
+    int fused_steps = 0; // forwards answered by the CUDA backend's graph-replayed decode plan
+    void count_fused(BackendType device) {
+#ifdef USE_CUDA
+        if (device == MLLM_CUDA) fused_steps += static_cast<CUDABackend *>(Backend::global_backends[MLLM_CUDA].get())->last_forward_fused;
+#endif
+    }
     std::vector<unsigned> tokens;
     std::vector<double> ms;
     FILE *dump = nullptr;
@@ -164,8 +170,8 @@ static void print_json(const char *model, int device, int prompt_tokens, const S
     std::vector<double> tail(m.inference_times_.begin() + std::min<size_t>(m.inference_times_.size(), 1), m.inference_times_.end());
     std::sort(tail.begin(), tail.end());
     printf("{\"model\": \"%s\", \"device\": %d, \"prompt_tokens\": %d, \"decode\": %zu, \"prefill_ms\": %.3f, \"decode_ms_per_step\": %.4f, \"decode_ms_median\": %.4f, "
-           "\"decode_ms_max\": %.3f, \"tokens\": [", model, device, prompt_tokens, log.tokens.size(), m.inference_times_.empty() ? 0.0 : m.inference_times_[0],
-           m.inference_times_.size() > 1 ? dec / (m.inference_times_.size() - 1) : 0.0, tail.empty() ? 0.0 : tail[tail.size() / 2], tail.empty() ? 0.0 : tail.back());
+           "\"decode_ms_max\": %.3f, \"fused_steps\": %d, \"tokens\": [", model, device, prompt_tokens, log.tokens.size(), m.inference_times_.empty() ? 0.0 : m.inference_times_[0],
+           m.inference_times_.size() > 1 ? dec / (m.inference_times_.size() - 1) : 0.0, tail.empty() ? 0.0 : tail[tail.size() / 2], tail.empty() ? 0.0 : tail.back(), log.fused_steps);
     for (size_t i = 0; i < log.tokens.size(); i++) printf("%s%u", i ? ", " : "", log.tokens[i]);
     printf("]}\n");
 }
@@ -244,6 +250,7 @@ int main(int argc, char **argv) {
         const int prompt_tokens = S - 1 + (img / patch) * (img / patch);
         for (int step = 0; step < n_decode; step++) {
             auto result = model({ids, image});
+            log.count_fused(device);
             const unsigned tok = log.pick(result[0]);
             log.tokens.push_back(tok);
             chatPostProcessing(tok, ids, {&image});
@@ -299,6 +306,7 @@ int main(int argc, char **argv) {
         for (int step = 0; step < n_decode; step++) {
             model.get_position_ids(inputs);
             auto result = model(inputs);
+            log.count_fused(device);
             const unsigned tok = log.pick(result[0]);
             log.tokens.push_back(tok);
             chatPostProcessing(tok, inputs[0], {&inputs[1], &inputs[2]});

@@ -60,6 +60,8 @@ struct CUDAFuseInfo {
     int unit_offset = 0;
     const float *sin_t = nullptr, *cos_t = nullptr;
     int rope_type = 0, rot_dim = 0, pos_max = 0;
+    float rope_theta = 0.f; // MultimodalRoPE: the decode plan builds the (text-position) table itself
+    int mrope = 0;
 };
 class CUDAOpBase : public Op { // CUDA compute ops: adds the fusion hook
 public:

@@ -20,6 +20,7 @@
 #include "mllmcu.h"
 
 #include <algorithm>
+#include <cmath>
 #include <cstdlib>
 #include <iostream>
 
@@ -41,6 +42,9 @@ struct CUDABackend::DecodePlan {
     Tensor t1, t2, gu, lin_ws; // k-quant models: normalised row, Linear output, up projection, the Linears' Q8_K workspace
     size_t attn_ws_bytes = 0, lin_ws_bytes = 0;
     bool kquant = false;       // Linears are Q4_K / Q6_K: op-level kernels on fixed buffers inside the captured graph
+    bool mrope = false;        // Qwen2-VL: MultimodalRoPE ops; the rotary position comes with the call (position ids), not from the cache length
+    int rope_delta = 0;        // rotary position - cache length of the request being decoded (constant over its decode steps)
+    Tensor msin, mcos;         // mrope: rotate-half tables [limit][D] for text positions
     int launches = 0;
     int dev_pos = -2, ctl_host = 0;
     bool warmed = false, use_graph = true, use_pdl = true, unsupported = false;
@@ -67,12 +71,14 @@ struct DecodePlanBuilder {
         if (!ops.empty() && ops.back()->type() == F_CLIP) ops.pop_back();
         static const OpType block[18] = {RMSNORM, LINEAR, LINEAR, LINEAR, ROPE, ROPE, KVCACHE, KVCACHE, F_FA2, LINEAR, F_TTADD,
                                          RMSNORM, LINEAR, SILU, LINEAR, F_TTMUL, LINEAR, F_TTADD};
+        // QWen2Decoder of Qwen2-VL (modeling_qwen2_vl.hpp:225-262,310-330) is the same block with MultimodalRoPE in the two rotary slots
+        const bool mrope = ops.size() > 6 && ops[5]->type() == MULTIMODALROPE;
         if (ops.size() < 3 + 18 || (ops.size() - 3) % 18 != 0) return nullptr;
         const int nl = (int)(ops.size() - 3) / 18;
         if (ops[0]->type() != EMBEDDING || ops[ops.size() - 2]->type() != RMSNORM || ops[ops.size() - 1]->type() != LINEAR) return nullptr;
         for (int l = 0; l < nl; l++)
             for (int j = 0; j < 18; j++)
-                if (ops[1 + l * 18 + j]->type() != block[j]) return nullptr;
+                if (ops[1 + l * 18 + j]->type() != ((mrope && block[j] == ROPE) ? MULTIMODALROPE : block[j])) return nullptr;
         auto p = std::make_shared<CUDABackend::DecodePlan>();
         auto fi = [](Op *o, CUDAFuseInfo &f) {
             auto *c = dynamic_cast<CUDAOpBase *>(o);
@@ -80,6 +86,7 @@ struct DecodePlanBuilder {
         };
         if (!fi(ops[0], p->embd) || !fi(ops[ops.size() - 2], p->norm) || !fi(ops[ops.size() - 1], p->head)) return nullptr;
         p->layers.resize(nl);
+        p->mrope = mrope;
         for (int l = 0; l < nl; l++) {
             Op **o = &ops[1 + l * 18];
             auto &L = p->layers[l];
@@ -117,11 +124,36 @@ struct DecodePlanBuilder {
         if (p->embd.wtype != MLLM_TYPE_Q4_0 || p->norm.unit_offset) return nullptr;
         if (p->kquant && (p->H % 256 || p->F % 256 || (p->Hq * p->D) % 256)) return nullptr; // Q8_K super-blocks
         if (p->H % 128 || p->F % 128 || (p->D != 32 && p->D != 64 && p->D != 128) || L0.rope.rot_dim != p->D || B < 1 || B > 8) return nullptr;
+        if (mrope) { // one rotate-half table for text positions 0 .. limit - 1, as CUDARoPE / CPURoPE build it (theta in double -> float, libm)
+            if (B != 1 || p->kquant) return nullptr;
+            const int D = p->D, half = D / 2;
+            std::vector<float> theta(half), sn((size_t)p->limit * D), cs((size_t)p->limit * D);
+            for (int i = 0; i < half; i++) theta[i] = (float)(1.0 / pow((double)L0.rope.rope_theta, 2.0 * i / D));
+            for (int pos = 0; pos < p->limit; pos++)
+                for (int i = 0; i < half; i++) {
+                    const float value = theta[i] * (float)pos; // CPUMultimodalRoPE.cpp: theta * position id (a float)
+                    sn[(size_t)pos * D + i] = sn[(size_t)pos * D + i + half] = sinf(value);
+                    cs[(size_t)pos * D + i] = cs[(size_t)pos * D + i + half] = cosf(value);
+                }
+            auto up = [&](Tensor &t, const std::vector<float> &src) {
+                t.setBackend(bn);
+                t.reshape(1, 1, p->limit, D);
+                t.setDtype(MLLM_TYPE_F32);
+                bn->memory()->device_only = true;
+                t.alloc();
+                bn->memory()->device_only = false;
+                MLLMCU_CHECK(mllmcu_memcpy_h2d(t.rawHostPtr(), src.data(), src.size() * sizeof(float), bn->stream()));
+                bn->sync();
+            };
+            up(p->msin, sn);
+            up(p->mcos, cs);
+        }
         for (auto &L : p->layers) {
             Tensor &a = *L.kc->cache_, &b = *L.vc->cache_;
             if (a.batch() != B || b.batch() != B || a.sequence() != p->limit || b.sequence() != p->limit || a.head() != p->Hkv || a.dimension() != p->D ||
-                L.rope.rot_dim != p->D || L.rope.sin_t != L0.rope.sin_t)
+                L.rope.rot_dim != p->D || L.rope.sin_t != L0.rope.sin_t || L.rope.rope_theta != L0.rope.rope_theta)
                 return nullptr;
+            if (mrope) { L.rope.sin_t = p->msin.hostPtr<float>(); L.rope.cos_t = p->mcos.hostPtr<float>(); L.rope.pos_max = p->limit; }
         }
         auto mk = [&](Tensor &t, int rows, int cols) {
             t.setBackend(bn);
@@ -181,8 +213,11 @@ struct DecodePlanBuilder {
             // layer 0's projection releases its dependents only after its own wait: every later kernel then starts with the embedding
             // kernel (which bumps ctl[0]) complete and may read the position and its K/V rows ahead of its own wait
             if (!gemv({&l.q, &l.k, &l.v}, x, H, &l.n1, 0, nullptr, qkv, QKV, li == 0)) return false;
+            // the kernel rotates with table row ctl[0] (the cache length); a Qwen2-VL text token sits at rotary position ctl[0] + rope_delta,
+            // so the table base is moved by that many rows (rows in use stay inside [0, limit): checked before the launch)
+            const long long shift = (long long)p.rope_delta * l.rope.rot_dim;
             MLLMCU_CHECK(mllmcu_decode_attn_rope(l.rope.rope_type, qkv, QKV, l.kptr, l.vptr, ao, Hq * D, ctl, B, Hq,
-                                                 Hkv, D, l.rope.sin_t, l.rope.cos_t, l.rope.rot_dim, p.kv_bstride, p.limit, p.attn_ws.rawHostPtr(),
+                                                 Hkv, D, l.rope.sin_t + shift, l.rope.cos_t + shift, l.rope.rot_dim, p.kv_bstride, p.limit, p.attn_ws.rawHostPtr(),
                                                  p.attn_ws_bytes, pdl ? 2 : 0, st));
             if (!gemv({&l.o}, ao, Hq * D, nullptr, 1, x, x2, H)) return false;
             if (!gemv({&l.gate, &l.up}, x2, H, &l.n2, 2, nullptr, g, F)) return false;
@@ -233,9 +268,12 @@ bool DecodePlanBuilder::issue_kquant(CUDABackend *bn, CUDABackend::DecodePlan &p
 // Called by runForward for every outermost forward.  Returns true when `out` holds the logits of a fused step.
 bool CUDABackend::try_decode_plan(Module *module, std::vector<Tensor> &inputs, std::vector<std::any> &args, std::vector<Tensor> &out) {
     if (!fused_decode || inputs.empty()) return false;
-    for (size_t i = 1; i < inputs.size(); i++) // LLaVAModel's decode call: {ids, image emptied by chatPostProcessing} (demo_llava.cpp:57-61)
+    // LLaVAModel's decode call is {ids, image emptied by chatPostProcessing} (demo_llava.cpp:57-61); Qwen2VLModel's is {ids, pixels and
+    // grid emptied, position ids [3,1,1,1]} (demo_qwen2_vl.cpp:47-64, Qwen2VLModel::get_position_ids)
+    if (inputs.size() > 4) return false;
+    for (size_t i = 1; i < inputs.size() && i < 3; i++)
         if (inputs[i].count() != 0) return false;
-    if (inputs.size() > 2) return false; // graphs with position-id inputs (Qwen2-VL) stay op by op
+    if (inputs.size() == 4 && (inputs[3].batch() != 3 || inputs[3].count() != 3 || inputs[3].dtype() != MLLM_TYPE_F32)) return false;
     Tensor &in = inputs[0];
     const int B = in.batch();
     if (in.sequence() != 1 || in.head() != 1 || in.dimension() != 1 || in.dtype() != MLLM_TYPE_F32 || B < 1 || B > 8) return false;
@@ -270,7 +308,17 @@ bool CUDABackend::try_decode_plan(Module *module, std::vector<Tensor> &inputs, s
                   << "\n         Please set args `--limits` >" << p.limit << std::endl;
         throw std::runtime_error("[mllm-cuda] KV cache limit exceeded");
     }
-    if (len + 1 > p.layers[0].rope.pos_max) throw std::runtime_error("[mllm-cuda] RoPE: position exceeds max_position_embeddings");
+    if (p.mrope != (inputs.size() == 4)) return false;
+    if (p.mrope) { // a text token: the three axes carry one position; its distance to the cache length is fixed for the request
+        sync();
+        const float pt = inputs[3].dataAt<float>(0, 0, 0, 0), ph = inputs[3].dataAt<float>(1, 0, 0, 0), pw = inputs[3].dataAt<float>(2, 0, 0, 0);
+        if (pt != ph || pt != pw || pt < 0 || pt >= (float)p.limit || pt != (float)(int)pt) return false;
+        const int delta = (int)pt - len;
+        if (delta != p.rope_delta) { // another request: the captured launches hold the old table base
+            if (p.graph) { mllmcu_graph_destroy(p.graph); p.graph = nullptr; }
+            p.rope_delta = delta;
+        }
+    } else if (len + 1 > p.layers[0].rope.pos_max) throw std::runtime_error("[mllm-cuda] RoPE: position exceeds max_position_embeddings");
     dropQuantTag();
     // token ids: the demos build the input on the CPU backend (host memory); a CUDA-backend tensor is copied device to device
     if (in.backend()->type() == MLLM_CPU) {

@@ -655,6 +655,15 @@ public:
         return MLLM_NO_ERROR;
     }
 
+    // decode plan: a text token has the same position on the t / h / w axes, so its table row is the rotate-half (HF) row of that
+    // position when the sections cover the D / 2 frequencies; the plan builds that table from theta (CUDADecodePlan.cpp)
+    bool fuseInfo(CUDAFuseInfo &f) override {
+        int sum = 0;
+        for (int v : sec_) sum += v;
+        f.mrope = 1; f.rope_type = HFHUBROPE; f.rot_dim = 2 * sum; f.rope_theta = theta_;
+        return sum > 0;
+    }
+
 private:
     float theta_;
     vector<int> sec_;

@@ -59,6 +59,8 @@ def test_unchanged_vlm_graph_cpu_and_cuda_backends_agree(tmp_path, case):
     cpu = run(model, dims, "--device", 0, "--file", path, "--text", 10, "--decode", n_dec, "--limit", 256, "--dump", tmp_path / "cpu.bin")
     gpu = run(model, dims, "--device", 4, "--file", path, "--text", 10, "--decode", n_dec, "--limit", 256, "--dump", tmp_path / "gpu.bin")
     assert cpu["prompt_tokens"] == gpu["prompt_tokens"] and cpu["prompt_tokens"] > 15
+    if linear != "f32":  # the decode plan recognises both LLM bodies (LLaVA: Q4_K op-level kernels + the trailing clip; Qwen2-VL: M-RoPE as a
+        assert gpu["fused_steps"] == n_dec - 2, gpu  # shifted rotate-half table): step 0 is the prefill, step 1 is recorded, the rest replay the graph
     lc = np.fromfile(tmp_path / "cpu.bin", dtype=np.float32).reshape(n_dec, vocab)
     lg = np.fromfile(tmp_path / "gpu.bin", dtype=np.float32).reshape(n_dec, vocab)
     assert np.isfinite(lg).all()
