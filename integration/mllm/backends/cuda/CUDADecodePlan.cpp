@@ -153,8 +153,9 @@ struct DecodePlanBuilder {
             if (a.batch() != B || b.batch() != B || a.sequence() != p->limit || b.sequence() != p->limit || a.head() != p->Hkv || a.dimension() != p->D ||
                 L.rope.rot_dim != p->D || L.rope.sin_t != L0.rope.sin_t || L.rope.rope_theta != L0.rope.rope_theta)
                 return nullptr;
-            if (mrope) { L.rope.sin_t = p->msin.hostPtr<float>(); L.rope.cos_t = p->mcos.hostPtr<float>(); L.rope.pos_max = p->limit; }
         }
+        if (mrope)
+            for (auto &L : p->layers) { L.rope.sin_t = p->msin.hostPtr<float>(); L.rope.cos_t = p->mcos.hostPtr<float>(); L.rope.pos_max = p->limit; }
         auto mk = [&](Tensor &t, int rows, int cols) {
             t.setBackend(bn);
             t.reshape(1, 1, rows, cols);
