@@ -18,10 +18,10 @@ run_case() { # model limit text
   local t0=$(date +%s)
   $R --model $m --write $f 2>&1 | tail -1 >> $OUT
   echo "{\"case\": \"$m\", \"write_s\": $(( $(date +%s) - t0 ))}" >> $OUT
+  $R --model $m --device 4 --file $f --text $txt --decode $GPU_DEC --limit $lim --dump /tmp/vlm_$m.gpu.bin 2>&1 | tail -3 | grep -E '^\{|error|Error' >> $OUT
   $R --model $m --device 0 --file $f --text $txt --decode $CPU_DEC --limit $lim --thread $T --dump /tmp/vlm_$m.cpu.bin 2>&1 | grep '^{' | sed "s/^{/{\"threads\": $T, /" >> $OUT
   # noise floor: the SAME reference backend with every input pixel moved by one ulp
   $R --model $m --device 0 --file $f --text $txt --decode $CPU_DEC --limit $lim --thread $T --perturb 1 --dump /tmp/vlm_$m.cpu1.bin 2>&1 | grep '^{' | sed "s/^{/{\"perturbed_pixels_1ulp\": 1, /" >> $OUT
-  $R --model $m --device 4 --file $f --text $txt --decode $GPU_DEC --limit $lim --dump /tmp/vlm_$m.gpu.bin 2>&1 | tail -3 | grep -E '^\{|error|Error' >> $OUT
   python - $m $CPU_DEC $GPU_DEC >> $OUT <<'PY'
 import sys, json
 import numpy as np
