@@ -1,0 +1,253 @@
+// gemm_mma_q4k.cu -- Q4_K Linear with 9+ activation rows (prefill, batched decode) on the tensor cores.
+//
+// Reference arithmetic: mat_mul's generic path (compute/Matmul.cpp:104-115,223-276) with quantize_row_q8_K (ggml/QuantizeQ8.cpp:
+// 216-266) and vec_dot_q4_K_q8_K (ggml/VecDotQ4.cpp:32-345): per 256-element super-block TWO exact integers,
+//   sumi = sum_{j<8} scale_j * (q4_j . q8_j)            (q4 in 0..15, q8 in -128..127, scale_j 6 bits)
+//   summ = sum_{j<8} min_j * (bsums[2j] + bsums[2j+1])  (the group sums quantize_row_q8_K stores)
+// and y += (d_x * fp16(d_w)) * sumi - (d_x * fp16(dmin_w)) * summ in fp32.  The CUDA-core kernels of kquants.cu form the same
+// integers with dp4a (k_gemm_kq: "20 Tflop/s-equivalent"); here the 32-element dots are ONE mma.sync.m16n8k32.u8.s8 per 16 weight rows
+// x 8 activation rows x sub-block (weights as the A operand: nibbles as stored, no offset to remove -- the min term carries it), its
+// int32 results are multiplied by the 6-bit scales and summed with integer multiply-adds, exactly the reference's integers, and only the
+// per-super-block FMA pair runs in fp32.  Activations are the NATIVE block_q8_K rows kquants.cu's quantiser writes (bytes identical to
+// the reference's): the B fragments, the group sums and d_x are read from them directly.
+//
+// Layout: a tile = 16 consecutive weight rows; a stage = KC super-blocks of those rows (one cp.async.bulk per row into a padded pitch,
+// so the eight rows of a fragment start in different banks), staged through a ring filled ahead of the dependency wait.  16 warps =
+// MG groups of MTW x 8 activation rows x KS K-splits over the super-blocks of a stage; the partial sums of the K-splits meet in shared
+// memory in a fixed order.  M rows beyond 64 (128 for short K) are served by further launches over the same weights (they stay in L2).
+#include "common.cuh"
+#include "gemv_common.cuh"
+#include "mllmcu.h"
+#include <stdlib.h>
+
+#define KQ_WARPS 16
+#define KQ_Q4K 144
+#define KQ_Q8K 292
+
+struct GemmQ4KParams {
+    const uint8_t *W;   // [N][nsb] block_q4_K
+    const uint8_t *xq;  // [M][nsb] block_q8_K (native)
+    const float *bias;
+    void *y;
+    int N, M, nsb, ldy, out_f16;
+    int KC, nchunk, stages, pitch; // super-blocks per stage, stages per tile, ring depth, bytes between rows of a stage
+};
+
+static __device__ __forceinline__ void mma_u8s8(int (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0, uint32_t b1) {
+    asm volatile("mma.sync.aligned.m16n8k32.row.col.s32.u8.s8.s32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%10,%11,%12,%13};"
+                 : "=r"(c[0]), "=r"(c[1]), "=r"(c[2]), "=r"(c[3])
+                 : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1), "r"(0), "r"(0), "r"(0), "r"(0));
+}
+
+// get_scale_min_k4 (ggml/QuantizeQ4.cpp:177-184) for all eight sub-blocks of a super-block: s = the 12 scale bytes as three words;
+// sc / mn receive the eight 6-bit values packed one per byte (sub-blocks 0-3 in [0], 4-7 in [1])
+static __device__ __forceinline__ void q4k_scales8(uint32_t s0, uint32_t s1, uint32_t s2, uint32_t (&sc)[2], uint32_t (&mn)[2]) {
+    sc[0] = s0 & 0x3F3F3F3Fu;                                           // q[j] & 63, j < 4
+    mn[0] = s1 & 0x3F3F3F3Fu;                                           // q[j + 4] & 63
+    sc[1] = (s2 & 0x0F0F0F0Fu) | ((s0 >> 2) & 0x30303030u);             // (q[j + 4] & 0xF) | ((q[j - 4] >> 6) << 4), j >= 4
+    mn[1] = ((s2 >> 4) & 0x0F0F0F0Fu) | ((s1 >> 2) & 0x30303030u);      // (q[j + 4] >> 4) | ((q[j] >> 6) << 4)
+}
+static __device__ __forceinline__ int byte_of(const uint32_t (&v)[2], int j) { return (int)((v[j >> 2] >> (8 * (j & 3))) & 0xFFu); }
+
+template <int MTW, int MG, int KS>
+__global__ void __launch_bounds__(KQ_WARPS * 32) k_gemm_mma_q4k(const GemmQ4KParams p) {
+    static_assert(MG * KS == KQ_WARPS, "16 warps");
+    constexpr int Mp = MG * MTW * 8;
+    extern __shared__ __align__(128) uint8_t smem[];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int g = lane >> 2, t = lane & 3;
+    const int ks = warp % KS, mg = warp / KS;
+    const int nsb = p.nsb, S = p.stages, KC = p.KC, nchunk = p.nchunk, pitch = p.pitch;
+    const int stage_bytes = 16 * pitch;
+    uint64_t *bars = (uint64_t *)smem;  // [S]
+    float *red = (float *)(smem + 128); // [KS][16][Mp]
+    uint8_t *wbuf = smem + 128 + (((size_t)KS * 16 * Mp * 4 + 127) & ~(size_t)127);
+
+    const int T = p.N / 16;
+    const int n_tiles = (int)blockIdx.x < T ? (T - 1 - (int)blockIdx.x) / (int)gridDim.x + 1 : 0;
+    const int n_work = n_tiles * nchunk; // stages this CTA streams: (tile i, chunk c) = work / nchunk, work % nchunk
+    auto issue = [&](int w, int slot) {
+        const int i = w / nchunk, c = w % nchunk;
+        const int row0 = ((int)blockIdx.x + i * (int)gridDim.x) * 16;
+        const int sb0 = c * KC, nsbc = min(KC, nsb - sb0);
+        const uint32_t bar = smem_u32(&bars[slot]);
+        uint8_t *dst = wbuf + (size_t)slot * stage_bytes;
+        mbar_expect_tx(bar, (uint32_t)(16 * nsbc * KQ_Q4K));
+        for (int r = 0; r < 16; r++)
+            bulk_g2s(smem_u32(dst + (size_t)r * pitch), p.W + ((size_t)(row0 + r) * nsb + sb0) * KQ_Q4K, (uint32_t)(nsbc * KQ_Q4K), bar);
+    };
+    if (tid == 0) {
+        for (int s = 0; s < S; s++) mbar_init(smem_u32(&bars[s]), 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        for (int w = 0; w < S && w < n_work; w++) issue(w, w); // weights depend on nothing on the stream: ahead of the wait
+    }
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    __syncthreads();
+
+    const int colw = mg * MTW * 8;
+    // per batch tile: the B-fragment row (colw + 8 m + g) and the two output columns (colw + 8 m + 2 t, + 1), clamped into the rows that exist
+    const uint8_t *xb_frag[MTW], *xb_c0[MTW], *xb_c1[MTW];
+#pragma unroll
+    for (int m = 0; m < MTW; m++) {
+        xb_frag[m] = p.xq + (size_t)min(colw + m * 8 + g, p.M - 1) * nsb * KQ_Q8K;
+        xb_c0[m] = p.xq + (size_t)min(colw + m * 8 + 2 * t, p.M - 1) * nsb * KQ_Q8K;
+        xb_c1[m] = p.xq + (size_t)min(colw + m * 8 + 2 * t + 1, p.M - 1) * nsb * KQ_Q8K;
+    }
+    for (int i = 0; i < n_tiles; i++) {
+        float acc[MTW][4]; // [0],[1]: weight row g, columns 2t, 2t+1; [2],[3]: row g + 8
+#pragma unroll
+        for (int m = 0; m < MTW; m++) acc[m][0] = acc[m][1] = acc[m][2] = acc[m][3] = 0.f;
+        for (int c = 0; c < nchunk; c++) {
+            const int w = i * nchunk + c, slot = w % S;
+            mbar_wait(smem_u32(&bars[slot]), (uint32_t)((w / S) & 1));
+            const uint8_t *st = wbuf + (size_t)slot * stage_bytes;
+            const int sb0 = c * KC, nsbc = min(KC, nsb - sb0);
+            for (int sl = ks; sl < nsbc; sl += KS) {
+                const int sb = sb0 + sl;
+                const uint8_t *r0 = st + (size_t)g * pitch + (size_t)sl * KQ_Q4K, *r1 = r0 + (size_t)8 * pitch;
+                const uint32_t h0 = *(const uint32_t *)r0, h1 = *(const uint32_t *)r1; // d | dmin (fp16 pair)
+                const float dw0 = __half2float(__ushort_as_half((unsigned short)(h0 & 0xFFFFu))), dm0 = __half2float(__ushort_as_half((unsigned short)(h0 >> 16)));
+                const float dw1 = __half2float(__ushort_as_half((unsigned short)(h1 & 0xFFFFu))), dm1 = __half2float(__ushort_as_half((unsigned short)(h1 >> 16)));
+                uint32_t sc0[2], mn0[2], sc1[2], mn1[2];
+                q4k_scales8(*(const uint32_t *)(r0 + 4), *(const uint32_t *)(r0 + 8), *(const uint32_t *)(r0 + 12), sc0, mn0);
+                q4k_scales8(*(const uint32_t *)(r1 + 4), *(const uint32_t *)(r1 + 8), *(const uint32_t *)(r1 + 12), sc1, mn1);
+                int sumi[MTW][4];
+#pragma unroll
+                for (int m = 0; m < MTW; m++) sumi[m][0] = sumi[m][1] = sumi[m][2] = sumi[m][3] = 0;
+#pragma unroll
+                for (int pr = 0; pr < 4; pr++) { // sub-blocks 2 pr (low nibbles) and 2 pr + 1 (high nibbles) share their 32 bytes
+                    const uint32_t w00 = *(const uint32_t *)(r0 + 16 + pr * 32 + 4 * t), w01 = *(const uint32_t *)(r0 + 16 + pr * 32 + 16 + 4 * t);
+                    const uint32_t w10 = *(const uint32_t *)(r1 + 16 + pr * 32 + 4 * t), w11 = *(const uint32_t *)(r1 + 16 + pr * 32 + 16 + 4 * t);
+#pragma unroll
+                    for (int hi = 0; hi < 2; hi++) {
+                        const int j = 2 * pr + hi;
+                        const uint32_t a0 = (w00 >> (4 * hi)) & 0x0F0F0F0Fu, a1 = (w10 >> (4 * hi)) & 0x0F0F0F0Fu;
+                        const uint32_t a2 = (w01 >> (4 * hi)) & 0x0F0F0F0Fu, a3 = (w11 >> (4 * hi)) & 0x0F0F0F0Fu;
+                        const int s0 = byte_of(sc0, j), s1 = byte_of(sc1, j);
+#pragma unroll
+                        for (int m = 0; m < MTW; m++) {
+                            const uint8_t *xb = xb_frag[m] + (size_t)sb * KQ_Q8K + 4 + j * 32;
+                            const uint32_t b0 = *(const uint32_t *)(xb + 4 * t), b1 = *(const uint32_t *)(xb + 16 + 4 * t);
+                            int cc[4];
+                            mma_u8s8(cc, a0, a1, a2, a3, b0, b1);
+                            sumi[m][0] += s0 * cc[0]; sumi[m][1] += s0 * cc[1];
+                            sumi[m][2] += s1 * cc[2]; sumi[m][3] += s1 * cc[3];
+                        }
+                    }
+                }
+                // the min term and the super-block's two fp32 FMAs (same operations as k_gemm_kq: d = d_x * d_w, -d_x * dmin_w)
+#pragma unroll
+                for (int m = 0; m < MTW; m++) {
+                    const uint8_t *c0 = xb_c0[m] + (size_t)sb * KQ_Q8K, *c1 = xb_c1[m] + (size_t)sb * KQ_Q8K;
+                    const float dx0 = *(const float *)c0, dx1 = *(const float *)c1;
+                    uint32_t wa[8], wb[8]; // the 16 int16 group sums of columns 2t and 2t + 1 (a Q8_K block is 292 bytes: 4-byte aligned only)
+#pragma unroll
+                    for (int j = 0; j < 8; j++) { wa[j] = *(const uint32_t *)(c0 + 260 + 4 * j); wb[j] = *(const uint32_t *)(c1 + 260 + 4 * j); }
+                    int sm[4] = {0, 0, 0, 0};
+#pragma unroll
+                    for (int j = 0; j < 8; j++) {
+                        const int ba = (int)(short)(wa[j] & 0xFFFFu) + (int)(short)(wa[j] >> 16); // bsums[2j] + bsums[2j+1]
+                        const int bb = (int)(short)(wb[j] & 0xFFFFu) + (int)(short)(wb[j] >> 16);
+                        const int m0 = byte_of(mn0, j), m1 = byte_of(mn1, j);
+                        sm[0] += m0 * ba; sm[1] += m0 * bb; sm[2] += m1 * ba; sm[3] += m1 * bb;
+                    }
+                    acc[m][0] = fmaf(__fmul_rn(dx0, dw0), (float)sumi[m][0], acc[m][0]);
+                    acc[m][1] = fmaf(__fmul_rn(dx1, dw0), (float)sumi[m][1], acc[m][1]);
+                    acc[m][2] = fmaf(__fmul_rn(dx0, dw1), (float)sumi[m][2], acc[m][2]);
+                    acc[m][3] = fmaf(__fmul_rn(dx1, dw1), (float)sumi[m][3], acc[m][3]);
+                    acc[m][0] = fmaf(__fmul_rn(-dx0, dm0), (float)sm[0], acc[m][0]);
+                    acc[m][1] = fmaf(__fmul_rn(-dx1, dm0), (float)sm[1], acc[m][1]);
+                    acc[m][2] = fmaf(__fmul_rn(-dx0, dm1), (float)sm[2], acc[m][2]);
+                    acc[m][3] = fmaf(__fmul_rn(-dx1, dm1), (float)sm[3], acc[m][3]);
+                }
+            }
+            __syncthreads(); // every warp is done reading the slot
+            if (tid == 0 && w + S < n_work) issue(w + S, slot);
+        }
+        // partial sums of the K-splits -> shared memory, added in a fixed order
+        {
+            float *r = red + ((size_t)ks * 16) * Mp;
+#pragma unroll
+            for (int m = 0; m < MTW; m++) {
+                const int col0 = colw + m * 8 + 2 * t;
+                *(float2 *)(r + (size_t)g * Mp + col0) = make_float2(acc[m][0], acc[m][1]);
+                *(float2 *)(r + (size_t)(g + 8) * Mp + col0) = make_float2(acc[m][2], acc[m][3]);
+            }
+        }
+        __syncthreads();
+        const int row0 = ((int)blockIdx.x + i * (int)gridDim.x) * 16;
+        for (int idx = tid; idx < 16 * p.M; idx += KQ_WARPS * 32) {
+            const int r = idx & 15, m = idx >> 4;
+            float v = 0.f;
+#pragma unroll
+            for (int k = 0; k < KS; k++) v += red[((size_t)k * 16 + r) * Mp + m];
+            const int n = row0 + r;
+            if (p.bias) v = __fadd_rn(v, p.bias[n]);
+            const size_t at = (size_t)m * p.ldy + n;
+            if (p.out_f16) ((__half *)p.y)[at] = __float2half_rn(v);
+            else ((float *)p.y)[at] = v;
+        }
+        __syncthreads(); // red is reused by the next tile
+    }
+}
+
+template <int MTW, int MG, int KS>
+static int launch_q4k(const GemmQ4KParams &p, int grid, size_t smem, cudaStream_t st) {
+    static size_t configured = 0;
+    if (smem > configured) {
+        CU_TRY(cudaFuncSetAttribute(k_gemm_mma_q4k<MTW, MG, KS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        configured = smem;
+    }
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid);
+    cfg.blockDim = dim3(KQ_WARPS * 32);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    CU_TRY(cudaLaunchKernelEx(&cfg, k_gemm_mma_q4k<MTW, MG, KS>, p));
+    return 0;
+}
+
+bool gemm_mma_q4k_supported(int M, int N, int K, const void *W) {
+    static int on = -1, min_rows = 9;
+    if (on < 0) {
+        const char *e = getenv("MLLMCU_Q4K_MMA");
+        on = (e && e[0] == '0') ? 0 : 1;
+        const char *r = getenv("MLLMCU_Q4K_MMA_MIN");
+        if (r && r[0]) min_rows = atoi(r);
+    }
+    return on == 1 && M >= min_rows && N > 0 && N % 16 == 0 && K > 0 && K % 256 == 0 && !((uintptr_t)W & 15);
+}
+
+// xq: native block_q8_K rows of the M activation rows (mllmcu_quantize_q8_K).  Serves M in chunks of 64 rows (128 when K has fewer
+// than 8 super-blocks): each chunk streams the weights again -- they stay in L2 between chunks.
+int launch_gemm_mma_q4k(const void *W, const void *xq, const float *bias, void *y, int M, int N, int K, int ldy, int out_f16, cudaStream_t st) {
+    if (!gemm_mma_q4k_supported(M, N, K, W)) return -2;
+    const int nsb = K / 256;
+    const bool wide = nsb < 8; // few super-blocks: 4 K-splits x 4 row groups (128 rows) instead of 8 x 2 (64 rows)
+    const int Mp = wide ? 128 : 64, KS = wide ? 4 : 8;
+    GemmQ4KParams p = {};
+    p.W = (const uint8_t *)W; p.bias = bias; p.N = N; p.nsb = nsb; p.ldy = ldy; p.out_f16 = out_f16;
+    // a stage of 16 rows x KC super-blocks <= ~40 KB, the ring gets what the reduction buffer leaves
+    int KC = nsb < 16 ? nsb : 16;
+    p.KC = KC; p.nchunk = (nsb + KC - 1) / KC;
+    p.pitch = KC * KQ_Q4K + 16; // 2304 + 16: rows g = 0..7 of a fragment start 16 bytes apart in the banks
+    const size_t red = ((size_t)KS * 16 * Mp * 4 + 127) & ~(size_t)127, stage = (size_t)16 * p.pitch;
+    int S = (int)((200 * 1024 - red) / stage);
+    if (S > 8) S = 8;
+    if (S < 2) return -2;
+    p.stages = S;
+    const size_t smem = 128 + red + (size_t)S * stage;
+    int grid = cu_sm_count();
+    if (grid > N / 16) grid = N / 16;
+    const size_t esz = out_f16 ? 2 : 4;
+    for (int m0 = 0; m0 < M; m0 += Mp) {
+        p.M = M - m0 < Mp ? M - m0 : Mp;
+        p.xq = (const uint8_t *)xq + (size_t)m0 * nsb * KQ_Q8K;
+        p.y = (char *)y + (size_t)m0 * ldy * esz;
+        const int rc = wide ? launch_q4k<4, 4, 4>(p, grid, smem, st) : launch_q4k<4, 2, 8>(p, grid, smem, st);
+        if (rc) return rc;
+    }
+    return 0;
+}

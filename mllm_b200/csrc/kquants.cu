@@ -325,6 +325,7 @@ static int launch_kq(const uint8_t *W, const uint8_t *xq, const float *bias, voi
     return 0;
 }
 
+int launch_gemm_mma_q4k(const void *W, const void *xq, const float *bias, void *y, int M, int N, int K, int ldy, int out_f16, cudaStream_t st); // gemm_mma_q4k.cu
 // called by mllmcu_linear for wtype 12 (Q4_K) / 14 (Q6_K)
 int launch_linear_kq(int wtype, const void *W, const float *x, const float *bias, void *y, int M, int N, int K, int ldx, int ldy, int out_f16,
                      void *ws, cudaStream_t st) {
@@ -333,6 +334,10 @@ int launch_linear_kq(int wtype, const void *W, const float *x, const float *bias
     if (wtype == 14 && ((uintptr_t)W & 1)) return -1;
     const int rc = mllmcu_quantize_q8_K(x, ws, M, K, ldx, st);
     if (rc) return rc;
+    if (wtype == 12) { // 9+ rows: the tensor-core kernel (gemm_mma_q4k.cu); -2 = shape outside it
+        const int rm = launch_gemm_mma_q4k(W, ws, bias, y, M, N, K, ldy, out_f16, st);
+        if (rm != -2) return rm;
+    }
     return wtype == 12 ? launch_kq<12>((const uint8_t *)W, (const uint8_t *)ws, bias, y, M, N, K / QK_K, ldy, out_f16, st)
                        : launch_kq<14>((const uint8_t *)W, (const uint8_t *)ws, bias, y, M, N, K / QK_K, ldy, out_f16, st);
 }

@@ -94,7 +94,10 @@ def test_linear_q4_K_q6_K_golden(cu, g2):
     kq_check(y, g2["lin_q6k"])
 
 
-@pytest.mark.parametrize("M,N,K", [(1, 64, 256), (1, 4096, 4096), (3, 50, 11008), (8, 33, 1024), (9, 130, 512), (70, 200, 2048), (130, 64, 4096)])
+# rows >= 9 with N % 16 == 0 take the tensor-core kernel (gemm_mma_q4k.cu: u8 x s8 mma.sync, integer scale / min sums): short K (4 K-splits x
+# 128 rows), K = 2048 / 4096 (one stage per tile), K = 11008 (three stages per tile, the last one short), several row chunks, a partial chunk
+@pytest.mark.parametrize("M,N,K", [(1, 64, 256), (1, 4096, 4096), (3, 50, 11008), (8, 33, 1024), (9, 130, 512), (70, 200, 2048), (130, 64, 4096),
+                                   (9, 128, 512), (70, 208, 2048), (200, 96, 11008), (64, 2048, 4096), (608, 64, 1024), (577, 48, 4096)])
 @pytest.mark.parametrize("wt", ["q4k", "q6k"])
 def test_linear_k_quants(cu, oracle, M, N, K, wt):
     rng = np.random.default_rng(M * 5 + N + K)
