@@ -137,30 +137,37 @@ __global__ void __launch_bounds__(KQ_WARPS * 32) k_gemm_mma_q4k(const GemmQ4KPar
                         }
                     }
                 }
-                // the min term and the super-block's two fp32 FMAs (same operations as k_gemm_kq: d = d_x * d_w, -d_x * dmin_w)
+                // The min term summ[row][col] = sum_j min_j[row] * bs_j[col], bs_j = bsums[2j] + bsums[2j+1] (|bs_j| <= 4096: 13 bits), as two more
+                // MMAs instead of 8 multiply-adds per output: bs_j = 64 * hi_j + lo_j (hi_j = bs_j >> 6 in [-64, 63], lo_j in [0, 63]) are the B
+                // operands (k = j, the other 24 k are zero), the eight 6-bit mins of the 16 rows the A operand; summ = 64 * S_hi + S_lo, exact.
+                const uint32_t ma0 = t == 0 ? mn0[0] : t == 1 ? mn0[1] : 0u, ma1 = t == 0 ? mn1[0] : t == 1 ? mn1[1] : 0u; // k = 4t .. 4t+3 -> j
 #pragma unroll
                 for (int m = 0; m < MTW; m++) {
+                    uint32_t bh = 0, bl = 0;
+                    if (t < 2) { // B-fragment row = column (colw + 8 m + g): its group sums 8t .. 8t+7 -> bs_j for j = 4t .. 4t+3
+                        const uint8_t *xb = xb_frag[m] + (size_t)sb * KQ_Q8K + 260 + 16 * t;
+#pragma unroll
+                        for (int q = 0; q < 4; q++) {
+                            const uint32_t wq = *(const uint32_t *)(xb + 4 * q);
+                            const int bs = (int)(short)(wq & 0xFFFFu) + (int)(short)(wq >> 16);
+                            bh |= ((uint32_t)(bs >> 6) & 0xFFu) << (8 * q);
+                            bl |= ((uint32_t)bs & 63u) << (8 * q);
+                        }
+                    }
+                    int sh[4], sl[4];
+                    mma_u8s8(sh, ma0, ma1, 0u, 0u, bh, 0u);
+                    mma_u8s8(sl, ma0, ma1, 0u, 0u, bl, 0u);
                     const uint8_t *c0 = xb_c0[m] + (size_t)sb * KQ_Q8K, *c1 = xb_c1[m] + (size_t)sb * KQ_Q8K;
                     const float dx0 = *(const float *)c0, dx1 = *(const float *)c1;
-                    uint32_t wa[8], wb[8]; // the 16 int16 group sums of columns 2t and 2t + 1 (a Q8_K block is 292 bytes: 4-byte aligned only)
-#pragma unroll
-                    for (int j = 0; j < 8; j++) { wa[j] = *(const uint32_t *)(c0 + 260 + 4 * j); wb[j] = *(const uint32_t *)(c1 + 260 + 4 * j); }
-                    int sm[4] = {0, 0, 0, 0};
-#pragma unroll
-                    for (int j = 0; j < 8; j++) {
-                        const int ba = (int)(short)(wa[j] & 0xFFFFu) + (int)(short)(wa[j] >> 16); // bsums[2j] + bsums[2j+1]
-                        const int bb = (int)(short)(wb[j] & 0xFFFFu) + (int)(short)(wb[j] >> 16);
-                        const int m0 = byte_of(mn0, j), m1 = byte_of(mn1, j);
-                        sm[0] += m0 * ba; sm[1] += m0 * bb; sm[2] += m1 * ba; sm[3] += m1 * bb;
-                    }
+                    // the super-block's two fp32 FMAs (same operations as k_gemm_kq: d = d_x * d_w, -d_x * dmin_w)
                     acc[m][0] = fmaf(__fmul_rn(dx0, dw0), (float)sumi[m][0], acc[m][0]);
                     acc[m][1] = fmaf(__fmul_rn(dx1, dw0), (float)sumi[m][1], acc[m][1]);
                     acc[m][2] = fmaf(__fmul_rn(dx0, dw1), (float)sumi[m][2], acc[m][2]);
                     acc[m][3] = fmaf(__fmul_rn(dx1, dw1), (float)sumi[m][3], acc[m][3]);
-                    acc[m][0] = fmaf(__fmul_rn(-dx0, dm0), (float)sm[0], acc[m][0]);
-                    acc[m][1] = fmaf(__fmul_rn(-dx1, dm0), (float)sm[1], acc[m][1]);
-                    acc[m][2] = fmaf(__fmul_rn(-dx0, dm1), (float)sm[2], acc[m][2]);
-                    acc[m][3] = fmaf(__fmul_rn(-dx1, dm1), (float)sm[3], acc[m][3]);
+                    acc[m][0] = fmaf(__fmul_rn(-dx0, dm0), (float)(64 * sh[0] + sl[0]), acc[m][0]);
+                    acc[m][1] = fmaf(__fmul_rn(-dx1, dm0), (float)(64 * sh[1] + sl[1]), acc[m][1]);
+                    acc[m][2] = fmaf(__fmul_rn(-dx0, dm1), (float)(64 * sh[2] + sl[2]), acc[m][2]);
+                    acc[m][3] = fmaf(__fmul_rn(-dx1, dm1), (float)(64 * sh[3] + sl[3]), acc[m][3]);
                 }
             }
             __syncthreads(); // every warp is done reading the slot
