@@ -88,13 +88,15 @@ __global__ void __launch_bounds__(KQ_WARPS * 32) k_gemm_mma_q4k(const GemmQ4KPar
 
     const int colw = mg * MTW * 8;
     // per batch tile: the B-fragment row (colw + 8 m + g) and the two output columns (colw + 8 m + 2 t, + 1), clamped into the rows that exist
-    const uint8_t *xb_frag[MTW], *xb_c0[MTW], *xb_c1[MTW];
+    // (32-bit byte offsets from xq: at most 640 rows x 64 super-blocks x 292 bytes)
+    uint32_t of_frag[MTW], of_c0[MTW], of_c1[MTW];
 #pragma unroll
     for (int m = 0; m < MTW; m++) {
-        xb_frag[m] = p.xq + (size_t)min(colw + m * 8 + g, p.M - 1) * nsb * KQ_Q8K;
-        xb_c0[m] = p.xq + (size_t)min(colw + m * 8 + 2 * t, p.M - 1) * nsb * KQ_Q8K;
-        xb_c1[m] = p.xq + (size_t)min(colw + m * 8 + 2 * t + 1, p.M - 1) * nsb * KQ_Q8K;
+        of_frag[m] = (uint32_t)min(colw + m * 8 + g, p.M - 1) * (uint32_t)(nsb * KQ_Q8K);
+        of_c0[m] = (uint32_t)min(colw + m * 8 + 2 * t, p.M - 1) * (uint32_t)(nsb * KQ_Q8K);
+        of_c1[m] = (uint32_t)min(colw + m * 8 + 2 * t + 1, p.M - 1) * (uint32_t)(nsb * KQ_Q8K);
     }
+    const uint8_t *xq = p.xq;
     for (int i = 0; i < n_tiles; i++) {
         float acc[MTW][4]; // [0],[1]: weight row g, columns 2t, 2t+1; [2],[3]: row g + 8
 #pragma unroll
@@ -128,7 +130,7 @@ __global__ void __launch_bounds__(KQ_WARPS * 32) k_gemm_mma_q4k(const GemmQ4KPar
                         const int s0 = byte_of(sc0, j), s1 = byte_of(sc1, j);
 #pragma unroll
                         for (int m = 0; m < MTW; m++) {
-                            const uint8_t *xb = xb_frag[m] + (size_t)sb * KQ_Q8K + 4 + j * 32;
+                            const uint8_t *xb = xq + of_frag[m] + (uint32_t)(sb * KQ_Q8K + 4 + j * 32);
                             const uint32_t b0 = *(const uint32_t *)(xb + 4 * t), b1 = *(const uint32_t *)(xb + 16 + 4 * t);
                             int cc[4];
                             mma_u8s8(cc, a0, a1, a2, a3, b0, b1);
@@ -145,7 +147,7 @@ __global__ void __launch_bounds__(KQ_WARPS * 32) k_gemm_mma_q4k(const GemmQ4KPar
                 for (int m = 0; m < MTW; m++) {
                     uint32_t bh = 0, bl = 0;
                     if (t < 2) { // B-fragment row = column (colw + 8 m + g): its group sums 8t .. 8t+7 -> bs_j for j = 4t .. 4t+3
-                        const uint8_t *xb = xb_frag[m] + (size_t)sb * KQ_Q8K + 260 + 16 * t;
+                        const uint8_t *xb = xq + of_frag[m] + (uint32_t)(sb * KQ_Q8K + 260 + 16 * t);
 #pragma unroll
                         for (int q = 0; q < 4; q++) {
                             const uint32_t wq = *(const uint32_t *)(xb + 4 * q);
@@ -157,7 +159,7 @@ __global__ void __launch_bounds__(KQ_WARPS * 32) k_gemm_mma_q4k(const GemmQ4KPar
                     int sh[4], sl[4];
                     mma_u8s8(sh, ma0, ma1, 0u, 0u, bh, 0u);
                     mma_u8s8(sl, ma0, ma1, 0u, 0u, bl, 0u);
-                    const uint8_t *c0 = xb_c0[m] + (size_t)sb * KQ_Q8K, *c1 = xb_c1[m] + (size_t)sb * KQ_Q8K;
+                    const uint8_t *c0 = xq + of_c0[m] + (uint32_t)(sb * KQ_Q8K), *c1 = xq + of_c1[m] + (uint32_t)(sb * KQ_Q8K);
                     const float dx0 = *(const float *)c0, dx1 = *(const float *)c1;
                     // the super-block's two fp32 FMAs (same operations as k_gemm_kq: d = d_x * d_w, -d_x * dmin_w)
                     acc[m][0] = fmaf(__fmul_rn(dx0, dw0), (float)sumi[m][0], acc[m][0]);
@@ -232,8 +234,14 @@ bool gemm_mma_q4k_supported(int M, int N, int K, const void *W) {
 int launch_gemm_mma_q4k(const void *W, const void *xq, const float *bias, void *y, int M, int N, int K, int ldy, int out_f16, cudaStream_t st) {
     if (!gemm_mma_q4k_supported(M, N, K, W)) return -2;
     const int nsb = K / 256;
-    const bool wide = nsb < 8; // few super-blocks: 4 K-splits x 4 row groups (128 rows) instead of 8 x 2 (64 rows)
-    const int Mp = wide ? 128 : 64, KS = wide ? 4 : 8;
+    // row groups x K-splits of the 16 warps: up to 64 rows 2 x 8, up to 128 rows (or short K) 4 x 4; prefill-sized M gives every warp its own
+    // 8 MTW rows over the whole K (16 x 1: no partial sums to merge, long steady loops), MTW = 2..5 -> 256..640 rows per pass over the weights
+    static int big = -1;
+    if (big < 0) { const char *e = getenv("MLLMCU_Q4K_MMA_BIG"); big = (e && e[0] == '0') ? 0 : 1; }
+    int variant; // 0: <4,2,8>  1: <4,4,4>  2..5: <MTW,16,1>
+    if (M > 128 && big) variant = M > 512 ? 5 : M > 384 ? 4 : M > 256 ? 3 : 2;
+    else variant = (nsb < 8 || M > 64) ? 1 : 0;
+    const int Mp = variant == 0 ? 64 : variant == 1 ? 128 : 128 * variant, KS = variant == 0 ? 8 : variant == 1 ? 4 : 1;
     GemmQ4KParams p = {};
     p.W = (const uint8_t *)W; p.bias = bias; p.N = N; p.nsb = nsb; p.ldy = ldy; p.out_f16 = out_f16;
     // a stage of 16 rows x KC super-blocks <= ~40 KB, the ring gets what the reduction buffer leaves
@@ -253,7 +261,15 @@ int launch_gemm_mma_q4k(const void *W, const void *xq, const float *bias, void *
         p.M = M - m0 < Mp ? M - m0 : Mp;
         p.xq = (const uint8_t *)xq + (size_t)m0 * nsb * KQ_Q8K;
         p.y = (char *)y + (size_t)m0 * ldy * esz;
-        const int rc = wide ? launch_q4k<4, 4, 4>(p, grid, smem, st) : launch_q4k<4, 2, 8>(p, grid, smem, st);
+        int rc;
+        switch (variant) {
+        case 0: rc = launch_q4k<4, 2, 8>(p, grid, smem, st); break;
+        case 1: rc = launch_q4k<4, 4, 4>(p, grid, smem, st); break;
+        case 2: rc = launch_q4k<2, 16, 1>(p, grid, smem, st); break;
+        case 3: rc = launch_q4k<3, 16, 1>(p, grid, smem, st); break;
+        case 4: rc = launch_q4k<4, 16, 1>(p, grid, smem, st); break;
+        default: rc = launch_q4k<5, 16, 1>(p, grid, smem, st); break;
+        }
         if (rc) return rc;
     }
     return 0;
