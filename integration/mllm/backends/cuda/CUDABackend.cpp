@@ -46,10 +46,23 @@ void CUDAMemoryManager::alloc(void **ptr, size_t size, size_t /*alignment: block
         pool_hits++;
         return;
     }
+    constexpr size_t SLAB = (size_t)128 << 20;
+    auto raw = [&](size_t n) {
+        void *q = nullptr;
+        if (kind) MLLMCU_CHECK(mllmcu_malloc(&q, n));
+        else MLLMCU_CHECK(mllmcu_malloc_managed(&q, n, device_));
+        owned_.push_back(q);
+        bytes_allocated += n;
+        return q;
+    };
     void *p = nullptr;
-    if (kind) MLLMCU_CHECK(mllmcu_malloc(&p, cls));
-    else MLLMCU_CHECK(mllmcu_malloc_managed(&p, cls, device_));
-    bytes_allocated += cls;
+    if (cls > SLAB / 4) p = raw(cls);
+    else {
+        auto &sl = slabs_[kind];
+        if (sl.empty() || sl.back().used + cls > sl.back().size) sl.push_back({(char *)raw(SLAB), SLAB, 0});
+        p = sl.back().base + sl.back().used; // classes are multiples of 256 bytes: every carved block is 256-byte aligned
+        sl.back().used += cls;
+    }
     pool_misses++;
     live_[p] = {cls, kind};
     *ptr = p;
@@ -64,9 +77,7 @@ void CUDAMemoryManager::free(void *ptr) {
 }
 
 CUDAMemoryManager::~CUDAMemoryManager() {
-    for (auto &fl : free_list_)
-        for (auto &kv : fl) mllmcu_free(kv.second);
-    for (auto &kv : live_) mllmcu_free(kv.first);
+    for (void *q : owned_) mllmcu_free(q);
 }
 
 // ------------------------------------------------------------------ backend

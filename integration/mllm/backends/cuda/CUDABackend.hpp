@@ -32,7 +32,9 @@ namespace mllm {
 class Module;
 class Layer;
 
-// Size-class pool over CUDA unified memory (replaces MemoryPoolManager for this backend; mllm/memory/MemoryPoolManager.hpp).
+// Size-class pool over CUDA unified memory (replaces MemoryPoolManager for this backend; mllm/memory/MemoryPoolManager.hpp).  Blocks up
+// to a quarter slab are carved from 128 MiB slabs (one cudaMallocManaged / cudaMalloc per slab), so a first forward -- hundreds of new
+// tensor sizes -- costs a handful of driver allocations instead of one each; freed blocks go to the size-class free lists.
 class CUDAMemoryManager final : public MemoryManager {
 public:
     explicit CUDAMemoryManager(int device) : device_(device) {}
@@ -48,6 +50,9 @@ private:
     int device_;
     std::multimap<size_t, void *> free_list_[2];    // [unified | device-only] size class -> free blocks (stream-ordered reuse: one stream per backend)
     std::unordered_map<void *, std::pair<size_t, int>> live_; // block -> (size class, kind)
+    struct Slab { char *base; size_t size, used; };
+    std::vector<Slab> slabs_[2];
+    std::vector<void *> owned_; // what the destructor returns to the driver: slabs and the blocks too large for one
 };
 
 // What the decode-step fuser reads from an op it folds into a fused launch (pointers stay owned by the op).
