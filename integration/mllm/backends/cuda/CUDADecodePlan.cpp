@@ -243,18 +243,19 @@ bool DecodePlanBuilder::issue_kquant(CUDABackend *bn, CUDABackend::DecodePlan &p
         MLLMCU_CHECK(mllmcu_linear_ex(f.wtype, f.weight, in, f.bias, out, B, f.out, K, K, ldy, 0, ws, p.lin_ws_bytes, reuse, st));
         n += 2 - reuse;
     };
+    auto kq = [](const CUDAFuseInfo &f) { return f.wtype == MLLM_TYPE_Q4_K || f.wtype == MLLM_TYPE_Q6_K; };
     for (auto &l : p.layers) {
         MLLMCU_CHECK(mllmcu_rmsnorm(x, l.n1.norm_w, t1, B, H, l.n1.eps, 0, st));
         lin(l.q, t1, H, qkv, QKV, 0);
-        lin(l.k, t1, H, qkv + (size_t)Hq * D, QKV, 0); // the k-quant Linear re-quantises per call (its Q8_K image is not shared yet)
-        lin(l.v, t1, H, qkv + (size_t)(Hq + Hkv) * D, QKV, 0);
+        lin(l.k, t1, H, qkv + (size_t)Hq * D, QKV, kq(l.q) && kq(l.k)); // q / k / v read one block_q8_K image of the normalised row
+        lin(l.v, t1, H, qkv + (size_t)(Hq + Hkv) * D, QKV, kq(l.q) && kq(l.k) && kq(l.v));
         MLLMCU_CHECK(mllmcu_decode_attn_rope(l.rope.rope_type, qkv, QKV, l.kptr, l.vptr, ao, Hq * D, ctl, B, Hq, Hkv, D, l.rope.sin_t, l.rope.cos_t,
                                              l.rope.rot_dim, p.kv_bstride, p.limit, p.attn_ws.rawHostPtr(), p.attn_ws_bytes, 0, st));
         lin(l.o, ao, Hq * D, t2, H, 0);
         MLLMCU_CHECK(mllmcu_add(x, t2, x2, (size_t)B * H, st));
         MLLMCU_CHECK(mllmcu_rmsnorm(x2, l.n2.norm_w, t1, B, H, l.n2.eps, 0, st));
         lin(l.gate, t1, H, g, F, 0);
-        lin(l.up, t1, H, gu, F, 0);
+        lin(l.up, t1, H, gu, F, kq(l.gate) && kq(l.up));
         MLLMCU_CHECK(mllmcu_silu_mul(g, gu, g, (size_t)B * F, st));
         lin(l.down, g, F, t2, H, 0);
         MLLMCU_CHECK(mllmcu_add(x2, t2, x, (size_t)B * H, st));

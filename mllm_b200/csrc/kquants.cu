@@ -328,12 +328,14 @@ static int launch_kq(const uint8_t *W, const uint8_t *xq, const float *bias, voi
 int launch_gemm_mma_q4k(const void *W, const void *xq, const float *bias, void *y, int M, int N, int K, int ldy, int out_f16, cudaStream_t st); // gemm_mma_q4k.cu
 // called by mllmcu_linear for wtype 12 (Q4_K) / 14 (Q6_K)
 int launch_linear_kq(int wtype, const void *W, const float *x, const float *bias, void *y, int M, int N, int K, int ldx, int ldy, int out_f16,
-                     void *ws, cudaStream_t st) {
+                     void *ws, int skip_quant, cudaStream_t st) {
     if (K % QK_K || ldx % 4 || ((uintptr_t)x & 15)) return -1;
     if (wtype == 12 && ((uintptr_t)W & 15)) return -1;
     if (wtype == 14 && ((uintptr_t)W & 1)) return -1;
-    const int rc = mllmcu_quantize_q8_K(x, ws, M, K, ldx, st);
-    if (rc) return rc;
+    if (!skip_quant) { // skip: ws already holds the block_q8_K rows of these activations (q / k / v, gate / up share one input)
+        const int rc = mllmcu_quantize_q8_K(x, ws, M, K, ldx, st);
+        if (rc) return rc;
+    }
     if (wtype == 12) { // 9+ rows: the tensor-core kernel (gemm_mma_q4k.cu); -2 = shape outside it
         const int rm = launch_gemm_mma_q4k(W, ws, bias, y, M, N, K, ldy, out_f16, st);
         if (rm != -2) return rm;

@@ -219,7 +219,7 @@ int launch_gemm_q4_0_tc(const void *W, const float *x, int ldx, const float *bia
 // k-quant weights (kquants.cu)
 size_t kq_workspace_bytes(int M, int K);
 int launch_linear_kq(int wtype, const void *W, const float *x, const float *bias, void *y, int M, int N, int K, int ldx, int ldy, int out_f16,
-                     void *ws, cudaStream_t st);
+                     void *ws, int skip_quant, cudaStream_t st);
 
 MLLMCU_API size_t mllmcu_linear_workspace_bytes(int M, int K) {
     if (M <= 0 || K <= 0) return 0;
@@ -252,7 +252,8 @@ static bool linear_mma_enabled() {
 }
 
 MLLMCU_API int mllmcu_linear_quant_kind(int wtype, int M, int N, int K, const void *W) {
-    if (wtype != 2 && wtype != 8) return 0; // k-quants keep their own Q8_K image
+    if (wtype == 12 || wtype == 14) return (K % 256) ? 0 : 4; // 4: native block_q8_K rows at the start of ws (shared by Q4_K and Q6_K)
+    if (wtype != 2 && wtype != 8) return 0;
     if (wtype == 2 && M >= 3 && M <= 64 && linear_mma_enabled() && gemv_mma_supported(wtype, M, K, &N, 1, &W)) return 0; // own image, not in ws
     return (gemm_tc_supported(wtype, M, N, K) && !((uintptr_t)W & 15)) ? gemm_tc_quant_kind() : 3; // 3: split Q8_0 (GEMV / dp4a / scaled tcgen05)
 }
@@ -270,7 +271,7 @@ MLLMCU_API int mllmcu_linear_ex(int wtype, const void *W, const float *x, const 
     if (wtype != 2 && wtype != 8 && wtype != 12 && wtype != 14) return -2;
     if (ws == nullptr || ws_bytes < mllmcu_linear_workspace_bytes(M, K)) return -3;
     cudaStream_t st = (cudaStream_t)stream;
-    if (wtype == 12 || wtype == 14) return launch_linear_kq(wtype, W, x, bias, y, M, N, K, ldx, ldy, out_f16, ws, st);
+    if (wtype == 12 || wtype == 14) return launch_linear_kq(wtype, W, x, bias, y, M, N, K, ldx, ldy, out_f16, ws, flags & 1, st);
     // 3..64 rows of Q4_0 (batched decode, short prompts): the tensor-core GEMV (gemv_mma.cu), which keeps its own activation image
     if (wtype == 2 && M >= 3 && M <= 64 && linear_mma_enabled()) {
         mllmcu_gemv_desc d = {};
