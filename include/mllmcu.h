@@ -53,6 +53,10 @@ int mllmcu_free(void *dptr);
  * backend's MemoryManager hands to TensorImpl::host_ptr_, so the reference's pointer-arithmetic tensor views work on device
  * memory and host code may still dereference a tensor (integration/mllm/backends/cuda/CUDABackend.hpp).  Freed with mllmcu_free. */
 int mllmcu_malloc_managed(void **ptr, size_t bytes, int device);
+/* Bring a range of unified memory (back) to `device` after host code wrote it -- CPUKVCache zero-fills its cache with memset at
+ * construction (op/CPUKVCache.cpp:55-66, :85-96), which moves those pages to the host; without this every first kernel write to a cache
+ * page faults.  A hint: ranges that are not managed memory are left alone. */
+int mllmcu_mem_prefetch(void *ptr, size_t bytes, int device, void *stream);
 int mllmcu_memset(void *dptr, int value, size_t bytes, void *stream);
 int mllmcu_memcpy_h2d(void *dst, const void *host_src, size_t bytes, void *stream);
 int mllmcu_memcpy_d2h(void *host_dst, const void *src, size_t bytes, void *stream);
@@ -258,6 +262,21 @@ int mllmcu_quantize_q8_K(const float *x, void *y_blocks, int rows, int k, int ld
  * sumi[n][m][i] = sum_sb scale_sb * (q4_sb . q8_sb), summ[n][m][i] = sum_sb min_sb * (bsums[2sb] + bsums[2sb+1]).
  * Test/diagnostic entry point. */
 int mllmcu_block_isums_q4_K_q8_K(const void *W, const void *xq_blocks, int32_t *sumi, int32_t *summ, int M, int N, int K, void *stream);
+
+/* ---- single-token step of a Q4_K body (LLaVA-1.5-7B): the ops in front of a Linear folded into the activation quantiser, the residual
+ * add folded into the GEMV, every launch a programmatic dependent of the previous one (pdl != 0).
+ * mllmcu_prep_q8_K writes the block_q8_K rows (as mllmcu_quantize_q8_K) of
+ *   mode 0: x;   mode 1: RMSNorm(x) with weight aux[k] (CPURMSNorm::execute, op/CPURMSNorm.cpp:31-95; the arithmetic of mllmcu_rmsnorm);
+ *   mode 2: SiLU(x) * aux, aux laid out as x (CPUSiLU + CPUMul of the MLP, models/llama/modeling_llama.hpp:20-41; the arithmetic of
+ *   mllmcu_silu_mul) -- values and bytes identical to running the separate ops and then mllmcu_quantize_q8_K.
+ * mllmcu_gemv_q4k: y[s][m * ldy + n] = sum_k W[s][n][k] x[m][k] (+ bias[s][n]) for nW <= 3 Q4_K matrices sharing the M <= 8 activation
+ * rows xq_blocks (q | k | v, gate | up: one launch), the reference's vec_dot_q4_K_q8_K integers (ggml/VecDotQ4.cpp:220-283) and the fp32
+ * accumulation order of mllmcu_linear's GEMV (bit-identical to it); residual != NULL (nW == 1): y = residual + that (CPUAdd after o_proj /
+ * down_proj).  W, N, bias, y are HOST arrays of nW entries (bias may be NULL). */
+int mllmcu_prep_q8_K(int mode, const float *x, const float *aux, float eps, int add_unit_offset, void *y_blocks, int rows, int k, int ldx,
+                     int pdl, void *stream);
+int mllmcu_gemv_q4k(int nW, const void *const *W, const int *N, const float *const *bias, float *const *y, int ldy, const void *xq_blocks,
+                    int M, int K, const float *residual, int ldr, int pdl, void *stream);
 
 /* ---- Q4_0_4_4 weights (block_q4_0x4, mllm/DataType.hpp:104-107; make_block_q4_0x4 + quantize_q4_0_nr_bl,
  * ggml/GemmPack.cpp:45-60, :308-344; consumed by gemv/gemm_q4_0_4x4_q8_0 when W.dtype == MLLM_TYPE_Q4_0_4_4,

@@ -279,6 +279,7 @@ std::vector<Tensor> CUDABackend::runOp(Op *op, std::vector<Tensor> inputs, std::
         }
     }
     op->reshape(input_tensors, out_tensors);
+    if (op->type() == KVCACHE) settleKVCache(op);
     if (!in_place) {
         for (auto &out_tensor : out_tensors) {
             auto act_it = activation_tensors.find(out_tensor->name());

@@ -103,8 +103,10 @@ public:
 
     bool addCreator(OpType t, Creator *c);
     void *stream() const { return stream_; }
+    int device() const { return device_; }
     CUDAMemoryManager *memory() const { return static_cast<CUDAMemoryManager *>(mem_manager_.get()); }
     void sync();
+    void settleKVCache(Op *op); // CUDAOps.cpp: a cache the host has just zero-filled goes back to the device
     void *workspace(size_t bytes); // scratch shared by ops (activation quantisation, split-K partials); grows monotonically
     size_t workspaceBytes() const { return ws_bytes_; }
     // q/k/v and gate/up read one activation tensor back to back: the later Linears reuse the first one's quantised image
@@ -130,6 +132,7 @@ private:
     void *ws_ = nullptr;
     size_t ws_bytes_ = 0;
     QuantTag qtag_;
+    std::unordered_map<Op *, void *> settled_caches_;
     void *stage_ = nullptr; // pinned staging for load_from_file
     size_t stage_bytes_ = 0;
     int load_fd_ = -1;

@@ -42,6 +42,7 @@ struct CUDABackend::DecodePlan {
     Tensor t1, t2, gu, lin_ws; // k-quant models: normalised row, Linear output, up projection, the Linears' Q8_K workspace
     size_t attn_ws_bytes = 0, lin_ws_bytes = 0;
     bool kquant = false;       // Linears are Q4_K / Q6_K: op-level kernels on fixed buffers inside the captured graph
+    bool q4k_chain = true;     // ... every one of them Q4_K: the nine-launch chain of kquants.cu (prep + multi-matrix GEMV, PDL)
     bool mrope = false;        // Qwen2-VL: MultimodalRoPE ops; the rotary position comes with the call (position ids), not from the cache length
     int rope_delta = 0;        // rotary position - cache length of the request being decoded (constant over its decode steps)
     Tensor msin, mcos;         // mrope: rotate-half tables [limit][D] for text positions
@@ -103,6 +104,7 @@ struct DecodePlanBuilder {
             for (const CUDAFuseInfo *f : {&L.q, &L.k, &L.v, &L.o, &L.gate, &L.up, &L.down}) {
                 if (f->wtype == MLLM_TYPE_Q4_K || f->wtype == MLLM_TYPE_Q6_K) p->kquant = true;
                 else if (f->wtype != MLLM_TYPE_Q4_0) return nullptr;
+                if (f->wtype != MLLM_TYPE_Q4_K) p->q4k_chain = false;
             }
             if (L.n1.unit_offset || L.n2.unit_offset) return nullptr;
         }
@@ -121,6 +123,7 @@ struct DecodePlanBuilder {
         p->kv_bstride = (long long)kc.sequence() * kc.head() * kc.dimension();
         if (p->head.wtype == MLLM_TYPE_Q4_K || p->head.wtype == MLLM_TYPE_Q6_K) p->kquant = true;
         else if (p->head.wtype != MLLM_TYPE_Q4_0) return nullptr;
+        if (p->head.wtype != MLLM_TYPE_Q4_K || getenv("MLLM_CUDA_Q4K_CHAIN_OFF")) p->q4k_chain = false;
         if (p->embd.wtype != MLLM_TYPE_Q4_0 || p->norm.unit_offset) return nullptr;
         if (p->kquant && (p->H % 256 || p->F % 256 || (p->Hq * p->D) % 256)) return nullptr; // Q8_K super-blocks
         if (p->H % 128 || p->F % 128 || (p->D != 32 && p->D != 64 && p->D != 128) || L0.rope.rot_dim != p->D || B < 1 || B > 8) return nullptr;
@@ -228,9 +231,11 @@ struct DecodePlanBuilder {
     }
 };
 
-// k-quant models (the LLaVA body is Q4_K): the same step from the op-level kernels -- RMSNorm, Linear (Q8_K activations, integer
-// super-block sums), the fused RoPE + append + attention kernel, add, SiLU * mul -- on the plan's fixed buffers, so the sequence is still
-// captured once and replayed without host dispatch (no fused k-quant GEMV yet).
+// k-quant models (the LLaVA body is Q4_K).  All Linears Q4_K: nine launches per block -- the op in front of each Linear (RMSNorm, SiLU * up) folded
+// into the block_q8_K quantiser, q | k | v and gate | up as one GEMV launch each, the residual add in the epilogue of o / down, every kernel a
+// programmatic dependent of the one before it (kquants.cu, mllmcu_prep_q8_K / mllmcu_gemv_q4k; values bit-identical to the op-by-op sequence).
+// Mixed Q4_K / Q6_K / Q4_0 bodies: the same step from the op-level kernels -- RMSNorm, Linear, the fused RoPE + append + attention kernel, add,
+// SiLU * mul -- on the plan's fixed buffers.  Either way the sequence is captured once and replayed without host dispatch.
 bool DecodePlanBuilder::issue_kquant(CUDABackend *bn, CUDABackend::DecodePlan &p) {
     void *st = bn->stream();
     const int B = p.B, H = p.H, D = p.D, Hq = p.Hq, Hkv = p.Hkv, F = p.F, QKV = (Hq + 2 * Hkv) * D;
@@ -239,6 +244,40 @@ bool DecodePlanBuilder::issue_kquant(CUDABackend *bn, CUDABackend::DecodePlan &p
     float *t1 = p.t1.hostPtr<float>(), *t2 = p.t2.hostPtr<float>(), *gu = p.gu.hostPtr<float>();
     void *ws = p.lin_ws.rawHostPtr();
     int n = 1;
+    if (p.q4k_chain) {
+        auto prep = [&](int mode, const float *in, const float *aux, float eps, int K) {
+            MLLMCU_CHECK(mllmcu_prep_q8_K(mode, in, aux, eps, 0, ws, B, K, K, 1, st));
+            n++;
+        };
+        auto gemv = [&](std::initializer_list<const CUDAFuseInfo *> fs, std::initializer_list<float *> outs, int ldy, int K, const float *res) {
+            const void *W[3] = {};
+            const float *bias[3] = {};
+            float *y[3] = {};
+            int N[3] = {}, k = 0;
+            for (const CUDAFuseInfo *f : fs) { W[k] = f->weight; bias[k] = f->bias; N[k] = f->out; k++; }
+            k = 0;
+            for (float *o : outs) y[k++] = o;
+            MLLMCU_CHECK(mllmcu_gemv_q4k(k, W, N, bias, y, ldy, ws, B, K, res, ldy, 1, st));
+            n++;
+        };
+        for (auto &l : p.layers) {
+            prep(1, x, l.n1.norm_w, l.n1.eps, H);
+            gemv({&l.q, &l.k, &l.v}, {qkv, qkv + (size_t)Hq * D, qkv + (size_t)(Hq + Hkv) * D}, QKV, H, nullptr);
+            MLLMCU_CHECK(mllmcu_decode_attn_rope(l.rope.rope_type, qkv, QKV, l.kptr, l.vptr, ao, Hq * D, ctl, B, Hq, Hkv, D, l.rope.sin_t, l.rope.cos_t,
+                                                 l.rope.rot_dim, p.kv_bstride, p.limit, p.attn_ws.rawHostPtr(), p.attn_ws_bytes, 1, st));
+            n++;
+            prep(0, ao, nullptr, 0.f, Hq * D);
+            gemv({&l.o}, {x2}, H, Hq * D, x);
+            prep(1, x2, l.n2.norm_w, l.n2.eps, H);
+            gemv({&l.gate, &l.up}, {g, gu}, F, H, nullptr);
+            prep(2, g, gu, 0.f, F);
+            gemv({&l.down}, {x}, H, F, x2);
+        }
+        prep(1, x, p.norm.norm_w, p.norm.eps, H);
+        gemv({&p.head}, {p.logits.hostPtr<float>()}, p.V, H, nullptr);
+        p.launches = n;
+        return true;
+    }
     auto lin = [&](const CUDAFuseInfo &f, const float *in, int K, float *out, int ldy, int reuse) {
         MLLMCU_CHECK(mllmcu_linear_ex(f.wtype, f.weight, in, f.bias, out, B, f.out, K, K, ldy, 0, ws, p.lin_ws_bytes, reuse, st));
         n += 2 - reuse;

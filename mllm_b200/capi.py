@@ -26,6 +26,7 @@ SYMBOLS = {
     "mllmcu_malloc": (_i, [C.POINTER(_vp), _sz]),
     "mllmcu_free": (_i, [_vp]),
     "mllmcu_malloc_managed": (_i, [C.POINTER(_vp), _sz, _i]),
+    "mllmcu_mem_prefetch": (_i, [_vp, _sz, _i, _vp]),
     "mllmcu_memset": (_i, [_vp, _i, _sz, _vp]),
     "mllmcu_memcpy_h2d": (_i, [_vp, _vp, _sz, _vp]),
     "mllmcu_memcpy_d2h": (_i, [_vp, _vp, _sz, _vp]),
@@ -72,6 +73,8 @@ SYMBOLS = {
     "mllmcu_flash_attn_f16kv": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _ll, _vp, _sz, _vp]),
     "mllmcu_quantize_q8_K": (_i, [_vp, _vp, _i, _i, _i, _vp]),
     "mllmcu_block_isums_q4_K_q8_K": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _vp]),
+    "mllmcu_prep_q8_K": (_i, [_i, _vp, _vp, C.c_float, _i, _vp, _i, _i, _i, _i, _vp]),
+    "mllmcu_gemv_q4k": (_i, [_i, _vp, _vp, _vp, _vp, _i, _vp, _i, _i, _vp, _i, _i, _vp]),
     "mllmcu_q4_0_4x4_to_q4_0": (_i, [_vp, _vp, _i, _i, _vp]),
     "mllmcu_gelu_table": (_i, [_vp, _vp, _sz, _vp, _vp]),
     "mllmcu_softmax": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _vp]),
@@ -291,6 +294,38 @@ def quantize_q8_K(x):
     y = torch.zeros((rows, k // 256 * Q8_K_BYTES), dtype=torch.uint8, device=x.device)
     check(lib().mllmcu_quantize_q8_K(_ptr(x), _ptr(y), rows, k, x.stride(0), _stream()), "quantize_q8_K")
     return y
+
+
+def prep_q8_K(x, mode=0, aux=None, eps=0.0, add_unit_offset=False, pdl=False):
+    """block_q8_K rows of x (mode 0), RMSNorm(x; aux) (mode 1) or SiLU(x) * aux (mode 2): x cuda fp32 [rows,k]."""
+    import torch
+    rows, k = x.shape
+    y = torch.zeros((rows, k // 256 * Q8_K_BYTES), dtype=torch.uint8, device=x.device)
+    check(lib().mllmcu_prep_q8_K(mode, _ptr(x), _ptr(aux) if aux is not None else None, float(eps), int(add_unit_offset), _ptr(y), rows, k,
+                                 x.stride(0), int(pdl), _stream()), "prep_q8_K")
+    return y
+
+
+def gemv_q4k(Ws, xq, K, biases=None, residual=None, pdl=False):
+    """Ws: 1..3 cuda uint8 [N_s, K/256*144] Q4_K matrices; xq: block_q8_K rows [M, ...] -> list of fp32 [M, N_s] (one launch)."""
+    import torch
+    M, n = xq.shape[0], len(Ws)
+    ys = [torch.empty((M, W.shape[0]), dtype=torch.float32, device=xq.device) for W in Ws]
+    ld = ys[0].stride(0)
+    if n > 1:  # one leading dimension for every segment: views of one [M, sum N] buffer
+        big = torch.empty((M, sum(W.shape[0] for W in Ws)), dtype=torch.float32, device=xq.device)
+        off, ys = 0, []
+        for W in Ws:
+            ys.append(big[:, off:off + W.shape[0]])
+            off += W.shape[0]
+        ld = big.stride(0)
+    Wp = (C.c_void_p * n)(*[_ptr(W) for W in Ws])
+    Np = (C.c_int * n)(*[int(W.shape[0]) for W in Ws])
+    bp = (C.c_void_p * n)(*[(_ptr(b) if b is not None else None) for b in (biases or [None] * n)])
+    yp = (C.c_void_p * n)(*[y.data_ptr() for y in ys])
+    check(lib().mllmcu_gemv_q4k(n, Wp, Np, bp, yp, ld, _ptr(xq), M, K, _ptr(residual) if residual is not None else None,
+                                residual.stride(0) if residual is not None else 0, int(pdl), _stream()), "gemv_q4k")
+    return ys
 
 
 def block_isums_q4_K_q8_K(W, xq, K):

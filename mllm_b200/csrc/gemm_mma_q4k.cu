@@ -17,6 +17,7 @@
 // memory in a fixed order.  M rows beyond 64 (128 for short K) are served by further launches over the same weights (they stay in L2).
 #include "common.cuh"
 #include "gemv_common.cuh"
+#include "kq_common.cuh"
 #include "mllmcu.h"
 #include <stdlib.h>
 
@@ -38,16 +39,6 @@ static __device__ __forceinline__ void mma_u8s8(int (&c)[4], uint32_t a0, uint32
                  : "=r"(c[0]), "=r"(c[1]), "=r"(c[2]), "=r"(c[3])
                  : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1), "r"(0), "r"(0), "r"(0), "r"(0));
 }
-
-// get_scale_min_k4 (ggml/QuantizeQ4.cpp:177-184) for all eight sub-blocks of a super-block: s = the 12 scale bytes as three words;
-// sc / mn receive the eight 6-bit values packed one per byte (sub-blocks 0-3 in [0], 4-7 in [1])
-static __device__ __forceinline__ void q4k_scales8(uint32_t s0, uint32_t s1, uint32_t s2, uint32_t (&sc)[2], uint32_t (&mn)[2]) {
-    sc[0] = s0 & 0x3F3F3F3Fu;                                           // q[j] & 63, j < 4
-    mn[0] = s1 & 0x3F3F3F3Fu;                                           // q[j + 4] & 63
-    sc[1] = (s2 & 0x0F0F0F0Fu) | ((s0 >> 2) & 0x30303030u);             // (q[j + 4] & 0xF) | ((q[j - 4] >> 6) << 4), j >= 4
-    mn[1] = ((s2 >> 4) & 0x0F0F0F0Fu) | ((s1 >> 2) & 0x30303030u);      // (q[j + 4] >> 4) | ((q[j] >> 6) << 4)
-}
-static __device__ __forceinline__ int byte_of(const uint32_t (&v)[2], int j) { return (int)((v[j >> 2] >> (8 * (j & 3))) & 0xFFu); }
 
 template <int MTW, int MG, int KS>
 __global__ void __launch_bounds__(KQ_WARPS * 32) k_gemm_mma_q4k(const GemmQ4KParams p) {

@@ -36,7 +36,7 @@ enum ErrorCode { MLLM_NO_ERROR = 0, OUT_OF_MEMORY = 1, NOT_SUPPORT = 2, COMPUTE_
 // ---- mllm/Types.hpp:63-96 (values used on this path)
 enum DataType { MLLM_TYPE_F32 = 0, MLLM_TYPE_F16 = 1, MLLM_TYPE_Q4_0 = 2, MLLM_TYPE_Q8_0 = 8, MLLM_TYPE_Q4_K = 12, MLLM_TYPE_Q6_K = 14, MLLM_TYPE_Q8_K = 15, MLLM_TYPE_I32 = 18, MLLM_TYPE_Q4_0_4_4 = 19, MLLM_TYPE_COUNT = 34 };
 enum ChlType { BSHD = 0 };
-enum RoPEType { NONE = 0, PERSIMMONROPE = 1, LLAMAROPE = 2, HFHUBROPE = 4 };
+enum RoPEType { NONE = 0, LLAMAROPE = 2, PERSIMMONROPE = 3, HFHUBROPE = 4, MLAROPE = 5, NTKROPE = 6 }; // mllm/Types.hpp:171-178 (only 2 and 4 have kernels; the rest are refused by CUDARoPE)
 // ---- mllm/OpDefined.hpp:10-134 (numeric values must match: OpParam["type"] carries them)
 enum OpType {
     INVALID_VALUE_OP = 0, PARAMETER = 1, ADD = 2, SOFTMAX = 3, SILU = 4, MATMUL = 6, ROPE = 8, RMSNORM = 11, LINEAR = 14,

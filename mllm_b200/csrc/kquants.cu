@@ -10,6 +10,7 @@
 // d = d_x * fp16(d_w), dmin = -d_x * fp16(dmin_w) with one fp32 FMA each; only the order of the fp32 accumulation over
 // super-blocks differs from the 8 AVX lanes (tolerance in the tests).
 #include "common.cuh"
+#include "kq_common.cuh"
 
 #define QK_K 256
 #define Q4K_BYTES 144
@@ -23,16 +24,8 @@ static __device__ __forceinline__ int nearest_int_dev(float f) {
 }
 
 // ------------------------------------------------------------ quantize_row_q8_K
-// one warp per super-block, lane l owns elements 8l..8l+7
-__global__ void __launch_bounds__(128) k_quantize_q8_K(const float *__restrict__ x, uint8_t *__restrict__ y, long long nblk, int nb, int ldx) {
-    const int lane = threadIdx.x & 31;
-    const long long blk = (long long)blockIdx.x * 4 + (threadIdx.x >> 5);
-    if (blk >= nblk) return;
-    const long long row = blk / nb;
-    const int b = (int)(blk % nb);
-    const float *xp = x + (size_t)row * ldx + (size_t)b * QK_K + lane * 8;
-    const float4 v0 = *(const float4 *)xp, v1 = *(const float4 *)(xp + 4);
-    const float v[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
+// one warp per super-block, lane l owns elements 8l..8l+7 (v) and writes its share of the 292-byte block at `out`
+static __device__ __forceinline__ void q8K_block_from_warp(const float (&v)[8], int lane, uint8_t *out) {
     // first element with the largest |x| decides the sign of the scale (strict > in the reference's scan)
     float amax = 0.f, mx = 0.f;
     int idx = 0x7fffffff;
@@ -48,7 +41,6 @@ __global__ void __launch_bounds__(128) k_quantize_q8_K(const float *__restrict__
         const int oi = __shfl_xor_sync(0xffffffffu, idx, o);
         if (oa > amax || (oa == amax && oi < idx)) { amax = oa; mx = om; idx = oi; }
     }
-    uint8_t *out = y + (size_t)blk * Q8K_BYTES;
     int q[8];
     float d = 0.f;
     if (amax == 0.f) {
@@ -71,6 +63,18 @@ __global__ void __launch_bounds__(128) k_quantize_q8_K(const float *__restrict__
     *(uint32_t *)(out + 8 + lane * 8) = w1;
     if ((lane & 1) == 0) *(int16_t *)(out + 260 + (lane >> 1) * 2) = (int16_t)s2; // all-zero block: 0 (the reference leaves it unwritten)
     if (lane == 0) *(float *)out = d;
+}
+
+__global__ void __launch_bounds__(128) k_quantize_q8_K(const float *__restrict__ x, uint8_t *__restrict__ y, long long nblk, int nb, int ldx) {
+    const int lane = threadIdx.x & 31;
+    const long long blk = (long long)blockIdx.x * 4 + (threadIdx.x >> 5);
+    if (blk >= nblk) return;
+    const long long row = blk / nb;
+    const int b = (int)(blk % nb);
+    const float *xp = x + (size_t)row * ldx + (size_t)b * QK_K + lane * 8;
+    const float4 v0 = *(const float4 *)xp, v1 = *(const float4 *)(xp + 4);
+    const float v[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
+    q8K_block_from_warp(v, lane, y + (size_t)blk * Q8K_BYTES);
 }
 
 MLLMCU_API int mllmcu_quantize_q8_K(const float *x, void *y_blocks, int rows, int k, int ldx, void *stream) {
@@ -342,6 +346,213 @@ int launch_linear_kq(int wtype, const void *W, const float *x, const float *bias
     }
     return wtype == 12 ? launch_kq<12>((const uint8_t *)W, (const uint8_t *)ws, bias, y, M, N, K / QK_K, ldy, out_f16, st)
                        : launch_kq<14>((const uint8_t *)W, (const uint8_t *)ws, bias, y, M, N, K / QK_K, ldy, out_f16, st);
+}
+
+// ------------------------------------------------------------------- decode-step chain for Q4_K bodies
+// The single-token step of a Q4_K model (LLaVA-1.5-7B, BASELINE configs[2]) as nine launches per decoder block instead of eighteen:
+//   prep(RMSNorm) -> GEMV[q|k|v] -> attention -> prep -> GEMV[o] + residual -> prep(RMSNorm) -> GEMV[gate|up] -> prep(SiLU * up) -> GEMV[down] + residual
+// "prep" writes the block_q8_K image of the NEXT Linear's input, folding the op in front of it (CPURMSNorm.cpp:31-95, CPUSiLU / CPUMul)
+// into the quantiser with the arithmetic of k_rmsnorm / k_ew, so every value is the one the op-by-op sequence produces.  The GEMV reads
+// up to three matrices that share the activation rows and can add the residual stream in its epilogue.  Every kernel is a programmatic
+// dependent of the one before it: it fetches what does not depend on its predecessor (weights) before griddepcontrol.wait.
+static __device__ __forceinline__ void kq_pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+static __device__ __forceinline__ void kq_pdl_launch() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
+// grid (ceil(nb / 8), rows), 8 warps: warp w of CTA c owns super-block 8c + w of its row.  MODE 0: x; 1: RMSNorm(x; aux = weight);
+// 2: SiLU(x) * aux (aux has x's layout).  With MODE 1 every CTA of a row repeats k_rmsnorm's sum (same order, same rounding).
+template <int MODE>
+__global__ void __launch_bounds__(256) k_prep_q8_K(const float *__restrict__ x, const float *__restrict__ aux, uint8_t *__restrict__ y, int nb,
+                                                   int ldx, float eps, int add_unit_offset) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int row = blockIdx.y, b = blockIdx.x * 8 + warp;
+    const float *xr = x + (size_t)row * ldx;
+    kq_pdl_launch();
+    kq_pdl_wait();
+    float rms = 1.f;
+    if (MODE == 1) {
+        const int dim = nb * QK_K;
+        const float4 *x4 = (const float4 *)xr;
+        double s0 = 0.0, s1 = 0.0;
+        for (int d = threadIdx.x; d < (dim >> 2); d += 256) {
+            const float4 v = x4[d];
+            s0 = fma((double)v.x, (double)v.x, s0); s1 = fma((double)v.y, (double)v.y, s1);
+            s0 = fma((double)v.z, (double)v.z, s0); s1 = fma((double)v.w, (double)v.w, s1);
+        }
+        __shared__ double sred[8];
+        __shared__ float s_rms;
+        const double ss = warp_sum_d(s0 + s1);
+        if (lane == 0) sred[warp] = ss;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            double t = 0.0;
+            for (int i = 0; i < 8; i++) t += sred[i];
+            const float mean = (float)(t / (double)dim);
+            s_rms = __fdiv_rn(1.0f, __fsqrt_rn(__fadd_rn(mean, eps)));
+        }
+        __syncthreads();
+        rms = s_rms;
+    }
+    if (b >= nb) return;
+    const float *xp = xr + (size_t)b * QK_K + lane * 8;
+    const float4 v0 = *(const float4 *)xp, v1 = *(const float4 *)(xp + 4);
+    float v[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
+    if (MODE == 1) {
+        const float4 w0 = *(const float4 *)(aux + (size_t)b * QK_K + lane * 8), w1 = *(const float4 *)(aux + (size_t)b * QK_K + lane * 8 + 4);
+        float w[8] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w};
+#pragma unroll
+        for (int j = 0; j < 8; j++) {
+            if (add_unit_offset) w[j] = __fadd_rn(1.0f, w[j]);
+            v[j] = __fmul_rn(__fmul_rn(v[j], rms), w[j]);
+        }
+    } else if (MODE == 2) {
+        const float *up = aux + (size_t)row * ldx + (size_t)b * QK_K + lane * 8;
+        const float4 u0 = *(const float4 *)up, u1 = *(const float4 *)(up + 4);
+        const float u[8] = {u0.x, u0.y, u0.z, u0.w, u1.x, u1.y, u1.z, u1.w};
+#pragma unroll
+        for (int j = 0; j < 8; j++) v[j] = __fmul_rn(__fdiv_rn(v[j], __fadd_rn(1.0f, v_expf(__fsub_rn(0.0f, v[j])))), u[j]); // silu_f (elementwise.cu)
+    }
+    q8K_block_from_warp(v, lane, y + ((size_t)row * nb + b) * Q8K_BYTES);
+}
+
+static cudaError_t kq_launch_cfg(cudaLaunchConfig_t &cfg, cudaLaunchAttribute *attr, dim3 grid, dim3 block, int pdl, cudaStream_t st) {
+    cfg = cudaLaunchConfig_t{};
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.stream = st;
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl ? 1 : 0;
+    return cudaSuccess;
+}
+
+MLLMCU_API int mllmcu_prep_q8_K(int mode, const float *x, const float *aux, float eps, int add_unit_offset, void *y_blocks, int rows, int k, int ldx,
+                                int pdl, void *stream) {
+    if (mode < 0 || mode > 2 || rows <= 0 || k <= 0 || k % QK_K || ldx % 4 || ((uintptr_t)x & 15) || ((uintptr_t)y_blocks & 3)) return -1;
+    if (mode != 0 && (aux == nullptr || ((uintptr_t)aux & 15))) return -1;
+    const int nb = k / QK_K;
+    cudaLaunchConfig_t cfg;
+    cudaLaunchAttribute attr[1];
+    kq_launch_cfg(cfg, attr, dim3((unsigned)((nb + 7) / 8), (unsigned)rows), dim3(256), pdl, (cudaStream_t)stream);
+    uint8_t *y = (uint8_t *)y_blocks;
+    if (mode == 0) CU_TRY(cudaLaunchKernelEx(&cfg, k_prep_q8_K<0>, x, aux, y, nb, ldx, eps, add_unit_offset));
+    else if (mode == 1) CU_TRY(cudaLaunchKernelEx(&cfg, k_prep_q8_K<1>, x, aux, y, nb, ldx, eps, add_unit_offset));
+    else CU_TRY(cudaLaunchKernelEx(&cfg, k_prep_q8_K<2>, x, aux, y, nb, ldx, eps, add_unit_offset));
+    return 0;
+}
+
+struct KqGemvParams {
+    const uint8_t *W[3];
+    const float *bias[3];
+    float *y[3];
+    int N[3];
+    int nW, Ntot, nb, ldy, ldr;
+    const uint8_t *xq;
+    const float *res;
+};
+
+// One warp per output row, M <= 8 activation rows.  Lane (g, t) = (lane / 8, lane % 8) takes 16 weight bytes of super-block g + 4 it:
+// bytes [16 (t & 1), +16) of nibble pair t / 2, i.e. half of sub-block 2 (t / 2) in the low nibbles and half of sub-block 2 (t / 2) + 1 in
+// the high ones -- every weight byte is fetched by exactly one lane, 16 bytes at a time, and four super-block groups (up to 16 super-
+// blocks, 2.3 KB per warp) are in flight before the first is consumed.  The eight lanes of a super-block add their integers (the two exact
+// integers the reference forms) before the fp32 FMA pair; lane group g accumulates super-blocks g, g + 4, ... in order and the groups meet
+// in warp_sum, which is k_gemv_kq's order: results are bit-identical to it.
+template <int M>
+__global__ void __launch_bounds__(128) k_gemv_q4k(const KqGemvParams p) {
+    const int lane = threadIdx.x & 31;
+    int n = blockIdx.x * 4 + (threadIdx.x >> 5);
+    if (n >= p.Ntot) return;
+    int s = 0;
+    if (n >= p.N[0]) { n -= p.N[0]; s = 1; if (n >= p.N[1]) { n -= p.N[1]; s = 2; } }
+    const int nb = p.nb, g = lane >> 3, t = lane & 7, j = t >> 1, h = t & 1;
+    // selects, not p.W[s]: a run-time index would copy the parameter arrays to local memory
+    const uint8_t *row = (s == 0 ? p.W[0] : s == 1 ? p.W[1] : p.W[2]) + (size_t)n * nb * Q4K_BYTES;
+    float acc[M], accm[M];
+#pragma unroll
+    for (int m = 0; m < M; m++) { acc[m] = 0.f; accm[m] = 0.f; }
+    for (int i0 = 0; i0 < nb; i0 += 16) {
+        uint4 hq[4], wq[4];
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            const int i = i0 + 4 * u + g;
+            const uint8_t *blk = row + (size_t)(i < nb ? i : 0) * Q4K_BYTES;
+            hq[u] = ld_stream_u4(blk);                       // d, dmin, the 12 scale bytes
+            wq[u] = ld_stream_u4(blk + 16 + j * 32 + h * 16);
+        }
+        if (i0 == 0) { kq_pdl_launch(); kq_pdl_wait(); }     // the activations are the predecessor's output
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            const int i = i0 + 4 * u + g;
+            const bool on = i < nb;
+            if (i0 + 4 * u >= nb) break;                     // warp-uniform
+            uint32_t sc[2], mn[2];
+            q4k_scales8(hq[u].y, hq[u].z, hq[u].w, sc, mn);
+            const int sc_lo = byte_of(sc, 2 * j), sc_hi = byte_of(sc, 2 * j + 1), mn_lo = byte_of(mn, 2 * j), mn_hi = byte_of(mn, 2 * j + 1);
+            const float dw = __half2float(__ushort_as_half((unsigned short)(hq[u].x & 0xFFFFu)));
+            const float dminw = __half2float(__ushort_as_half((unsigned short)(hq[u].x >> 16)));
+            const uint32_t wr[4] = {wq[u].x, wq[u].y, wq[u].z, wq[u].w};
+#pragma unroll
+            for (int m = 0; m < M; m++) {
+                const uint8_t *xb = p.xq + ((size_t)m * nb + (on ? i : 0)) * Q8K_BYTES;
+                const int *alo = (const int *)(xb + 4 + (2 * j) * 32 + h * 16), *ahi = (const int *)(xb + 4 + (2 * j + 1) * 32 + h * 16);
+                int is_lo = 0, is_hi = 0;
+#pragma unroll
+                for (int q = 0; q < 4; q++) {
+                    is_lo = __dp4a((int)(wr[q] & 0x0F0F0F0Fu), alo[q], is_lo);
+                    is_hi = __dp4a((int)((wr[q] >> 4) & 0x0F0F0F0Fu), ahi[q], is_hi);
+                }
+                const int16_t *bs = (const int16_t *)(xb + 260);
+                int vi = sc_lo * is_lo + sc_hi * is_hi;
+                int vm = mn_lo * (int)bs[4 * j + h] + mn_hi * (int)bs[4 * j + 2 + h];
+                if (!on) { vi = 0; vm = 0; }
+#pragma unroll
+                for (int o = 1; o < 8; o <<= 1) {
+                    vi += __shfl_xor_sync(0xffffffffu, vi, o);
+                    vm += __shfl_xor_sync(0xffffffffu, vm, o);
+                }
+                if (t == 0 && on) {
+                    const float dx = *(const float *)xb;
+                    acc[m] = fmaf(__fmul_rn(dx, dw), (float)vi, acc[m]);
+                    accm[m] = fmaf(__fmul_rn(-dx, dminw), (float)vm, accm[m]);
+                }
+            }
+        }
+    }
+    const float *bias = s == 0 ? p.bias[0] : s == 1 ? p.bias[1] : p.bias[2];
+    float *y = s == 0 ? p.y[0] : s == 1 ? p.y[1] : p.y[2];
+#pragma unroll
+    for (int m = 0; m < M; m++) {
+        float v = __fadd_rn(warp_sum(acc[m]), warp_sum(accm[m]));
+        if (lane == 0) {
+            if (bias) v = __fadd_rn(v, bias[n]);
+            if (p.res) v = __fadd_rn(p.res[(size_t)m * p.ldr + n], v);
+            y[(size_t)m * p.ldy + n] = v;
+        }
+    }
+}
+
+MLLMCU_API int mllmcu_gemv_q4k(int nW, const void *const *W, const int *N, const float *const *bias, float *const *y, int ldy, const void *xq_blocks,
+                               int M, int K, const float *residual, int ldr, int pdl, void *stream) {
+    if (nW < 1 || nW > 3 || M < 1 || M > 8 || K <= 0 || K % QK_K || ((uintptr_t)xq_blocks & 3)) return -1;
+    if (residual && nW != 1) return -1;
+    KqGemvParams p = {};
+    p.nW = nW; p.nb = K / QK_K; p.ldy = ldy; p.ldr = ldr; p.xq = (const uint8_t *)xq_blocks; p.res = residual;
+    for (int s = 0; s < 3; s++) p.N[s] = 0x7fffffff;
+    long long tot = 0;
+    for (int s = 0; s < nW; s++) {
+        if (W[s] == nullptr || y[s] == nullptr || N[s] <= 0 || ((uintptr_t)W[s] & 15)) return -1;
+        p.W[s] = (const uint8_t *)W[s]; p.bias[s] = bias ? bias[s] : nullptr; p.y[s] = y[s]; p.N[s] = N[s];
+        tot += N[s];
+    }
+    if (tot > 0x7fffffff) return -1;
+    p.Ntot = (int)tot;
+    cudaLaunchConfig_t cfg;
+    cudaLaunchAttribute attr[1];
+    kq_launch_cfg(cfg, attr, dim3((unsigned)((p.Ntot + 3) / 4)), dim3(128), pdl, (cudaStream_t)stream);
+    switch (M) {
+#define CASE(m) case m: CU_TRY(cudaLaunchKernelEx(&cfg, k_gemv_q4k<m>, p)); break;
+        CASE(1) CASE(2) CASE(3) CASE(4) CASE(5) CASE(6) CASE(7) CASE(8)
+#undef CASE
+    }
+    return 0;
 }
 
 // ------------------------------------------------- exact integers per super-block (test / diagnostic hook)

@@ -31,6 +31,12 @@ MLLMCU_API int mllmcu_malloc_managed(void **ptr, size_t bytes, int device) {
     (void)cudaGetLastError(); // advice / prefetch are hints: unsupported configurations keep plain managed behaviour
     return 0;
 }
+MLLMCU_API int mllmcu_mem_prefetch(void *ptr, size_t bytes, int device, void *stream) {
+    if (ptr == nullptr || bytes == 0) return 0;
+    cudaMemPrefetchAsync(ptr, bytes, device, (cudaStream_t)stream);
+    (void)cudaGetLastError(); // a hint: not managed memory / unsupported configuration -> nothing to do
+    return 0;
+}
 MLLMCU_API int mllmcu_memset(void *dptr, int value, size_t bytes, void *stream) {
     CU_TRY(cudaMemsetAsync(dptr, value, bytes, (cudaStream_t)stream)); return 0;
 }
