@@ -264,19 +264,23 @@ int mllmcu_quantize_q8_K(const float *x, void *y_blocks, int rows, int k, int ld
 int mllmcu_block_isums_q4_K_q8_K(const void *W, const void *xq_blocks, int32_t *sumi, int32_t *summ, int M, int N, int K, void *stream);
 
 /* ---- single-token step of a Q4_K body (LLaVA-1.5-7B): the ops in front of a Linear folded into the activation quantiser, the residual
- * add folded into the GEMV, every launch a programmatic dependent of the previous one (pdl != 0).
+ * add folded into the GEMV, every launch a programmatic dependent of the previous one.
  * mllmcu_prep_q8_K writes the block_q8_K rows (as mllmcu_quantize_q8_K) of
  *   mode 0: x;   mode 1: RMSNorm(x) with weight aux[k] (CPURMSNorm::execute, op/CPURMSNorm.cpp:31-95; the arithmetic of mllmcu_rmsnorm);
  *   mode 2: SiLU(x) * aux, aux laid out as x (CPUSiLU + CPUMul of the MLP, models/llama/modeling_llama.hpp:20-41; the arithmetic of
  *   mllmcu_silu_mul) -- values and bytes identical to running the separate ops and then mllmcu_quantize_q8_K.
+ *   flags: 1 = programmatic dependent launch; 2 = each block re-pitched to 304 bytes (d at 0, the 256 int8 at 16 -- 16-byte aligned, which
+ *   the native 292-byte block cannot be --, the 16 group sums at 272; bytes 4..15 unused; y_blocks 16-byte aligned).
  * mllmcu_gemv_q4k: y[s][m * ldy + n] = sum_k W[s][n][k] x[m][k] (+ bias[s][n]) for nW <= 3 Q4_K matrices sharing the M <= 8 activation
- * rows xq_blocks (q | k | v, gate | up: one launch), the reference's vec_dot_q4_K_q8_K integers (ggml/VecDotQ4.cpp:220-283) and the fp32
- * accumulation order of mllmcu_linear's GEMV (bit-identical to it); residual != NULL (nW == 1): y = residual + that (CPUAdd after o_proj /
- * down_proj).  W, N, bias, y are HOST arrays of nW entries (bias may be NULL). */
+ * rows xq_blocks (q | k | v, gate | up: one launch) with the reference's exact integers (ggml/VecDotQ4.cpp:220-283: scale * dot and
+ * min * group sum), formed per lane over 32 weights and folded into fp32 with the super-block's two factors -- only the fp32 summation
+ * order differs from vec_dot_q4_K_q8_K's (as it does between its own AVX lanes).  residual != NULL (nW == 1): y = residual + that (CPUAdd
+ * after o_proj / down_proj).  W, N, bias, y are HOST arrays of nW entries (bias may be NULL).  flags: 1 = programmatic dependent launch;
+ * 2 = xq_blocks are the 304-byte blocks. */
 int mllmcu_prep_q8_K(int mode, const float *x, const float *aux, float eps, int add_unit_offset, void *y_blocks, int rows, int k, int ldx,
-                     int pdl, void *stream);
+                     int flags, void *stream);
 int mllmcu_gemv_q4k(int nW, const void *const *W, const int *N, const float *const *bias, float *const *y, int ldy, const void *xq_blocks,
-                    int M, int K, const float *residual, int ldr, int pdl, void *stream);
+                    int M, int K, const float *residual, int ldr, int flags, void *stream);
 
 /* ---- Q4_0_4_4 weights (block_q4_0x4, mllm/DataType.hpp:104-107; make_block_q4_0x4 + quantize_q4_0_nr_bl,
  * ggml/GemmPack.cpp:45-60, :308-344; consumed by gemv/gemm_q4_0_4x4_q8_0 when W.dtype == MLLM_TYPE_Q4_0_4_4,

@@ -153,6 +153,12 @@ struct StepLog {
     }
     std::vector<unsigned> tokens;
     std::vector<double> ms;
+    double pool_ms0 = 0; // driver time of the memory pool before the request (start-up, weight load)
+    void mark_pool(BackendType device) {
+#ifdef USE_CUDA
+        if (device == MLLM_CUDA) pool_ms0 = static_cast<CUDABackend *>(Backend::global_backends[MLLM_CUDA].get())->memory()->driver_ms;
+#endif
+    }
     FILE *dump = nullptr;
     unsigned pick(Tensor lg) { // argmax of the last position, first maximum wins (tokenizers/Tokenizer.hpp:160-170)
         if (lg.backend()->type() != MLLM_CPU) lg.cpu();
@@ -170,8 +176,16 @@ static void print_json(const char *model, int device, int prompt_tokens, const S
     std::vector<double> tail(m.inference_times_.begin() + std::min<size_t>(m.inference_times_.size(), 1), m.inference_times_.end());
     std::sort(tail.begin(), tail.end());
     printf("{\"model\": \"%s\", \"device\": %d, \"prompt_tokens\": %d, \"decode\": %zu, \"prefill_ms\": %.3f, \"decode_ms_per_step\": %.4f, \"decode_ms_median\": %.4f, "
-           "\"decode_ms_max\": %.3f, \"fused_steps\": %d, \"tokens\": [", model, device, prompt_tokens, log.tokens.size(), m.inference_times_.empty() ? 0.0 : m.inference_times_[0],
+           "\"decode_ms_max\": %.3f, \"fused_steps\": %d, ", model, device, prompt_tokens, log.tokens.size(), m.inference_times_.empty() ? 0.0 : m.inference_times_[0],
            m.inference_times_.size() > 1 ? dec / (m.inference_times_.size() - 1) : 0.0, tail.empty() ? 0.0 : tail[tail.size() / 2], tail.empty() ? 0.0 : tail.back(), log.fused_steps);
+#ifdef USE_CUDA
+    if (device == MLLM_CUDA) { // the memory pool's driver traffic: allocations (and device-page population) made while the process ran
+        auto *mm = static_cast<CUDABackend *>(Backend::global_backends[MLLM_CUDA].get())->memory();
+        printf("\"pool_mb\": %.0f, \"pool_driver_calls\": %zu, \"pool_driver_ms\": %.1f, \"pool_driver_ms_in_request\": %.1f, ", mm->bytes_allocated / 1048576.0, mm->driver_calls,
+               mm->driver_ms, mm->driver_ms - log.pool_ms0);
+    }
+#endif
+    printf("\"tokens\": [");
     for (size_t i = 0; i < log.tokens.size(); i++) printf("%s%u", i ? ", " : "", log.tokens[i]);
     printf("]}\n");
 }
@@ -248,6 +262,7 @@ int main(int argc, char **argv) {
             for (int h = 0; h < img; h++)
                 for (int w = 0; w < img; w++) { const float v = upix(rng); image.setDataAt<float>(0, h, c, w, cp.get<int>("perturb") ? std::nextafterf(v, 2.f) : v); }
         const int prompt_tokens = S - 1 + (img / patch) * (img / patch);
+        log.mark_pool(device);
         for (int step = 0; step < n_decode; step++) {
             auto result = model({ids, image});
             log.count_fused(device);
@@ -303,6 +318,7 @@ int main(int argc, char **argv) {
         grid.setDataAt<float>(0, 0, 0, 1, (float)gh);
         grid.setDataAt<float>(0, 0, 0, 2, (float)gw);
         vector<Tensor> inputs = {ids, patches, grid};
+        log.mark_pool(device);
         for (int step = 0; step < n_decode; step++) {
             model.get_position_ids(inputs);
             auto result = model(inputs);

@@ -1,6 +1,7 @@
 // mllm/backends/cuda/CUDABackend.cpp -- see CUDABackend.hpp.  Host side only: every CUDA call goes through the C ABI of
 // include/mllmcu.h (libmllmcu.so); this file contains no <<<>>> and includes no CUDA header.
 #include "CUDABackend.hpp"
+#include <chrono>
 
 #include "Layer.hpp"
 #include "Module.hpp"
@@ -34,6 +35,25 @@ static size_t size_class(size_t bytes) { // 256 B granules up to 64 KiB, then 1/
     return (bytes + step - 1) / step * step;
 }
 
+void *CUDAMemoryManager::raw(size_t n, int kind) {
+    const auto t0 = std::chrono::steady_clock::now();
+    void *q = nullptr;
+    if (kind) MLLMCU_CHECK(mllmcu_malloc(&q, n));
+    else MLLMCU_CHECK(mllmcu_malloc_managed(&q, n, device_)); // returns with the range resident on the device
+    owned_.push_back(q);
+    bytes_allocated += n;
+    driver_ms += std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    driver_calls++;
+    return q;
+}
+
+// Unified-memory slabs made ahead of the first forward (MLLM_CUDA_POOL_MB, default 1024): creating one costs a driver allocation plus
+// the population of 128 MiB of device pages, which belongs to start-up, not to the first request.
+void CUDAMemoryManager::reserve(size_t bytes) {
+    constexpr size_t SLAB = (size_t)128 << 20;
+    for (size_t have = 0; have < bytes; have += SLAB) spare_.push_back(raw(SLAB, 0));
+}
+
 void CUDAMemoryManager::alloc(void **ptr, size_t size, size_t /*alignment: blocks are 256 B aligned or better*/) {
     if (size == 0) size = 1;
     const size_t cls = size_class(size);
@@ -47,19 +67,14 @@ void CUDAMemoryManager::alloc(void **ptr, size_t size, size_t /*alignment: block
         return;
     }
     constexpr size_t SLAB = (size_t)128 << 20;
-    auto raw = [&](size_t n) {
-        void *q = nullptr;
-        if (kind) MLLMCU_CHECK(mllmcu_malloc(&q, n));
-        else MLLMCU_CHECK(mllmcu_malloc_managed(&q, n, device_));
-        owned_.push_back(q);
-        bytes_allocated += n;
-        return q;
-    };
     void *p = nullptr;
-    if (cls > SLAB / 4) p = raw(cls);
+    if (cls > SLAB / 4) p = raw(cls, kind);
     else {
         auto &sl = slabs_[kind];
-        if (sl.empty() || sl.back().used + cls > sl.back().size) sl.push_back({(char *)raw(SLAB), SLAB, 0});
+        if (sl.empty() || sl.back().used + cls > sl.back().size) {
+            if (kind == 0 && !spare_.empty()) { sl.push_back({(char *)spare_.back(), SLAB, 0}); spare_.pop_back(); }
+            else sl.push_back({(char *)raw(SLAB, kind), SLAB, 0});
+        }
         p = sl.back().base + sl.back().used; // classes are multiples of 256 bytes: every carved block is 256-byte aligned
         sl.back().used += cls;
     }
@@ -89,6 +104,8 @@ CUDABackend::CUDABackend(const BackendConfig &, int device) : device_(device) {
     if (mllmcu_device_count() <= 0) throw std::runtime_error("[mllm-cuda] no CUDA device: the CUDA backend has no CPU fallback");
     MLLMCU_CHECK(mllmcu_set_device(device));
     MLLMCU_CHECK(mllmcu_stream_create(&stream_));
+    const char *pool = getenv("MLLM_CUDA_POOL_MB");
+    memory()->reserve((size_t)(pool ? std::max(0, atoi(pool)) : 1024) << 20);
     const char *e = getenv("MLLM_CUDA_EAGER_DECODE");
     fused_decode = !(e && e[0] == '1');
     registerOps();

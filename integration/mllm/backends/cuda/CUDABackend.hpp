@@ -41,7 +41,9 @@ public:
     ~CUDAMemoryManager() override;
     void alloc(void **ptr, size_t size, size_t alignment) override;
     void free(void *ptr) override;
-    size_t bytes_allocated = 0, pool_hits = 0, pool_misses = 0;
+    void reserve(size_t bytes); // unified-memory slabs made ahead of use (start-up, not the first request)
+    size_t bytes_allocated = 0, pool_hits = 0, pool_misses = 0, driver_calls = 0;
+    double driver_ms = 0; // time spent inside driver allocations (and the population of the new range)
     // Weights and the decode plan's buffers are never dereferenced by host code: while this is set, blocks come from plain device
     // memory (cudaMalloc: large pages, no unified-memory bookkeeping on the streaming path) instead of unified memory.
     bool device_only = false;
@@ -52,6 +54,8 @@ private:
     std::unordered_map<void *, std::pair<size_t, int>> live_; // block -> (size class, kind)
     struct Slab { char *base; size_t size, used; };
     std::vector<Slab> slabs_[2];
+    std::vector<void *> spare_; // reserved unified slabs not yet in use
+    void *raw(size_t bytes, int kind);
     std::vector<void *> owned_; // what the destructor returns to the driver: slabs and the blocks too large for one
 };
 

@@ -173,7 +173,7 @@ struct DecodePlanBuilder {
         if (p->kquant) {
             const int widest = std::max(std::max(p->H, p->F), QKV);
             mk(p->t1, B, widest); mk(p->t2, B, std::max(p->H, p->V)); mk(p->gu, B, p->F);
-            p->lin_ws_bytes = mllmcu_linear_workspace_bytes(B, widest);
+            p->lin_ws_bytes = std::max(mllmcu_linear_workspace_bytes(B, widest), (size_t)B * (widest / 256) * 304 + 256); // 304: the chain's re-pitched Q8_K blocks
             mk(p->lin_ws, 1, (int)((p->lin_ws_bytes + 3) / 4));
         }
         p->attn_ws_bytes = mllmcu_decode_attn_workspace_bytes(B, p->Hq, p->D);
@@ -233,7 +233,7 @@ struct DecodePlanBuilder {
 
 // k-quant models (the LLaVA body is Q4_K).  All Linears Q4_K: nine launches per block -- the op in front of each Linear (RMSNorm, SiLU * up) folded
 // into the block_q8_K quantiser, q | k | v and gate | up as one GEMV launch each, the residual add in the epilogue of o / down, every kernel a
-// programmatic dependent of the one before it (kquants.cu, mllmcu_prep_q8_K / mllmcu_gemv_q4k; values bit-identical to the op-by-op sequence).
+// programmatic dependent of the one before it (kquants.cu, mllmcu_prep_q8_K / mllmcu_gemv_q4k; same quantised bytes and integers as the op-by-op sequence, another fp32 summation order).
 // Mixed Q4_K / Q6_K / Q4_0 bodies: the same step from the op-level kernels -- RMSNorm, Linear, the fused RoPE + append + attention kernel, add,
 // SiLU * mul -- on the plan's fixed buffers.  Either way the sequence is captured once and replayed without host dispatch.
 bool DecodePlanBuilder::issue_kquant(CUDABackend *bn, CUDABackend::DecodePlan &p) {
@@ -246,7 +246,7 @@ bool DecodePlanBuilder::issue_kquant(CUDABackend *bn, CUDABackend::DecodePlan &p
     int n = 1;
     if (p.q4k_chain) {
         auto prep = [&](int mode, const float *in, const float *aux, float eps, int K) {
-            MLLMCU_CHECK(mllmcu_prep_q8_K(mode, in, aux, eps, 0, ws, B, K, K, 1, st));
+            MLLMCU_CHECK(mllmcu_prep_q8_K(mode, in, aux, eps, 0, ws, B, K, K, 3, st)); // 3: PDL + 304-byte blocks
             n++;
         };
         auto gemv = [&](std::initializer_list<const CUDAFuseInfo *> fs, std::initializer_list<float *> outs, int ldy, int K, const float *res) {
@@ -257,7 +257,7 @@ bool DecodePlanBuilder::issue_kquant(CUDABackend *bn, CUDABackend::DecodePlan &p
             for (const CUDAFuseInfo *f : fs) { W[k] = f->weight; bias[k] = f->bias; N[k] = f->out; k++; }
             k = 0;
             for (float *o : outs) y[k++] = o;
-            MLLMCU_CHECK(mllmcu_gemv_q4k(k, W, N, bias, y, ldy, ws, B, K, res, ldy, 1, st));
+            MLLMCU_CHECK(mllmcu_gemv_q4k(k, W, N, bias, y, ldy, ws, B, K, res, ldy, 3, st));
             n++;
         };
         for (auto &l : p.layers) {

@@ -296,18 +296,30 @@ def quantize_q8_K(x):
     return y
 
 
-def prep_q8_K(x, mode=0, aux=None, eps=0.0, add_unit_offset=False, pdl=False):
-    """block_q8_K rows of x (mode 0), RMSNorm(x; aux) (mode 1) or SiLU(x) * aux (mode 2): x cuda fp32 [rows,k]."""
+Q8_K_PITCH = 304  # the decode chain's re-pitched block_q8_K: d at 0, qs at 16, the 16 group sums at 272 (bytes 4..15 unused)
+
+
+def prep_q8_K(x, mode=0, aux=None, eps=0.0, add_unit_offset=False, pdl=False, aligned=False):
+    """block_q8_K rows of x (mode 0), RMSNorm(x; aux) (mode 1) or SiLU(x) * aux (mode 2): x cuda fp32 [rows,k].
+    aligned: 304-byte blocks (see Q8_K_PITCH) instead of the native 292-byte ones."""
     import torch
     rows, k = x.shape
-    y = torch.zeros((rows, k // 256 * Q8_K_BYTES), dtype=torch.uint8, device=x.device)
-    check(lib().mllmcu_prep_q8_K(mode, _ptr(x), _ptr(aux) if aux is not None else None, float(eps), int(add_unit_offset), _ptr(y), rows, k,
-                                 x.stride(0), int(pdl), _stream()), "prep_q8_K")
+    y = torch.zeros((rows, k // 256 * (Q8_K_PITCH if aligned else Q8_K_BYTES)), dtype=torch.uint8, device=x.device)
+    check(lib().mllmcu_prep_q8_K(mode, _ptr(x), _ptr(aux), float(eps), int(add_unit_offset), _ptr(y), rows, k,
+                                 x.stride(0), int(pdl) | (2 if aligned else 0), _stream()), "prep_q8_K")
     return y
 
 
-def gemv_q4k(Ws, xq, K, biases=None, residual=None, pdl=False):
-    """Ws: 1..3 cuda uint8 [N_s, K/256*144] Q4_K matrices; xq: block_q8_K rows [M, ...] -> list of fp32 [M, N_s] (one launch)."""
+def q8_K_unpitch(y):
+    """304-byte blocks -> native 292-byte block_q8_K bytes."""
+    import torch
+    b = y.reshape(y.shape[0], -1, Q8_K_PITCH)
+    return torch.cat([b[:, :, 0:4], b[:, :, 16:304]], dim=2).reshape(y.shape[0], -1).contiguous()
+
+
+def gemv_q4k(Ws, xq, K, biases=None, residual=None, pdl=False, aligned=False):
+    """Ws: 1..3 cuda uint8 [N_s, K/256*144] Q4_K matrices; xq: block_q8_K rows [M, ...] (native, or 304-byte blocks with aligned=True)
+    -> list of fp32 [M, N_s] (one launch)."""
     import torch
     M, n = xq.shape[0], len(Ws)
     ys = [torch.empty((M, W.shape[0]), dtype=torch.float32, device=xq.device) for W in Ws]
@@ -324,7 +336,7 @@ def gemv_q4k(Ws, xq, K, biases=None, residual=None, pdl=False):
     bp = (C.c_void_p * n)(*[(_ptr(b) if b is not None else None) for b in (biases or [None] * n)])
     yp = (C.c_void_p * n)(*[y.data_ptr() for y in ys])
     check(lib().mllmcu_gemv_q4k(n, Wp, Np, bp, yp, ld, _ptr(xq), M, K, _ptr(residual) if residual is not None else None,
-                                residual.stride(0) if residual is not None else 0, int(pdl), _stream()), "gemv_q4k")
+                                residual.stride(0) if residual is not None else 0, int(pdl) | (2 if aligned else 0), _stream()), "gemv_q4k")
     return ys
 
 

@@ -16,6 +16,7 @@
 #define Q4K_BYTES 144
 #define Q6K_BYTES 210
 #define Q8K_BYTES 292
+#define Q8K_PITCH 304 // the decode chain's re-pitched block: d at 0, qs at 16 (16-byte aligned), the 16 group sums at 272
 
 // nearest_int (ggml/Quantize.hpp:174-180)
 static __device__ __forceinline__ int nearest_int_dev(float f) {
@@ -25,7 +26,7 @@ static __device__ __forceinline__ int nearest_int_dev(float f) {
 
 // ------------------------------------------------------------ quantize_row_q8_K
 // one warp per super-block, lane l owns elements 8l..8l+7 (v) and writes its share of the 292-byte block at `out`
-static __device__ __forceinline__ void q8K_block_from_warp(const float (&v)[8], int lane, uint8_t *out) {
+static __device__ __forceinline__ void q8K_block_from_warp(const float (&v)[8], int lane, uint8_t *out, int qs_off = 4, int bs_off = 260) {
     // first element with the largest |x| decides the sign of the scale (strict > in the reference's scan)
     float amax = 0.f, mx = 0.f;
     int idx = 0x7fffffff;
@@ -59,9 +60,9 @@ static __device__ __forceinline__ void q8K_block_from_warp(const float (&v)[8], 
     uint32_t w0 = 0, w1 = 0;
 #pragma unroll
     for (int j = 0; j < 4; j++) { w0 |= (uint32_t)(q[j] & 0xFF) << (8 * j); w1 |= (uint32_t)(q[4 + j] & 0xFF) << (8 * j); }
-    *(uint32_t *)(out + 4 + lane * 8) = w0; // blocks are 292 B apart: only 4-byte alignment is guaranteed
-    *(uint32_t *)(out + 8 + lane * 8) = w1;
-    if ((lane & 1) == 0) *(int16_t *)(out + 260 + (lane >> 1) * 2) = (int16_t)s2; // all-zero block: 0 (the reference leaves it unwritten)
+    *(uint32_t *)(out + qs_off + lane * 8) = w0; // blocks are 292 B apart: only 4-byte alignment is guaranteed
+    *(uint32_t *)(out + qs_off + 4 + lane * 8) = w1;
+    if ((lane & 1) == 0) *(int16_t *)(out + bs_off + (lane >> 1) * 2) = (int16_t)s2; // all-zero block: 0 (the reference leaves it unwritten)
     if (lane == 0) *(float *)out = d;
 }
 
@@ -362,7 +363,7 @@ static __device__ __forceinline__ void kq_pdl_launch() { asm volatile("griddepco
 // 2: SiLU(x) * aux (aux has x's layout).  With MODE 1 every CTA of a row repeats k_rmsnorm's sum (same order, same rounding).
 template <int MODE>
 __global__ void __launch_bounds__(256) k_prep_q8_K(const float *__restrict__ x, const float *__restrict__ aux, uint8_t *__restrict__ y, int nb,
-                                                   int ldx, float eps, int add_unit_offset) {
+                                                   int ldx, float eps, int add_unit_offset, int aligned) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int row = blockIdx.y, b = blockIdx.x * 8 + warp;
     const float *xr = x + (size_t)row * ldx;
@@ -411,7 +412,8 @@ __global__ void __launch_bounds__(256) k_prep_q8_K(const float *__restrict__ x, 
 #pragma unroll
         for (int j = 0; j < 8; j++) v[j] = __fmul_rn(__fdiv_rn(v[j], __fadd_rn(1.0f, v_expf(__fsub_rn(0.0f, v[j])))), u[j]); // silu_f (elementwise.cu)
     }
-    q8K_block_from_warp(v, lane, y + ((size_t)row * nb + b) * Q8K_BYTES);
+    if (aligned) q8K_block_from_warp(v, lane, y + ((size_t)row * nb + b) * Q8K_PITCH, 16, 272);
+    else q8K_block_from_warp(v, lane, y + ((size_t)row * nb + b) * Q8K_BYTES);
 }
 
 static cudaError_t kq_launch_cfg(cudaLaunchConfig_t &cfg, cudaLaunchAttribute *attr, dim3 grid, dim3 block, int pdl, cudaStream_t st) {
@@ -425,7 +427,9 @@ static cudaError_t kq_launch_cfg(cudaLaunchConfig_t &cfg, cudaLaunchAttribute *a
 }
 
 MLLMCU_API int mllmcu_prep_q8_K(int mode, const float *x, const float *aux, float eps, int add_unit_offset, void *y_blocks, int rows, int k, int ldx,
-                                int pdl, void *stream) {
+                                int flags, void *stream) {
+    const int pdl = flags & 1, aligned = (flags & 2) ? 1 : 0;
+    if (aligned && ((uintptr_t)y_blocks & 15)) return -1;
     if (mode < 0 || mode > 2 || rows <= 0 || k <= 0 || k % QK_K || ldx % 4 || ((uintptr_t)x & 15) || ((uintptr_t)y_blocks & 3)) return -1;
     if (mode != 0 && (aux == nullptr || ((uintptr_t)aux & 15))) return -1;
     const int nb = k / QK_K;
@@ -433,9 +437,9 @@ MLLMCU_API int mllmcu_prep_q8_K(int mode, const float *x, const float *aux, floa
     cudaLaunchAttribute attr[1];
     kq_launch_cfg(cfg, attr, dim3((unsigned)((nb + 7) / 8), (unsigned)rows), dim3(256), pdl, (cudaStream_t)stream);
     uint8_t *y = (uint8_t *)y_blocks;
-    if (mode == 0) CU_TRY(cudaLaunchKernelEx(&cfg, k_prep_q8_K<0>, x, aux, y, nb, ldx, eps, add_unit_offset));
-    else if (mode == 1) CU_TRY(cudaLaunchKernelEx(&cfg, k_prep_q8_K<1>, x, aux, y, nb, ldx, eps, add_unit_offset));
-    else CU_TRY(cudaLaunchKernelEx(&cfg, k_prep_q8_K<2>, x, aux, y, nb, ldx, eps, add_unit_offset));
+    if (mode == 0) CU_TRY(cudaLaunchKernelEx(&cfg, k_prep_q8_K<0>, x, aux, y, nb, ldx, eps, add_unit_offset, aligned));
+    else if (mode == 1) CU_TRY(cudaLaunchKernelEx(&cfg, k_prep_q8_K<1>, x, aux, y, nb, ldx, eps, add_unit_offset, aligned));
+    else CU_TRY(cudaLaunchKernelEx(&cfg, k_prep_q8_K<2>, x, aux, y, nb, ldx, eps, add_unit_offset, aligned));
     return 0;
 }
 
@@ -452,11 +456,15 @@ struct KqGemvParams {
 // One warp per output row, M <= 8 activation rows.  Lane (g, t) = (lane / 8, lane % 8) takes 16 weight bytes of super-block g + 4 it:
 // bytes [16 (t & 1), +16) of nibble pair t / 2, i.e. half of sub-block 2 (t / 2) in the low nibbles and half of sub-block 2 (t / 2) + 1 in
 // the high ones -- every weight byte is fetched by exactly one lane, 16 bytes at a time, and four super-block groups (up to 16 super-
-// blocks, 2.3 KB per warp) are in flight before the first is consumed.  The eight lanes of a super-block add their integers (the two exact
-// integers the reference forms) before the fp32 FMA pair; lane group g accumulates super-blocks g, g + 4, ... in order and the groups meet
-// in warp_sum, which is k_gemv_kq's order: results are bit-identical to it.
-template <int M>
+// blocks, 2.3 KB per warp) are in flight before the first is consumed.  Each lane keeps its own exact integers (scale * dot and
+// min * group sum over its 32 weights) and folds them into fp32 accumulators of its own with the super-block's two factors; the lanes meet
+// once per row.  Against the reference (integers summed over the whole super-block before the FMA pair) only the fp32 summation order
+// differs, as it already does between its AVX lanes and any other order (tolerance in the tests).  Measured (profiles/r02_q4k_gemv_micro_*):
+// the kernel is issue-bound, not byte-bound, which is why the per-super-block shuffles and the unaligned activation loads were removed.
+// ALIGNED: the activation blocks are the 304-byte re-pitched form (qs 16-byte aligned), else native block_q8_K (4-byte aligned).
+template <int M, bool ALIGNED>
 __global__ void __launch_bounds__(128) k_gemv_q4k(const KqGemvParams p) {
+    constexpr int XB = ALIGNED ? Q8K_PITCH : Q8K_BYTES, XQS = ALIGNED ? 16 : 4, XBS = ALIGNED ? 272 : 260;
     const int lane = threadIdx.x & 31;
     int n = blockIdx.x * 4 + (threadIdx.x >> 5);
     if (n >= p.Ntot) return;
@@ -475,44 +483,44 @@ __global__ void __launch_bounds__(128) k_gemv_q4k(const KqGemvParams p) {
             const int i = i0 + 4 * u + g;
             const uint8_t *blk = row + (size_t)(i < nb ? i : 0) * Q4K_BYTES;
             hq[u] = ld_stream_u4(blk);                       // d, dmin, the 12 scale bytes
-            wq[u] = ld_stream_u4(blk + 16 + j * 32 + h * 16);
+            wq[u] = ld_stream_u4(blk + 16 + t * 16);
         }
         if (i0 == 0) { kq_pdl_launch(); kq_pdl_wait(); }     // the activations are the predecessor's output
 #pragma unroll
         for (int u = 0; u < 4; u++) {
             const int i = i0 + 4 * u + g;
-            const bool on = i < nb;
-            if (i0 + 4 * u >= nb) break;                     // warp-uniform
+            if (i >= nb) continue;
             uint32_t sc[2], mn[2];
             q4k_scales8(hq[u].y, hq[u].z, hq[u].w, sc, mn);
             const int sc_lo = byte_of(sc, 2 * j), sc_hi = byte_of(sc, 2 * j + 1), mn_lo = byte_of(mn, 2 * j), mn_hi = byte_of(mn, 2 * j + 1);
             const float dw = __half2float(__ushort_as_half((unsigned short)(hq[u].x & 0xFFFFu)));
             const float dminw = __half2float(__ushort_as_half((unsigned short)(hq[u].x >> 16)));
-            const uint32_t wr[4] = {wq[u].x, wq[u].y, wq[u].z, wq[u].w};
+            const uint32_t wl[4] = {wq[u].x & 0x0F0F0F0Fu, wq[u].y & 0x0F0F0F0Fu, wq[u].z & 0x0F0F0F0Fu, wq[u].w & 0x0F0F0F0Fu};
+            const uint32_t wh[4] = {(wq[u].x >> 4) & 0x0F0F0F0Fu, (wq[u].y >> 4) & 0x0F0F0F0Fu, (wq[u].z >> 4) & 0x0F0F0F0Fu, (wq[u].w >> 4) & 0x0F0F0F0Fu};
 #pragma unroll
             for (int m = 0; m < M; m++) {
-                const uint8_t *xb = p.xq + ((size_t)m * nb + (on ? i : 0)) * Q8K_BYTES;
-                const int *alo = (const int *)(xb + 4 + (2 * j) * 32 + h * 16), *ahi = (const int *)(xb + 4 + (2 * j + 1) * 32 + h * 16);
+                const uint8_t *xb = p.xq + ((size_t)m * nb + i) * XB;
+                int al[4], ah[4];
+                if (ALIGNED) {
+                    const int4 a0 = *(const int4 *)(xb + XQS + (2 * j) * 32 + h * 16), a1 = *(const int4 *)(xb + XQS + (2 * j + 1) * 32 + h * 16);
+                    al[0] = a0.x; al[1] = a0.y; al[2] = a0.z; al[3] = a0.w; ah[0] = a1.x; ah[1] = a1.y; ah[2] = a1.z; ah[3] = a1.w;
+                } else {
+                    const int *pl = (const int *)(xb + XQS + (2 * j) * 32 + h * 16), *ph = (const int *)(xb + XQS + (2 * j + 1) * 32 + h * 16);
+#pragma unroll
+                    for (int q = 0; q < 4; q++) { al[q] = pl[q]; ah[q] = ph[q]; }
+                }
                 int is_lo = 0, is_hi = 0;
 #pragma unroll
                 for (int q = 0; q < 4; q++) {
-                    is_lo = __dp4a((int)(wr[q] & 0x0F0F0F0Fu), alo[q], is_lo);
-                    is_hi = __dp4a((int)((wr[q] >> 4) & 0x0F0F0F0Fu), ahi[q], is_hi);
+                    is_lo = __dp4a((int)wl[q], al[q], is_lo);
+                    is_hi = __dp4a((int)wh[q], ah[q], is_hi);
                 }
-                const int16_t *bs = (const int16_t *)(xb + 260);
-                int vi = sc_lo * is_lo + sc_hi * is_hi;
-                int vm = mn_lo * (int)bs[4 * j + h] + mn_hi * (int)bs[4 * j + 2 + h];
-                if (!on) { vi = 0; vm = 0; }
-#pragma unroll
-                for (int o = 1; o < 8; o <<= 1) {
-                    vi += __shfl_xor_sync(0xffffffffu, vi, o);
-                    vm += __shfl_xor_sync(0xffffffffu, vm, o);
-                }
-                if (t == 0 && on) {
-                    const float dx = *(const float *)xb;
-                    acc[m] = fmaf(__fmul_rn(dx, dw), (float)vi, acc[m]);
-                    accm[m] = fmaf(__fmul_rn(-dx, dminw), (float)vm, accm[m]);
-                }
+                const int16_t *bs = (const int16_t *)(xb + XBS);
+                const int vi = sc_lo * is_lo + sc_hi * is_hi;                                   // |vi| < 2^23: exact in fp32
+                const int vm = mn_lo * (int)bs[4 * j + h] + mn_hi * (int)bs[4 * j + 2 + h];
+                const float dx = *(const float *)xb;
+                acc[m] = fmaf(__fmul_rn(dx, dw), (float)vi, acc[m]);
+                accm[m] = fmaf(__fmul_rn(-dx, dminw), (float)vm, accm[m]);
             }
         }
     }
@@ -520,7 +528,7 @@ __global__ void __launch_bounds__(128) k_gemv_q4k(const KqGemvParams p) {
     float *y = s == 0 ? p.y[0] : s == 1 ? p.y[1] : p.y[2];
 #pragma unroll
     for (int m = 0; m < M; m++) {
-        float v = __fadd_rn(warp_sum(acc[m]), warp_sum(accm[m]));
+        float v = warp_sum(__fadd_rn(acc[m], accm[m]));
         if (lane == 0) {
             if (bias) v = __fadd_rn(v, bias[n]);
             if (p.res) v = __fadd_rn(p.res[(size_t)m * p.ldr + n], v);
@@ -530,7 +538,9 @@ __global__ void __launch_bounds__(128) k_gemv_q4k(const KqGemvParams p) {
 }
 
 MLLMCU_API int mllmcu_gemv_q4k(int nW, const void *const *W, const int *N, const float *const *bias, float *const *y, int ldy, const void *xq_blocks,
-                               int M, int K, const float *residual, int ldr, int pdl, void *stream) {
+                               int M, int K, const float *residual, int ldr, int flags, void *stream) {
+    const int pdl = flags & 1, aligned = flags & 2;
+    if (aligned && ((uintptr_t)xq_blocks & 15)) return -1;
     if (nW < 1 || nW > 3 || M < 1 || M > 8 || K <= 0 || K % QK_K || ((uintptr_t)xq_blocks & 3)) return -1;
     if (residual && nW != 1) return -1;
     KqGemvParams p = {};
@@ -548,7 +558,7 @@ MLLMCU_API int mllmcu_gemv_q4k(int nW, const void *const *W, const int *N, const
     cudaLaunchAttribute attr[1];
     kq_launch_cfg(cfg, attr, dim3((unsigned)((p.Ntot + 3) / 4)), dim3(128), pdl, (cudaStream_t)stream);
     switch (M) {
-#define CASE(m) case m: CU_TRY(cudaLaunchKernelEx(&cfg, k_gemv_q4k<m>, p)); break;
+#define CASE(m) case m: if (aligned) CU_TRY(cudaLaunchKernelEx(&cfg, k_gemv_q4k<m, true>, p)); else CU_TRY(cudaLaunchKernelEx(&cfg, k_gemv_q4k<m, false>, p)); break;
         CASE(1) CASE(2) CASE(3) CASE(4) CASE(5) CASE(6) CASE(7) CASE(8)
 #undef CASE
     }

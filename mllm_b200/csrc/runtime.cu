@@ -27,7 +27,8 @@ MLLMCU_API int mllmcu_malloc_managed(void **ptr, size_t bytes, int device) {
     CU_TRY(cudaMallocManaged(ptr, bytes, cudaMemAttachGlobal));
     // device-resident from the start: kernels never fault on it; a host touch migrates only the touched pages
     cudaMemAdvise(*ptr, bytes, cudaMemAdviseSetPreferredLocation, device);
-    cudaMemPrefetchAsync(*ptr, bytes, device, 0);
+    cudaMemPrefetchAsync(*ptr, bytes, device, cudaStreamPerThread);
+    cudaStreamSynchronize(cudaStreamPerThread); // resident when this returns: a kernel touching the range while the prefetch is still running faults page by page
     (void)cudaGetLastError(); // advice / prefetch are hints: unsupported configurations keep plain managed behaviour
     return 0;
 }
