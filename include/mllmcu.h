@@ -348,8 +348,11 @@ int mllmcu_conv3d_valid(const float *x, const float *w, const float *bias, float
                         int kh, int kw, int st, int sh, int sw, int channels_last, void *stream);
 
 /* ---- flash attention with fp32 K/V (no cache): the vision towers' attention (flash_attention_2_forward fp32 variant,
- * compute/FlashAttention2.hpp:87-1210; models/vit/modeling_vit.hpp:42-45).  D in {32, 64, 80, 128}; workspace as
- * mllmcu_flash_attn_workspace_bytes. */
+ * compute/FlashAttention2.hpp:87-1210; models/vit/modeling_vit.hpp:42-45).  D in {32, 64, 80, 128}.  Workspace:
+ * mllmcu_flash_attn_f32kv_workspace_bytes gives room for K and V split once into fp16 hi / lo planes (the tensor-core kernel then streams
+ * them like a cache); with only mllmcu_flash_attn_workspace_bytes every CTA splits the tiles it reads (same values, slower on long
+ * sequences). */
+size_t mllmcu_flash_attn_f32kv_workspace_bytes(int B, int Sq, int Sk, int Hq, int Hkv, int D);
 int mllmcu_flash_attn_f32kv(const float *q, const float *k, const float *v, float *o, int B, int Sq, int Sk, int Hq, int Hkv, int D,
                             int causal, long long kv_bstride, void *ws, size_t ws_bytes, void *stream);
 

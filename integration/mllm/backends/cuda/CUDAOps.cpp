@@ -369,7 +369,7 @@ public:
         if (!dense(q) || !dense(o)) throw std::runtime_error("[mllm-cuda] flash attention: dense q / o expected");
         const View ks = strides(k), vs = strides(v);
         if (ks.ss != (long long)Hkv * D || vs.ss != ks.ss || vs.bs != ks.bs) throw std::runtime_error("[mllm-cuda] flash attention: k / v must share one [B][limit][Hkv][D] layout");
-        const size_t wsb = mllmcu_flash_attn_workspace_bytes(B, Sq, Hq, D);
+        const size_t wsb = k.dtype() == MLLM_TYPE_F16 ? mllmcu_flash_attn_workspace_bytes(B, Sq, Hq, D) : mllmcu_flash_attn_f32kv_workspace_bytes(B, Sq, Sk, Hq, Hkv, D);
         void *ws = b->workspace(wsb);
         b->dropQuantTag();
         if (k.dtype() == MLLM_TYPE_F16)

@@ -70,6 +70,7 @@ SYMBOLS = {
     "mllmcu_embedding_q4_0": (_i, [_vp, _vp, _vp, _i, _i, _vp]),
     "mllmcu_embedding_f32": (_i, [_vp, _vp, _vp, _i, _i, _vp]),
     "mllmcu_flash_attn_workspace_bytes": (_sz, [_i, _i, _i, _i]),
+    "mllmcu_flash_attn_f32kv_workspace_bytes": (_sz, [_i, _i, _i, _i, _i, _i]),
     "mllmcu_flash_attn_f16kv": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _ll, _vp, _sz, _vp]),
     "mllmcu_quantize_q8_K": (_i, [_vp, _vp, _i, _i, _i, _vp]),
     "mllmcu_block_isums_q4_K_q8_K": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _vp]),
@@ -437,16 +438,16 @@ def conv3d_valid(x, w, bias, stride, channels_last=False):
     return y
 
 
-def flash_attn_f32kv(q, k, v, causal=False):
-    """q cuda fp32 [B,Sq,Hq,D]; k,v cuda fp32 [B,Sk,Hkv,D]"""
+def flash_attn_f32kv(q, k, v, causal=False, small_ws=False):
+    """q cuda fp32 [B,Sq,Hq,D]; k,v cuda fp32 [B,Sk,Hkv,D].  small_ws: only the split-K scratch (K/V are then split tile by tile in the kernel)."""
     import torch
     B, Sq, Hq, D = q.shape
     Sk, Hkv = k.shape[1], k.shape[2]
     o = torch.empty_like(q)
-    need = lib().mllmcu_flash_attn_workspace_bytes(B, Sq, Hq, D)
+    need = lib().mllmcu_flash_attn_workspace_bytes(B, Sq, Hq, D) if small_ws else lib().mllmcu_flash_attn_f32kv_workspace_bytes(B, Sq, Sk, Hq, Hkv, D)
     ws = _workspace(need, q.device)
     check(lib().mllmcu_flash_attn_f32kv(_ptr(q), _ptr(k), _ptr(v), _ptr(o), B, Sq, Sk, Hq, Hkv, D, int(causal), k.stride(0),
-                                        _ptr(ws), ws.numel(), _stream()), "flash_attn_f32kv")
+                                        _ptr(ws), need, _stream()), "flash_attn_f32kv")
     return o
 
 

@@ -19,6 +19,7 @@
 // merged by k_attn_merge.  Decode is HBM-bound on the KV read
 // (2 * Sk * Hkv * D * 2 bytes per sequence).
 #include "common.cuh"
+#include <algorithm>
 #include <stdlib.h>
 
 static __device__ __forceinline__ float kv_to_f32(__half h) { return __half2float(h); }
@@ -177,8 +178,9 @@ static int launch_attn(const float *q, const KT *k, const KT *v, float *o, int B
 // attention_tc.cu: tensor-core prefill kernels; return 1 when the shape is not theirs
 int attn_prefill_tc_f16(const float *q, const void *k, const void *v, float *o, int B, int Sq, int Sk, int Hq, int Hkv, int D, int causal,
                         long long kvb, cudaStream_t st);
+size_t attn_tc_f32_planes_bytes(int B, int Sq, int Sk, int Hkv, int D);
 int attn_prefill_tc_f32(const float *q, const void *k, const void *v, float *o, int B, int Sq, int Sk, int Hq, int Hkv, int D, int causal,
-                        long long kvb, cudaStream_t st);
+                        long long kvb, void *ws, size_t ws_bytes, cudaStream_t st);
 static bool use_tc() { // MLLM_CUDA_ATTN_TC=0 keeps every shape on the CUDA-core kernel (A/B measurements)
     const char *e = getenv("MLLM_CUDA_ATTN_TC"); // read per call so one process can compare both
     return !(e && e[0] == '0');
@@ -204,13 +206,17 @@ MLLMCU_API int mllmcu_flash_attn_f16kv(const float *q, const void *k, const void
 
 // fp32 K/V (no cache): the attention of the vision towers -- CLIP ViT-L/14 (D 64), Qwen2-VL ViT (D 80) -- and of any graph
 // that calls flash_attention_2_forward on fp32 tensors.  k,v: element (b,s,h,d) at b*kv_bstride + s*Hkv*D + h*D + d.
+MLLMCU_API size_t mllmcu_flash_attn_f32kv_workspace_bytes(int B, int Sq, int Sk, int Hq, int Hkv, int D) {
+    return std::max(mllmcu_flash_attn_workspace_bytes(B, Sq, Hq, D), attn_tc_f32_planes_bytes(B, Sq, Sk, Hkv, D));
+}
+
 MLLMCU_API int mllmcu_flash_attn_f32kv(const float *q, const float *k, const float *v, float *o, int B, int Sq, int Sk, int Hq,
                                        int Hkv, int D, int causal, long long kv_bstride, void *ws, size_t ws_bytes, void *stream) {
     if (B <= 0 || Sq <= 0 || Sk <= 0 || Hq <= 0 || Hkv <= 0 || Hq % Hkv) return -1;
     if (causal && Sq > Sk) return -1;
     cudaStream_t st = (cudaStream_t)stream;
     if (use_tc()) {
-        const int rc = attn_prefill_tc_f32(q, k, v, o, B, Sq, Sk, Hq, Hkv, D, causal, kv_bstride, st);
+        const int rc = attn_prefill_tc_f32(q, k, v, o, B, Sq, Sk, Hq, Hkv, D, causal, kv_bstride, ws, ws_bytes, st);
         if (rc != 1) return rc;
     }
     switch (D) {

@@ -11,12 +11,17 @@
 // tests hold.  fp32 K/V (vision towers, no cache) are split the same way at tile load: three products per
 // contraction (hi.hi + lo.hi + hi.lo).
 //
+// fp32 K/V over long sequences (Qwen2-VL's tower: 5476 patches) are split ONCE per call by k_split_kv into four fp16 planes (K hi, K lo, V hi,
+// V lo) in the caller's workspace; the attention kernel then streams those planes with cp.async, two stages, exactly like fp16 K/V (MODE 2)
+// instead of every 64-row CTA re-reading and re-splitting all of K and V between two barriers (MODE 1, kept for callers without workspace).
+//
 // One CTA = 4 warps x 16 query rows of one (batch, head); keys in tiles of 64, staged in shared memory
 // (fp16 K/V: cp.async, two stages; 16-byte chunks XOR-swizzled by row so ldmatrix is conflict-free), fragments through
 // ldmatrix (K as stored, V transposed), mma.sync.m16n8k16 fp16 -> fp32, online softmax in registers (FA-2 layout).
 // Work: 4 * Sq * Sk/2 * Hq * D flop per layer (causal), x2 for the split; the old warp-per-row CUDA-core kernel
 // (attention.cu) remains for short query runs (Sq < 16) and head dims outside {64, 80, 128}.
 #include "common.cuh"
+#include <stdlib.h>
 
 static __device__ __forceinline__ void mma16816(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
     asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
@@ -40,23 +45,28 @@ static __device__ __forceinline__ void split2(float x, float y, uint32_t &hi, ui
     lo = *(const uint32_t *)&l;
 }
 
-// D: head dim (multiple of 16).  F32KV: K/V are fp32 and are split into hi/lo tiles at load.
-// Shared-memory rows are RS halves (a power-of-two number of 16-byte chunks >= D/8, so the XOR swizzle stays in the row).
-template <int D, bool F32KV>
+// D: head dim (multiple of 16).  MODE 0: fp16 K/V.  MODE 1: fp32 K/V, split into hi/lo tiles at load.  MODE 2: fp32 K/V already split into
+// fp16 planes (kp = K hi; K lo, V hi, V lo follow at multiples of `pstride` halves; vp unused).
+// Shared-memory rows: MODE 0/1 a power-of-two number of 16-byte chunks >= D/8 with an XOR swizzle by row; MODE 2 D/8 + 1 chunks, no swizzle
+// (row pitch = 4 banks mod 32: the 8 rows of an ldmatrix phase land in 8 different bank groups, and D = 80 needs 176 bytes instead of 256).
+template <int D, int MODE>
 __global__ void __launch_bounds__(128) k_attn_prefill_tc(const float *__restrict__ q, const void *__restrict__ kp, const void *__restrict__ vp,
-                                                         float *__restrict__ o, int Sq, int Sk, int Hq, int Hkv, int causal, long long kvb) {
+                                                         float *__restrict__ o, int Sq, int Sk, int Hq, int Hkv, int causal, long long kvb,
+                                                         long long pstride) {
+    constexpr bool F32KV = MODE != 0, PAD = MODE == 2;
     constexpr int BC = 64;           // keys per tile
     constexpr int KS = D / 16;       // k-steps of q.k
     constexpr int NB = BC / 8;       // score column blocks
     constexpr int DB = D / 8;        // output column blocks
     constexpr int CH = D / 8;        // 16-byte chunks per row that hold data
-    constexpr int RCH = (CH <= 8) ? 8 : 16; // chunks per shared-memory row
+    constexpr int RCH = PAD ? CH + 1 : (CH <= 8) ? 8 : 16; // chunks per shared-memory row
     constexpr int RB = RCH * 16;     // row bytes
     constexpr int TILE = BC * RB;    // bytes of one tile
     constexpr int NPL = F32KV ? 2 : 1;      // planes per operand (hi, lo)
     extern __shared__ __align__(128) unsigned char smem[];
     // [stage][K planes | V planes]
     const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(smem);
+    auto soff = [](int r, int c) { return (uint32_t)(PAD ? r * RB + (c << 4) : r * RB + ((c ^ (r & 7)) << 4)); };
     auto k_tile = [&](int st, int pl) { return sbase + (uint32_t)((st * 2 * NPL + pl) * TILE); };
     auto v_tile = [&](int st, int pl) { return sbase + (uint32_t)((st * 2 * NPL + NPL + pl) * TILE); };
 
@@ -87,13 +97,33 @@ __global__ void __launch_bounds__(128) k_attn_prefill_tc(const float *__restrict
     const int ntile = last / BC + 1;
 
     auto load_tile = [&](int jt, int st) {
-        if (!F32KV) {
+        if (MODE == 2) {
+            const __half *pb = (const __half *)kp + (size_t)b * kvb + (size_t)kvh * D;
+            for (int i = tid; i < BC * CH; i += 128) {
+                const int r = i / CH, c = i % CH;
+                const int key = jt * BC + r;
+                const uint32_t so = soff(r, c);
+                if (key < Sk) {
+                    const __half *src = pb + (size_t)key * rs + c * 8;
+                    cp_async16(k_tile(st, 0) + so, src);
+                    cp_async16(k_tile(st, 1) + so, src + pstride);
+                    cp_async16(v_tile(st, 0) + so, src + 2 * pstride);
+                    cp_async16(v_tile(st, 1) + so, src + 3 * pstride);
+                } else {
+                    asm volatile("st.shared.v4.u32 [%0], {%1,%1,%1,%1};" ::"r"(k_tile(st, 0) + so), "r"(0));
+                    asm volatile("st.shared.v4.u32 [%0], {%1,%1,%1,%1};" ::"r"(k_tile(st, 1) + so), "r"(0));
+                    asm volatile("st.shared.v4.u32 [%0], {%1,%1,%1,%1};" ::"r"(v_tile(st, 0) + so), "r"(0));
+                    asm volatile("st.shared.v4.u32 [%0], {%1,%1,%1,%1};" ::"r"(v_tile(st, 1) + so), "r"(0));
+                }
+            }
+            asm volatile("cp.async.commit_group;");
+        } else if (MODE == 0) {
             const __half *kb = (const __half *)kp + (size_t)b * kvb + (size_t)kvh * D;
             const __half *vb = (const __half *)vp + (size_t)b * kvb + (size_t)kvh * D;
             for (int i = tid; i < BC * CH; i += 128) {
                 const int r = i / CH, c = i % CH;
                 const int key = jt * BC + r;
-                const uint32_t so = (uint32_t)(r * RB + ((c ^ (r & 7)) << 4));
+                const uint32_t so = soff(r, c);
                 if (key < Sk) {
                     cp_async16(k_tile(st, 0) + so, kb + (size_t)key * rs + c * 8);
                     cp_async16(v_tile(st, 0) + so, vb + (size_t)key * rs + c * 8);
@@ -109,7 +139,7 @@ __global__ void __launch_bounds__(128) k_attn_prefill_tc(const float *__restrict
             for (int i = tid; i < BC * CH; i += 128) {
                 const int r = i / CH, c = i % CH;
                 const int key = jt * BC + r;
-                const uint32_t so = (uint32_t)(r * RB + ((c ^ (r & 7)) << 4));
+                const uint32_t so = soff(r, c);
                 uint32_t kh4[4] = {0, 0, 0, 0}, kl4[4] = {0, 0, 0, 0}, vh4[4] = {0, 0, 0, 0}, vl4[4] = {0, 0, 0, 0};
                 if (key < Sk) {
                     const float4 k0 = *(const float4 *)(kb + (size_t)key * rs + c * 8), k1 = *(const float4 *)(kb + (size_t)key * rs + c * 8 + 4);
@@ -132,10 +162,11 @@ __global__ void __launch_bounds__(128) k_attn_prefill_tc(const float *__restrict
     for (int d = 0; d < DB; d++) acc[d][0] = acc[d][1] = acc[d][2] = acc[d][3] = 0.f;
     float m0 = -INFINITY, m1 = -INFINITY, l0 = 0.f, l1 = 0.f; // rows g and g+8
 
-    if (!F32KV) load_tile(0, 0);
+    constexpr bool ASYNC = MODE != 1;
+    if (ASYNC) load_tile(0, 0);
     for (int jt = 0; jt < ntile; jt++) {
-        const int st = F32KV ? 0 : (jt & 1);
-        if (!F32KV) {
+        const int st = ASYNC ? (jt & 1) : 0;
+        if (ASYNC) {
             asm volatile("cp.async.wait_group 0;");
             __syncthreads();
             if (jt + 1 < ntile) load_tile(jt + 1, st ^ 1);
@@ -156,7 +187,7 @@ __global__ void __launch_bounds__(128) k_attn_prefill_tc(const float *__restrict
 #pragma unroll
             for (int kk2 = 0; kk2 < (KS + 1) / 2; kk2++) {
                 const int c = 4 * kk2 + mat; // for odd KS the last pair's upper half reads pad chunks (unused)
-                const uint32_t so = (uint32_t)(r * RB + ((c ^ (r & 7)) << 4));
+                const uint32_t so = soff(r, c);
                 uint32_t kf[4];
                 ldsm4(kf, k_tile(st, 0) + so);
                 mma16816(s[nb], qh[2 * kk2], kf[0], kf[1]);
@@ -230,7 +261,7 @@ __global__ void __launch_bounds__(128) k_attn_prefill_tc(const float *__restrict
 #pragma unroll
             for (int dp = 0; dp < DB / 2; dp++) {
                 const int c = 2 * dp + (mat >> 1);
-                const uint32_t so = (uint32_t)(r * RB + ((c ^ (r & 7)) << 4));
+                const uint32_t so = soff(r, c);
                 uint32_t vf[4];
                 ldsm4t(vf, v_tile(st, 0) + so);
                 mma16816(acc[2 * dp], ph, vf[0], vf[1]);
@@ -262,18 +293,43 @@ __global__ void __launch_bounds__(128) k_attn_prefill_tc(const float *__restrict
     }
 }
 
-template <int D, bool F32KV>
+// fp32 K/V -> fp16 planes (hi = fp16(x), lo = fp16(x - hi)): dst[0] K hi, [1] K lo, [2] V hi, [3] V lo, each [B][Sk][Hkv * D] dense
+__global__ void k_split_kv(const float *__restrict__ k, const float *__restrict__ v, __half *__restrict__ dst, int Sk, long long row, long long kvb,
+                           long long pstride, long long total2) {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; // one float2 of K and of V
+    if (i >= total2) return;
+    const long long e = 2 * i, r = e / row, c = e % row, b = r / Sk, s = r % Sk; // row = Hkv * D (even)
+    const size_t src = (size_t)b * kvb + (size_t)s * row + c;
+    const float2 kk = *(const float2 *)(k + src), vv = *(const float2 *)(v + src);
+    uint32_t kh, kl, vh, vl;
+    split2(kk.x, kk.y, kh, kl);
+    split2(vv.x, vv.y, vh, vl);
+    uint32_t *d = (uint32_t *)(dst + e);
+    d[0] = kh;
+    d[pstride / 2] = kl;
+    d[pstride] = vh;
+    d[pstride / 2 * 3] = vl;
+}
+
+size_t attn_tc_f32_planes_bytes(int B, int Sq, int Sk, int Hkv, int D) {
+    if (Sq < 16 || (D != 64 && D != 80 && D != 128)) return 0;
+    const size_t ps = (((size_t)B * Sk * Hkv * D) + 7) & ~(size_t)7;
+    return 4 * ps * sizeof(__half) + 256;
+}
+
+template <int D, int MODE>
 static int launch_tc(const float *q, const void *k, const void *v, float *o, int B, int Sq, int Sk, int Hq, int Hkv, int causal,
-                     long long kvb, cudaStream_t st) {
-    constexpr int CH = D / 8, RCH = (CH <= 8) ? 8 : 16;
-    constexpr int smem = 64 * RCH * 16 * 2 * (F32KV ? 2 : 1) * (F32KV ? 1 : 2);
+                     long long kvb, long long pstride, cudaStream_t st) {
+    constexpr int CH = D / 8, RCH = MODE == 2 ? CH + 1 : (CH <= 8) ? 8 : 16;
+    // MODE 2: + 64 bytes -- for an odd number of k-steps (D = 80) the last ldmatrix of a row also names the chunk after the pad
+    constexpr int smem = 64 * RCH * 16 * 2 * (MODE != 0 ? 2 : 1) * (MODE != 1 ? 2 : 1) + (MODE == 2 ? 64 : 0);
     static bool attr = false;
     if (!attr) {
-        CU_TRY(cudaFuncSetAttribute(k_attn_prefill_tc<D, F32KV>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        CU_TRY(cudaFuncSetAttribute(k_attn_prefill_tc<D, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
         attr = true;
     }
     dim3 grid((Sq + 63) / 64, Hq, B);
-    k_attn_prefill_tc<D, F32KV><<<grid, 128, smem, st>>>(q, k, v, o, Sq, Sk, Hq, Hkv, causal, kvb);
+    k_attn_prefill_tc<D, MODE><<<grid, 128, smem, st>>>(q, k, v, o, Sq, Sk, Hq, Hkv, causal, kvb, pstride);
     CU_LAUNCH_CHECK();
     return 0;
 }
@@ -284,19 +340,33 @@ int attn_prefill_tc_f16(const float *q, const void *k, const void *v, float *o, 
     if (Sq < 16 || (kvb % 8) != 0) return 1;
     if (((uintptr_t)k | (uintptr_t)v) & 15) return 1;
     switch (D) {
-    case 64: return launch_tc<64, false>(q, k, v, o, B, Sq, Sk, Hq, Hkv, causal, kvb, st);
-    case 128: return launch_tc<128, false>(q, k, v, o, B, Sq, Sk, Hq, Hkv, causal, kvb, st);
+    case 64: return launch_tc<64, 0>(q, k, v, o, B, Sq, Sk, Hq, Hkv, causal, kvb, 0, st);
+    case 128: return launch_tc<128, 0>(q, k, v, o, B, Sq, Sk, Hq, Hkv, causal, kvb, 0, st);
     default: return 1;
     }
 }
+// ws / ws_bytes: room for the four planes (attn_tc_f32_planes_bytes) selects the pre-split kernel; less keeps the in-kernel split
 int attn_prefill_tc_f32(const float *q, const void *k, const void *v, float *o, int B, int Sq, int Sk, int Hq, int Hkv, int D, int causal,
-                        long long kvb, cudaStream_t st) {
+                        long long kvb, void *ws, size_t ws_bytes, cudaStream_t st) {
     if (Sq < 16 || (kvb % 4) != 0) return 1;
     if (((uintptr_t)k | (uintptr_t)v) & 15) return 1;
+    const size_t need = attn_tc_f32_planes_bytes(B, Sq, Sk, Hkv, D);
+    static const bool presplit_on = !(getenv("MLLMCU_ATTN_PRESPLIT") && atoi(getenv("MLLMCU_ATTN_PRESPLIT")) == 0);
+    if (presplit_on && need && ws && ws_bytes >= need && !((uintptr_t)ws & 15) && (Hkv * D) % 8 == 0) {
+        const long long row = (long long)Hkv * D, dense = (long long)Sk * row;
+        const long long ps = (((long long)B * dense) + 7) & ~7LL, total2 = (long long)B * dense / 2;
+        k_split_kv<<<(unsigned)((total2 + 255) / 256), 256, 0, st>>>((const float *)k, (const float *)v, (__half *)ws, Sk, row, kvb, ps, total2);
+        CU_LAUNCH_CHECK();
+        switch (D) {
+        case 64: return launch_tc<64, 2>(q, ws, nullptr, o, B, Sq, Sk, Hq, Hkv, causal, dense, ps, st);
+        case 80: return launch_tc<80, 2>(q, ws, nullptr, o, B, Sq, Sk, Hq, Hkv, causal, dense, ps, st);
+        case 128: return launch_tc<128, 2>(q, ws, nullptr, o, B, Sq, Sk, Hq, Hkv, causal, dense, ps, st);
+        }
+    }
     switch (D) {
-    case 64: return launch_tc<64, true>(q, k, v, o, B, Sq, Sk, Hq, Hkv, causal, kvb, st);
-    case 80: return launch_tc<80, true>(q, k, v, o, B, Sq, Sk, Hq, Hkv, causal, kvb, st);
-    case 128: return launch_tc<128, true>(q, k, v, o, B, Sq, Sk, Hq, Hkv, causal, kvb, st);
+    case 64: return launch_tc<64, 1>(q, k, v, o, B, Sq, Sk, Hq, Hkv, causal, kvb, 0, st);
+    case 80: return launch_tc<80, 1>(q, k, v, o, B, Sq, Sk, Hq, Hkv, causal, kvb, 0, st);
+    case 128: return launch_tc<128, 1>(q, k, v, o, B, Sq, Sk, Hq, Hkv, causal, kvb, 0, st);
     default: return 1;
     }
 }

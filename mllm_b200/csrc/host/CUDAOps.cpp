@@ -530,7 +530,8 @@ public:
         if (k.dtype() != v.dtype() || (k.dtype() != MLLM_TYPE_F16 && k.dtype() != MLLM_TYPE_F32))
             throw std::runtime_error("[mllm-cuda] flash_attention2: K/V must both be fp16 (KV cache) or both fp32 (no cache: vision towers)");
         if (k.seqStride() != (long long)k.head() * k.dimension()) throw std::runtime_error("[mllm-cuda] flash_attention2: K/V rows must be dense");
-        const size_t wsb = mllmcu_flash_attn_workspace_bytes(q.batch(), q.sequence(), q.head(), q.dimension());
+        const size_t wsb = k.dtype() == MLLM_TYPE_F32 ? mllmcu_flash_attn_f32kv_workspace_bytes(q.batch(), q.sequence(), k.sequence(), q.head(), k.head(), q.dimension())
+                                                      : mllmcu_flash_attn_workspace_bytes(q.batch(), q.sequence(), q.head(), q.dimension());
         void *ws = b->workspace(wsb);
         if (k.dtype() == MLLM_TYPE_F32) { // flash_attention_2_forward's fp32 variant (compute/FlashAttention2.hpp:87-1210): ViT blocks keep no cache
             MLLMCU_CHECK(mllmcu_flash_attn_f32kv(q.devPtr<float>(), k.devPtr<float>(), v.devPtr<float>(), out[0]->devPtr<float>(), q.batch(), q.sequence(),

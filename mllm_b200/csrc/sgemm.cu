@@ -112,6 +112,18 @@ static int conv_launch(const float *x, const float *w, const float *bias, float 
     a.kt = kt; a.kh = kh; a.kw = kw; a.st = st; a.sh = sh; a.sw = sw;
     a.ot = (T - kt) / st + 1; a.oh = (H - kh) / sh + 1; a.ow = (W - kw) / sw + 1;
     const int M = a.ot * a.oh * a.ow, K = C * kt * kh * kw;
+    if (kt == T && kh == H && kw == W) {
+        // the kernel covers the whole input (Qwen2-VL's patch embed: every "batch" entry is ONE 3 x 2 x 14 x 14 patch): one output position
+        // per entry, the receptive field is the entry itself in memory order -- a plain [B x K] . [O x K]^T product with the entries as rows
+        // (one launch of 64-row tiles instead of B launches' worth of tiles with one live row each; same k order, same sums)
+        AView pa{};
+        pa.p = x;
+        pa.ld = K;
+        const dim3 g1((O + 63) / 64, (B + 63) / 64, 1);
+        k_sgemm<0><<<g1, 256, 0, stream>>>(pa, 0, w, K, 1, 0, bias, y, O, 1, 0, B, O, K);
+        CU_LAUNCH_CHECK();
+        return 0;
+    }
     const dim3 grid((O + 63) / 64, (M + 63) / 64, B);
     // output element (m = position, n = channel): channels-first [B][O][M] -> ldcm 1, ldcn M; channels-last [B][M][O] -> ldcm O, ldcn 1
     k_sgemm<1><<<grid, 256, 0, stream>>>(a, (long long)C * T * H * W, w, K, 1, 0, bias, y, channels_last ? O : 1, channels_last ? 1 : M,

@@ -327,17 +327,49 @@ def test_conv3d_qwen2vl_patch_embed(cu, oracle):
         assert got.shape == want.shape and np.abs(got - want).max() <= 2e-5 * np.abs(want).max()
 
 
+def test_conv3d_one_patch_per_batch_entry(cu, oracle):
+    """How modeling_qwen2_vl.hpp calls it: the processor hands over [patches, 3, 2, 14, 14] and the kernel covers a whole entry -- one output
+    position per entry (sgemm.cu runs it as one plain product over the entries)."""
+    rng = np.random.default_rng(8)
+    x = rng.standard_normal((150, 3, 2, 14, 14)).astype(np.float32)
+    w = (rng.standard_normal((96, 3, 2, 14, 14)) * 0.02).astype(np.float32)
+    b = rng.standard_normal(96).astype(np.float32)
+    for cl in (False, True):
+        want = oracle.only.conv3d_valid(x, w, b, (2, 14, 14), channels_last=cl)
+        got = cu.conv3d_valid(dev(x), dev(w), dev(b), (2, 14, 14), channels_last=cl).cpu().numpy()
+        assert got.shape == want.shape and np.abs(got - want).max() <= 2e-5 * np.abs(want).max()
+
+
 # ------------------------------------------------------------------ ViT attention (fp32 K/V, non-causal)
-@pytest.mark.parametrize("S,H,D", [(577, 16, 64), (100, 16, 80), (64, 4, 128)])
+# default workspace: K / V split once into fp16 hi / lo planes, streamed with cp.async; small_ws: every CTA splits the tiles it reads.
+# Same split values, same MMA order: the two agree bit for bit, and both hold the 2e-5 bar against float64.
+@pytest.mark.parametrize("S,H,D", [(577, 16, 64), (100, 16, 80), (64, 4, 128), (1111, 3, 80), (130, 2, 128)])
 def test_flash_attn_f32kv_noncausal(cu, S, H, D):
+    import torch
     rng = np.random.default_rng(S + D)
     q, k, v = (rng.standard_normal((1, S, H, D)).astype(np.float32) for _ in range(3))
-    got = cu.flash_attn_f32kv(dev(q), dev(k), dev(v), causal=False).cpu().numpy()[0]
+    got_t = cu.flash_attn_f32kv(dev(q), dev(k), dev(v), causal=False)
+    assert torch.equal(got_t, cu.flash_attn_f32kv(dev(q), dev(k), dev(v), causal=False, small_ws=True))
+    got = got_t.cpu().numpy()[0]
     s = np.einsum("qhd,khd->hqk", q[0].astype(np.float64), k[0].astype(np.float64)) / np.sqrt(D)
     p = np.exp(s - s.max(-1, keepdims=True))
     p /= p.sum(-1, keepdims=True)
     want = np.einsum("hqk,khd->qhd", p, v[0].astype(np.float64))
     assert np.abs(got - want).max() <= 2e-5
+
+
+def test_flash_attn_f32kv_batched_and_causal_planes(cu):
+    """two batch entries with a strided (non-dense) K/V batch stride, causal, GQA: the planes are dense whatever the source stride"""
+    import torch
+    rng = np.random.default_rng(5)
+    B, S, Hq, Hkv, D = 2, 200, 4, 2, 64
+    q = dev(rng.standard_normal((B, S, Hq, D)).astype(np.float32))
+    kbig, vbig = (dev(rng.standard_normal((B, S + 56, Hkv, D)).astype(np.float32)) for _ in range(2))
+    k, v = kbig[:, :S], vbig[:, :S]
+    a = cu.flash_attn_f32kv(q, k, v, causal=True)
+    b = cu.flash_attn_f32kv(q, k, v, causal=True, small_ws=True)
+    c = cu.flash_attn_f32kv(q, k.contiguous(), v.contiguous(), causal=True)
+    assert torch.equal(a, b) and torch.equal(a, c)
 
 
 def test_flash_attn_f32kv_matches_reference_variant(cu, ref_lib):
