@@ -49,6 +49,28 @@ def test_unchanged_llama_graph_same_tokens_on_cpu_and_cuda_backends(have_bin, tm
     assert eager["fused_steps"] == 0 and eager["tokens"] == cpu["tokens"]
 
 
+@pytest.mark.parametrize("B", [1, 2])
+def test_q4_k_body_takes_the_nine_launch_chain(have_bin, tmp_path, B):
+    """A LLaMA body with Q4_K Linears (what LLaVA's LLM is): single-token forwards are answered by the plan's prep + multi-matrix GEMV chain
+    (mllmcu_prep_q8_K / mllmcu_gemv_q4k, PDL).  The chain, the op-level plan (MLLM_CUDA_Q4K_CHAIN_OFF=1) and the op-by-op path form the same
+    quantised bytes and integers and differ in fp32 summation order only: on this 2-block graph they pick the same tokens as the CPU backend
+    for the first steps (the horizon any two non-bit-identical backends share on random-init weights) and engage for every step."""
+    dims = "512,256,4,4,512,2,2"
+    cfg = mf.config("toy-llama", cache_limit=128)
+    cfg["wtype"] = mf.Q4_K
+    path = str(tmp_path / "q4k.mllm")
+    mf.write_model(path, cfg, mf.random_tensors(cfg, seed=9))
+    cpu = run(0, "llama-generic", path, 16, 24, batch=B, limit=128, dims=dims)
+    chain = run(4, "llama-generic", path, 16, 24, batch=B, limit=128, dims=dims)
+    plain = run(4, "llama-generic", path, 16, 24, batch=B, limit=128, dims=dims, env={"MLLM_CUDA_Q4K_CHAIN_OFF": "1"})
+    eager = run(4, "llama-generic", path, 16, 24, batch=B, limit=128, dims=dims, env={"MLLM_CUDA_EAGER_DECODE": "1"})
+    assert chain["fused_steps"] == 24 - 2 and plain["fused_steps"] == 24 - 2 and eager["fused_steps"] == 0
+    for r in (chain, plain, eager):
+        for b in range(B):
+            assert r["tokens"][b][:6] == cpu["tokens"][b][:6]
+    assert plain["tokens"] == eager["tokens"]  # the op-level plan IS the op-by-op arithmetic on fixed buffers
+
+
 def test_tinyllama_graph_on_cuda_backend(have_bin):
     """BASELINE configs[0] model through the unchanged TinyLLaMAModel header: tokens agree with the CPU backend over the first steps
     (the horizon any two non-bit-identical backends share on random-init weights: tests/test_baseline_configs_gpu.py) and the
