@@ -32,19 +32,24 @@ static Tensor make_input(const std::vector<unsigned> &ids, int B, int S) {
 }
 
 template <typename Model>
-static int run(Model &model, BackendType device, const std::string &file, int vocab, int B, int S, int n_decode, unsigned seed) {
+static int run(Model &model, BackendType device, const std::string &file, int vocab, int B, int S, int n_decode, unsigned seed, int repeat = 1) {
     if (device != MLLM_CPU) model.to(device);
     model.load(file);
     std::mt19937 rng(seed);
     std::vector<unsigned> ids((size_t)B * S);
     for (auto &v : ids) v = rng() % vocab;
     std::vector<std::vector<unsigned>> out(B);
-    Tensor in = make_input(ids, B, S);
     int fused_steps = 0;
+    std::vector<double> pre_all, med_all; // --repeat: the same request again after clear_kvcache() (first-request costs -- lazy kernel
+                                          // loading, host-built RoPE tables, pool growth -- show up in entry 0 only)
+    double pre_ms = 0.0, dec_ms = 0.0, dec_median = 0.0;
+    for (int rep = 0; rep < repeat; rep++) {
+    if (rep) { model.clear_kvcache(); model.inference_times_.clear(); }
+    Tensor in = make_input(ids, B, S);
     for (int step = 0; step < n_decode; step++) {
         auto result = model({in});
 #ifdef USE_CUDA
-        if (device == MLLM_CUDA) fused_steps += static_cast<CUDABackend *>(Backend::global_backends[MLLM_CUDA].get())->last_forward_fused;
+        if (device == MLLM_CUDA && rep == 0) fused_steps += static_cast<CUDABackend *>(Backend::global_backends[MLLM_CUDA].get())->last_forward_fused;
 #endif
         Tensor lg = result[0];
         if (lg.backend()->type() != MLLM_CPU) lg.cpu(); // as the OpenCL demos do before reading a result on the host
@@ -58,17 +63,30 @@ static int run(Model &model, BackendType device, const std::string &file, int vo
                 if (v > bv) { bv = v; best = i; }
             }
             next[b] = (unsigned)best;
-            out[b].push_back((unsigned)best);
+            if (rep == 0) out[b].push_back((unsigned)best);
         }
         in = make_input(next, B, 1);
     }
-    double pre_ms = model.inference_times_.empty() ? 0.0 : model.inference_times_[0], dec_ms = 0.0;
-    for (size_t i = 1; i < model.inference_times_.size(); i++) dec_ms += model.inference_times_[i];
-    std::vector<double> tail(model.inference_times_.begin() + std::min<size_t>(model.inference_times_.size(), 4), model.inference_times_.end());
+    const double p_ms = model.inference_times_.empty() ? 0.0 : model.inference_times_[0];
+    double d_ms = 0.0;
+    for (size_t i = 1; i < model.inference_times_.size(); i++) d_ms += model.inference_times_[i];
+    std::vector<double> tail(model.inference_times_.begin() + std::min<size_t>(model.inference_times_.size(), rep ? 1 : 4), model.inference_times_.end());
     std::sort(tail.begin(), tail.end());
-    const double dec_median = tail.empty() ? 0.0 : tail[tail.size() / 2];
-    printf("{\"device\": %d, \"B\": %d, \"prompt\": %d, \"decode\": %d, \"prefill_ms\": %.3f, \"decode_ms_per_step\": %.4f, \"decode_ms_median\": %.4f, \"fused_steps\": %d, \"tokens\": [", (int)device, B,
+    const double med = tail.empty() ? 0.0 : tail[tail.size() / 2];
+    pre_all.push_back(p_ms);
+    med_all.push_back(med);
+    if (rep == 0) { pre_ms = p_ms; dec_ms = d_ms; dec_median = med; }
+    }
+    printf("{\"device\": %d, \"B\": %d, \"prompt\": %d, \"decode\": %d, \"prefill_ms\": %.3f, \"decode_ms_per_step\": %.4f, \"decode_ms_median\": %.4f, \"fused_steps\": %d, ", (int)device, B,
            S, n_decode, pre_ms, n_decode > 1 ? dec_ms / (n_decode - 1) : 0.0, dec_median, fused_steps);
+    if (repeat > 1) {
+        printf("\"prefill_ms_per_request\": [");
+        for (size_t i = 0; i < pre_all.size(); i++) printf("%s%.3f", i ? ", " : "", pre_all[i]);
+        printf("], \"decode_ms_median_per_request\": [");
+        for (size_t i = 0; i < med_all.size(); i++) printf("%s%.4f", i ? ", " : "", med_all[i]);
+        printf("], ");
+    }
+    printf("\"tokens\": [");
     for (int b = 0; b < B; b++) {
         printf("%s[", b ? ", " : "");
         for (size_t i = 0; i < out[b].size(); i++) printf("%s%u", i ? ", " : "", out[b][i]);
@@ -89,6 +107,7 @@ int main(int argc, char **argv) {
     cmd.add<int>("limit", 'l', "KV cache limit", false, 512);
     cmd.add<int>("thread", 't', "CPU threads", false, 4);
     cmd.add<int>("seed", 's', "token seed", false, 7);
+    cmd.add<int>("repeat", 'r', "run the request this many times (clear_kvcache between); times per request are reported", false, 1);
     cmd.add<std::string>("dims", 'x', "llama-generic: vocab,hidden,heads,kv_heads,ffn,layers,rope_type(2|4)", false, "");
     cmd.parse_check(argc, argv);
     const auto device = (BackendType)cmd.get<int>("device");
@@ -97,21 +116,22 @@ int main(int argc, char **argv) {
     const std::string name = cmd.get<std::string>("model"), file = cmd.get<std::string>("file");
     const int S = cmd.get<int>("prompt"), n = cmd.get<int>("decode"), B = cmd.get<int>("batch"), limit = cmd.get<int>("limit");
     const unsigned seed = (unsigned)cmd.get<int>("seed");
+    const int repeat = std::max(1, cmd.get<int>("repeat"));
     Module::initBackend(MLLM_CPU);
     if (name == "llama2-7b") {
         LLaMAConfig config(limit, "7B", LLAMAROPE);
         LLaMAModel model(config);
-        return run(model, device, file, config.vocab_size, B, S, n, seed);
+        return run(model, device, file, config.vocab_size, B, S, n, seed, repeat);
     }
     if (name == "tinyllama-1.1b") {
         TinyLLaMAConfig config(limit, "1.1B", HFHUBROPE);
         TinyLLaMAModel model(config);
-        return run(model, device, file, config.vocab_size, B, S, n, seed);
+        return run(model, device, file, config.vocab_size, B, S, n, seed, repeat);
     }
     if (name == "qwen1.5-1.8b") {
         QWenConfig config(limit, "1.8B", RoPEType::HFHUBROPE);
         QWenForCausalLM model(config);
-        return run(model, device, file, config.vocab_size, B, S, n, seed);
+        return run(model, device, file, config.vocab_size, B, S, n, seed, repeat);
     }
     if (name == "llama-generic") { // LLaMAModel's public dimension constructor (modeling_llama.hpp:92-106): small graphs for exact checks
         int d[7] = {512, 256, 4, 4, 512, 2, 2};
@@ -119,7 +139,7 @@ int main(int argc, char **argv) {
         LLaMANameConfig names;
         names.init((RoPEType)d[6]);
         LLaMAModel model(d[0], d[1], d[2], d[3], d[4], d[5], (RoPEType)d[6], 10000.f, limit, limit, "flash_attention_2", names, names.blk_name);
-        return run(model, device, file, d[0], B, S, n, seed);
+        return run(model, device, file, d[0], B, S, n, seed, repeat);
     }
     fprintf(stderr, "unknown model %s\n", name.c_str());
     return 2;
