@@ -140,7 +140,33 @@ private:
 // -------------------------------------------------------------------- RoPE (op/CPURoPE.cpp:22-128,200-515)
 // Tables are built on the host as the reference builds them (theta in double -> float, t = s * theta in float, libm sin / cos)
 // and uploaded once per (pose type, width, theta, positions); the rotation kernel uses the compiled reference's FMA form.
-struct RopeTables { Tensor sin_t, cos_t; };
+// Rows are built when a position first needs them, 2048 at a time: the reference fills all max_position_embeddings rows on first use
+// (LLaMA-2: 16384 x 64 sinf + cosf, 16 ms of host time inside the first prefill) although a request never passes its KV-cache limit.
+struct RopeTables {
+    Tensor sin_t, cos_t;
+    std::vector<float> theta;
+    int rows = 0, ready = 0, dim = 0, pose = 0;
+    void ensure(CUDABackend *b, int upto) {
+        upto = std::min(rows, (upto + 2047) / 2048 * 2048);
+        if (upto <= ready) return;
+        const int n = upto - ready;
+        std::vector<float> s((size_t)n * dim), c((size_t)n * dim);
+        for (int p = ready; p < upto; p++)
+            for (int i = 0; i < dim / 2; i++) {
+                const float ang = p * theta[i];
+                const float sv = sinf(ang), cv = cosf(ang);
+                const int d0 = pose == LLAMAROPE ? 2 * i : i;
+                const int d1 = pose == LLAMAROPE ? 2 * i + 1 : i + dim / 2;
+                const size_t at = (size_t)(p - ready) * dim;
+                s[at + d0] = sv; c[at + d0] = cv;
+                s[at + d1] = sv; c[at + d1] = cv;
+            }
+        MLLMCU_CHECK(mllmcu_memcpy_h2d(sin_t.hostPtr<float>() + (size_t)ready * dim, s.data(), s.size() * sizeof(float), b->stream()));
+        MLLMCU_CHECK(mllmcu_memcpy_h2d(cos_t.hostPtr<float>() + (size_t)ready * dim, c.data(), c.size() * sizeof(float), b->stream()));
+        b->sync(); // the staging vectors go away
+        ready = upto;
+    }
+};
 static map<string, shared_ptr<RopeTables>> g_rope_tables;
 
 class CUDARoPE final : public CUDAOpBase {
@@ -176,6 +202,7 @@ public:
         Tensor &x = *in[0], &y = *out[0];
         if (h_cnt_ + x.sequence() > pos_max_) throw std::runtime_error("[mllm-cuda] RoPE " + name() + ": position exceeds max_position_embeddings");
         if (!dense(x)) throw std::runtime_error("[mllm-cuda] RoPE " + name() + ": dense input expected");
+        tab_->ensure(b, h_cnt_ + x.sequence());
         const View ys = strides(y);
         MLLMCU_CHECK(mllmcu_rope(pose_type_, fbase(x), base(y), x.batch(), x.sequence(), x.head(), x.dimension(), ishape_, h_cnt_,
                                  tab_->sin_t.hostPtr<float>(), tab_->cos_t.hostPtr<float>(), ishape_, y.dtype() == MLLM_TYPE_F16, ys.bs, ys.ss, b->stream()));
@@ -186,17 +213,21 @@ public:
     void clearCache() override { h_cnt_ = 0; }
     bool fuseInfo(CUDAFuseInfo &f) override {
         if (!tab_) return false;
+        tab_->ensure(cb(backend_), h_cnt_ + 2);
         f.sin_t = tab_->sin_t.hostPtr<float>(); f.cos_t = tab_->cos_t.hostPtr<float>();
         f.rope_type = pose_type_; f.rot_dim = ishape_; f.pos_max = pos_max_;
         return true;
     }
-    void advance(int tokens) override { h_cnt_ += tokens; }
+    void advance(int tokens) override { // a fused step was replayed: the next one reads the row of position h_cnt_
+        h_cnt_ += tokens;
+        tab_->ensure(cb(backend_), h_cnt_ + 1);
+    }
     int position() const { return h_cnt_; }
 
 private:
     shared_ptr<RopeTables> build() {
         const int dim = ishape_;
-        vector<float> theta(dim / 2), s((size_t)pos_max_ * dim), c((size_t)pos_max_ * dim);
+        vector<float> theta(dim / 2);
         for (int i = 0; i < dim / 2; i++) theta[i] = (float)(1.0 / pow((double)rope_theta_, 2.0 * i / dim));
         if (theta_type_ == 1) { // _compute_llama3_theta (op/CPURoPE.cpp:34-72), statement for statement in float
             const float low_freq_wavelen = l3_old_ctx_ / l3_low_, high_freq_wavelen = l3_old_ctx_ / l3_high_;
@@ -210,28 +241,18 @@ private:
                 }
             }
         }
-        for (int p = 0; p < pos_max_; p++)
-            for (int i = 0; i < dim / 2; i++) {
-                const float ang = p * theta[i];
-                const float sv = sinf(ang), cv = cosf(ang);
-                const int d0 = pose_type_ == LLAMAROPE ? 2 * i : i;
-                const int d1 = pose_type_ == LLAMAROPE ? 2 * i + 1 : i + dim / 2;
-                s[(size_t)p * dim + d0] = sv; c[(size_t)p * dim + d0] = cv;
-                s[(size_t)p * dim + d1] = sv; c[(size_t)p * dim + d1] = cv;
-            }
         auto t = std::make_shared<RopeTables>();
-        auto up = [&](Tensor &dst, const vector<float> &src) {
+        auto mk = [&](Tensor &dst) {
             dst.setBackend(backend_);
             dst.reshape(1, 1, pos_max_, dim);
             dst.setDtype(MLLM_TYPE_F32);
             cb(backend_)->memory()->device_only = true;
             dst.alloc();
             cb(backend_)->memory()->device_only = false;
-            MLLMCU_CHECK(mllmcu_memcpy_h2d(dst.rawHostPtr(), src.data(), src.size() * sizeof(float), cb(backend_)->stream()));
-            cb(backend_)->sync();
         };
-        up(t->sin_t, s);
-        up(t->cos_t, c);
+        mk(t->sin_t);
+        mk(t->cos_t);
+        t->theta = theta; t->rows = pos_max_; t->dim = dim; t->pose = pose_type_;
         return t;
     }
     int pose_type_, pos_max_, ishape_ = 0, h_cnt_ = 0, tab_dim_ = -1;
