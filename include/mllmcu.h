@@ -276,7 +276,8 @@ int mllmcu_block_isums_q4_K_q8_K(const void *W, const void *xq_blocks, int32_t *
  * min * group sum), formed per lane over 32 weights and folded into fp32 with the super-block's two factors -- only the fp32 summation
  * order differs from vec_dot_q4_K_q8_K's (as it does between its own AVX lanes).  residual != NULL (nW == 1): y = residual + that (CPUAdd
  * after o_proj / down_proj).  W, N, bias, y are HOST arrays of nW entries (bias may be NULL).  flags: 1 = programmatic dependent launch;
- * 2 = xq_blocks are the 304-byte blocks. */
+ * 2 = xq_blocks are the 304-byte blocks; 4 = never the variant that holds the activation row in registers (one row, K <= 4096, 304-byte
+ * blocks take it by default: a persistent grid, the weight loads the only loads per row; same sums). */
 int mllmcu_prep_q8_K(int mode, const float *x, const float *aux, float eps, int add_unit_offset, void *y_blocks, int rows, int k, int ldx,
                      int flags, void *stream);
 int mllmcu_gemv_q4k(int nW, const void *const *W, const int *N, const float *const *bias, float *const *y, int ldy, const void *xq_blocks,

@@ -318,7 +318,7 @@ def q8_K_unpitch(y):
     return torch.cat([b[:, :, 0:4], b[:, :, 16:304]], dim=2).reshape(y.shape[0], -1).contiguous()
 
 
-def gemv_q4k(Ws, xq, K, biases=None, residual=None, pdl=False, aligned=False):
+def gemv_q4k(Ws, xq, K, biases=None, residual=None, pdl=False, aligned=False, no_areg=False):
     """Ws: 1..3 cuda uint8 [N_s, K/256*144] Q4_K matrices; xq: block_q8_K rows [M, ...] (native, or 304-byte blocks with aligned=True)
     -> list of fp32 [M, N_s] (one launch)."""
     import torch
@@ -337,7 +337,7 @@ def gemv_q4k(Ws, xq, K, biases=None, residual=None, pdl=False, aligned=False):
     bp = (C.c_void_p * n)(*[(_ptr(b) if b is not None else None) for b in (biases or [None] * n)])
     yp = (C.c_void_p * n)(*[y.data_ptr() for y in ys])
     check(lib().mllmcu_gemv_q4k(n, Wp, Np, bp, yp, ld, _ptr(xq), M, K, _ptr(residual) if residual is not None else None,
-                                residual.stride(0) if residual is not None else 0, int(pdl) | (2 if aligned else 0), _stream()), "gemv_q4k")
+                                residual.stride(0) if residual is not None else 0, int(pdl) | (2 if aligned else 0) | (4 if no_areg else 0), _stream()), "gemv_q4k")
     return ys
 
 

@@ -10,6 +10,8 @@
 // d = d_x * fp16(d_w), dmin = -d_x * fp16(dmin_w) with one fp32 FMA each; only the order of the fp32 accumulation over
 // super-blocks differs from the 8 AVX lanes (tolerance in the tests).
 #include "common.cuh"
+#include <algorithm>
+#include <stdlib.h>
 #include "kq_common.cuh"
 
 #define QK_K 256
@@ -537,9 +539,96 @@ __global__ void __launch_bounds__(128) k_gemv_q4k(const KqGemvParams p) {
     }
 }
 
+// One activation row, K <= 4096 (q|k|v, o, gate|up, lm_head of a 7B body): the lane's share of the activation row -- the same 4 x (32 int8,
+// 2 group sums, d) for EVERY weight row -- lives in registers, and a persistent grid's warps walk rows w, w + W, ... with only the two
+// 16-byte weight loads per super-block left on the load path.  ncu on k_gemv_q4k (profiles/r02_ncu_gemv_q4k.txt): DRAM traffic equals the
+// algorithmic bytes, but the L1 data pipe is 70 % busy and the issue slots 65 % -- five of the seven loads per super-block and lane were
+// activation gathers repeated for every row.  Same integers, same per-lane fp32 folding as k_gemv_q4k.
+template <int DUMMY>
+__global__ void __launch_bounds__(128, 4) k_gemv_q4k_areg(const KqGemvParams p) {
+    const int lane = threadIdx.x & 31;
+    const int W = gridDim.x * 4, w = blockIdx.x * 4 + (threadIdx.x >> 5);
+    const int nb = p.nb, g = lane >> 3, t = lane & 7, j = t >> 1, h = t & 1;
+    const int sh16 = 16 * (j & 1);
+    const bool upper = j >= 2;
+    if (w >= p.Ntot) return;
+    auto load = [&](int n, uint4 (&hq)[4], uint4 (&wq)[4]) {
+        const uint8_t *Wp = p.W[0];
+        if (n >= p.N[0]) { n -= p.N[0]; Wp = p.W[1]; if (n >= p.N[1]) { n -= p.N[1]; Wp = p.W[2]; } }
+        const uint8_t *row = Wp + (size_t)n * nb * Q4K_BYTES;
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            const uint8_t *blk = row + (size_t)min(4 * u + g, nb - 1) * Q4K_BYTES;
+            hq[u] = ld_stream_u4(blk);
+            wq[u] = ld_stream_u4(blk + 16 + t * 16);
+        }
+    };
+    uint4 hq[4], wq[4];
+    load(w, hq, wq);
+    kq_pdl_launch();
+    kq_pdl_wait(); // the activations are the predecessor's output; the first row's weights are already on their way
+    int4 al[4], ah[4];
+    int bl[4], bh[4];
+    float dx[4];
+#pragma unroll
+    for (int u = 0; u < 4; u++) {
+        const int i = min(4 * u + g, nb - 1);
+        const uint8_t *xb = p.xq + (size_t)i * Q8K_PITCH;
+        al[u] = *(const int4 *)(xb + 16 + (2 * j) * 32 + h * 16);
+        ah[u] = *(const int4 *)(xb + 16 + (2 * j + 1) * 32 + h * 16);
+        const int16_t *bs = (const int16_t *)(xb + 272);
+        bl[u] = (int)bs[4 * j + h];
+        bh[u] = (int)bs[4 * j + 2 + h];
+        dx[u] = 4 * u + g < nb ? *(const float *)xb : 0.f; // a lane past the end of the row contributes with factor 0
+    }
+    auto row_ptr = [&](int n) {
+        const uint8_t *Wp = p.W[0];
+        if (n >= p.N[0]) { n -= p.N[0]; Wp = p.W[1]; if (n >= p.N[1]) { n -= p.N[1]; Wp = p.W[2]; } }
+        return Wp + (size_t)n * nb * Q4K_BYTES;
+    };
+    for (int n = w; n < p.Ntot; n += W) {
+        float acc = 0.f, accm = 0.f;
+        const bool more = n + W < p.Ntot;
+        const uint8_t *next = row_ptr(more ? n + W : n);
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            const uint32_t y2 = hq[u].y >> sh16, z2 = hq[u].z >> sh16, w2 = hq[u].w >> sh16; // get_scale_min_k4 for sub-blocks 2j, 2j+1 only
+            const uint32_t sc2 = upper ? ((w2 & 0x0F0Fu) | ((y2 >> 2) & 0x3030u)) : (y2 & 0x3F3Fu);
+            const uint32_t mn2 = upper ? (((w2 >> 4) & 0x0F0Fu) | ((z2 >> 2) & 0x3030u)) : (z2 & 0x3F3Fu);
+            const int sc_lo = (int)(sc2 & 0xFFu), sc_hi = (int)(sc2 >> 8), mn_lo = (int)(mn2 & 0xFFu), mn_hi = (int)(mn2 >> 8);
+            const float dw = __half2float(__ushort_as_half((unsigned short)(hq[u].x & 0xFFFFu)));
+            const float dminw = __half2float(__ushort_as_half((unsigned short)(hq[u].x >> 16)));
+            int is_lo = 0, is_hi = 0;
+            is_lo = __dp4a((int)(wq[u].x & 0x0F0F0F0Fu), al[u].x, is_lo); is_hi = __dp4a((int)((wq[u].x >> 4) & 0x0F0F0F0Fu), ah[u].x, is_hi);
+            is_lo = __dp4a((int)(wq[u].y & 0x0F0F0F0Fu), al[u].y, is_lo); is_hi = __dp4a((int)((wq[u].y >> 4) & 0x0F0F0F0Fu), ah[u].y, is_hi);
+            is_lo = __dp4a((int)(wq[u].z & 0x0F0F0F0Fu), al[u].z, is_lo); is_hi = __dp4a((int)((wq[u].z >> 4) & 0x0F0F0F0Fu), ah[u].z, is_hi);
+            is_lo = __dp4a((int)(wq[u].w & 0x0F0F0F0Fu), al[u].w, is_lo); is_hi = __dp4a((int)((wq[u].w >> 4) & 0x0F0F0F0Fu), ah[u].w, is_hi);
+            if (more) { // this group's registers are free: the next row's same group starts its trip now
+                const uint8_t *blk = next + (size_t)min(4 * u + g, nb - 1) * Q4K_BYTES;
+                hq[u] = ld_stream_u4(blk);
+                wq[u] = ld_stream_u4(blk + 16 + t * 16);
+            }
+            const int vi = sc_lo * is_lo + sc_hi * is_hi;
+            const int vm = mn_lo * bl[u] + mn_hi * bh[u];
+            acc = fmaf(__fmul_rn(dx[u], dw), (float)vi, acc);
+            accm = fmaf(__fmul_rn(-dx[u], dminw), (float)vm, accm);
+        }
+        int nn = n, s = 0;
+        if (nn >= p.N[0]) { nn -= p.N[0]; s = 1; if (nn >= p.N[1]) { nn -= p.N[1]; s = 2; } }
+        const float *bias = s == 0 ? p.bias[0] : s == 1 ? p.bias[1] : p.bias[2];
+        float *y = s == 0 ? p.y[0] : s == 1 ? p.y[1] : p.y[2];
+        float v = warp_sum(__fadd_rn(acc, accm));
+        if (lane == 0) {
+            if (bias) v = __fadd_rn(v, bias[nn]);
+            if (p.res) v = __fadd_rn(p.res[nn], v);
+            y[nn] = v;
+        }
+    }
+}
+
 MLLMCU_API int mllmcu_gemv_q4k(int nW, const void *const *W, const int *N, const float *const *bias, float *const *y, int ldy, const void *xq_blocks,
                                int M, int K, const float *residual, int ldr, int flags, void *stream) {
-    const int pdl = flags & 1, aligned = flags & 2;
+    const int pdl = flags & 1, aligned = flags & 2, no_areg = flags & 4;
     if (aligned && ((uintptr_t)xq_blocks & 15)) return -1;
     if (nW < 1 || nW > 3 || M < 1 || M > 8 || K <= 0 || K % QK_K || ((uintptr_t)xq_blocks & 3)) return -1;
     if (residual && nW != 1) return -1;
@@ -556,6 +645,12 @@ MLLMCU_API int mllmcu_gemv_q4k(int nW, const void *const *W, const int *N, const
     p.Ntot = (int)tot;
     cudaLaunchConfig_t cfg;
     cudaLaunchAttribute attr[1];
+    static const int areg_ctas = getenv("MLLMCU_Q4K_AREG_CTAS") ? atoi(getenv("MLLMCU_Q4K_AREG_CTAS")) : 4; // resident CTAs per SM the persistent grid is sized for; 0 = off
+    if (M == 1 && aligned && p.nb <= 16 && !no_areg && areg_ctas > 0) { // one activation row held in registers
+        kq_launch_cfg(cfg, attr, dim3((unsigned)std::min((p.Ntot + 3) / 4, cu_sm_count() * areg_ctas)), dim3(128), pdl, (cudaStream_t)stream);
+        CU_TRY(cudaLaunchKernelEx(&cfg, k_gemv_q4k_areg<0>, p));
+        return 0;
+    }
     kq_launch_cfg(cfg, attr, dim3((unsigned)((p.Ntot + 3) / 4)), dim3(128), pdl, (cudaStream_t)stream);
     switch (M) {
 #define CASE(m) case m: if (aligned) CU_TRY(cudaLaunchKernelEx(&cfg, k_gemv_q4k<m, true>, p)); else CU_TRY(cudaLaunchKernelEx(&cfg, k_gemv_q4k<m, false>, p)); break;

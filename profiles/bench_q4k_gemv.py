@@ -50,6 +50,7 @@ for M in (1, 8):
         sets = [[rand_q4k(N, K) for N in Ns] for _ in range(copies)]
         x = torch.randn((M, K), device=dev)
         xqs = {1: cu.prep_q8_K(x), 3: cu.prep_q8_K(x, aligned=True)}
+        xqs[7] = xqs[3]
         ys = [torch.empty((M, N), device=dev) for N in Ns]
         n = len(Ns)
         Np = (C.c_int * n)(*Ns)
@@ -58,7 +59,7 @@ for M in (1, 8):
         bp = (C.c_void_p * n)(*[None] * n)
         reps = copies * 2
         out = {"M": M, "shape": name, "MB": round(bytes_w / 1e6, 1)}
-        for label, flags in (("native", 1), ("aligned", 3)):
+        for label, flags in (("native", 1), ("aligned", 3), ("aligned_no_areg", 7)):
             def fn(r, flags=flags):
                 st = torch.cuda.current_stream().cuda_stream
                 # all segments share ldy only when equal N; launch per distinct ldy otherwise -- here every segment has the same N

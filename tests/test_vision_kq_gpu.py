@@ -142,8 +142,8 @@ def test_gemv_q4k_segments(cu, oracle, M, Ns, K):
             kq_check(w, oracle.linear_kq(W, xn, b if b is not None else np.zeros(W.shape[0], np.float32), cu.TYPE_Q4_K))
     for al in (False, True):
         xq = cu.prep_q8_K(x, aligned=al)
-        for pdl in (False, True):
-            got = cu.gemv_q4k(Ws, xq, K, bs, pdl=pdl, aligned=al)
+        for pdl, no_areg in ((False, False), (True, False), (True, True)):  # one row, K <= 4096, 304-byte blocks: activations held in registers
+            got = cu.gemv_q4k(Ws, xq, K, bs, pdl=pdl, aligned=al, no_areg=no_areg)
             for g, w in zip(got, want):
                 kq_check(g.cpu().numpy(), w)
         if len(Ns) == 1:
