@@ -191,6 +191,20 @@ bool LlamaModel::decode_plan_usable(int B) {
     if (plan_ && plan_->unsupported) return false;
     const int H = cfg_.hidden, D = cfg_.head_dim();
     if (H % 128 || cfg_.ffn % 128 || (D != 32 && D != 64 && D != 128)) return false;
+    if (plan_ && plan_->B == B) {
+        // the plan (and its captured graph) holds the KV-cache addresses: a prefill at another batch size re-makes the caches
+        // (CUDAKVCache::ensure), and coming back to this batch size need not hand back the same blocks
+        for (int i = 0; i < cfg_.layers; i++) {
+            FuseInfo k, v;
+            Block &b = blocks_[i];
+            if (!(b.k_cache.op() && b.k_cache.op()->fuseInfo(k) && b.v_cache.op() && b.v_cache.op()->fuseInfo(v)) ||
+                k.cache != plan_->layers[i].kc.cache || v.cache != plan_->layers[i].vc.cache) {
+                st_.backend->sync();
+                plan_.reset();
+                break;
+            }
+        }
+    }
     if (!(plan_ && plan_->B == B)) {
         // (re)build: collect the device state of every op on the path
         auto p = std::make_unique<DecodePlan>();

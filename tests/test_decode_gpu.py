@@ -310,3 +310,24 @@ def test_second_request_continues_the_cache_without_clear(be, oracle, tmp_path_f
                 cur = np.array([[tok]], dtype=np.float32)   # the last pick of a request is never fed back (it is not in the cache)
     assert compared >= 6
     assert len(set(got[1])) > 1 or len(set(got[0])) > 1
+
+
+def test_plan_is_rebuilt_when_the_caches_are_remade(be, tmp_path_factory):
+    """Round-1 advisor finding: the plan (and its captured graph) bakes in the KV-cache addresses, and a prefill at another batch size
+    re-makes the caches.  Batch 2 request, batch 1 request, batch 2 request again: the third must equal the first (same prompts, greedy),
+    and equal what a model that never saw the batch-1 request in between produces."""
+    cfg, t, path = make(tmp_path_factory, "toy-gqa", 64, seed=8)
+    rng = np.random.default_rng(21)
+    two = rng.integers(0, cfg["vocab"], (2, 6)).astype(np.float32)
+    one = rng.integers(0, cfg["vocab"], (1, 9)).astype(np.float32)
+    m = be.LlamaModel(cfg).load(path)
+    first = m.generate(two, 10).tolist()
+    m.clear_kvcache()
+    mid = m.generate(one, 10).tolist()
+    m.clear_kvcache()
+    again = m.generate(two, 10).tolist()
+    m.close()
+    fresh = be.LlamaModel(cfg).load(path)
+    want_mid = fresh.generate(one, 10).tolist()
+    fresh.close()
+    assert again == first and mid == want_mid
