@@ -23,7 +23,7 @@
 
 #define KQ_WARPS 16
 #define KQ_Q4K 144
-#define KQ_Q8K 292
+#define KQ_Q8K 304 // the re-pitched activation block (kquants.cu, Q8K_PITCH): d at 0, the 256 int8 at 16, the 16 group sums at 272
 
 struct GemmQ4KParams {
     const uint8_t *W;   // [N][nsb] block_q4_K
@@ -111,8 +111,11 @@ __global__ void __launch_bounds__(KQ_WARPS * 32) k_gemm_mma_q4k(const GemmQ4KPar
                 for (int m = 0; m < MTW; m++) sumi[m][0] = sumi[m][1] = sumi[m][2] = sumi[m][3] = 0;
 #pragma unroll
                 for (int pr = 0; pr < 4; pr++) { // sub-blocks 2 pr (low nibbles) and 2 pr + 1 (high nibbles) share their 32 bytes
-                    const uint32_t w00 = *(const uint32_t *)(r0 + 16 + pr * 32 + 4 * t), w01 = *(const uint32_t *)(r0 + 16 + pr * 32 + 16 + 4 * t);
-                    const uint32_t w10 = *(const uint32_t *)(r1 + 16 + pr * 32 + 4 * t), w11 = *(const uint32_t *)(r1 + 16 + pr * 32 + 16 + 4 * t);
+                    // The contraction index of the MMA is only a label: lane t feeds k = 4t..4t+3 and 16+4t..16+4t+3 with elements 8t..8t+3 and
+                    // 8t+4..8t+7 of the sub-block on BOTH operands, so every fragment is one 8-byte load (the activation gathers -- 8 rows, 8
+                    // cache lines per instruction -- were the L1 pipe's main load: half as many now)
+                    const uint2 wa = *(const uint2 *)(r0 + 16 + pr * 32 + 8 * t), wb = *(const uint2 *)(r1 + 16 + pr * 32 + 8 * t);
+                    const uint32_t w00 = wa.x, w01 = wa.y, w10 = wb.x, w11 = wb.y;
 #pragma unroll
                     for (int hi = 0; hi < 2; hi++) {
                         const int j = 2 * pr + hi;
@@ -121,10 +124,9 @@ __global__ void __launch_bounds__(KQ_WARPS * 32) k_gemm_mma_q4k(const GemmQ4KPar
                         const int s0 = byte_of(sc0, j), s1 = byte_of(sc1, j);
 #pragma unroll
                         for (int m = 0; m < MTW; m++) {
-                            const uint8_t *xb = xq + of_frag[m] + (uint32_t)(sb * KQ_Q8K + 4 + j * 32);
-                            const uint32_t b0 = *(const uint32_t *)(xb + 4 * t), b1 = *(const uint32_t *)(xb + 16 + 4 * t);
+                            const uint2 bb = *(const uint2 *)(xq + of_frag[m] + (uint32_t)(sb * KQ_Q8K + 16 + j * 32 + 8 * t));
                             int cc[4];
-                            mma_u8s8(cc, a0, a1, a2, a3, b0, b1);
+                            mma_u8s8(cc, a0, a1, a2, a3, bb.x, bb.y);
                             sumi[m][0] += s0 * cc[0]; sumi[m][1] += s0 * cc[1];
                             sumi[m][2] += s1 * cc[2]; sumi[m][3] += s1 * cc[3];
                         }
@@ -138,10 +140,11 @@ __global__ void __launch_bounds__(KQ_WARPS * 32) k_gemm_mma_q4k(const GemmQ4KPar
                 for (int m = 0; m < MTW; m++) {
                     uint32_t bh = 0, bl = 0;
                     if (t < 2) { // B-fragment row = column (colw + 8 m + g): its group sums 8t .. 8t+7 -> bs_j for j = 4t .. 4t+3
-                        const uint8_t *xb = xq + of_frag[m] + (uint32_t)(sb * KQ_Q8K + 260 + 16 * t);
+                        const uint4 gs = *(const uint4 *)(xq + of_frag[m] + (uint32_t)(sb * KQ_Q8K + 272 + 16 * t));
+                        const uint32_t gsw[4] = {gs.x, gs.y, gs.z, gs.w};
 #pragma unroll
                         for (int q = 0; q < 4; q++) {
-                            const uint32_t wq = *(const uint32_t *)(xb + 4 * q);
+                            const uint32_t wq = gsw[q];
                             const int bs = (int)(short)(wq & 0xFFFFu) + (int)(short)(wq >> 16);
                             bh |= ((uint32_t)(bs >> 6) & 0xFFu) << (8 * q);
                             bl |= ((uint32_t)bs & 63u) << (8 * q);
@@ -220,7 +223,7 @@ bool gemm_mma_q4k_supported(int M, int N, int K, const void *W) {
     return on == 1 && M >= min_rows && N > 0 && N % 16 == 0 && K > 0 && K % 256 == 0 && !((uintptr_t)W & 15);
 }
 
-// xq: native block_q8_K rows of the M activation rows (mllmcu_quantize_q8_K).  Serves M in chunks of 64 rows (128 when K has fewer
+// xq: the M activation rows as 304-byte block_q8_K blocks (mllmcu_prep_q8_K mode 0, flag 2).  Serves M in chunks of 64 rows (128 when K has fewer
 // than 8 super-blocks): each chunk streams the weights again -- they stay in L2 between chunks.
 int launch_gemm_mma_q4k(const void *W, const void *xq, const float *bias, void *y, int M, int N, int K, int ldy, int out_f16, cudaStream_t st) {
     if (!gemm_mma_q4k_supported(M, N, K, W)) return -2;
@@ -238,7 +241,7 @@ int launch_gemm_mma_q4k(const void *W, const void *xq, const float *bias, void *
     // a stage of 16 rows x KC super-blocks <= ~40 KB, the ring gets what the reduction buffer leaves
     int KC = nsb < 16 ? nsb : 16;
     p.KC = KC; p.nchunk = (nsb + KC - 1) / KC;
-    p.pitch = KC * KQ_Q4K + 16; // 2304 + 16: rows g = 0..7 of a fragment start 16 bytes apart in the banks
+    p.pitch = KC * KQ_Q4K + 32; // 2304 + 32: rows g = 0..7 of a fragment start 8 banks apart (8-byte fragment loads: 4 rows x 32 bytes per half-warp)
     const size_t red = ((size_t)KS * 16 * Mp * 4 + 127) & ~(size_t)127, stage = (size_t)16 * p.pitch;
     int S = (int)((200 * 1024 - red) / stage);
     if (S > 8) S = 8;

@@ -313,7 +313,7 @@ __global__ void __launch_bounds__(256) k_gemm_kq(const uint8_t *__restrict__ W, 
     }
 }
 
-size_t kq_workspace_bytes(int M, int K) { return (K % QK_K) ? 0 : (size_t)M * (K / QK_K) * Q8K_BYTES + 256; }
+size_t kq_workspace_bytes(int M, int K) { return (K % QK_K) ? 0 : (size_t)M * (K / QK_K) * Q8K_PITCH + 256; } // room for either block form
 
 template <int WT>
 static int launch_kq(const uint8_t *W, const uint8_t *xq, const float *bias, void *y, int M, int N, int nb, int ldy, int out_f16, cudaStream_t st) {
@@ -333,19 +333,27 @@ static int launch_kq(const uint8_t *W, const uint8_t *xq, const float *bias, voi
 }
 
 int launch_gemm_mma_q4k(const void *W, const void *xq, const float *bias, void *y, int M, int N, int K, int ldy, int out_f16, cudaStream_t st); // gemm_mma_q4k.cu
+bool gemm_mma_q4k_supported(int M, int N, int K, const void *W);
+MLLMCU_API int mllmcu_prep_q8_K(int mode, const float *x, const float *aux, float eps, int add_unit_offset, void *y_blocks, int rows, int k, int ldx,
+                                int flags, void *stream); // below
 // called by mllmcu_linear for wtype 12 (Q4_K) / 14 (Q6_K)
 int launch_linear_kq(int wtype, const void *W, const float *x, const float *bias, void *y, int M, int N, int K, int ldx, int ldy, int out_f16,
                      void *ws, int skip_quant, cudaStream_t st) {
     if (K % QK_K || ldx % 4 || ((uintptr_t)x & 15)) return -1;
     if (wtype == 12 && ((uintptr_t)W & 15)) return -1;
     if (wtype == 14 && ((uintptr_t)W & 1)) return -1;
-    if (!skip_quant) { // skip: ws already holds the block_q8_K rows of these activations (q / k / v, gate / up share one input)
-        const int rc = mllmcu_quantize_q8_K(x, ws, M, K, ldx, st);
-        if (rc) return rc;
-    }
-    if (wtype == 12) { // 9+ rows: the tensor-core kernel (gemm_mma_q4k.cu); -2 = shape outside it
+    if (wtype == 12 && gemm_mma_q4k_supported(M, N, K, W)) { // 9+ rows: the tensor-core kernel (gemm_mma_q4k.cu) on 304-byte activation blocks
+        if (!skip_quant) { // skip: ws already holds this image of these activations (q / k / v, gate / up share one input)
+            const int rc = mllmcu_prep_q8_K(0, x, nullptr, 0.f, 0, ws, M, K, ldx, 2, st);
+            if (rc) return rc;
+        }
         const int rm = launch_gemm_mma_q4k(W, ws, bias, y, M, N, K, ldy, out_f16, st);
         if (rm != -2) return rm;
+        skip_quant = 0; // a shape the kernel turned down after all: the kernels below read native blocks
+    }
+    if (!skip_quant) {
+        const int rc = mllmcu_quantize_q8_K(x, ws, M, K, ldx, st);
+        if (rc) return rc;
     }
     return wtype == 12 ? launch_kq<12>((const uint8_t *)W, (const uint8_t *)ws, bias, y, M, N, K / QK_K, ldy, out_f16, st)
                        : launch_kq<14>((const uint8_t *)W, (const uint8_t *)ws, bias, y, M, N, K / QK_K, ldy, out_f16, st);

@@ -251,8 +251,12 @@ static bool linear_mma_enabled() {
     return on == 1;
 }
 
+bool gemm_mma_q4k_supported(int M, int N, int K, const void *W); // gemm_mma_q4k.cu
 MLLMCU_API int mllmcu_linear_quant_kind(int wtype, int M, int N, int K, const void *W) {
-    if (wtype == 12 || wtype == 14) return (K % 256) ? 0 : 4; // 4: native block_q8_K rows at the start of ws (shared by Q4_K and Q6_K)
+    if (wtype == 12 || wtype == 14) { // 4: native block_q8_K rows at the start of ws (shared by Q4_K and Q6_K); 5: the 304-byte blocks of the Q4_K tensor-core kernel
+        if (K % 256) return 0;
+        return (wtype == 12 && gemm_mma_q4k_supported(M, N, K, W)) ? 5 : 4;
+    }
     if (wtype != 2 && wtype != 8) return 0;
     if (wtype == 2 && M >= 3 && M <= 64 && linear_mma_enabled() && gemv_mma_supported(wtype, M, K, &N, 1, &W)) return 0; // own image, not in ws
     return (gemm_tc_supported(wtype, M, N, K) && !((uintptr_t)W & 15)) ? gemm_tc_quant_kind() : 3; // 3: split Q8_0 (GEMV / dp4a / scaled tcgen05)
