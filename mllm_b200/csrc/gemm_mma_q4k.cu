@@ -23,11 +23,12 @@
 
 #define KQ_WARPS 16
 #define KQ_Q4K 144
-#define KQ_Q8K 304 // the re-pitched activation block (kquants.cu, Q8K_PITCH): d at 0, the 256 int8 at 16, the 16 group sums at 272
 
 struct GemmQ4KParams {
     const uint8_t *W;   // [N][nsb] block_q4_K
-    const uint8_t *xq;  // [M][nsb] block_q8_K (native)
+    const uint8_t *xq;  // fragment-major activation image (kquants.cu, k_quantize_q8_K_frag): QS region
+    const uint8_t *xdx, *xbs; // its DX and BS regions
+    int grp0, G;        // first 8-row group of this launch, groups in the image
     const float *bias;
     void *y;
     int N, M, nsb, ldy, out_f16;
@@ -78,15 +79,11 @@ __global__ void __launch_bounds__(KQ_WARPS * 32) k_gemm_mma_q4k(const GemmQ4KPar
     __syncthreads();
 
     const int colw = mg * MTW * 8;
-    // per batch tile: the B-fragment row (colw + 8 m + g) and the two output columns (colw + 8 m + 2 t, + 1), clamped into the rows that exist
-    // (32-bit byte offsets from xq: at most 640 rows x 64 super-blocks x 292 bytes)
-    uint32_t of_frag[MTW], of_c0[MTW], of_c1[MTW];
+    // per batch tile (8 activation rows = one row group of the image): its cell row, clamped into the groups that exist (a tile past the
+    // last row reads a valid group again; its columns are never stored)
+    uint32_t cellb[MTW];
 #pragma unroll
-    for (int m = 0; m < MTW; m++) {
-        of_frag[m] = (uint32_t)min(colw + m * 8 + g, p.M - 1) * (uint32_t)(nsb * KQ_Q8K);
-        of_c0[m] = (uint32_t)min(colw + m * 8 + 2 * t, p.M - 1) * (uint32_t)(nsb * KQ_Q8K);
-        of_c1[m] = (uint32_t)min(colw + m * 8 + 2 * t + 1, p.M - 1) * (uint32_t)(nsb * KQ_Q8K);
-    }
+    for (int m = 0; m < MTW; m++) cellb[m] = (uint32_t)min(p.grp0 + (colw >> 3) + m, p.G - 1) * (uint32_t)nsb;
     const uint8_t *xq = p.xq;
     for (int i = 0; i < n_tiles; i++) {
         float acc[MTW][4]; // [0],[1]: weight row g, columns 2t, 2t+1; [2],[3]: row g + 8
@@ -124,7 +121,7 @@ __global__ void __launch_bounds__(KQ_WARPS * 32) k_gemm_mma_q4k(const GemmQ4KPar
                         const int s0 = byte_of(sc0, j), s1 = byte_of(sc1, j);
 #pragma unroll
                         for (int m = 0; m < MTW; m++) {
-                            const uint2 bb = *(const uint2 *)(xq + of_frag[m] + (uint32_t)(sb * KQ_Q8K + 16 + j * 32 + 8 * t));
+                            const uint2 bb = *(const uint2 *)(xq + (size_t)(cellb[m] + sb) * 2048 + j * 256 + lane * 8); // 256 contiguous bytes per warp
                             int cc[4];
                             mma_u8s8(cc, a0, a1, a2, a3, bb.x, bb.y);
                             sumi[m][0] += s0 * cc[0]; sumi[m][1] += s0 * cc[1];
@@ -139,22 +136,20 @@ __global__ void __launch_bounds__(KQ_WARPS * 32) k_gemm_mma_q4k(const GemmQ4KPar
 #pragma unroll
                 for (int m = 0; m < MTW; m++) {
                     uint32_t bh = 0, bl = 0;
-                    if (t < 2) { // B-fragment row = column (colw + 8 m + g): its group sums 8t .. 8t+7 -> bs_j for j = 4t .. 4t+3
-                        const uint4 gs = *(const uint4 *)(xq + of_frag[m] + (uint32_t)(sb * KQ_Q8K + 272 + 16 * t));
-                        const uint32_t gsw[4] = {gs.x, gs.y, gs.z, gs.w};
+                    if (t < 2) { // B-fragment row = column (colw + 8 m + g): the sums of its sub-blocks j = 4t .. 4t+3
+                        const uint2 gs = *(const uint2 *)(p.xbs + (size_t)(cellb[m] + sb) * 128 + g * 16 + t * 8);
+                        const int bsv[4] = {(int)(short)(gs.x & 0xFFFFu), (int)(short)(gs.x >> 16), (int)(short)(gs.y & 0xFFFFu), (int)(short)(gs.y >> 16)};
 #pragma unroll
                         for (int q = 0; q < 4; q++) {
-                            const uint32_t wq = gsw[q];
-                            const int bs = (int)(short)(wq & 0xFFFFu) + (int)(short)(wq >> 16);
-                            bh |= ((uint32_t)(bs >> 6) & 0xFFu) << (8 * q);
-                            bl |= ((uint32_t)bs & 63u) << (8 * q);
+                            bh |= ((uint32_t)(bsv[q] >> 6) & 0xFFu) << (8 * q);
+                            bl |= ((uint32_t)bsv[q] & 63u) << (8 * q);
                         }
                     }
                     int sh[4], sl[4];
                     mma_u8s8(sh, ma0, ma1, 0u, 0u, bh, 0u);
                     mma_u8s8(sl, ma0, ma1, 0u, 0u, bl, 0u);
-                    const uint8_t *c0 = xq + of_c0[m] + (uint32_t)(sb * KQ_Q8K), *c1 = xq + of_c1[m] + (uint32_t)(sb * KQ_Q8K);
-                    const float dx0 = *(const float *)c0, dx1 = *(const float *)c1;
+                    const float2 dxp = *(const float2 *)(p.xdx + (size_t)(cellb[m] + sb) * 32 + 8 * t); // d of columns 2t, 2t+1
+                    const float dx0 = dxp.x, dx1 = dxp.y;
                     // the super-block's two fp32 FMAs (same operations as k_gemm_kq: d = d_x * d_w, -d_x * dmin_w)
                     acc[m][0] = fmaf(__fmul_rn(dx0, dw0), (float)sumi[m][0], acc[m][0]);
                     acc[m][1] = fmaf(__fmul_rn(dx1, dw0), (float)sumi[m][1], acc[m][1]);
@@ -223,7 +218,7 @@ bool gemm_mma_q4k_supported(int M, int N, int K, const void *W) {
     return on == 1 && M >= min_rows && N > 0 && N % 16 == 0 && K > 0 && K % 256 == 0 && !((uintptr_t)W & 15);
 }
 
-// xq: the M activation rows as 304-byte block_q8_K blocks (mllmcu_prep_q8_K mode 0, flag 2).  Serves M in chunks of 64 rows (128 when K has fewer
+// xq: the M activation rows as the fragment-major image (launch_quantize_q8_K_frag, kquants.cu).  Serves M in chunks of 64 rows (128 when K has fewer
 // than 8 super-blocks): each chunk streams the weights again -- they stay in L2 between chunks.
 int launch_gemm_mma_q4k(const void *W, const void *xq, const float *bias, void *y, int M, int N, int K, int ldy, int out_f16, cudaStream_t st) {
     if (!gemm_mma_q4k_supported(M, N, K, W)) return -2;
@@ -251,9 +246,13 @@ int launch_gemm_mma_q4k(const void *W, const void *xq, const float *bias, void *
     int grid = cu_sm_count();
     if (grid > N / 16) grid = N / 16;
     const size_t esz = out_f16 ? 2 : 4;
+    p.G = (M + 7) / 8;
+    p.xq = (const uint8_t *)xq;
+    p.xdx = p.xq + (size_t)p.G * nsb * 2048;
+    p.xbs = p.xdx + (size_t)p.G * nsb * 32;
     for (int m0 = 0; m0 < M; m0 += Mp) {
         p.M = M - m0 < Mp ? M - m0 : Mp;
-        p.xq = (const uint8_t *)xq + (size_t)m0 * nsb * KQ_Q8K;
+        p.grp0 = m0 / 8;
         p.y = (char *)y + (size_t)m0 * ldy * esz;
         int rc;
         switch (variant) {

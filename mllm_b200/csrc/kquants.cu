@@ -28,7 +28,9 @@ static __device__ __forceinline__ int nearest_int_dev(float f) {
 
 // ------------------------------------------------------------ quantize_row_q8_K
 // one warp per super-block, lane l owns elements 8l..8l+7 (v) and writes its share of the 292-byte block at `out`
-static __device__ __forceinline__ void q8K_block_from_warp(const float (&v)[8], int lane, uint8_t *out, int qs_off = 4, int bs_off = 260) {
+// the warp's super-block quantised: w0 / w1 = this lane's eight int8 (elements 8 lane .. 8 lane + 7), s2 = the sum of the 16-element group the
+// lane pair (lane, lane ^ 1) covers, d = the block scale
+static __device__ __forceinline__ void q8K_quant_warp(const float (&v)[8], int lane, uint32_t &w0, uint32_t &w1, int &s2, float &d) {
     // first element with the largest |x| decides the sign of the scale (strict > in the reference's scan)
     float amax = 0.f, mx = 0.f;
     int idx = 0x7fffffff;
@@ -45,7 +47,7 @@ static __device__ __forceinline__ void q8K_block_from_warp(const float (&v)[8], 
         if (oa > amax || (oa == amax && oi < idx)) { amax = oa; mx = om; idx = oi; }
     }
     int q[8];
-    float d = 0.f;
+    d = 0.f;
     if (amax == 0.f) {
 #pragma unroll
         for (int j = 0; j < 8; j++) q[j] = 0;
@@ -58,14 +60,59 @@ static __device__ __forceinline__ void q8K_block_from_warp(const float (&v)[8], 
     int s = 0;
 #pragma unroll
     for (int j = 0; j < 8; j++) s += q[j];
-    const int s2 = s + __shfl_xor_sync(0xffffffffu, s, 1);
-    uint32_t w0 = 0, w1 = 0;
+    s2 = s + __shfl_xor_sync(0xffffffffu, s, 1);
+    w0 = 0; w1 = 0;
 #pragma unroll
     for (int j = 0; j < 4; j++) { w0 |= (uint32_t)(q[j] & 0xFF) << (8 * j); w1 |= (uint32_t)(q[4 + j] & 0xFF) << (8 * j); }
+}
+
+// one warp per super-block, lane l owns elements 8l..8l+7 (v) and writes its share of the 292-byte block at `out`
+static __device__ __forceinline__ void q8K_block_from_warp(const float (&v)[8], int lane, uint8_t *out, int qs_off = 4, int bs_off = 260) {
+    uint32_t w0, w1;
+    int s2;
+    float d;
+    q8K_quant_warp(v, lane, w0, w1, s2, d);
     *(uint32_t *)(out + qs_off + lane * 8) = w0; // blocks are 292 B apart: only 4-byte alignment is guaranteed
     *(uint32_t *)(out + qs_off + 4 + lane * 8) = w1;
     if ((lane & 1) == 0) *(int16_t *)(out + bs_off + (lane >> 1) * 2) = (int16_t)s2; // all-zero block: 0 (the reference leaves it unwritten)
     if (lane == 0) *(float *)out = d;
+}
+
+// The activation image of the Q4_K tensor-core Linear (gemm_mma_q4k.cu), "fragment-major": the same block_q8_K values, placed so that
+// every operand load of a warp is contiguous.  Rows in groups of 8 (G groups, the last one padded), nb super-blocks:
+//   QS  [G][nb][8 sub-blocks][32 lanes = row-in-group * 4 + t][8 int8: elements 8t..8t+7 of the sub-block]   2048 B per (group, super-block)
+//   DX  [G][nb][8 rows] float d
+//   BS  [G][nb][8 rows][8] int16: bsums[2j] + bsums[2j+1], the sum of sub-block j
+// A B fragment of mma.m16n8k32 (8 activation rows x 32 elements, lane (g, t) = row g, elements 8t..8t+7 with the relabelled contraction
+// index) is then 256 contiguous bytes instead of 8 rows in 8 cache lines.
+__global__ void __launch_bounds__(128) k_quantize_q8_K_frag(const float *__restrict__ x, uint8_t *__restrict__ y, long long nblk, int nb, int ldx, int G) {
+    const int lane = threadIdx.x & 31;
+    const long long blk = (long long)blockIdx.x * 4 + (threadIdx.x >> 5);
+    if (blk >= nblk) return;
+    const int row = (int)(blk / nb), b = (int)(blk % nb);
+    const float *xp = x + (size_t)row * ldx + (size_t)b * QK_K + lane * 8;
+    const float4 v0 = *(const float4 *)xp, v1 = *(const float4 *)(xp + 4);
+    const float v[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
+    uint32_t w0, w1;
+    int s2;
+    float d;
+    q8K_quant_warp(v, lane, w0, w1, s2, d);
+    const int grp = row >> 3, g = row & 7, j = lane >> 2, t = lane & 3;
+    const size_t cell = (size_t)grp * nb + b;
+    *(uint2 *)(y + cell * 2048 + j * 256 + (g * 4 + t) * 8) = make_uint2(w0, w1);
+    const int s4 = s2 + __shfl_xor_sync(0xffffffffu, s2, 2); // lanes 4j..4j+3: the 32 elements of sub-block j
+    uint8_t *dx = y + (size_t)G * nb * 2048, *bs = dx + (size_t)G * nb * 32;
+    if (t == 0) *(int16_t *)(bs + cell * 128 + g * 16 + j * 2) = (int16_t)s4;
+    if (lane == 0) *(float *)(dx + cell * 32 + g * 4) = d;
+}
+
+size_t kq_frag_image_bytes(int M, int K) { return (size_t)((M + 7) / 8) * (K / QK_K) * (2048 + 32 + 128) + 256; }
+int launch_quantize_q8_K_frag(const float *x, void *y, int M, int K, int ldx, cudaStream_t st) {
+    if (M <= 0 || K <= 0 || K % QK_K || ldx % 4 || ((uintptr_t)x & 15) || ((uintptr_t)y & 15)) return -1;
+    const long long nblk = (long long)M * (K / QK_K);
+    k_quantize_q8_K_frag<<<(unsigned)((nblk + 3) / 4), 128, 0, st>>>(x, (uint8_t *)y, nblk, K / QK_K, ldx, (M + 7) / 8);
+    CU_LAUNCH_CHECK();
+    return 0;
 }
 
 __global__ void __launch_bounds__(128) k_quantize_q8_K(const float *__restrict__ x, uint8_t *__restrict__ y, long long nblk, int nb, int ldx) {
@@ -313,7 +360,7 @@ __global__ void __launch_bounds__(256) k_gemm_kq(const uint8_t *__restrict__ W, 
     }
 }
 
-size_t kq_workspace_bytes(int M, int K) { return (K % QK_K) ? 0 : (size_t)M * (K / QK_K) * Q8K_PITCH + 256; } // room for either block form
+size_t kq_workspace_bytes(int M, int K) { return (K % QK_K) ? 0 : std::max((size_t)M * (K / QK_K) * Q8K_PITCH + 256, kq_frag_image_bytes(M, K)); } // room for every image form
 
 template <int WT>
 static int launch_kq(const uint8_t *W, const uint8_t *xq, const float *bias, void *y, int M, int N, int nb, int ldy, int out_f16, cudaStream_t st) {
@@ -342,9 +389,9 @@ int launch_linear_kq(int wtype, const void *W, const float *x, const float *bias
     if (K % QK_K || ldx % 4 || ((uintptr_t)x & 15)) return -1;
     if (wtype == 12 && ((uintptr_t)W & 15)) return -1;
     if (wtype == 14 && ((uintptr_t)W & 1)) return -1;
-    if (wtype == 12 && gemm_mma_q4k_supported(M, N, K, W)) { // 9+ rows: the tensor-core kernel (gemm_mma_q4k.cu) on 304-byte activation blocks
+    if (wtype == 12 && gemm_mma_q4k_supported(M, N, K, W)) { // 9+ rows: the tensor-core kernel (gemm_mma_q4k.cu) on the fragment-major image
         if (!skip_quant) { // skip: ws already holds this image of these activations (q / k / v, gate / up share one input)
-            const int rc = mllmcu_prep_q8_K(0, x, nullptr, 0.f, 0, ws, M, K, ldx, 2, st);
+            const int rc = launch_quantize_q8_K_frag(x, ws, M, K, ldx, st);
             if (rc) return rc;
         }
         const int rm = launch_gemm_mma_q4k(W, ws, bias, y, M, N, K, ldy, out_f16, st);

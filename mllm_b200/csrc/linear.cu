@@ -253,7 +253,7 @@ static bool linear_mma_enabled() {
 
 bool gemm_mma_q4k_supported(int M, int N, int K, const void *W); // gemm_mma_q4k.cu
 MLLMCU_API int mllmcu_linear_quant_kind(int wtype, int M, int N, int K, const void *W) {
-    if (wtype == 12 || wtype == 14) { // 4: native block_q8_K rows at the start of ws (shared by Q4_K and Q6_K); 5: the 304-byte blocks of the Q4_K tensor-core kernel
+    if (wtype == 12 || wtype == 14) { // 4: native block_q8_K rows at the start of ws (shared by Q4_K and Q6_K); 5: the fragment-major image of the Q4_K tensor-core kernel (kquants.cu)
         if (K % 256) return 0;
         return (wtype == 12 && gemm_mma_q4k_supported(M, N, K, W)) ? 5 : 4;
     }
