@@ -106,6 +106,10 @@ CUDABackend::CUDABackend(const BackendConfig &, int device) : device_(device) {
     MLLMCU_CHECK(mllmcu_stream_create(&stream_));
     const char *pool = getenv("MLLM_CUDA_POOL_MB");
     memory()->reserve((size_t)(pool ? std::max(0, atoi(pool)) : 1024) << 20);
+    // the scratch shared by the ops starts large enough for a 7B prefill / a ViT tower's attention planes: growing it in the middle of a
+    // forward drains the stream and goes through cudaFree + cudaMalloc (MLLM_CUDA_WS_MB, default 128)
+    const char *wsmb = getenv("MLLM_CUDA_WS_MB");
+    workspace((size_t)(wsmb ? std::max(1, atoi(wsmb)) : 128) << 20);
     const char *e = getenv("MLLM_CUDA_EAGER_DECODE");
     fused_decode = !(e && e[0] == '1');
     registerOps();
